@@ -1,0 +1,186 @@
+/* kreeq_b200.h -- C-ABI of libkreeq_b200.so, the B200 (sm_100a) implementation of
+ * kreeq's data-parallel k-mer hot path: DBG k-mer counting, .kreeq database
+ * save/load/union, and assembly k-mer validation (QV + per-base profile).
+ *
+ * The reference (vgl-hub/kreeq) has no FFI; its seam is the CRTP base
+ * Kmap<DBG,...> (gfalibs/include/kmer.h:53-240) specialised by class DBG
+ * (include/kreeq.h:150-277).  Each entry point below names the reference
+ * member(s) it replaces (paths relative to the reference tree).
+ *
+ * Conventions: plain pointers and sizes, caller-owned HOST memory unless a
+ * parameter is named d_* (device pointer on the context's GPU).  Every call
+ * returns 0 or a negative KQ_E* code and never exit()s; kq_last_error() gives
+ * the message.  There is NO CPU fallback: without a usable CUDA device
+ * kq_create fails with KQ_ENODEV.
+ * One handle = one GPU = one shard of the key space.  Multi-GPU = one process
+ * (or handle) per GPU, kq_set_shard(rank, nranks), with tuples routed by
+ * kq_owner_of().
+ */
+#ifndef KREEQ_B200_H
+#define KREEQ_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define KQ_OK        0
+#define KQ_EINVAL   -1   /* bad argument (k outside 1..32, NULL, ...)              */
+#define KQ_ENODEV   -2   /* no CUDA device / CUDA runtime failure at start-up      */
+#define KQ_ECUDA    -3   /* CUDA error during a call                               */
+#define KQ_ENOMEM   -4   /* host or device allocation failed / table cannot grow   */
+#define KQ_EIO      -5   /* file missing, unreadable or not a .kreeq layout        */
+#define KQ_ECORRUPT -6   /* "int32 map missing 255 value from int8 map"            */
+#define KQ_ESTATE   -7   /* call not valid in the handle's current state           */
+
+#define KQ_MAP_COUNT 128 /* Kmap::mapCount, gfalibs/include/kmer.h:68 */
+
+typedef struct kq_ctx kq_ctx;
+
+/* == DBGkmer32, include/kreeq.h:69-70 */
+typedef struct { uint32_t fw[4], bw[4], cov; } kq_rec32;
+/* == DBGbase, include/input.h:4-9 (16 bytes; isFw is a C++ bool there) */
+typedef struct { uint32_t fw, bw, cov; uint8_t isFw; uint8_t pad[3]; } kq_base;
+/* DBG::summary/DBstats counters, src/graph-builder.cpp:240-295 */
+typedef struct { uint64_t total, unique, distinct, missing, edges; } kq_stats;
+/* totMissingKmers, totKcount, totEdgeMissingKmers, src/kreeq.cpp:223-225 */
+typedef struct { uint64_t missing, kcount, edge_missing; } kq_qv;
+
+/* ---- lifetime ------------------------------------------------------------ */
+
+/* replaces DBG knav(userInput) / Kmap ctor, kmer.h:126-153.  device = CUDA
+ * ordinal.  expected_distinct sizes the first table (0 = small default; the
+ * table doubles on demand). */
+int  kq_create(kq_ctx **out, int k, int device, uint64_t expected_distinct);
+void kq_destroy(kq_ctx *ctx);
+const char *kq_last_error(kq_ctx *ctx);          /* ctx may be NULL: last create error */
+int  kq_k(kq_ctx *ctx);
+
+/* Run the context's kernels on a caller-owned stream (a cudaStream_t, e.g.
+ * torch.cuda.current_stream().cuda_stream).  NULL restores the internal one. */
+int  kq_set_stream(kq_ctx *ctx, void *cuda_stream);
+int  kq_sync(kq_ctx *ctx);
+
+/* Key-space shard of this handle: it owns maps [rank*128/nranks,
+ * (rank+1)*128/nranks).  nranks in {1,2,4,8,...,128}. */
+int  kq_set_shard(kq_ctx *ctx, int rank, int nranks);
+/* owner rank of a canonical key: (key % 128) / (128 / nranks) */
+int  kq_owner_of(uint64_t key, int nranks);
+
+/* ---- count (rows A1-A3) ---------------------------------------------------- */
+
+/* replaces Kmap::traverseInReads(std::string*) kmer.h:753-764 +
+ * DBG::hashSequences gb:34-126 + DBG::processBuffers gb:128-223.
+ * ascii is one batch of reads each followed by 'N' exactly as getKmers()
+ * (gfalibs/include/functions.h:69-122) builds it; BORROWED, consumed (packed
+ * to 2 bit into pinned staging) before return; H2D copy and kernels are
+ * asynchronous.  With nranks>1 only keys owned by this shard are inserted
+ * (every rank may be fed the same batch), see also kq_dev_extract_route. */
+int  kq_count_push(kq_ctx *ctx, const char *ascii, size_t len);
+/* replaces Kmap::finalize kmer.h:821-828: barrier, table resident and final. */
+int  kq_count_finish(kq_ctx *ctx);
+/* k-mer instances inserted so far by this handle (valid windows, row A2) */
+int  kq_count_instances(kq_ctx *ctx, uint64_t *n);
+/* drop every record, keep allocations */
+int  kq_clear(kq_ctx *ctx);
+
+/* ---- persistence (row A8) -------------------------------------------------- */
+
+/* replaces Kmap::dumpMap kmer.h:698-709 + dumpHighCopyKmers :563-576 + the
+ * .index writer src/kreeq-output.cpp:88-94.  Writes the maps this shard owns;
+ * rank 0 also writes .index; .map.hc.bin is written when nranks==1, otherwise
+ * use kq_db_save_hc_part / kq_db_merge_hc_parts. */
+int  kq_db_save(kq_ctx *ctx, const char *dir);
+int  kq_db_save_hc_part(kq_ctx *ctx, const char *dir);       /* <dir>/.hc.part.<rank> */
+int  kq_db_merge_hc_parts(const char *dir, int nranks);      /* -> <dir>/.map.hc.bin  */
+/* replaces Input::loadGraph src/input.cpp:56-74 + Kmap::loadMap kmer.h:592-602 +
+ * loadHighCopyKmers :605-618 (k must equal the one in <dir>/.index). */
+int  kq_db_load(kq_ctx *ctx, const char *dir);
+/* k stored in <dir>/.index, or a negative error */
+int  kq_db_read_k(const char *dir);
+
+/* ---- union (row A4) ---------------------------------------------------------- */
+
+/* replaces DBG::kunion gb:297-351 / Kmap::mergeMaps kmer.h:666-695 /
+ * DBG::mergeSubMaps gb:353-432.  dirs[0] is "DB0".  ref_compatible=1
+ * reproduces the reference's order-dependent treatment of high-copy keys;
+ * 0 gives the exact saturating sum.  Result replaces the handle's table. */
+int  kq_union(kq_ctx *ctx, const char *const *dirs, int n, int ref_compatible);
+
+/* ---- stats (row A3s) ---------------------------------------------------------- */
+
+/* replaces Kmap::stats kmer.h:831-852 + DBG::summary/DBstats gb:240-295 */
+int  kq_stats_get(kq_ctx *ctx, kq_stats *out);
+/* finalHistogram (kmer.h:895-899) sorted by coverage; *len in: capacity, out: bins */
+int  kq_hist(kq_ctx *ctx, uint64_t *cov, uint64_t *n, size_t *len);
+
+/* ---- validate (rows A5, A6) ---------------------------------------------------- */
+
+/* replaces DBG::evaluateSegment src/kreeq.cpp:110-229 for one segment (no
+ * N/n/X/x inside).  out has len entries; entries >= len-k+1 are zeroed.
+ * acc ACCUMULATES.  With nranks>1 only positions whose key this shard owns are
+ * filled/counted (same as the reference's mapRange test, kreeq.cpp:150). */
+int  kq_validate_segment(kq_ctx *ctx, const char *seq, uint64_t len,
+                         uint32_t cov_cutoff, kq_base *out, kq_qv *acc);
+/* errorRate src/kreeq.cpp:36-40 and QV = -10 log10(err) :87,96 */
+double kq_error_rate(uint64_t missing, uint64_t total, int k);
+double kq_qv_value(uint64_t missing, uint64_t total, int k);
+
+/* ---- host consumers (subgraph / variants) ---------------------------------------- */
+
+/* replaces the lookup idiom maps[i]->find(key) [+ maps32[i]->find(key)]
+ * src/kreeq.cpp:150-166,231-244; src/subgraph.cpp:235-245; src/variants.cpp:118-133.
+ * found[i]=0 leaves rec[i] untouched. */
+int  kq_lookup_batch(kq_ctx *ctx, const uint64_t *keys, size_t n, kq_rec32 *rec, uint8_t *found);
+
+/* logical {key -> record} set of this shard sorted by key (parity checks,
+ * writers).  *n in: capacity of keys/recs, out: records present. */
+int  kq_export(kq_ctx *ctx, uint64_t *keys, kq_rec32 *recs, size_t *n);
+int  kq_distinct(kq_ctx *ctx, uint64_t *n);
+
+/* ---- packed-sequence stage API (device-resident; bench `value`, multi-GPU) ------ */
+
+/* 2-bit packing used on the wire: base i -> bits [2*(i%32), +2) of word i/32
+ * (A0 C1 G2 T3, first base least significant == the key's digit order,
+ * kmer.h:785-788); invalid[i/64] bit i%64 set for every non-ACGT byte.
+ * kq_packed_words(len) gives the number of uint64 words of EACH array the
+ * kernels may read (includes the zero / all-invalid tail padding). */
+size_t kq_packed_words(size_t len);
+int    kq_pack_host(const char *ascii, size_t len, uint64_t *bases, uint64_t *invalid, int nthreads);
+
+/* fused extract + insert of k-mer start positions [pos0, pos0+npos) of a packed
+ * device-resident sequence of `len` bases (only keys this shard owns). */
+int  kq_dev_count_packed(kq_ctx *ctx, const uint64_t *d_bases, const uint64_t *d_invalid,
+                         uint64_t len, uint64_t pos0, uint64_t npos);
+/* extract only: tuples of every valid window routed by owner.  Tuples for
+ * rank r are appended at d_keys[r*cap_per_rank + ...], d_edges[...]; d_counts
+ * (nranks uint64, zeroed by the caller) receives the number per rank.  Overflow
+ * of cap_per_rank is reported by kq_sync/KQ_ENOMEM. */
+int  kq_dev_extract_route(kq_ctx *ctx, const uint64_t *d_bases, const uint64_t *d_invalid,
+                          uint64_t len, uint64_t pos0, uint64_t npos,
+                          uint64_t *d_keys, uint8_t *d_edges, uint64_t cap_per_rank,
+                          unsigned long long *d_counts);
+/* insert (key, edgeBit) tuples (row A3) already resident on the device */
+int  kq_dev_insert_tuples(kq_ctx *ctx, const uint64_t *d_keys, const uint8_t *d_edges, uint64_t n);
+/* probe positions [0, len-k+1) of one packed device-resident segment;
+ * d_out (len entries) and d_acc (kq_qv, accumulates) are device memory. */
+int  kq_dev_validate_packed(kq_ctx *ctx, const uint64_t *d_bases, const uint64_t *d_invalid,
+                            uint64_t len, uint32_t cov_cutoff, kq_base *d_out, kq_qv *d_acc);
+/* make sure the table can take `extra` more distinct keys without growing
+ * inside a timed region */
+int  kq_reserve(kq_ctx *ctx, uint64_t extra_distinct);
+
+/* counters for bench.py: kernels launched by this handle, bytes copied */
+int  kq_counters(kq_ctx *ctx, uint64_t *kernel_launches, uint64_t *h2d_bytes, uint64_t *d2h_bytes);
+/* CUDA-event time (ms) spent in the dominant kernel class since the last call
+ * with reset=1: which = 0 count/insert, 1 validate/probe.  Only measured when
+ * kq_set_timing(ctx,1). */
+int  kq_set_timing(kq_ctx *ctx, int on);
+int  kq_kernel_time_ms(kq_ctx *ctx, int which, double *ms, uint64_t *launches, int reset);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KREEQ_B200_H */
