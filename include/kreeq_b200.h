@@ -100,6 +100,12 @@ int  kq_db_merge_hc_parts(const char *dir, int nranks);      /* -> <dir>/.map.hc
 int  kq_db_load(kq_ctx *ctx, const char *dir);
 /* k stored in <dir>/.index, or a negative error */
 int  kq_db_read_k(const char *dir);
+/* host-only codec of the same layout (no GPU needed; tools and format tests):
+ * write logical records (<=254 instances -> 8-bit record, else cov=255 placeholder
+ * + 32-bit record in .map.hc.bin), read back the lookup-visible
+ * records sorted by key (*n in: capacity, out: count). */
+int  kq_db_write_records(const char *dir, int k, const uint64_t *keys, const kq_rec32 *recs, size_t n);
+int  kq_db_read_records(const char *dir, uint64_t *keys, kq_rec32 *recs, size_t *n);
 
 /* ---- union (row A4) ---------------------------------------------------------- */
 

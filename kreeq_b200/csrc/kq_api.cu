@@ -1,0 +1,970 @@
+// kq_api.cu -- implementation of the C-ABI in include/kreeq_b200.h.
+//
+// One kq_ctx = one GPU = one shard of the key space.  Host buffers are staged through a ring of
+// pinned buffers (pack to 2 bit on the host pool -> cudaMemcpyAsync -> kernel), everything is
+// enqueued on one stream (the caller's, after kq_set_stream) so the host packs batch i+1 while the
+// GPU inserts batch i.  There is no CPU fallback anywhere in this file.
+#include "../../include/kreeq_b200.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include <sys/stat.h>
+
+#include "kq_host.h"
+#include "kq_kernels.h"
+
+using namespace kq;
+
+static_assert(sizeof(kq_rec32) == sizeof(Rec32), "kq_rec32 layout");
+static_assert(sizeof(kq_base) == sizeof(Base) && sizeof(kq_base) == 16, "kq_base layout");
+
+namespace {
+
+constexpr int NBUF = 3;                          // staging ring depth
+constexpr uint64_t CHUNK = 16ull << 20;          // k-mer start positions per staged batch
+constexpr double MAX_LOAD = 0.60;                // grow T beyond this
+constexpr double TARGET_LOAD = 0.40;             // load right after a grow / reserve
+constexpr uint64_t MIN_CAP = 1ull << 16;
+constexpr uint64_t MIN_SCAP = 1ull << 14;
+
+thread_local std::string g_create_error;
+
+struct Stage {                                   // one staging slot (count and validate share them)
+    uint64_t *h_bases = nullptr, *h_inv = nullptr;    // pinned
+    uint64_t *d_bases = nullptr, *d_inv = nullptr;
+    Base *h_out = nullptr, *d_out = nullptr;          // validate results (pinned / device)
+    size_t words = 0, out_n = 0;
+    cudaEvent_t done = nullptr; bool busy = false;
+};
+
+struct TimedRange { cudaEvent_t a, b; int which; };
+
+}  // namespace
+
+struct kq_ctx {
+    int k = 0, device = 0;
+    cudaStream_t own_stream = nullptr, stream = nullptr;
+    Slot *T = nullptr; uint64_t cap = 0;
+    SideSlot *S = nullptr; uint64_t scap = 0;
+    unsigned long long *d_occ = nullptr;         // [0] T, [1] S
+    unsigned long long *d_inst = nullptr;        // k-mer instances inserted
+    unsigned long long *d_acc = nullptr;         // validate counters (3)
+    int *d_err = nullptr;
+    uint64_t occ_bound = 0;                      // upper bound of T occupancy
+    int rank = 0, nranks = 1;
+    bool loaded_db = false;                      // table holds literal database entries (load/union)
+    Stage st[NBUF]; int next_stage = 0;
+    uint64_t launches = 0, h2d = 0, d2h = 0;
+    bool timing = false; std::vector<TimedRange> ranges; std::vector<cudaEvent_t> ev_pool;
+    double time_ms[2] = {0, 0}; uint64_t time_n[2] = {0, 0};
+    std::string err;
+};
+
+namespace {
+
+int fail(kq_ctx *c, int code, const std::string &msg) { if (c) c->err = msg; else g_create_error = msg; return code; }
+
+#define CU(call)                                                                                     \
+    do { cudaError_t e_ = (call);                                                                   \
+         if (e_ != cudaSuccess) return fail(c, e_ == cudaErrorMemoryAllocation ? KQ_ENOMEM : KQ_ECUDA, \
+                                            std::string(#call) + ": " + cudaGetErrorString(e_)); } while (0)
+
+TableView view(const kq_ctx *c) {
+    TableView tv;
+    tv.T = c->T; tv.cap = c->cap; tv.S = c->S; tv.scap = c->scap; tv.occ = c->d_occ; tv.err = c->d_err; tv.k = c->k;
+    tv.shard_rank = c->nranks > 1 ? c->rank : -1;
+    int shift = 0; while ((128 >> shift) > c->nranks) ++shift;       // 128 >> shift == nranks
+    tv.shard_shift = shift;                                          // owner = (key & 127) >> log2(128/nranks)
+    return tv;
+}
+
+// check the sticky device error word (requires a synchronised stream)
+int check_device_error(kq_ctx *c) {
+    int e = 0;
+    CU(cudaMemcpyAsync(&e, c->d_err, sizeof e, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    if (!e) return KQ_OK;
+    CU(cudaMemsetAsync(c->d_err, 0, sizeof(int), c->stream));
+    if (e & 4) return fail(c, KQ_ECORRUPT, "Error: int32 map missing 255 value from int8 map");
+    if (e & 8) return fail(c, KQ_ENOMEM, "route buffer overflow (cap_per_rank too small)");
+    if (e & 2) return fail(c, KQ_ENOMEM, "high-copy side table full");
+    return fail(c, KQ_ENOMEM, "k-mer table full");
+}
+
+int read_occ(kq_ctx *c, uint64_t occ[2]) {
+    unsigned long long h[2];
+    CU(cudaMemcpyAsync(h, c->d_occ, sizeof h, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    occ[0] = h[0]; occ[1] = h[1];
+    return KQ_OK;
+}
+
+int alloc_table(kq_ctx *c, uint64_t cap, Slot **out) {
+    cap = std::max<uint64_t>(MIN_CAP, (cap + 3) & ~3ull);            // whole 128-byte lines
+    CU(cudaMalloc(out, cap * sizeof(Slot)));
+    CU(cudaMemsetAsync(*out, 0, cap * sizeof(Slot), c->stream));
+    return KQ_OK;
+}
+
+int grow_table(kq_ctx *c, uint64_t new_cap) {
+    new_cap = std::max<uint64_t>(MIN_CAP, (new_cap + 3) & ~3ull);
+    Slot *old = c->T; const uint64_t old_cap = c->cap;
+    Slot *nt = nullptr;
+    int rc = alloc_table(c, new_cap, &nt);
+    if (rc) return rc;
+    c->T = nt; c->cap = new_cap;
+    if (old) {
+        CU(launch_rehash(c->stream, view(c), old, old_cap, &c->launches));
+        CU(cudaStreamSynchronize(c->stream));
+        CU(cudaFree(old));
+    }
+    return KQ_OK;
+}
+
+int grow_side(kq_ctx *c, uint64_t new_scap) {
+    SideSlot *old = c->S; const uint64_t old_cap = c->scap;
+    SideSlot *ns = nullptr;
+    CU(cudaMalloc(&ns, new_scap * sizeof(SideSlot)));
+    CU(cudaMemsetAsync(ns, 0, new_scap * sizeof(SideSlot), c->stream));
+    c->S = ns; c->scap = new_scap;
+    if (old) {
+        CU(cudaMemsetAsync(c->d_occ + 1, 0, sizeof(unsigned long long), c->stream));   // re-counted by the rehash
+        CU(launch_side_rehash(c->stream, view(c), old, old_cap, &c->launches));
+        CU(cudaStreamSynchronize(c->stream));
+        CU(cudaFree(old));
+    }
+    return KQ_OK;
+}
+
+// make room for `extra` more distinct keys; synchronises only when the cheap bound says it must
+int ensure_capacity(kq_ctx *c, uint64_t extra) {
+    if ((double)(c->occ_bound + extra) <= MAX_LOAD * (double)c->cap) { c->occ_bound += extra; return KQ_OK; }
+    uint64_t occ[2];
+    int rc = read_occ(c, occ); if (rc) return rc;
+    rc = check_device_error(c); if (rc) return rc;
+    c->occ_bound = occ[0];
+    if ((double)occ[1] > 0.5 * (double)c->scap) { rc = grow_side(c, c->scap * 4); if (rc) return rc; }
+    if ((double)(occ[0] + extra) > MAX_LOAD * (double)c->cap) {
+        uint64_t want = (uint64_t)((double)(occ[0] + extra) / TARGET_LOAD);
+        want = std::max(want, c->cap * 2);
+        rc = grow_table(c, want);
+        if (rc == KQ_ENOMEM) {                                       // retry with the tightest table that still works
+            cudaGetLastError();
+            rc = grow_table(c, (uint64_t)((double)(occ[0] + extra) / MAX_LOAD) + 1024);
+        }
+        if (rc) return rc;
+    }
+    c->occ_bound += extra;
+    return KQ_OK;
+}
+
+int stage_reserve(kq_ctx *c, Stage &s, size_t words, size_t out_n) {
+    if (words > s.words) {
+        if (s.h_bases) { cudaFreeHost(s.h_bases); cudaFreeHost(s.h_inv); cudaFree(s.d_bases); cudaFree(s.d_inv); }
+        s.h_bases = s.h_inv = s.d_bases = s.d_inv = nullptr; s.words = 0;
+        CU(cudaMallocHost(&s.h_bases, words * 8)); CU(cudaMallocHost(&s.h_inv, words * 8));
+        CU(cudaMalloc(&s.d_bases, words * 8));     CU(cudaMalloc(&s.d_inv, words * 8));
+        s.words = words;
+    }
+    if (out_n > s.out_n) {
+        if (s.h_out) { cudaFreeHost(s.h_out); cudaFree(s.d_out); }
+        s.h_out = s.d_out = nullptr; s.out_n = 0;
+        CU(cudaMallocHost(&s.h_out, out_n * sizeof(Base))); CU(cudaMalloc(&s.d_out, out_n * sizeof(Base)));
+        s.out_n = out_n;
+    }
+    return KQ_OK;
+}
+
+// wait until the GPU is done with staging slot s
+int stage_acquire(kq_ctx *c, Stage &s) {
+    if (s.busy) { CU(cudaEventSynchronize(s.done)); s.busy = false; }
+    return KQ_OK;
+}
+
+cudaEvent_t get_event(kq_ctx *c) {
+    if (!c->ev_pool.empty()) { cudaEvent_t e = c->ev_pool.back(); c->ev_pool.pop_back(); return e; }
+    cudaEvent_t e = nullptr; cudaEventCreate(&e); return e;
+}
+void time_begin(kq_ctx *c, int which) {
+    if (!c->timing) return;
+    TimedRange r{get_event(c), get_event(c), which};
+    cudaEventRecord(r.a, c->stream); c->ranges.push_back(r);
+}
+void time_end(kq_ctx *c) {
+    if (!c->timing) return;
+    cudaEventRecord(c->ranges.back().b, c->stream);
+}
+void time_collect(kq_ctx *c) {
+    for (auto &r : c->ranges) {
+        float ms = 0; cudaEventSynchronize(r.b); cudaEventElapsedTime(&ms, r.a, r.b);
+        c->time_ms[r.which] += ms; ++c->time_n[r.which];
+        c->ev_pool.push_back(r.a); c->ev_pool.push_back(r.b);
+    }
+    c->ranges.clear();
+}
+
+}  // namespace
+
+// ---- lifetime -----------------------------------------------------------------------------------------
+
+extern "C" int kq_create(kq_ctx **out, int k, int device, uint64_t expected_distinct) {
+    kq_ctx *c = nullptr;
+    if (!out) return fail(c, KQ_EINVAL, "kq_create: out is NULL");
+    *out = nullptr;
+    if (k < 1 || k > 32) return fail(c, KQ_EINVAL, "Invalid kmer length.");            // src/input.cpp:142
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail(c, KQ_ENODEV, std::string("no CUDA device: ") + (e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e)));
+    if (device < 0 || device >= ndev) return fail(c, KQ_ENODEV, "CUDA device ordinal out of range");
+    if (cudaSetDevice(device) != cudaSuccess) return fail(c, KQ_ENODEV, "cudaSetDevice failed");
+    kq_ctx *ctx = new kq_ctx;
+    ctx->k = k; ctx->device = device;
+    c = ctx;
+    auto bail = [&](int rc) { g_create_error = ctx->err; kq_destroy(ctx); return rc; };
+#define CC(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { ctx->err = std::string(#call) + ": " + cudaGetErrorString(e_); \
+                      return bail(e_ == cudaErrorMemoryAllocation ? KQ_ENOMEM : KQ_ENODEV); } } while (0)
+    CC(cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
+    ctx->stream = ctx->own_stream;
+    CC(cudaMalloc(&ctx->d_occ, 2 * sizeof(unsigned long long)));
+    CC(cudaMalloc(&ctx->d_inst, sizeof(unsigned long long)));
+    CC(cudaMalloc(&ctx->d_acc, 3 * sizeof(unsigned long long)));
+    CC(cudaMalloc(&ctx->d_err, sizeof(int)));
+    CC(cudaMemsetAsync(ctx->d_occ, 0, 2 * sizeof(unsigned long long), ctx->stream));
+    CC(cudaMemsetAsync(ctx->d_inst, 0, sizeof(unsigned long long), ctx->stream));
+    CC(cudaMemsetAsync(ctx->d_acc, 0, 3 * sizeof(unsigned long long), ctx->stream));
+    CC(cudaMemsetAsync(ctx->d_err, 0, sizeof(int), ctx->stream));
+    for (auto &s : ctx->st) CC(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
+#undef CC
+    const uint64_t want = expected_distinct ? (uint64_t)((double)expected_distinct / TARGET_LOAD) : (1ull << 20);
+    int rc = grow_table(ctx, want); if (rc) return bail(rc);
+    rc = grow_side(ctx, MIN_SCAP);  if (rc) return bail(rc);
+    if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) { ctx->err = "stream sync failed"; return bail(KQ_ECUDA); }
+    *out = ctx;
+    return KQ_OK;
+}
+
+extern "C" void kq_destroy(kq_ctx *c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    for (auto &s : c->st) {
+        if (s.h_bases) { cudaFreeHost(s.h_bases); cudaFreeHost(s.h_inv); cudaFree(s.d_bases); cudaFree(s.d_inv); }
+        if (s.h_out) { cudaFreeHost(s.h_out); cudaFree(s.d_out); }
+        if (s.done) cudaEventDestroy(s.done);
+    }
+    for (auto &r : c->ranges) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
+    for (auto e : c->ev_pool) cudaEventDestroy(e);
+    cudaFree(c->T); cudaFree(c->S); cudaFree(c->d_occ); cudaFree(c->d_inst); cudaFree(c->d_acc); cudaFree(c->d_err);
+    if (c->own_stream) cudaStreamDestroy(c->own_stream);
+    delete c;
+}
+
+extern "C" const char *kq_last_error(kq_ctx *c) { return c ? c->err.c_str() : g_create_error.c_str(); }
+extern "C" int kq_k(kq_ctx *c) { return c ? c->k : KQ_EINVAL; }
+
+extern "C" int kq_set_stream(kq_ctx *c, void *stream) {
+    if (!c) return KQ_EINVAL;
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    for (auto &s : c->st) s.busy = false;
+    c->stream = stream ? (cudaStream_t)stream : c->own_stream;
+    return KQ_OK;
+}
+
+extern "C" int kq_sync(kq_ctx *c) {
+    if (!c) return KQ_EINVAL;
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    for (auto &s : c->st) s.busy = false;
+    return check_device_error(c);
+}
+
+extern "C" int kq_owner_of(uint64_t key, int nranks) {
+    if (nranks < 1 || nranks > 128 || (nranks & (nranks - 1))) return KQ_EINVAL;
+    return (int)((key % 128) / (128 / (unsigned)nranks));
+}
+
+extern "C" int kq_set_shard(kq_ctx *c, int rank, int nranks) {
+    if (!c) return KQ_EINVAL;
+    if (nranks < 1 || nranks > 128 || (nranks & (nranks - 1)) || rank < 0 || rank >= nranks)
+        return fail(c, KQ_EINVAL, "kq_set_shard: nranks must be a power of two <= 128 and 0 <= rank < nranks");
+    c->rank = rank; c->nranks = nranks;
+    return KQ_OK;
+}
+
+extern "C" int kq_set_timing(kq_ctx *c, int on) { if (!c) return KQ_EINVAL; c->timing = on != 0; return KQ_OK; }
+
+extern "C" int kq_kernel_time_ms(kq_ctx *c, int which, double *ms, uint64_t *launches, int reset) {
+    if (!c || which < 0 || which > 1) return KQ_EINVAL;
+    CU(cudaSetDevice(c->device));
+    time_collect(c);
+    if (ms) *ms = c->time_ms[which];
+    if (launches) *launches = c->time_n[which];
+    if (reset) { c->time_ms[which] = 0; c->time_n[which] = 0; }
+    return KQ_OK;
+}
+
+extern "C" int kq_counters(kq_ctx *c, uint64_t *kernel_launches, uint64_t *h2d_bytes, uint64_t *d2h_bytes) {
+    if (!c) return KQ_EINVAL;
+    if (kernel_launches) *kernel_launches = c->launches;
+    if (h2d_bytes) *h2d_bytes = c->h2d;
+    if (d2h_bytes) *d2h_bytes = c->d2h;
+    return KQ_OK;
+}
+
+extern "C" int kq_reserve(kq_ctx *c, uint64_t extra) {
+    if (!c) return KQ_EINVAL;
+    CU(cudaSetDevice(c->device));
+    uint64_t occ[2];
+    int rc = read_occ(c, occ); if (rc) return rc;
+    c->occ_bound = occ[0];
+    if ((double)(occ[0] + extra) > TARGET_LOAD * (double)c->cap) {
+        rc = grow_table(c, (uint64_t)((double)(occ[0] + extra) / TARGET_LOAD)); if (rc) return rc;
+    }
+    return KQ_OK;
+}
+
+extern "C" int kq_clear(kq_ctx *c) {
+    if (!c) return KQ_EINVAL;
+    CU(cudaSetDevice(c->device));
+    CU(cudaMemsetAsync(c->T, 0, c->cap * sizeof(Slot), c->stream));
+    CU(cudaMemsetAsync(c->S, 0, c->scap * sizeof(SideSlot), c->stream));
+    CU(cudaMemsetAsync(c->d_occ, 0, 2 * sizeof(unsigned long long), c->stream));
+    CU(cudaMemsetAsync(c->d_inst, 0, sizeof(unsigned long long), c->stream));
+    CU(cudaMemsetAsync(c->d_err, 0, sizeof(int), c->stream));
+    c->occ_bound = 0; c->loaded_db = false;
+    return KQ_OK;
+}
+
+// ---- count ------------------------------------------------------------------------------------------------
+
+extern "C" size_t kq_packed_words(size_t len) { return packed_words(len); }
+
+extern "C" int kq_pack_host(const char *ascii, size_t len, uint64_t *bases, uint64_t *invalid, int nthreads) {
+    if ((!ascii && len) || !bases || !invalid) return KQ_EINVAL;
+    pack_sequence(ascii, len, bases, invalid, nthreads == 1 ? nullptr : &global_pool());
+    return KQ_OK;
+}
+
+extern "C" int kq_count_push(kq_ctx *c, const char *ascii, size_t len) {
+    if (!c || (!ascii && len)) return KQ_EINVAL;
+    if (c->loaded_db) return fail(c, KQ_ESTATE, "kq_count_push: the table holds a loaded/merged database");
+    const uint64_t k = (uint64_t)c->k;
+    if (len < k) return KQ_OK;                                         // src/graph-builder.cpp:60-64
+    CU(cudaSetDevice(c->device));
+    const uint64_t P = len - k + 1;                                    // k-mer start positions
+    for (uint64_t c0 = 0; c0 < P; c0 += CHUNK) {
+        const uint64_t npos = std::min(CHUNK, P - c0);
+        int rc = ensure_capacity(c, npos); if (rc) return rc;
+        // slice of the batch this chunk needs: one base before c0 (64-aligned down) .. k bases after the last start
+        const uint64_t a0 = c0 == 0 ? 0 : ((c0 - 1) & ~63ull);
+        const uint64_t a1 = std::min<uint64_t>(len, c0 + npos + k);
+        const size_t words = packed_words(a1 - a0);
+        Stage &s = c->st[c->next_stage]; c->next_stage = (c->next_stage + 1) % NBUF;
+        rc = stage_acquire(c, s); if (rc) return rc;
+        rc = stage_reserve(c, s, packed_words(CHUNK + k + 64), 0); if (rc) return rc;
+        pack_sequence(ascii + a0, a1 - a0, s.h_bases, s.h_inv, &global_pool());
+        // a1 < len means real bases follow: the padding after the slice must not read as "end of batch"
+        // for the last window's next base -- it cannot, because the slice extends k bases past the last start.
+        CU(cudaMemcpyAsync(s.d_bases, s.h_bases, words * 8, cudaMemcpyHostToDevice, c->stream));
+        CU(cudaMemcpyAsync(s.d_inv, s.h_inv, (words / 2 + 1) * 8, cudaMemcpyHostToDevice, c->stream));
+        c->h2d += words * 8 + (words / 2 + 1) * 8;
+        time_begin(c, 0);
+        CU(launch_count_packed(c->stream, view(c), s.d_bases, s.d_inv, c0 - a0, npos, c->d_inst, &c->launches));
+        time_end(c);
+        CU(cudaEventRecord(s.done, c->stream)); s.busy = true;
+    }
+    return KQ_OK;
+}
+
+extern "C" int kq_count_finish(kq_ctx *c) { return kq_sync(c); }
+
+extern "C" int kq_count_instances(kq_ctx *c, uint64_t *n) {
+    if (!c || !n) return KQ_EINVAL;
+    CU(cudaSetDevice(c->device));
+    unsigned long long v = 0;
+    CU(cudaMemcpyAsync(&v, c->d_inst, sizeof v, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    *n = v;
+    return KQ_OK;
+}
+
+extern "C" int kq_distinct(kq_ctx *c, uint64_t *n) {
+    if (!c || !n) return KQ_EINVAL;
+    CU(cudaSetDevice(c->device));
+    uint64_t occ[2]; int rc = read_occ(c, occ); if (rc) return rc;
+    *n = occ[0];
+    return KQ_OK;
+}
+
+extern "C" int kq_dev_count_packed(kq_ctx *c, const uint64_t *d_bases, const uint64_t *d_invalid,
+                                   uint64_t len, uint64_t pos0, uint64_t npos) {
+    if (!c || !d_bases || !d_invalid) return KQ_EINVAL;
+    if (len < (uint64_t)c->k) return KQ_OK;
+    if (pos0 + npos > len - c->k + 1) return fail(c, KQ_EINVAL, "kq_dev_count_packed: positions beyond len-k+1");
+    CU(cudaSetDevice(c->device));
+    int rc = ensure_capacity(c, npos); if (rc) return rc;
+    time_begin(c, 0);
+    CU(launch_count_packed(c->stream, view(c), d_bases, d_invalid, pos0, npos, c->d_inst, &c->launches));
+    time_end(c);
+    return KQ_OK;
+}
+
+extern "C" int kq_dev_extract_route(kq_ctx *c, const uint64_t *d_bases, const uint64_t *d_invalid,
+                                    uint64_t len, uint64_t pos0, uint64_t npos,
+                                    uint64_t *d_keys, uint8_t *d_edges, uint64_t cap_per_rank,
+                                    unsigned long long *d_counts) {
+    if (!c || !d_bases || !d_invalid || !d_keys || !d_edges || !d_counts) return KQ_EINVAL;
+    if (len < (uint64_t)c->k) return KQ_OK;
+    if (pos0 + npos > len - c->k + 1) return fail(c, KQ_EINVAL, "kq_dev_extract_route: positions beyond len-k+1");
+    CU(cudaSetDevice(c->device));
+    int rc = ensure_capacity(c, npos); if (rc) return rc;
+    const TableView tv = view(c);
+    RouteArgs ra{d_keys, d_edges, cap_per_rank, d_counts, c->nranks, c->rank, tv.shard_shift};
+    time_begin(c, 0);
+    CU(launch_extract_route(c->stream, tv, d_bases, d_invalid, pos0, npos, ra, c->d_inst, &c->launches));
+    time_end(c);
+    return KQ_OK;
+}
+
+extern "C" int kq_dev_insert_tuples(kq_ctx *c, const uint64_t *d_keys, const uint8_t *d_edges, uint64_t n) {
+    if (!c || (n && (!d_keys || !d_edges))) return KQ_EINVAL;
+    CU(cudaSetDevice(c->device));
+    int rc = ensure_capacity(c, n); if (rc) return rc;
+    time_begin(c, 0);
+    CU(launch_insert_tuples(c->stream, view(c), d_keys, d_edges, n, c->d_inst, &c->launches));
+    time_end(c);
+    return KQ_OK;
+}
+
+// ---- validate -----------------------------------------------------------------------------------------------
+
+extern "C" double kq_error_rate(uint64_t missing, uint64_t total, int k) {      // src/kreeq.cpp:36-40
+    return 1 - pow(1 - (double)missing / total, (double)1 / k);
+}
+extern "C" double kq_qv_value(uint64_t missing, uint64_t total, int k) {        // src/kreeq.cpp:87,96
+    return -10 * log10(kq_error_rate(missing, total, k));
+}
+
+extern "C" int kq_dev_validate_packed(kq_ctx *c, const uint64_t *d_bases, const uint64_t *d_invalid,
+                                      uint64_t len, uint32_t cutoff, kq_base *d_out, kq_qv *d_acc) {
+    if (!c || !d_bases || !d_invalid || !d_out || !d_acc) return KQ_EINVAL;
+    CU(cudaSetDevice(c->device));
+    const uint64_t kcount = len >= (uint64_t)c->k ? len - c->k + 1 : 0;
+    time_begin(c, 1);
+    CU(launch_validate(c->stream, view(c), d_bases, d_invalid, 0, 0, len, kcount, cutoff,
+                       reinterpret_cast<Base *>(d_out), reinterpret_cast<unsigned long long *>(d_acc), &c->launches));
+    time_end(c);
+    return KQ_OK;
+}
+
+extern "C" int kq_validate_segment(kq_ctx *c, const char *seq, uint64_t len, uint32_t cutoff, kq_base *out, kq_qv *acc) {
+    if (!c || (!seq && len) || (!out && len) || !acc) return KQ_EINVAL;
+    if (len == 0) return KQ_OK;
+    CU(cudaSetDevice(c->device));
+    const uint64_t k = (uint64_t)c->k;
+    const uint64_t kcount = len >= k ? len - k + 1 : 0;                // src/kreeq.cpp:123-126
+    CU(cudaMemsetAsync(c->d_acc, 0, 3 * sizeof(unsigned long long), c->stream));
+    const uint64_t VCH = 4ull << 20;                                   // output entries per staged chunk
+    struct Pending { Stage *s; uint64_t c0, n; };
+    Pending pend[NBUF]; int npend = 0;
+    auto drain_one = [&](Pending &p) -> int {                          // pinned -> caller memory, on the pool
+        int rc = stage_acquire(c, *p.s); if (rc) return rc;
+        const size_t grain = 1 << 18, tasks = (p.n + grain - 1) / grain;
+        Base *src = p.s->h_out; kq_base *dst = out + p.c0; const uint64_t n = p.n;
+        global_pool().parallel_for(tasks, [&](size_t t) {
+            const size_t b = t * grain, e = std::min<size_t>(n, b + grain);
+            std::memcpy(dst + b, src + b, (e - b) * sizeof(Base));
+        });
+        return KQ_OK;
+    };
+    for (uint64_t c0 = 0; c0 < len; c0 += VCH) {
+        const uint64_t n = std::min(VCH, len - c0);
+        if (npend == NBUF) { int rc = drain_one(pend[0]); if (rc) return rc; for (int i = 1; i < NBUF; ++i) pend[i - 1] = pend[i]; --npend; }
+        Stage &s = c->st[c->next_stage]; c->next_stage = (c->next_stage + 1) % NBUF;
+        int rc = stage_acquire(c, s); if (rc) return rc;
+        rc = stage_reserve(c, s, packed_words(std::max(CHUNK, VCH) + k + 64), VCH); if (rc) return rc;
+        const uint64_t a0 = c0 == 0 ? 0 : ((c0 - 1) & ~63ull);
+        const uint64_t a1 = std::min<uint64_t>(len, c0 + n + k);
+        const size_t words = packed_words(a1 - a0);
+        pack_sequence(seq + a0, a1 - a0, s.h_bases, s.h_inv, &global_pool());
+        CU(cudaMemcpyAsync(s.d_bases, s.h_bases, words * 8, cudaMemcpyHostToDevice, c->stream));
+        CU(cudaMemcpyAsync(s.d_inv, s.h_inv, (words / 2 + 1) * 8, cudaMemcpyHostToDevice, c->stream));
+        c->h2d += words * 8 + (words / 2 + 1) * 8;
+        time_begin(c, 1);
+        CU(launch_validate(c->stream, view(c), s.d_bases, s.d_inv, a0, c0, n, kcount, cutoff, s.d_out, c->d_acc, &c->launches));
+        time_end(c);
+        CU(cudaMemcpyAsync(s.h_out, s.d_out, n * sizeof(Base), cudaMemcpyDeviceToHost, c->stream));
+        c->d2h += n * sizeof(Base);
+        CU(cudaEventRecord(s.done, c->stream)); s.busy = true;
+        pend[npend++] = Pending{&s, c0, n};
+    }
+    for (int i = 0; i < npend; ++i) { int rc = drain_one(pend[i]); if (rc) return rc; }
+    unsigned long long h[3];
+    CU(cudaMemcpyAsync(h, c->d_acc, sizeof h, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    c->d2h += sizeof h;
+    int rc = check_device_error(c); if (rc) return rc;
+    acc->missing += h[0]; acc->kcount += h[1]; acc->edge_missing += h[2];
+    return KQ_OK;
+}
+
+extern "C" int kq_lookup_batch(kq_ctx *c, const uint64_t *keys, size_t n, kq_rec32 *rec, uint8_t *found) {
+    if (!c || (n && (!keys || !rec || !found))) return KQ_EINVAL;
+    if (!n) return KQ_OK;
+    CU(cudaSetDevice(c->device));
+    uint64_t *dk = nullptr; Rec32 *dr = nullptr; uint8_t *df = nullptr;
+    CU(cudaMalloc(&dk, n * 8)); CU(cudaMalloc(&dr, n * sizeof(Rec32))); CU(cudaMalloc(&df, n));
+    CU(cudaMemcpyAsync(dk, keys, n * 8, cudaMemcpyHostToDevice, c->stream));
+    CU(launch_lookup(c->stream, view(c), dk, n, dr, df, &c->launches));
+    std::vector<Rec32> hr(n);
+    CU(cudaMemcpyAsync(hr.data(), dr, n * sizeof(Rec32), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(found, df, n, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    c->h2d += n * 8; c->d2h += n * (sizeof(Rec32) + 1);
+    cudaFree(dk); cudaFree(dr); cudaFree(df);
+    for (size_t i = 0; i < n; ++i) if (found[i]) std::memcpy(&rec[i], &hr[i], sizeof(Rec32));
+    return check_device_error(c);
+}
+
+// ---- stats / export ---------------------------------------------------------------------------------------------
+
+namespace {
+
+// copy the side table to the host
+int fetch_side(kq_ctx *c, std::vector<SideSlot> &side) {
+    side.resize(c->scap);
+    CU(cudaMemcpyAsync(side.data(), c->S, c->scap * sizeof(SideSlot), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    c->d2h += c->scap * sizeof(SideSlot);
+    return KQ_OK;
+}
+
+inline uint32_t clamp_u32(unsigned long long v) { return v > KQ_LARGEST ? KQ_LARGEST : (uint32_t)v; }
+
+struct FullStats { kq_stats s; std::vector<std::pair<uint64_t, uint64_t>> hist; };
+
+// DBG::summary over all maps + DBG::DBstats, src/graph-builder.cpp:240-295
+int compute_stats(kq_ctx *c, FullStats &fs) {
+    CU(cudaSetDevice(c->device));
+    DevStats *d_ds = nullptr; unsigned long long *d_hist = nullptr, *d_big = nullptr;
+    const unsigned long long big_cap = c->scap;
+    CU(cudaMalloc(&d_ds, sizeof(DevStats))); CU(cudaMalloc(&d_hist, HIST_BINS * 8)); CU(cudaMalloc(&d_big, big_cap * 8));
+    CU(cudaMemsetAsync(d_ds, 0, sizeof(DevStats), c->stream));
+    CU(cudaMemsetAsync(d_hist, 0, HIST_BINS * 8, c->stream));
+    CU(launch_stats(c->stream, view(c), d_ds, d_hist, d_big, big_cap, &c->launches));
+    DevStats ds; std::vector<unsigned long long> hist(HIST_BINS);
+    CU(cudaMemcpyAsync(&ds, d_ds, sizeof ds, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(hist.data(), d_hist, HIST_BINS * 8, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    if (ds.big_n > big_cap) { cudaFree(d_ds); cudaFree(d_hist); cudaFree(d_big); return fail(c, KQ_ENOMEM, "stats: high-coverage list overflow"); }
+    std::vector<unsigned long long> big(ds.big_n);
+    if (ds.big_n) CU(cudaMemcpy(big.data(), d_big, ds.big_n * 8, cudaMemcpyDeviceToHost));
+    cudaFree(d_ds); cudaFree(d_hist); cudaFree(d_big);
+    c->d2h += sizeof ds + HIST_BINS * 8 + ds.big_n * 8;
+
+    std::vector<std::pair<uint64_t, uint64_t>> extra;                 // coverages outside the device histogram
+    uint64_t total = ds.total, uniq = ds.unique, distinct = ds.distinct, edges = ds.edges;
+    for (auto v : big) { total += v; extra.emplace_back(v, 1); }
+    // every maps32 entry counts (src/graph-builder.cpp:259-266)
+    std::vector<SideSlot> side; int rc = fetch_side(c, side); if (rc) return rc;
+    for (const auto &q : side) {
+        if (!q.tag || !(q.kind & KQ_SIDE_MAP32)) continue;
+        const uint32_t cov = clamp_u32(q.cov);
+        for (int w = 0; w < 4; ++w) edges += (q.fw[w] > 0 || q.bw[w] > 0);
+        ++distinct; total += cov;
+        if (cov < (uint32_t)HIST_BINS) ++hist[cov]; else extra.emplace_back(cov, 1);
+    }
+    fs.hist.clear();
+    for (int i = 0; i < HIST_BINS; ++i) if (hist[i]) fs.hist.emplace_back((uint64_t)i, (uint64_t)hist[i]);
+    std::sort(extra.begin(), extra.end());
+    for (auto &e : extra) { if (!fs.hist.empty() && fs.hist.back().first == e.first) fs.hist.back().second += e.second; else fs.hist.push_back(e); }
+    fs.s.total = total; fs.s.unique = uniq; fs.s.distinct = distinct; fs.s.edges = edges;
+    fs.s.missing = (uint64_t)(pow(4, c->k) - distinct);               // evaluated in double, src/graph-builder.cpp:286
+    return KQ_OK;
+}
+
+// all occupied T slots as XRec (unsorted) + the side table
+int fetch_records(kq_ctx *c, std::vector<XRec> &recs, std::vector<SideSlot> &side) {
+    CU(cudaSetDevice(c->device));
+    uint64_t occ[2]; int rc = read_occ(c, occ); if (rc) return rc;
+    XRec *d_out = nullptr; unsigned long long *d_n = nullptr;
+    const unsigned long long cap = occ[0] + 1;
+    CU(cudaMalloc(&d_out, cap * sizeof(XRec))); CU(cudaMalloc(&d_n, 8));
+    CU(cudaMemsetAsync(d_n, 0, 8, c->stream));
+    CU(launch_export(c->stream, view(c), d_out, cap, d_n, &c->launches));
+    unsigned long long n = 0;
+    CU(cudaMemcpyAsync(&n, d_n, 8, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    if (n > cap) { cudaFree(d_out); cudaFree(d_n); return fail(c, KQ_ECUDA, "export: occupancy counter out of sync"); }
+    recs.resize(n);
+    if (n) CU(cudaMemcpy(recs.data(), d_out, n * sizeof(XRec), cudaMemcpyDeviceToHost));
+    cudaFree(d_out); cudaFree(d_n);
+    c->d2h += n * sizeof(XRec);
+    return fetch_side(c, side);
+}
+
+const SideSlot *host_side_find(const std::vector<SideSlot> &side, uint64_t key) {
+    const uint64_t scap = side.size();
+    uint64_t i = (uint64_t)(((unsigned __int128)mix64(key ^ 0x9E3779B97F4A7C15ULL) * scap) >> 64);
+    for (uint64_t n = 0; n < scap; ++n) {
+        if (side[i].tag == key + 1) return &side[i];
+        if (side[i].tag == 0) return nullptr;
+        if (++i == scap) i = 0;
+    }
+    return nullptr;
+}
+
+}  // namespace
+
+extern "C" int kq_stats_get(kq_ctx *c, kq_stats *out) {
+    if (!c || !out) return KQ_EINVAL;
+    FullStats fs; int rc = compute_stats(c, fs); if (rc) return rc;
+    *out = fs.s;
+    return KQ_OK;
+}
+
+extern "C" int kq_hist(kq_ctx *c, uint64_t *cov, uint64_t *n, size_t *len) {
+    if (!c || !len) return KQ_EINVAL;
+    FullStats fs; int rc = compute_stats(c, fs); if (rc) return rc;
+    const size_t cap = *len; *len = fs.hist.size();
+    if (cov && n) for (size_t i = 0; i < fs.hist.size() && i < cap; ++i) { cov[i] = fs.hist[i].first; n[i] = fs.hist[i].second; }
+    return KQ_OK;
+}
+
+extern "C" int kq_export(kq_ctx *c, uint64_t *keys, kq_rec32 *recs, size_t *n) {
+    if (!c || !n) return KQ_EINVAL;
+    std::vector<XRec> xs; std::vector<SideSlot> side;
+    int rc = fetch_records(c, xs, side); if (rc) return rc;
+    std::sort(xs.begin(), xs.end(), [](const XRec &a, const XRec &b) { return a.key < b.key; });
+    const size_t cap = *n; size_t m = 0;
+    for (const auto &x : xs) {
+        Rec32 r = x.r;
+        if (x.flags & F_PLACEHOLDER) {                                 // resolve through maps32 (src/kreeq.cpp:158-166)
+            const SideSlot *q = host_side_find(side, x.key);
+            if (!q || !(q->kind & KQ_SIDE_MAP32)) return fail(c, KQ_ECORRUPT, "Error: int32 map missing 255 value from int8 map");
+            for (int w = 0; w < 4; ++w) { r.fw[w] = clamp_u32(q->fw[w]); r.bw[w] = clamp_u32(q->bw[w]); }
+            r.cov = clamp_u32(q->cov);
+        }
+        if (keys && recs && m < cap) { keys[m] = x.key; std::memcpy(&recs[m], &r, sizeof r); }
+        ++m;
+    }
+    *n = m;
+    return KQ_OK;
+}
+
+// ---- persistence -------------------------------------------------------------------------------------------------
+
+namespace {
+
+std::string map_path(const std::string &dir, int m) { return dir + "/.map." + std::to_string(m) + ".bin"; }
+void owned_maps(const kq_ctx *c, int &lo, int &hi) { const int per = 128 / c->nranks; lo = c->rank * per; hi = lo + per; }
+
+// split the resident database into the reference's on-disk representation
+int gather_for_save(kq_ctx *c, std::vector<std::vector<Rec8Entry>> &maps, std::vector<Rec32Entry> &hc) {
+    std::vector<XRec> xs; std::vector<SideSlot> side;
+    int rc = fetch_records(c, xs, side); if (rc) return rc;
+    maps.assign(128, {});
+    for (const auto &x : xs) {
+        Rec8Entry e; e.key = x.key;
+        if (!(x.flags & F_PLACEHOLDER) && x.r.cov <= 254) {            // exact 8-bit record
+            for (int w = 0; w < 4; ++w) { e.fw[w] = (uint8_t)x.r.fw[w]; e.bw[w] = (uint8_t)x.r.bw[w]; }
+            e.cov = (uint8_t)x.r.cov;
+        } else if (x.flags & F_PLACEHOLDER) {                          // literal placeholder of a loaded database
+            for (int w = 0; w < 4; ++w) { e.fw[w] = (uint8_t)x.r.fw[w]; e.bw[w] = (uint8_t)x.r.bw[w]; }
+            e.cov = 255;
+        } else {                                                       // >= 255 instances: placeholder + 32-bit record
+            std::memset(e.fw, 0, 4); std::memset(e.bw, 0, 4); e.cov = 255;
+            Rec32Entry h; h.key = x.key; std::memcpy(h.fw, x.r.fw, 16); std::memcpy(h.bw, x.r.bw, 16); h.cov = x.r.cov;
+            hc.push_back(h);
+        }
+        maps[x.key % 128].push_back(e);
+    }
+    for (const auto &q : side) {
+        if (!q.tag || !(q.kind & KQ_SIDE_MAP32)) continue;
+        Rec32Entry h; h.key = q.tag - 1;
+        for (int w = 0; w < 4; ++w) { h.fw[w] = clamp_u32(q.fw[w]); h.bw[w] = clamp_u32(q.bw[w]); }
+        h.cov = clamp_u32(q.cov);
+        hc.push_back(h);
+    }
+    return KQ_OK;
+}
+
+std::string hc_part_path(const std::string &dir, int rank) { return dir + "/.hc.part." + std::to_string(rank); }
+
+int write_hc_part(kq_ctx *c, const std::string &dir, const std::vector<Rec32Entry> &hc) {
+    FILE *f = std::fopen(hc_part_path(dir, c->rank).c_str(), "wb");
+    if (!f) return fail(c, KQ_EIO, "cannot write " + hc_part_path(dir, c->rank));
+    const uint64_t n = hc.size();
+    bool ok = std::fwrite(&n, 8, 1, f) == 1 && (n == 0 || std::fwrite(hc.data(), sizeof(Rec32Entry), n, f) == n);
+    ok = std::fclose(f) == 0 && ok;
+    return ok ? KQ_OK : fail(c, KQ_EIO, "short write on " + hc_part_path(dir, c->rank));
+}
+
+int save_impl(kq_ctx *c, const char *dir_c, bool maps_too) {
+    if (!c || !dir_c) return KQ_EINVAL;
+    const std::string dir(dir_c);
+    mkdir(dir.c_str(), 0777);
+    std::vector<std::vector<Rec8Entry>> maps; std::vector<Rec32Entry> hc;
+    int rc = gather_for_save(c, maps, hc); if (rc) return rc;
+    if (maps_too) {
+        int lo, hi; owned_maps(c, lo, hi);
+        std::vector<std::string> errs(128);
+        global_pool().parallel_for((size_t)(hi - lo), [&](size_t i) { errs[lo + i] = write_map8(map_path(dir, lo + (int)i), maps[lo + i]); });
+        for (const auto &e : errs) if (!e.empty()) return fail(c, KQ_EIO, e);
+        if (c->rank == 0) { const std::string e = write_index(dir, c->k); if (!e.empty()) return fail(c, KQ_EIO, e); }
+    }
+    if (c->nranks == 1 && maps_too) {
+        const std::string e = write_map32(dir + "/.map.hc.bin", hc);
+        return e.empty() ? KQ_OK : fail(c, KQ_EIO, e);
+    }
+    return write_hc_part(c, dir, hc);
+}
+
+// upload literal maps32 entries as the side table
+int upload_map32(kq_ctx *c, const std::vector<Rec32Entry> &hc, uint64_t min_scap) {
+    uint64_t scap = std::max<uint64_t>(min_scap, MIN_SCAP);
+    while (scap < 4 * hc.size()) scap *= 2;
+    std::vector<SideSlot> side(scap);
+    std::memset(side.data(), 0, scap * sizeof(SideSlot));
+    for (const auto &h : hc) {
+        uint64_t i = (uint64_t)(((unsigned __int128)mix64(h.key ^ 0x9E3779B97F4A7C15ULL) * scap) >> 64);
+        while (side[i].tag && side[i].tag != h.key + 1) if (++i == scap) i = 0;
+        SideSlot &q = side[i];
+        q.tag = h.key + 1; q.kind = KQ_SIDE_MAP32; q.cov = h.cov;
+        for (int w = 0; w < 4; ++w) { q.fw[w] = h.fw[w]; q.bw[w] = h.bw[w]; }
+    }
+    CU(cudaFree(c->S)); c->S = nullptr;
+    CU(cudaMalloc(&c->S, scap * sizeof(SideSlot))); c->scap = scap;
+    CU(cudaMemcpyAsync(c->S, side.data(), scap * sizeof(SideSlot), cudaMemcpyHostToDevice, c->stream));
+    const unsigned long long n = hc.size();
+    CU(cudaMemcpyAsync(c->d_occ + 1, &n, 8, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    c->h2d += scap * sizeof(SideSlot);
+    return KQ_OK;
+}
+
+// read the 8-bit maps this shard owns of one database
+int read_owned_maps(kq_ctx *c, const std::string &dir, std::vector<Rec8Entry> &all) {
+    int lo, hi; owned_maps(c, lo, hi);
+    std::vector<std::vector<Rec8Entry>> per((size_t)(hi - lo)); std::vector<std::string> errs((size_t)(hi - lo));
+    global_pool().parallel_for((size_t)(hi - lo), [&](size_t i) { errs[i] = read_map8(map_path(dir, lo + (int)i), per[i]); });
+    for (const auto &e : errs) if (!e.empty()) return fail(c, KQ_EIO, e);
+    size_t n = 0; for (auto &v : per) n += v.size();
+    all.clear(); all.reserve(n);
+    for (auto &v : per) { all.insert(all.end(), v.begin(), v.end()); std::vector<Rec8Entry>().swap(v); }
+    return KQ_OK;
+}
+
+int read_owned_hc(kq_ctx *c, const std::string &dir, std::vector<Rec32Entry> &hc) {
+    std::vector<Rec32Entry> all;
+    const std::string e = read_map32(dir + "/.map.hc.bin", all);
+    if (!e.empty()) return fail(c, KQ_EIO, e);
+    int lo, hi; owned_maps(c, lo, hi);
+    for (const auto &h : all) { const int m = (int)(h.key % 128); if (m >= lo && m < hi) hc.push_back(h); }
+    return KQ_OK;
+}
+
+enum class Feed { Put, MergeRef, AddLogical };
+
+// stream host records through a device buffer into one of the table kernels, in sub-batches small
+// enough that the side table can never fill up inside a launch
+int feed_records(kq_ctx *c, const std::vector<XRec> &xs, Feed mode) {
+    if (xs.empty()) return KQ_OK;
+    XRec *d = nullptr;
+    const uint64_t max_batch = 8ull << 20;
+    CU(cudaMalloc(&d, std::min<uint64_t>(xs.size(), max_batch) * sizeof(XRec)));
+    for (uint64_t off = 0; off < xs.size();) {
+        uint64_t n = std::min<uint64_t>(xs.size() - off, max_batch);
+        if (mode != Feed::Put) {
+            uint64_t occ[2]; int rc = read_occ(c, occ); if (rc) { cudaFree(d); return rc; }
+            if (occ[1] * 4 > c->scap) { rc = grow_side(c, c->scap * 4); if (rc) { cudaFree(d); return rc; } }
+            n = std::min<uint64_t>(n, c->scap / 4);
+        }
+        int rc = ensure_capacity(c, n); if (rc) { cudaFree(d); return rc; }
+        CU(cudaMemcpyAsync(d, xs.data() + off, n * sizeof(XRec), cudaMemcpyHostToDevice, c->stream));
+        c->h2d += n * sizeof(XRec);
+        const TableView tv = view(c);
+        cudaError_t e = mode == Feed::Put ? launch_put(c->stream, tv, d, n, &c->launches)
+                      : mode == Feed::MergeRef ? launch_merge_ref(c->stream, tv, d, n, &c->launches)
+                                               : launch_add_records(c->stream, tv, d, n, &c->launches);
+        if (e != cudaSuccess) { cudaFree(d); return fail(c, KQ_ECUDA, cudaGetErrorString(e)); }
+        CU(cudaStreamSynchronize(c->stream));
+        off += n;
+    }
+    cudaFree(d);
+    return check_device_error(c);
+}
+
+XRec raw_xrec(const Rec8Entry &e) {
+    XRec x; x.key = e.key; x.flags = e.cov == 255 ? F_PLACEHOLDER : 0u;
+    for (int w = 0; w < 4; ++w) { x.r.fw[w] = e.fw[w]; x.r.bw[w] = e.bw[w]; }
+    x.r.cov = e.cov;
+    return x;
+}
+
+}  // namespace
+
+extern "C" int kq_db_save(kq_ctx *c, const char *dir) { return save_impl(c, dir, true); }
+extern "C" int kq_db_save_hc_part(kq_ctx *c, const char *dir) { return save_impl(c, dir, false); }
+
+extern "C" int kq_db_merge_hc_parts(const char *dir_c, int nranks) {
+    if (!dir_c || nranks < 1) return KQ_EINVAL;
+    const std::string dir(dir_c);
+    std::vector<Rec32Entry> hc;
+    for (int r = 0; r < nranks; ++r) {
+        FILE *f = std::fopen(hc_part_path(dir, r).c_str(), "rb");
+        if (!f) return KQ_EIO;
+        uint64_t n = 0;
+        if (std::fread(&n, 8, 1, f) != 1) { std::fclose(f); return KQ_EIO; }
+        const size_t at = hc.size(); hc.resize(at + n);
+        if (n && std::fread(hc.data() + at, sizeof(Rec32Entry), n, f) != n) { std::fclose(f); return KQ_EIO; }
+        std::fclose(f);
+    }
+    if (!write_map32(dir + "/.map.hc.bin", hc).empty()) return KQ_EIO;
+    for (int r = 0; r < nranks; ++r) std::remove(hc_part_path(dir, r).c_str());
+    return KQ_OK;
+}
+
+extern "C" int kq_db_read_k(const char *dir) {
+    if (!dir) return KQ_EINVAL;
+    const int k = read_index_k(dir);
+    return k < 0 ? KQ_EIO : k;
+}
+
+extern "C" int kq_db_load(kq_ctx *c, const char *dir_c) {
+    if (!c || !dir_c) return KQ_EINVAL;
+    const std::string dir(dir_c);
+    const int k = read_index_k(dir);
+    if (k < 0) return fail(c, KQ_EIO, "Cannot load DBG input. Exiting.");          // src/input.cpp:70-72
+    if (k != c->k) return fail(c, KQ_EINVAL, "database k-mer length " + std::to_string(k) + " differs from the handle's " + std::to_string(c->k));
+    int rc = kq_clear(c); if (rc) return rc;
+    std::vector<Rec8Entry> all; rc = read_owned_maps(c, dir, all); if (rc) return rc;
+    std::vector<Rec32Entry> hc; rc = read_owned_hc(c, dir, hc); if (rc) return rc;
+    rc = upload_map32(c, hc, MIN_SCAP); if (rc) return rc;
+    std::vector<XRec> xs(all.size());
+    global_pool().parallel_for((all.size() + (1 << 20) - 1) >> 20, [&](size_t t) {
+        const size_t b = t << 20, e = std::min(all.size(), b + (1 << 20));
+        for (size_t i = b; i < e; ++i) xs[i] = raw_xrec(all[i]);
+    });
+    rc = kq_reserve(c, xs.size()); if (rc) return rc;
+    rc = feed_records(c, xs, Feed::Put); if (rc) return rc;
+    c->loaded_db = true;
+    return KQ_OK;
+}
+
+// ---- union -----------------------------------------------------------------------------------------------------------
+
+extern "C" int kq_union(kq_ctx *c, const char *const *dirs, int n, int ref_compatible) {
+    if (!c || !dirs || n < 1) return KQ_EINVAL;
+    CU(cudaSetDevice(c->device));
+    for (int i = 0; i < n; ++i) {                                      // src/input.cpp:126-145
+        if (!dirs[i]) return KQ_EINVAL;
+        const int k = read_index_k(dirs[i]);
+        if (k < 0) return fail(c, KQ_EIO, std::string("cannot read ") + dirs[i] + "/.index");
+        if (k != c->k) return fail(c, KQ_EINVAL, "Cannot merge databases with different kmer length.");
+    }
+    int rc = kq_clear(c); if (rc) return rc;
+    auto sat = [](uint32_t a, uint32_t b) { return KQ_LARGEST - a >= b ? a + b : KQ_LARGEST; };
+
+    if (ref_compatible) {
+        // 1. saturating sum of all high-copy maps (src/graph-builder.cpp:301-336)
+        std::vector<Rec32Entry> hc;
+        for (int i = 0; i < n; ++i) { rc = read_owned_hc(c, dirs[i], hc); if (rc) return rc; }
+        std::sort(hc.begin(), hc.end(), [](const Rec32Entry &a, const Rec32Entry &b) { return a.key < b.key; });
+        std::vector<Rec32Entry> m32;
+        for (const auto &h : hc) {
+            if (!m32.empty() && m32.back().key == h.key) {
+                Rec32Entry &d = m32.back();
+                for (int w = 0; w < 4; ++w) { d.fw[w] = sat(d.fw[w], h.fw[w]); d.bw[w] = sat(d.bw[w], h.bw[w]); }
+                d.cov = sat(d.cov, h.cov);
+            } else m32.push_back(h);
+        }
+        rc = upload_map32(c, m32, 1ull << 20); if (rc) return rc;
+        // 2. DB0's 8-bit maps raw (kmer.h:668-672), 3. later databases in order (kmer.h:674-686)
+        for (int i = 0; i < n; ++i) {
+            std::vector<Rec8Entry> all; rc = read_owned_maps(c, dirs[i], all); if (rc) return rc;
+            std::vector<XRec> xs(all.size());
+            for (size_t j = 0; j < all.size(); ++j) xs[j] = raw_xrec(all[j]);
+            std::vector<Rec8Entry>().swap(all);
+            rc = feed_records(c, xs, i == 0 ? Feed::Put : Feed::MergeRef); if (rc) return rc;
+        }
+        c->loaded_db = true;
+        return KQ_OK;
+    }
+
+    // exact mode: saturating sum of every database's lookup-visible records
+    rc = grow_side(c, std::max<uint64_t>(c->scap, 1ull << 20)); if (rc) return rc;
+    for (int i = 0; i < n; ++i) {
+        std::vector<Rec32Entry> hc; rc = read_owned_hc(c, dirs[i], hc); if (rc) return rc;
+        std::sort(hc.begin(), hc.end(), [](const Rec32Entry &a, const Rec32Entry &b) { return a.key < b.key; });
+        std::vector<Rec8Entry> all; rc = read_owned_maps(c, dirs[i], all); if (rc) return rc;
+        std::vector<XRec> xs(all.size());
+        for (size_t j = 0; j < all.size(); ++j) {
+            xs[j] = raw_xrec(all[j]); xs[j].flags = 0;
+            if (all[j].cov != 255) continue;
+            auto it = std::lower_bound(hc.begin(), hc.end(), all[j].key, [](const Rec32Entry &a, uint64_t key) { return a.key < key; });
+            if (it == hc.end() || it->key != all[j].key) return fail(c, KQ_ECORRUPT, "Error: int32 map missing 255 value from int8 map");
+            std::memcpy(xs[j].r.fw, it->fw, 16); std::memcpy(xs[j].r.bw, it->bw, 16); xs[j].r.cov = it->cov;
+        }
+        rc = feed_records(c, xs, Feed::AddLogical); if (rc) return rc;
+    }
+    return KQ_OK;
+}
+
+// ---- host-only codec entry points ---------------------------------------------------------------------------------------
+
+extern "C" int kq_db_write_records(const char *dir_c, int k, const uint64_t *keys, const kq_rec32 *recs, size_t n) {
+    if (!dir_c || k < 1 || k > 32 || (n && (!keys || !recs))) return KQ_EINVAL;
+    const std::string dir(dir_c);
+    mkdir(dir.c_str(), 0777);
+    std::vector<std::vector<Rec8Entry>> maps(128); std::vector<Rec32Entry> hc;
+    for (size_t i = 0; i < n; ++i) {
+        Rec8Entry e; e.key = keys[i];
+        if (recs[i].cov <= 254) {
+            for (int w = 0; w < 4; ++w) { e.fw[w] = (uint8_t)recs[i].fw[w]; e.bw[w] = (uint8_t)recs[i].bw[w]; }
+            e.cov = (uint8_t)recs[i].cov;
+        } else {
+            std::memset(e.fw, 0, 4); std::memset(e.bw, 0, 4); e.cov = 255;
+            Rec32Entry h; h.key = keys[i]; std::memcpy(h.fw, recs[i].fw, 16); std::memcpy(h.bw, recs[i].bw, 16); h.cov = recs[i].cov;
+            hc.push_back(h);
+        }
+        maps[keys[i] % 128].push_back(e);
+    }
+    for (int m = 0; m < 128; ++m) if (!write_map8(map_path(dir, m), maps[m]).empty()) return KQ_EIO;
+    if (!write_map32(dir + "/.map.hc.bin", hc).empty()) return KQ_EIO;
+    return write_index(dir, k).empty() ? KQ_OK : KQ_EIO;
+}
+
+extern "C" int kq_db_read_records(const char *dir_c, uint64_t *keys, kq_rec32 *recs, size_t *n) {
+    if (!dir_c || !n) return KQ_EINVAL;
+    const std::string dir(dir_c);
+    std::vector<Rec32Entry> hc;
+    if (!read_map32(dir + "/.map.hc.bin", hc).empty()) return KQ_EIO;
+    std::sort(hc.begin(), hc.end(), [](const Rec32Entry &a, const Rec32Entry &b) { return a.key < b.key; });
+    std::vector<Rec8Entry> all;
+    for (int m = 0; m < 128; ++m) if (!read_map8(map_path(dir, m), all).empty()) return KQ_EIO;
+    std::sort(all.begin(), all.end(), [](const Rec8Entry &a, const Rec8Entry &b) { return a.key < b.key; });
+    const size_t cap = *n; size_t m = 0;
+    for (const auto &e : all) {
+        kq_rec32 r;
+        if (e.cov == 255) {
+            auto it = std::lower_bound(hc.begin(), hc.end(), e.key, [](const Rec32Entry &a, uint64_t key) { return a.key < key; });
+            if (it == hc.end() || it->key != e.key) return KQ_ECORRUPT;
+            std::memcpy(r.fw, it->fw, 16); std::memcpy(r.bw, it->bw, 16); r.cov = it->cov;
+        } else {
+            for (int w = 0; w < 4; ++w) { r.fw[w] = e.fw[w]; r.bw[w] = e.bw[w]; }
+            r.cov = e.cov;
+        }
+        if (keys && recs && m < cap) { keys[m] = e.key; recs[m] = r; }
+        ++m;
+    }
+    *n = m;
+    return KQ_OK;
+}

@@ -1,0 +1,189 @@
+"""GPU parity: the CUDA path through the C-ABI against the oracle, bit-exact (integer work)."""
+import numpy as np
+import pytest
+
+from helpers import assert_same_records, random_genome, sample_reads
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def mods():
+    import kreeq_b200
+    import kreeq_oracle as ko
+    return kreeq_b200, ko
+
+
+@pytest.mark.parametrize("k", [21, 31, 32, 15, 4, 1])
+def test_count_validate_matches_oracle(mods, k):
+    kb, ko = mods
+    rng = np.random.default_rng(100 + k)
+    genome = random_genome(rng, 30000)
+    batches = [sample_reads(rng, genome, 1500, 150, err=0.01, n_rate=0.002) for _ in range(3)]
+    ref = ko.Table(k)
+    with kb.DBG(k=k) as g:
+        n_ref = 0
+        for b in batches:
+            n_ref += ref.count_batch(b)
+            g.traverseInReads(b)
+        g.finalize()
+        assert g.instances() == n_ref
+        assert_same_records(g.export(), ref.export())
+        assert g.stats() == ref.stats()
+        hc, hn = g.hist(); rc_, rn = ref.hist()
+        assert np.array_equal(hc, rc_) and np.array_equal(hn, rn)
+        for cutoff in (0, 3):
+            g.tot_missing = g.tot_kcount = g.tot_edge_missing = 0
+            asm = genome.copy()
+            asm[rng.integers(0, asm.size, 40)] = ord("A")
+            out = g.evaluateSegment(asm.tobytes(), cov_cutoff=cutoff)
+            rc, rout, racc = ref.validate_segment(asm.tobytes(), cutoff)
+            assert rc == 0
+            assert out.tobytes() == rout.tobytes()
+            assert (g.tot_missing, g.tot_kcount, g.tot_edge_missing) == racc
+
+
+def test_high_copy_spill(mods):
+    """>254 and >65535 instances of one k-mer: 32-bit spill record and the side table."""
+    kb, ko = mods
+    k = 21
+    rng = np.random.default_rng(5)
+    unit = random_genome(rng, 60).tobytes()
+    batch = (b"A" * 500 + b"N") * 3 + (unit + b"N") * 300 + (b"ACGT" * 20000 + b"N")
+    ref = ko.Table(k); ref.count_batch(batch)
+    with kb.DBG(k=k) as g:
+        g.traverseInReads(batch); g.finalize()
+        assert_same_records(g.export(), ref.export())
+        assert g.stats() == ref.stats()
+        seg = b"A" * 100 + unit + b"ACGT" * 30
+        out = g.evaluateSegment(seg)
+        rc, rout, racc = ref.validate_segment(seg)
+        assert out.tobytes() == rout.tobytes()
+        assert (g.tot_missing, g.tot_kcount, g.tot_edge_missing) == racc
+
+
+def test_edge_cases(mods):
+    kb, ko = mods
+    with kb.DBG(k=21) as g:
+        g.traverseInReads(b"")                       # empty batch
+        g.traverseInReads(b"ACGTN")                  # shorter than k
+        g.traverseInReads(b"N" * 100)                # nothing valid
+        g.traverseInReads(b"ACGTACGTACGTACGTACGTA")  # exactly one k-mer, no trailing N
+        g.finalize()
+        ref = ko.Table(21)
+        for b in (b"", b"ACGTN", b"N" * 100, b"ACGTACGTACGTACGTACGTA"):
+            ref.count_batch(b)
+        assert_same_records(g.export(), ref.export())
+        assert g.stats() == ref.stats()
+        out = g.evaluateSegment(b"ACGT")             # segment shorter than k
+        assert out.size == 4 and not out["cov"].any() and g.tot_kcount == 0
+        out = g.evaluateSegment(b"ACGTACGTACGTACGTACGTAC")
+        rc, rout, racc = ref.validate_segment(b"ACGTACGTACGTACGTACGTAC")
+        assert out.tobytes() == rout.tobytes()
+
+
+def test_large_batch_chunking_and_growth(mods):
+    """One push larger than the staging chunk, table growing from its minimum size."""
+    kb, ko = mods
+    k = 21
+    rng = np.random.default_rng(11)
+    genome = random_genome(rng, 3_000_000)
+    batch = sample_reads(rng, genome, 130000, 150, err=0.01)     # ~19.6 M bases > 16 Mi chunk
+    ref = ko.Table(k); n_ref = ref.count_batch(batch)
+    with kb.DBG(k=k) as g:
+        g.traverseInReads(batch); g.finalize()
+        assert g.instances() == n_ref
+        assert_same_records(g.export(), ref.export())
+        out = g.evaluateSegment(genome.tobytes())                # > 4 Mi-entry validate chunks? no: 3 M; still chunk edge below
+        rc, rout, racc = ref.validate_segment(genome.tobytes())
+        assert out.tobytes() == rout.tobytes()
+        assert (g.tot_missing, g.tot_kcount, g.tot_edge_missing) == racc
+
+
+def test_save_load_roundtrip_and_union(mods, tmp_path):
+    kb, ko = mods
+    k = 21
+    rng = np.random.default_rng(21)
+    genome = random_genome(rng, 20000)
+    rep = (b"A" * 400 + b"N") * 2
+    dirs, refs = [], []
+    for i in range(3):
+        batch = sample_reads(rng, genome, 800, 150, err=0.02) + (rep if i != 1 else b"") + (b"ACGT" * 100 + b"N") * (i + 1)
+        ref = ko.Table(k); ref.count_batch(batch); ref.finalize(); refs.append(ref)
+        d = str(tmp_path / ("s%d.kreeq" % i)); dirs.append(d)
+        with kb.DBG(k=k) as g:
+            g.traverseInReads(batch); g.finalize(); g.save(d)
+        disk = ko.read_db(d, check=True)                          # strict phmap layout check
+        assert_same_records(disk.export(), ref.export())
+        assert disk.stats() == ref.stats()
+        with kb.DBG(k=k) as g2:
+            g2.load(d)
+            assert_same_records(g2.export(), ref.export())
+            assert g2.stats() == ref.stats()
+    for order in ([0, 1, 2], [1, 0, 2], [2, 1, 0]):
+        oracle_tabs = [ko.read_db(dirs[i], check=False) for i in order]
+        u = ko.union(oracle_tabs)
+        with kb.DBG(k=k) as g:
+            g.kunion([dirs[i] for i in order], ref_compatible=True)
+            assert_same_records(g.export(), u.export())
+            assert g.stats() == u.stats()
+            seg = genome.tobytes()[:5000] + b"A" * 60
+            out = g.evaluateSegment(seg)
+            rc, rout, racc = u.validate_segment(seg)
+            assert out.tobytes() == rout.tobytes()
+            ud = str(tmp_path / ("u%s.kreeq" % "".join(map(str, order))))
+            g.save(ud)
+        disk = ko.read_db(ud, check=True)
+        k8a, r8a = disk.dump8(); k8b, r8b = u.dump8()
+        assert np.array_equal(k8a, k8b)
+        k32a, r32a = disk.dump32(); k32b, r32b = u.dump32()
+        assert np.array_equal(k32a, k32b) and r32a.tobytes() == r32b.tobytes()
+        assert disk.stats() == u.stats()
+
+
+def test_sharded_handles_equal_single(mods):
+    """2 and 4 shards (handles on one GPU): union of shard exports == single-handle result."""
+    kb, ko = mods
+    k = 21
+    rng = np.random.default_rng(31)
+    genome = random_genome(rng, 40000)
+    batch = sample_reads(rng, genome, 3000, 150, err=0.01)
+    ref = ko.Table(k); ref.count_batch(batch)
+    rk, rr = ref.export()
+    for nr in (2, 4):
+        ks, rs, inst = [], [], 0
+        outs, accs = [], np.zeros(3, dtype=np.int64)
+        for r in range(nr):
+            with kb.DBG(k=k, rank=r, nranks=nr) as g:
+                g.traverseInReads(batch); g.finalize()
+                kk, rec = g.export()
+                assert np.all(((kk % np.uint64(128)) // np.uint64(128 // nr)) == r)
+                ks.append(kk); rs.append(rec); inst += g.instances()
+                outs.append(g.evaluateSegment(genome.tobytes()))
+                accs += np.array([g.tot_missing, g.tot_kcount, g.tot_edge_missing])
+        kk = np.concatenate(ks); rec = np.concatenate(rs)
+        o = np.argsort(kk)
+        assert np.array_equal(kk[o], rk) and rec[o].tobytes() == rr.tobytes()
+        rc, rout, racc = ref.validate_segment(genome.tobytes())
+        merged = np.zeros(rout.size, dtype=rout.dtype)
+        for f in ("fw", "bw", "cov", "isFw"):
+            merged[f] = sum(o_[f].astype(np.uint64) for o_ in outs).astype(merged[f].dtype)
+        assert merged.tobytes() == rout.tobytes()
+        assert tuple(int(x) for x in accs) == racc
+
+
+def test_find_lookup_batch(mods):
+    kb, ko = mods
+    rng = np.random.default_rng(41)
+    genome = random_genome(rng, 5000)
+    batch = sample_reads(rng, genome, 400, 100, err=0.0)
+    ref = ko.Table(21); ref.count_batch(batch)
+    rk, rr = ref.export()
+    with kb.DBG(k=21) as g:
+        g.traverseInReads(batch); g.finalize()
+        q = np.concatenate([rk[:500], rng.integers(0, 1 << 42, 500, dtype=np.uint64)])
+        rec, found = g.find(q)
+        assert found[:500].all()
+        assert rec[:500].tobytes() == rr[:500].tobytes()
+        present = np.isin(q[500:], rk)
+        assert np.array_equal(found[500:], present)
