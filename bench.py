@@ -1,0 +1,413 @@
+#!/usr/bin/env python
+"""bench.py -- k-mers counted/s and assembly k-mers validated/s of the kreeq hot path on N B200s.
+
+Workload (BASELINE.json configs[1], "C2"): synthetic 100 Mbp genome, 30x 150 bp paired reads with
+1 % substitution error, k=21: count, then validate the genome.  One step = one whole count+validate
+pass over that input.  At N>1 every rank extracts its own 30x read set (weak scaling), the key space
+is sharded (key % 128) / (128/N) and tuples are routed with an all-to-all per round.
+
+  value : k-mer instances counted / s, inputs (2-bit packed reads) already resident in HBM
+  e2e   : the same through the C-ABI with HOST ASCII buffers (pack + H2D inside the timed region),
+          validate results copied back to host memory
+  --impl reference : the unmodified reference binary (oracle/_ref/kreeq) on the host cores, bounded sample
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import shutil
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+K = 21
+READ_LEN = 150
+ERR = 0.01
+ALG_BYTES_COUNT = 26.25      # 0.25 in + 8 key + 9 record read + 9 record write
+ALG_BYTES_VALIDATE = 30.25   # 0.25 in + 17 slot + 13 out
+SECTOR_BYTES_COUNT = 64.25
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--genome-mbp", type=float, default=100.0, help="C2 genome size (default 100 Mbp)")
+    ap.add_argument("--coverage", type=float, default=30.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--ref-sample-reads", type=int, default=1_500_000)
+    return ap.parse_args()
+
+
+def workload(args):
+    genome = int(args.genome_mbp * 1e6)
+    pairs = int(genome * args.coverage / (2 * READ_LEN))
+    return {"workload": "C2: synthetic %g Mbp genome, %gx %d bp paired reads, %g%% error, k=%d: count then validate"
+                        % (args.genome_mbp, args.coverage, READ_LEN, ERR * 100, K),
+            "genome_bp": genome, "read_pairs_per_gpu": pairs, "k": K}
+
+
+# ---- clocks ------------------------------------------------------------------------------------------
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx, self.rows, self.proc = gpu_index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx = float(r[2])
+            except (ValueError, IndexError):
+                continue
+            for name, col in (("hw_slowdown", 4), ("hw_thermal_slowdown", 5), ("sw_thermal_slowdown", 6), ("sw_power_cap", 7)):
+                if len(r) > col and r[col].lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ---- reference arm (CPU) --------------------------------------------------------------------------------
+
+REF_BIN = os.path.join(ROOT, "oracle", "_ref", "kreeq")
+
+
+def write_fastq(path, ascii_n_joined, n_reads, read_len):
+    """'N'-joined uint8 array [n_reads*(L+1)] -> 4-line FASTQ (numpy, no Python loop)."""
+    import numpy as np
+    a = np.asarray(ascii_n_joined, dtype=np.uint8).reshape(n_reads, read_len + 1)[:, :read_len]
+    row = np.empty((n_reads, 3 + read_len + 3 + read_len + 1), dtype=np.uint8)
+    row[:, 0:3] = np.frombuffer(b"@r\n", dtype=np.uint8)
+    row[:, 3:3 + read_len] = a
+    row[:, 3 + read_len:6 + read_len] = np.frombuffer(b"\n+\n", dtype=np.uint8)
+    row[:, 6 + read_len:6 + 2 * read_len] = ord("I")
+    row[:, -1] = ord("\n")
+    row.tofile(path)
+
+
+def write_fasta(path, genome_ascii, name="chr"):
+    import numpy as np
+    with open(path, "wb") as f:
+        f.write((">%s\n" % name).encode())
+        np.asarray(genome_ascii, dtype=np.uint8).tofile(f)
+        f.write(b"\n")
+
+
+def reference_sample(args, workdir):
+    """A bounded sample of C2 for the CPU arms: same genome generator, fewer reads, 10 Mbp of assembly."""
+    import torch
+    from kreeq_b200 import synth
+    dev = "cuda" if torch.cuda.is_available() else "cpu"
+    gsize = int(args.genome_mbp * 1e6)
+    genome = synth.random_genome_codes(gsize, 2, dev)
+    n_pairs = args.ref_sample_reads // 2
+    reads = synth.paired_reads_ascii(genome, n_pairs, READ_LEN, ERR, 2).cpu().numpy()
+    asm = synth.codes_to_ascii(genome[:min(gsize, 10_000_000)]).cpu().numpy()
+    fq = os.path.join(workdir, "sample.fastq"); fa = os.path.join(workdir, "asm.fasta")
+    write_fastq(fq, reads, 2 * n_pairs, READ_LEN)
+    write_fasta(fa, asm)
+    return fq, fa, 2 * n_pairs * (READ_LEN - K + 1), asm.size - K + 1
+
+
+def run_reference_once(fq, fa, workdir, threads):
+    """count: `kreeq validate -r sample.fastq -k 21 -o db.kreeq`; validate: `-f asm.fasta -d db.kreeq -o out.kwig`
+    (BASELINE.md section 3), each timed by wall clock, run in a scratch CWD."""
+    db = os.path.join(workdir, "db.kreeq")
+    shutil.rmtree(db, ignore_errors=True)
+    t0 = time.perf_counter()
+    subprocess.check_call([REF_BIN, "validate", "-r", fq, "-k", str(K), "-o", db, "-j", str(threads)],
+                          cwd=workdir, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    t1 = time.perf_counter()
+    subprocess.check_call([REF_BIN, "validate", "-f", fa, "-d", db, "-o", os.path.join(workdir, "out.kwig"), "-j", str(threads)],
+                          cwd=workdir, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    t2 = time.perf_counter()
+    return t1 - t0, t2 - t1
+
+
+def cpu_baseline(args, steps, warmup):
+    """Times the unmodified reference on the host cores on a bounded sample of the workload."""
+    if not os.path.exists(REF_BIN):
+        return None
+    threads = os.cpu_count() or 1
+    base = "/dev/shm" if os.path.isdir("/dev/shm") else None
+    workdir = tempfile.mkdtemp(prefix="kreeq_ref_", dir=base)
+    try:
+        fq, fa, inst, asm_k = reference_sample(args, workdir)
+        tc, tv = [], []
+        for i in range(warmup + steps):
+            c, v = run_reference_once(fq, fa, workdir, threads)
+            if i >= warmup:
+                tc.append(c); tv.append(v)
+        c = sum(tc) / len(tc); v = sum(tv) / len(tv)
+        return {"value": inst / c, "unit": "k-mers/s", "cores": threads, "kind": "reference",
+                "sample": "%d reads x %d bp of the same C2 generator (%d k-mer instances) counted by `kreeq validate -r -o db.kreeq -j %d`; "
+                          "validate: first %d bp of the genome vs that DB" % (args.ref_sample_reads // 2 * 2, READ_LEN, inst, threads, asm_k + K - 1),
+                "count_s": c, "validate_value": asm_k / v, "validate_s": v}
+    finally:
+        shutil.rmtree(workdir, ignore_errors=True)
+
+
+def main_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cfg = workload(args)
+    if not os.path.exists(REF_BIN):
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/kreeq not built (run __graft_entry__.build() where /root/reference is mounted)"}))
+        return
+    w = min(args.warmup, 1) if args.warmup else 0      # the CPU arm is deterministic after one cold-cache run
+    cb = cpu_baseline(args, args.steps, w)
+    line = {"impl": "reference", "metric": "kmers_counted_per_sec", "value": cb["value"], "unit": "k-mers/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": w, "ms_per_step": 1e3 * (cb["count_s"] + cb["validate_s"]),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+            "config": cfg, "cpu_baseline": cb,
+            "validate": {"metric": "assembly_kmers_validated_per_sec", "value": cb["validate_value"], "unit": "k-mers/s"},
+            "e2e": {"value": cb["value"], "unit": "k-mers/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+# ---- our arm (GPU) ------------------------------------------------------------------------------------------
+
+def main_ours(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import kreeq_b200
+    from kreeq_b200 import shard, synth
+    from kreeq_b200._lib import check, lib
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py --impl ours needs a CUDA device (there is no CPU fallback)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    L = lib()
+    cfg = workload(args)
+    gsize, pairs = cfg["genome_bp"], cfg["read_pairs_per_gpu"]
+    n_reads = 2 * pairs
+    inst_per_rank = n_reads * (READ_LEN - K + 1)
+    n_contigs = 10
+    contig = gsize // n_contigs
+
+    # -- synthetic input: same genome on every rank, each rank its own 30x read set ---------------------
+    genome = synth.random_genome_codes(gsize, 2, dev)
+    reads_dev = synth.paired_reads_ascii(genome, pairs, READ_LEN, ERR, 2 + 1000 * rank)
+    reads_host = torch.empty(reads_dev.numel(), dtype=torch.uint8, pin_memory=True)
+    reads_host.copy_(reads_dev)
+    del reads_dev
+    asm_host = torch.empty(gsize, dtype=torch.uint8, pin_memory=True)
+    asm_host.copy_(synth.codes_to_ascii(genome))
+    del genome
+    torch.cuda.empty_cache()
+    reads_np, asm_np = reads_host.numpy(), asm_host.numpy()
+
+    def pack_to_device(a):
+        words = L.kq_packed_words(a.size)
+        b = torch.empty(words, dtype=torch.int64, pin_memory=True)
+        m = torch.empty(words, dtype=torch.int64, pin_memory=True)
+        check(L.kq_pack_host(C.c_void_p(a.ctypes.data), a.size, C.c_void_p(b.data_ptr()), C.c_void_p(m.data_ptr()), 0))
+        return b.to(dev), m.to(dev)
+
+    d_rb, d_rm = pack_to_device(reads_np)
+    d_asm = [pack_to_device(asm_np[i * contig:(i + 1) * contig]) for i in range(n_contigs)]
+    asm_k = n_contigs * (contig - K + 1)
+    d_out = torch.empty(contig * 4, dtype=torch.int32, device=dev)          # kq_base[contig]
+    d_acc = torch.zeros(3, dtype=torch.int64, device=dev)
+    h_out = np.zeros(contig, dtype=kreeq_b200.BASE)
+
+    # distinct k-mers per shard: genome k-mers + ~k novel k-mers per error, all ranks' reads together
+    est_distinct = int((gsize + world * n_reads * READ_LEN * ERR * K * 0.85) / world * 1.05)
+    g = kreeq_b200.DBG(k=K, device=local, expected_distinct=est_distinct, rank=rank, nranks=world)
+    stream = torch.cuda.current_stream()
+    g.set_stream(stream.cuda_stream)
+    router = shard.RoutedCounter(g, rank, world, 64 << 20, dev) if world > 1 else None
+    LAUNCH_POS = 512 << 20
+
+    def count_resident():
+        total = reads_np.size - K + 1
+        if world > 1:
+            router.count(d_rb, d_rm, reads_np.size)
+            return
+        for p0 in range(0, total, LAUNCH_POS):
+            check(L.kq_dev_count_packed(g.handle, C.c_void_p(d_rb.data_ptr()), C.c_void_p(d_rm.data_ptr()),
+                                        reads_np.size, p0, min(LAUNCH_POS, total - p0)), g.handle)
+
+    def validate_resident():
+        d_acc.zero_()
+        for b, m in d_asm:
+            check(L.kq_dev_validate_packed(g.handle, C.c_void_p(b.data_ptr()), C.c_void_p(m.data_ptr()), contig, 0,
+                                           C.c_void_p(d_out.data_ptr()), C.c_void_p(d_acc.data_ptr())), g.handle)
+            if world > 1:                       # every shard filled only the positions it owns
+                dist.reduce(d_out, 0, op=dist.ReduceOp.SUM)
+        if world > 1:
+            dist.all_reduce(d_acc)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+
+    def step_resident():
+        e0, e1, e2 = ev(), ev(), ev()
+        e0.record(stream)
+        g.clear()
+        count_resident()
+        e1.record(stream)
+        validate_resident()
+        e2.record(stream)
+        return e0, e1, e2
+
+    def step_e2e():
+        e0, e1, e2 = ev(), ev(), ev()
+        e0.record(stream)
+        g.clear()
+        B = 64 * (READ_LEN + 1) * 10000                       # ~97 MB pushes, cut at read boundaries
+        if world > 1:
+            for o in range(0, reads_np.size, B):
+                b, m = pack_to_device(reads_np[o:o + B])
+                router.count(b, m, min(B, reads_np.size - o))
+        else:
+            for o in range(0, reads_np.size, B):
+                g.traverseInReads(reads_np[o:o + B])
+        g.finalize()
+        e1.record(stream)
+        acc = kreeq_b200._lib.KqQV()
+        for i in range(n_contigs):
+            seg = asm_np[i * contig:(i + 1) * contig]
+            check(L.kq_validate_segment(g.handle, C.c_void_p(seg.ctypes.data), contig, 0,
+                                        C.c_void_p(h_out.ctypes.data), C.byref(acc)), g.handle)
+        e2.record(stream)
+        return e0, e1, e2
+
+    def run(step_fn, warmup, steps):
+        for _ in range(warmup):
+            step_fn()
+        barrier()
+        c0 = g.counters()
+        g.set_timing(True); g.kernel_time_ms(0); g.kernel_time_ms(1)
+        sampler = ClockSampler(local); sampler.start()
+        evs = [step_fn() for _ in range(steps)]
+        barrier()
+        clocks = sampler.stop()
+        kt_count, kn_count = g.kernel_time_ms(0)
+        kt_val, kn_val = g.kernel_time_ms(1)
+        g.set_timing(False)
+        c1 = g.counters()
+        tc = sum(a.elapsed_time(b) for a, b, _ in evs) / steps
+        tv = sum(b.elapsed_time(c) for _, b, c in evs) / steps
+        t = torch.tensor([tc, tv], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return {"count_ms": t[0].item(), "validate_ms": t[1].item(), "clocks": clocks,
+                "launches": c1["kernel_launches"] - c0["kernel_launches"],
+                "h2d": (c1["h2d_bytes"] - c0["h2d_bytes"]) / steps, "d2h": (c1["d2h_bytes"] - c0["d2h_bytes"]) / steps,
+                "kt_count": kt_count, "kn_count": kn_count, "kt_val": kt_val, "kn_val": kn_val}
+
+    res = run(step_resident, args.warmup, args.steps)
+    inst_total = inst_per_rank * world
+    value = inst_total / (res["count_ms"] * 1e-3)
+    peak, peak_src = measured_peaks()
+    line = {"metric": "kmers_counted_per_sec", "value": value, "unit": "k-mers/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": res["count_ms"] + res["validate_ms"],
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+            "config": dict(cfg, parallelism="keyshard%d" % world, kmer_instances_per_step=inst_total,
+                           assembly_kmers_per_step=asm_k, distinct_kmers=None,
+                           l2="no flush needed: table (%.1f GB/GPU) and inputs (%.2f GB/GPU) are far larger than the 126 MB L2"
+                              % (est_distinct / 0.4 * 32 / 1e9, reads_np.size * 0.375 / 1e9)),
+            "count_ms": res["count_ms"], "validate_ms": res["validate_ms"],
+            "validate": {"metric": "assembly_kmers_validated_per_sec", "value": asm_k / (res["validate_ms"] * 1e-3), "unit": "k-mers/s"},
+            "clocks": res["clocks"], "gpu_launches": res["launches"]}
+    # roofline of the dominant kernel (count/insert), per launch, from CUDA events around each launch
+    if res["kn_count"]:
+        per_launch_s = res["kt_count"] * 1e-3 / res["kn_count"]
+        units_per_launch = inst_per_rank * args.steps / res["kn_count"]
+        ach = ALG_BYTES_COUNT * units_per_launch / per_launch_s / 1e9
+        line["roofline"] = {"bound": "hbm", "kernel": "count_packed_kernel" if world == 1 else "extract_route_kernel+insert_tuples_kernel",
+                            "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+                            "peak_source": peak_src, "algorithmic_bytes_per_kmer": ALG_BYTES_COUNT,
+                            "sector_bound_frac": SECTOR_BYTES_COUNT * units_per_launch / per_launch_s / 1e9 / peak,
+                            "avg_launch_ms": per_launch_s * 1e3, "launches_timed": res["kn_count"]}
+        if res["kn_val"]:
+            vs = res["kt_val"] * 1e-3 / res["kn_val"]
+            va = ALG_BYTES_VALIDATE * (asm_k * args.steps / res["kn_val"]) / vs / 1e9
+            line["validate"]["roofline"] = {"bound": "hbm", "kernel": "validate_kernel", "achieved": va, "peak": peak,
+                                            "unit": "GB/s", "frac": va / peak, "avg_launch_ms": vs * 1e3}
+    try:
+        line["config"]["distinct_kmers"] = g.distinct() if world == 1 else None
+    except Exception:
+        pass
+    if not args.no_e2e:
+        e = run(step_e2e, min(args.warmup, 1), min(args.steps, 2))
+        line["e2e"] = {"value": inst_total / (e["count_ms"] * 1e-3), "unit": "k-mers/s",
+                       "h2d_bytes_per_step": e["h2d"] if world == 1 else reads_np.size * 0.375,
+                       "d2h_bytes_per_step": e["d2h"], "count_ms": e["count_ms"], "validate_ms": e["validate_ms"],
+                       "validate_value": asm_k / (e["validate_ms"] * 1e-3),
+                       "host_input_bytes_per_step": int(reads_np.size + asm_np.size), "steps": min(args.steps, 2)}
+    g.close()
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        del d_rb, d_rm, d_asm
+        torch.cuda.empty_cache()
+        cb = cpu_baseline(args, 1, 1)
+        if cb:
+            line["cpu_baseline"] = cb
+    if rank == 0:
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    if a.impl == "reference":
+        main_reference(a)
+    else:
+        main_ours(a)
