@@ -265,7 +265,10 @@ def main_ours(args):
     # distinct k-mers per shard: genome k-mers + ~k novel k-mers per error, all ranks' reads together
     est_distinct = int((gsize + world * n_reads * READ_LEN * ERR * K * 0.85) / world * 1.05)
     g = kreeq_b200.DBG(k=K, device=local, expected_distinct=est_distinct, rank=rank, nranks=world)
-    stream = torch.cuda.current_stream()
+    # a real (non-default) stream: kq_set_stream(NULL) would mean "the library's own stream", and the
+    # CUDA events below must be recorded on the stream the kernels are launched on
+    stream = torch.cuda.Stream(dev)
+    torch.cuda.set_stream(stream)
     g.set_stream(stream.cuda_stream)
     router = shard.RoutedCounter(g, rank, world, 64 << 20, dev) if world > 1 else None
     LAUNCH_POS = 512 << 20
