@@ -21,26 +21,41 @@ def owner_of(keys, nranks):
 
 
 def exchange_counts(send_counts, group=None):
-    """all-to-all of the per-destination tuple counts; returns the per-source counts (same device)."""
-    recv = torch.empty_like(send_counts)
-    dist.all_to_all_single(recv, send_counts, group=group)
-    return recv
+    """Every rank learns how many tuples each peer sends it: all-gather of the per-destination counts
+    (world x world int64, tiny); returns this rank's column (same device)."""
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    rows = [torch.empty_like(send_counts) for _ in range(world)]
+    dist.all_gather(rows, send_counts, group=group)
+    return torch.stack(rows)[:, rank].contiguous()
 
 
 def exchange_tuples(send_keys, send_edges, send_counts_host, recv_counts_host, recv_keys, recv_edges, group=None):
-    """Route tuples to their owners.
+    """Route tuples to their owners: one grouped send/recv per peer (ncclGroupStart ... ncclSend/ncclRecv
+    ... ncclGroupEnd under NCCL; plain point-to-point under gloo in the CPU tests).
 
     send_keys [nranks, cap] int64 / send_edges [nranks, cap] uint8 hold, for destination r, the first
     send_counts_host[r] tuples of slab r.  Received tuples are packed back to back into recv_keys /
     recv_edges (1-D, large enough); returns the number received."""
     n = len(send_counts_host)
-    ins_k = [send_keys[r, :int(send_counts_host[r])] for r in range(n)]
-    ins_e = [send_edges[r, :int(send_counts_host[r])] for r in range(n)]
+    me = dist.get_rank(group)
     offs = np.concatenate(([0], np.cumsum(recv_counts_host))).astype(np.int64)
-    outs_k = [recv_keys[int(offs[r]):int(offs[r + 1])] for r in range(n)]
-    outs_e = [recv_edges[int(offs[r]):int(offs[r + 1])] for r in range(n)]
-    dist.all_to_all(outs_k, ins_k, group=group)
-    dist.all_to_all(outs_e, ins_e, group=group)
+    ops = []
+    for r in range(n):
+        sc, rc = int(send_counts_host[r]), int(recv_counts_host[r])
+        dst_k, dst_e = recv_keys[int(offs[r]):int(offs[r + 1])], recv_edges[int(offs[r]):int(offs[r + 1])]
+        if r == me:
+            dst_k.copy_(send_keys[r, :sc]); dst_e.copy_(send_edges[r, :sc])
+            continue
+        if sc:
+            ops.append(dist.P2POp(dist.isend, send_keys[r, :sc], r, group))
+            ops.append(dist.P2POp(dist.isend, send_edges[r, :sc], r, group))
+        if rc:
+            ops.append(dist.P2POp(dist.irecv, dst_k, r, group))
+            ops.append(dist.P2POp(dist.irecv, dst_e, r, group))
+    if ops:
+        for w in dist.batch_isend_irecv(ops):
+            w.wait()
     return int(offs[-1])
 
 

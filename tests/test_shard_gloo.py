@@ -1,0 +1,84 @@
+"""Host-side logic of the multi-GPU path on CPU: world_size 2 over gloo.  Each rank extracts the
+(key, edgeBit) tuples of ITS read batch (oracle, standing in for kq_dev_extract_route), routes them
+by owner(key) = (key % 128) / (128 / nranks) with kreeq_b200.shard's all-to-all, inserts what it
+receives, and the union of the two shards must equal the single-table result (SURVEY 8e invariant)."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _free_port():
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close()
+    return p
+
+
+def _worker(rank, world, port, out_dir):
+    for p in (ROOT, os.path.join(ROOT, "oracle"), os.path.join(ROOT, "tests")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import kreeq_oracle as ko
+    from helpers import random_genome, sample_reads
+    from kreeq_b200 import shard
+    k = 21
+    rng = np.random.default_rng(77)
+    genome = random_genome(rng, 20000)
+    batches = [sample_reads(np.random.default_rng(100 + r), genome, 600, 120, err=0.01) + (b"A" * 300 + b"N") * 2 for r in range(world)]
+    keys, edges = ko.extract(k, batches[rank])
+    owner = shard.owner_of(keys, world)
+    cap = int(max(np.bincount(owner, minlength=world))) + 8
+    send_k = torch.zeros((world, cap), dtype=torch.int64); send_e = torch.zeros((world, cap), dtype=torch.uint8)
+    counts = torch.zeros(world, dtype=torch.int64)
+    for r in range(world):
+        sel = owner == r
+        n = int(sel.sum()); counts[r] = n
+        send_k[r, :n] = torch.from_numpy(keys[sel].view(np.int64)); send_e[r, :n] = torch.from_numpy(edges[sel])
+    recv_counts = shard.exchange_counts(counts)
+    recv_k = torch.zeros(int(recv_counts.sum()) + 4, dtype=torch.int64); recv_e = torch.zeros(recv_k.numel(), dtype=torch.uint8)
+    n = shard.exchange_tuples(send_k, send_e, counts.numpy(), recv_counts.numpy(), recv_k, recv_e)
+    assert n == int(recv_counts.sum())
+    rk = recv_k[:n].numpy().view(np.uint64); re_ = recv_e[:n].numpy()
+    assert np.all(shard.owner_of(rk, world) == rank)
+    t = ko.Table(k)
+    t.insert_tuples(rk, re_)
+    ek, er = t.export()
+    # validate: every rank probes the whole assembly against its shard; counters are summed, per-base rows merged
+    rc, out, acc = t.validate_segment(genome.tobytes())
+    # positions whose key another shard owns must not count here: mask them (what kq_validate_segment does on a shard)
+    gk, _ = ko.extract(k, genome.tobytes())
+    mine = shard.owner_of(gk, world) == rank
+    miss = int(((out["cov"][:gk.size] == 0) & mine).sum())
+    acc_t = torch.tensor([miss, int(mine.sum())], dtype=torch.int64)
+    dist.all_reduce(acc_t)
+    np.savez(os.path.join(out_dir, "shard%d.npz" % rank), keys=ek, recs=er, acc=acc_t.numpy())
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_rank_routing_equals_single_table(tmp_path):
+    world = 2
+    mp.spawn(_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import kreeq_oracle as ko
+    from helpers import random_genome, sample_reads
+    rng = np.random.default_rng(77)
+    genome = random_genome(rng, 20000)
+    ref = ko.Table(21)
+    for r in range(world):
+        ref.count_batch(sample_reads(np.random.default_rng(100 + r), genome, 600, 120, err=0.01) + (b"A" * 300 + b"N") * 2)
+    rk, rr = ref.export()
+    parts = [np.load(os.path.join(tmp_path, "shard%d.npz" % r)) for r in range(world)]
+    keys = np.concatenate([p["keys"] for p in parts]); recs = np.concatenate([p["recs"] for p in parts])
+    o = np.argsort(keys)
+    assert np.array_equal(keys[o], rk) and recs[o].tobytes() == rr.tobytes()
+    rc, out, acc = ref.validate_segment(genome.tobytes())
+    assert tuple(parts[0]["acc"]) == (acc[0], acc[1]) == tuple(parts[1]["acc"])
