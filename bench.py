@@ -270,17 +270,16 @@ def main_ours(args):
     stream = torch.cuda.Stream(dev)
     torch.cuda.set_stream(stream)
     g.set_stream(stream.cuda_stream)
-    router = shard.RoutedCounter(g, rank, world, 64 << 20, dev) if world > 1 else None
-    LAUNCH_POS = 512 << 20
+    router = shard.RoutedCounter(g, rank, world, 512 << 20, dev) if world > 1 else None
 
     def count_resident():
         total = reads_np.size - K + 1
         if world > 1:
             router.count(d_rb, d_rm, reads_np.size)
             return
-        for p0 in range(0, total, LAUNCH_POS):
-            check(L.kq_dev_count_packed(g.handle, C.c_void_p(d_rb.data_ptr()), C.c_void_p(d_rm.data_ptr()),
-                                        reads_np.size, p0, min(LAUNCH_POS, total - p0)), g.handle)
+        # one call: the pipeline plans its own batches (one sweep over the table for the whole read set)
+        check(L.kq_dev_count_packed(g.handle, C.c_void_p(d_rb.data_ptr()), C.c_void_p(d_rm.data_ptr()),
+                                    reads_np.size, 0, total), g.handle)
 
     def validate_resident():
         d_acc.zero_()
@@ -336,13 +335,17 @@ def main_ours(args):
             step_fn()
         barrier()
         c0 = g.counters()
-        g.set_timing(True); g.kernel_time_ms(0); g.kernel_time_ms(1)
+        g.set_timing(True)
+        for w in range(4):
+            g.kernel_time_ms(w)
         sampler = ClockSampler(local); sampler.start()
         evs = [step_fn() for _ in range(steps)]
         barrier()
         clocks = sampler.stop()
-        kt_count, kn_count = g.kernel_time_ms(0)
+        kt_count, kn_count = g.kernel_time_ms(2)           # insert_tuples_kernel launches
         kt_val, kn_val = g.kernel_time_ms(1)
+        kt_pipe, kn_pipe = g.kernel_time_ms(0)
+        kt_scat, kn_scat = g.kernel_time_ms(3)
         g.set_timing(False)
         c1 = g.counters()
         tc = sum(a.elapsed_time(b) for a, b, _ in evs) / steps
@@ -353,7 +356,8 @@ def main_ours(args):
         return {"count_ms": t[0].item(), "validate_ms": t[1].item(), "clocks": clocks,
                 "launches": c1["kernel_launches"] - c0["kernel_launches"],
                 "h2d": (c1["h2d_bytes"] - c0["h2d_bytes"]) / steps, "d2h": (c1["d2h_bytes"] - c0["d2h_bytes"]) / steps,
-                "kt_count": kt_count, "kn_count": kn_count, "kt_val": kt_val, "kn_val": kn_val}
+                "kt_count": kt_count, "kn_count": kn_count, "kt_val": kt_val, "kn_val": kn_val,
+                "kt_pipe": kt_pipe, "kn_pipe": kn_pipe, "kt_scat": kt_scat, "kn_scat": kn_scat}
 
     res = run(step_resident, args.warmup, args.steps)
     inst_total = inst_per_rank * world
@@ -365,7 +369,7 @@ def main_ours(args):
             "config": dict(cfg, parallelism="keyshard%d" % world, kmer_instances_per_step=inst_total,
                            assembly_kmers_per_step=asm_k, distinct_kmers=None,
                            l2="no flush needed: table (%.1f GB/GPU) and inputs (%.2f GB/GPU) are far larger than the 126 MB L2"
-                              % (est_distinct / 0.4 * 32 / 1e9, reads_np.size * 0.375 / 1e9)),
+                              % (est_distinct / 0.5 * 16 / 1e9, reads_np.size * 0.375 / 1e9)),
             "count_ms": res["count_ms"], "validate_ms": res["validate_ms"],
             "validate": {"metric": "assembly_kmers_validated_per_sec", "value": asm_k / (res["validate_ms"] * 1e-3), "unit": "k-mers/s"},
             "clocks": res["clocks"], "gpu_launches": res["launches"]}
@@ -374,11 +378,14 @@ def main_ours(args):
         per_launch_s = res["kt_count"] * 1e-3 / res["kn_count"]
         units_per_launch = inst_per_rank * args.steps / res["kn_count"]
         ach = ALG_BYTES_COUNT * units_per_launch / per_launch_s / 1e9
-        line["roofline"] = {"bound": "hbm", "kernel": "count_packed_kernel" if world == 1 else "extract_route_kernel+insert_tuples_kernel",
+        line["roofline"] = {"bound": "hbm", "kernel": "insert_tuples_kernel",
                             "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
                             "peak_source": peak_src, "algorithmic_bytes_per_kmer": ALG_BYTES_COUNT,
                             "sector_bound_frac": SECTOR_BYTES_COUNT * units_per_launch / per_launch_s / 1e9 / peak,
-                            "avg_launch_ms": per_launch_s * 1e3, "launches_timed": res["kn_count"]}
+                            "avg_launch_ms": per_launch_s * 1e3, "launches_timed": res["kn_count"],
+                            "share_of_count_ms": res["kt_count"] / args.steps / res["count_ms"],
+                            "hist_scatter_ms_per_step": res["kt_scat"] / args.steps,
+                            "pipeline_ms_per_step": res["kt_pipe"] / args.steps}
         if res["kn_val"]:
             vs = res["kt_val"] * 1e-3 / res["kn_val"]
             va = ALG_BYTES_VALIDATE * (asm_k * args.steps / res["kn_val"]) / vs / 1e9

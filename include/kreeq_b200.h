@@ -75,9 +75,10 @@ int  kq_owner_of(uint64_t key, int nranks);
  * DBG::hashSequences gb:34-126 + DBG::processBuffers gb:128-223.
  * ascii is one batch of reads each followed by 'N' exactly as getKmers()
  * (gfalibs/include/functions.h:69-122) builds it; BORROWED, consumed (packed
- * to 2 bit into pinned staging) before return; H2D copy and kernels are
- * asynchronous.  With nranks>1 only keys owned by this shard are inserted
- * (every rank may be fed the same batch), see also kq_dev_extract_route. */
+ * to 2 bit into pinned staging) before return; the H2D copy is asynchronous and
+ * the batch joins the device-resident pending stream (kq_set_flush_positions).
+ * With nranks>1 only keys owned by this shard are inserted (every rank may be
+ * fed the same batch), see also kq_dev_extract_route. */
 int  kq_count_push(kq_ctx *ctx, const char *ascii, size_t len);
 /* replaces Kmap::finalize kmer.h:821-828: barrier, table resident and final. */
 int  kq_count_finish(kq_ctx *ctx);
@@ -160,29 +161,36 @@ int    kq_pack_host(const char *ascii, size_t len, uint64_t *bases, uint64_t *in
  * device-resident sequence of `len` bases (only keys this shard owns). */
 int  kq_dev_count_packed(kq_ctx *ctx, const uint64_t *d_bases, const uint64_t *d_invalid,
                          uint64_t len, uint64_t pos0, uint64_t npos);
-/* extract only: tuples of every valid window routed by owner.  Tuples for
- * rank r are appended at d_keys[r*cap_per_rank + ...], d_edges[...]; d_counts
- * (nranks uint64, zeroed by the caller) receives the number per rank.  Overflow
- * of cap_per_rank is reported by kq_sync/KQ_ENOMEM. */
+/* (key, edgeBit) tuples on the device: 8 bytes (key << 8 | edgeBit) while 2k + 8 <= 64, else 16 bytes
+ * {uint64 key, uint64 edgeBit}.  kq_tuple_bytes gives the size for this handle's k. */
+int  kq_tuple_bytes(kq_ctx *ctx);
+/* extract only: the tuple of every valid window is appended to the slab of its owner rank
+ * (kq_owner_of): slab r starts at d_tuples + r * cap_per_rank * kq_tuple_bytes; d_counts (nranks
+ * uint64, zeroed by the caller) receives the number per rank.  Overflow of cap_per_rank is
+ * reported by kq_sync / KQ_ENOMEM. */
 int  kq_dev_extract_route(kq_ctx *ctx, const uint64_t *d_bases, const uint64_t *d_invalid,
                           uint64_t len, uint64_t pos0, uint64_t npos,
-                          uint64_t *d_keys, uint8_t *d_edges, uint64_t cap_per_rank,
-                          unsigned long long *d_counts);
-/* insert (key, edgeBit) tuples (row A3) already resident on the device */
-int  kq_dev_insert_tuples(kq_ctx *ctx, const uint64_t *d_keys, const uint8_t *d_edges, uint64_t n);
+                          void *d_tuples, uint64_t cap_per_rank, unsigned long long *d_counts);
+/* insert n tuples (row A3) already resident on the device (all owned by this shard) */
+int  kq_dev_insert_tuples(kq_ctx *ctx, const void *d_tuples, uint64_t n);
 /* probe positions [0, len-k+1) of one packed device-resident segment;
  * d_out (len entries) and d_acc (kq_qv, accumulates) are device memory. */
 int  kq_dev_validate_packed(kq_ctx *ctx, const uint64_t *d_bases, const uint64_t *d_invalid,
                             uint64_t len, uint32_t cov_cutoff, kq_base *d_out, kq_qv *d_acc);
 /* make sure the table can take `extra` more distinct keys without growing
- * inside a timed region */
+ * inside a timed region (also tells the count pipeline that the table is sized: it then plans
+ * large batches) */
 int  kq_reserve(kq_ctx *ctx, uint64_t extra_distinct);
+/* kq_count_push only appends the packed batch to a device-resident pending stream; the count
+ * pipeline runs once this many k-mer start positions are pending (0 = default 2^31), at
+ * kq_count_finish / kq_sync, and before anything that reads the table. */
+int  kq_set_flush_positions(kq_ctx *ctx, uint64_t positions);
 
 /* counters for bench.py: kernels launched by this handle, bytes copied */
 int  kq_counters(kq_ctx *ctx, uint64_t *kernel_launches, uint64_t *h2d_bytes, uint64_t *d2h_bytes);
-/* CUDA-event time (ms) spent in the dominant kernel class since the last call
- * with reset=1: which = 0 count/insert, 1 validate/probe.  Only measured when
- * kq_set_timing(ctx,1). */
+/* CUDA-event time (ms) on the launching stream since the last call with reset=1:
+ * which = 0 whole count pipeline (per batch), 1 validate/probe kernel, 2 insert kernel,
+ * 3 slice histogram + scatter (or extract_route).  Only measured when kq_set_timing(ctx,1). */
 int  kq_set_timing(kq_ctx *ctx, int on);
 int  kq_kernel_time_ms(kq_ctx *ctx, int which, double *ms, uint64_t *launches, int reset);
 

@@ -68,8 +68,10 @@ PROTOTYPES = {
     "kq_packed_words": (_sz, [_sz]),
     "kq_pack_host": (_i, [_vp, _sz, _vp, _vp, _i]),
     "kq_dev_count_packed": (_i, [_vp, _vp, _vp, _u64, _u64, _u64]),
-    "kq_dev_extract_route": (_i, [_vp, _vp, _vp, _u64, _u64, _u64, _vp, _vp, _u64, _vp]),
-    "kq_dev_insert_tuples": (_i, [_vp, _vp, _vp, _u64]),
+    "kq_tuple_bytes": (_i, [_vp]),
+    "kq_dev_extract_route": (_i, [_vp, _vp, _vp, _u64, _u64, _u64, _vp, _u64, _vp]),
+    "kq_dev_insert_tuples": (_i, [_vp, _vp, _u64]),
+    "kq_set_flush_positions": (_i, [_vp, _u64]),
     "kq_dev_validate_packed": (_i, [_vp, _vp, _vp, _u64, C.c_uint32, _vp, _vp]),
     "kq_reserve": (_i, [_vp, _u64]),
     "kq_counters": (_i, [_vp, C.POINTER(_u64), C.POINTER(_u64), C.POINTER(_u64)]),

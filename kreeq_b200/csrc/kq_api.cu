@@ -1,14 +1,17 @@
 // kq_api.cu -- implementation of the C-ABI in include/kreeq_b200.h.
 //
-// One kq_ctx = one GPU = one shard of the key space.  Host buffers are staged through a ring of
-// pinned buffers (pack to 2 bit on the host pool -> cudaMemcpyAsync -> kernel), everything is
-// enqueued on one stream (the caller's, after kq_set_stream) so the host packs batch i+1 while the
-// GPU inserts batch i.  There is no CPU fallback anywhere in this file.
+// One kq_ctx = one GPU = one shard of the key space.  kq_count_push packs a host batch to 2 bit on the
+// host pool into pinned staging and copies it (cudaMemcpyAsync, ring of 3) to the END of a device-
+// resident "pending reads" stream; the stream is turned into table updates by the count pipeline
+// (histogram -> scan -> scatter into slice order -> L2-resident insert) once enough k-mers are
+// pending to pay for one sweep over the table, or at kq_count_finish.  Everything is enqueued on one
+// stream (the caller's after kq_set_stream).  There is no CPU fallback anywhere in this file.
 #include "../../include/kreeq_b200.h"
 
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -26,19 +29,22 @@ static_assert(sizeof(kq_base) == sizeof(Base) && sizeof(kq_base) == 16, "kq_base
 namespace {
 
 constexpr int NBUF = 3;                          // staging ring depth
-constexpr uint64_t CHUNK = 16ull << 20;          // k-mer start positions per staged batch
-constexpr double MAX_LOAD = 0.60;                // grow T beyond this
-constexpr double TARGET_LOAD = 0.40;             // load right after a grow / reserve
-constexpr uint64_t MIN_CAP = 1ull << 16;
-constexpr uint64_t MIN_SCAP = 1ull << 14;
+constexpr uint64_t CHUNK = 16ull << 20;          // bases per staged chunk (multiple of 64)
+constexpr double MAX_LOAD = 0.80;                // never plan a batch that could push T beyond this
+constexpr double TARGET_LOAD = 0.50;             // load right after a grow / reserve
+constexpr uint64_t MIN_SLOTS = 1ull << 12;
+constexpr uint64_t MIN_SCAP = 1ull << 12;
+constexpr uint64_t OVF_CAP = 4ull << 20;         // tuples kept when their slice is full
+constexpr uint64_t DEFAULT_FLUSH = 1ull << 31;   // pending k-mer start positions that trigger the pipeline
+constexpr int NTIMERS = 4;                       // 0 count pipeline, 1 validate, 2 insert kernel, 3 hist + scatter
 
 thread_local std::string g_create_error;
 
 struct Stage {                                   // one staging slot (count and validate share them)
     uint64_t *h_bases = nullptr, *h_inv = nullptr;    // pinned
-    uint64_t *d_bases = nullptr, *d_inv = nullptr;
+    uint64_t *d_bases = nullptr, *d_inv = nullptr;    // validate only
     Base *h_out = nullptr, *d_out = nullptr;          // validate results (pinned / device)
-    size_t words = 0, out_n = 0;
+    size_t words = 0, dwords = 0, out_n = 0;
     cudaEvent_t done = nullptr; bool busy = false;
 };
 
@@ -49,19 +55,30 @@ struct TimedRange { cudaEvent_t a, b; int which; };
 struct kq_ctx {
     int k = 0, device = 0;
     cudaStream_t own_stream = nullptr, stream = nullptr;
-    Slot *T = nullptr; uint64_t cap = 0;
-    SideSlot *S = nullptr; uint64_t scap = 0;
-    unsigned long long *d_occ = nullptr;         // [0] T, [1] S
-    unsigned long long *d_inst = nullptr;        // k-mer instances inserted
+    Slot *T = nullptr; uint64_t nslices = 0; int slice_bits = 0;
+    SideSlot *R = nullptr; uint64_t rcap = 0;
+    SideSlot *M = nullptr; uint64_t mcap = 0;
+    unsigned long long *d_occ = nullptr;         // [0] T, [1] R, [2] M
+    unsigned long long *d_inst = nullptr;        // k-mer instances inserted from packed sequences ...
+    uint64_t inst_tuples = 0;                    // ... and from tuple sources (kq_dev_insert_tuples)
     unsigned long long *d_acc = nullptr;         // validate counters (3)
     int *d_err = nullptr;
-    uint64_t occ_bound = 0;                      // upper bound of T occupancy
+    uint64_t occ_known = 0;                      // T occupancy at the last synchronisation
+    uint64_t occ_bound = 0;                      // upper bound of it including batches in flight
+    bool optimistic = false;                     // the caller sized the table (kq_create / kq_reserve)
     int rank = 0, nranks = 1;
     bool loaded_db = false;                      // table holds literal database entries (load/union)
+    // pending reads (device-resident packed stream)
+    uint64_t *d_pb = nullptr, *d_pi = nullptr; uint64_t pend_cap = 0, pend_len = 0, flush_positions = DEFAULT_FLUSH;
+    // pipeline scratch
+    uint64_t *d_tuples = nullptr; uint64_t tup_cap = 0;          // tuples (not words)
+    unsigned long long *d_hist = nullptr, *d_cursor = nullptr; uint64_t hist_cap = 0;
+    unsigned long long *d_total = nullptr, *d_nsrc = nullptr;
+    uint64_t *d_ovf = nullptr; unsigned long long *d_ovf_n = nullptr; bool ovf_pending = false;
     Stage st[NBUF]; int next_stage = 0;
     uint64_t launches = 0, h2d = 0, d2h = 0;
     bool timing = false; std::vector<TimedRange> ranges; std::vector<cudaEvent_t> ev_pool;
-    double time_ms[2] = {0, 0}; uint64_t time_n[2] = {0, 0};
+    double time_ms[NTIMERS] = {0, 0, 0, 0}; uint64_t time_n[NTIMERS] = {0, 0, 0, 0};
     std::string err;
 };
 
@@ -74,9 +91,13 @@ int fail(kq_ctx *c, int code, const std::string &msg) { if (c) c->err = msg; els
          if (e_ != cudaSuccess) return fail(c, e_ == cudaErrorMemoryAllocation ? KQ_ENOMEM : KQ_ECUDA, \
                                             std::string(#call) + ": " + cudaGetErrorString(e_)); } while (0)
 
+inline uint64_t table_slots(const kq_ctx *c) { return c->nslices << c->slice_bits; }
+
 TableView view(const kq_ctx *c) {
     TableView tv;
-    tv.T = c->T; tv.cap = c->cap; tv.S = c->S; tv.scap = c->scap; tv.occ = c->d_occ; tv.err = c->d_err; tv.k = c->k;
+    tv.T = c->T; tv.nslices = c->nslices; tv.slice_bits = c->slice_bits;
+    tv.R = c->R; tv.rcap = c->rcap; tv.M = c->M; tv.mcap = c->mcap;
+    tv.occ = c->d_occ; tv.err = c->d_err; tv.k = c->k;
     tv.shard_rank = c->nranks > 1 ? c->rank : -1;
     int shift = 0; while ((128 >> shift) > c->nranks) ++shift;       // 128 >> shift == nranks
     tv.shard_shift = shift;                                          // owner = (key & 127) >> log2(128/nranks)
@@ -96,80 +117,71 @@ int check_device_error(kq_ctx *c) {
     return fail(c, KQ_ENOMEM, "k-mer table full");
 }
 
-int read_occ(kq_ctx *c, uint64_t occ[2]) {
-    unsigned long long h[2];
+int read_occ(kq_ctx *c, uint64_t occ[3]) {
+    unsigned long long h[3];
     CU(cudaMemcpyAsync(h, c->d_occ, sizeof h, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
-    occ[0] = h[0]; occ[1] = h[1];
+    occ[0] = h[0]; occ[1] = h[1]; occ[2] = h[2];
+    c->occ_known = h[0];
     return KQ_OK;
 }
 
-int alloc_table(kq_ctx *c, uint64_t cap, Slot **out) {
-    cap = std::max<uint64_t>(MIN_CAP, (cap + 3) & ~3ull);            // whole 128-byte lines
-    CU(cudaMalloc(out, cap * sizeof(Slot)));
-    CU(cudaMemsetAsync(*out, 0, cap * sizeof(Slot), c->stream));
-    return KQ_OK;
+// geometry of a table with at least `need` slots: one slice while it fits 2^21 slots (32 MiB), else
+// 32 MiB slices (64 MiB once there would be more slices than the scatter kernel has bins for)
+void table_geometry(uint64_t need, uint64_t &nslices, int &slice_bits) {
+    need = std::max(need, MIN_SLOTS);
+    static const int max_bits = [] { const char *e = std::getenv("KQ_SLICE_BITS"); const int v = e ? std::atoi(e) : 0;
+                                     return v >= 12 && v <= 26 ? v : KQ_MAX_SLICE_BITS; }();   // tuning knob
+    int b = 12; while (b < max_bits && (1ull << b) < need) ++b;
+    if ((1ull << b) >= need) { nslices = 1; slice_bits = b; return; }
+    slice_bits = max_bits;
+    if (((need + (1ull << slice_bits) - 1) >> slice_bits) > 1600) ++slice_bits;
+    nslices = (need + (1ull << slice_bits) - 1) >> slice_bits;
 }
 
-int grow_table(kq_ctx *c, uint64_t new_cap) {
-    new_cap = std::max<uint64_t>(MIN_CAP, (new_cap + 3) & ~3ull);
-    Slot *old = c->T; const uint64_t old_cap = c->cap;
+int grow_table(kq_ctx *c, uint64_t need) {
+    Slot *old = c->T; const uint64_t old_slots = table_slots(c);
+    uint64_t ns; int sb; table_geometry(need, ns, sb);
     Slot *nt = nullptr;
-    int rc = alloc_table(c, new_cap, &nt);
-    if (rc) return rc;
-    c->T = nt; c->cap = new_cap;
+    CU(cudaMalloc(&nt, (ns << sb) * sizeof(Slot)));
+    CU(cudaMemsetAsync(nt, 0, (ns << sb) * sizeof(Slot), c->stream));
+    c->T = nt; c->nslices = ns; c->slice_bits = sb;
     if (old) {
-        CU(launch_rehash(c->stream, view(c), old, old_cap, &c->launches));
+        CU(launch_rehash(c->stream, view(c), old, old_slots, &c->launches));
         CU(cudaStreamSynchronize(c->stream));
         CU(cudaFree(old));
     }
     return KQ_OK;
 }
 
-int grow_side(kq_ctx *c, uint64_t new_scap) {
-    SideSlot *old = c->S; const uint64_t old_cap = c->scap;
+int grow_side(kq_ctx *c, int which, uint64_t new_scap) {
+    SideSlot *&S = which == 1 ? c->R : c->M; uint64_t &cap = which == 1 ? c->rcap : c->mcap;
+    SideSlot *old = S; const uint64_t old_cap = cap;
     SideSlot *ns = nullptr;
     CU(cudaMalloc(&ns, new_scap * sizeof(SideSlot)));
     CU(cudaMemsetAsync(ns, 0, new_scap * sizeof(SideSlot), c->stream));
-    c->S = ns; c->scap = new_scap;
+    S = ns; cap = new_scap;
     if (old) {
-        CU(cudaMemsetAsync(c->d_occ + 1, 0, sizeof(unsigned long long), c->stream));   // re-counted by the rehash
-        CU(launch_side_rehash(c->stream, view(c), old, old_cap, &c->launches));
+        CU(cudaMemsetAsync(c->d_occ + which, 0, sizeof(unsigned long long), c->stream));   // re-counted by the rehash
+        CU(launch_side_rehash(c->stream, view(c), which, old, old_cap, &c->launches));
         CU(cudaStreamSynchronize(c->stream));
         CU(cudaFree(old));
     }
     return KQ_OK;
 }
 
-// make room for `extra` more distinct keys; synchronises only when the cheap bound says it must
-int ensure_capacity(kq_ctx *c, uint64_t extra) {
-    if ((double)(c->occ_bound + extra) <= MAX_LOAD * (double)c->cap) { c->occ_bound += extra; return KQ_OK; }
-    uint64_t occ[2];
-    int rc = read_occ(c, occ); if (rc) return rc;
-    rc = check_device_error(c); if (rc) return rc;
-    c->occ_bound = occ[0];
-    if ((double)occ[1] > 0.5 * (double)c->scap) { rc = grow_side(c, c->scap * 4); if (rc) return rc; }
-    if ((double)(occ[0] + extra) > MAX_LOAD * (double)c->cap) {
-        uint64_t want = (uint64_t)((double)(occ[0] + extra) / TARGET_LOAD);
-        want = std::max(want, c->cap * 2);
-        rc = grow_table(c, want);
-        if (rc == KQ_ENOMEM) {                                       // retry with the tightest table that still works
-            cudaGetLastError();
-            rc = grow_table(c, (uint64_t)((double)(occ[0] + extra) / MAX_LOAD) + 1024);
-        }
-        if (rc) return rc;
-    }
-    c->occ_bound += extra;
-    return KQ_OK;
-}
-
-int stage_reserve(kq_ctx *c, Stage &s, size_t words, size_t out_n) {
+int stage_reserve(kq_ctx *c, Stage &s, size_t words, size_t dwords, size_t out_n) {
     if (words > s.words) {
-        if (s.h_bases) { cudaFreeHost(s.h_bases); cudaFreeHost(s.h_inv); cudaFree(s.d_bases); cudaFree(s.d_inv); }
-        s.h_bases = s.h_inv = s.d_bases = s.d_inv = nullptr; s.words = 0;
+        if (s.h_bases) { cudaFreeHost(s.h_bases); cudaFreeHost(s.h_inv); }
+        s.h_bases = s.h_inv = nullptr; s.words = 0;
         CU(cudaMallocHost(&s.h_bases, words * 8)); CU(cudaMallocHost(&s.h_inv, words * 8));
-        CU(cudaMalloc(&s.d_bases, words * 8));     CU(cudaMalloc(&s.d_inv, words * 8));
         s.words = words;
+    }
+    if (dwords > s.dwords) {
+        if (s.d_bases) { cudaFree(s.d_bases); cudaFree(s.d_inv); }
+        s.d_bases = s.d_inv = nullptr; s.dwords = 0;
+        CU(cudaMalloc(&s.d_bases, dwords * 8)); CU(cudaMalloc(&s.d_inv, dwords * 8));
+        s.dwords = dwords;
     }
     if (out_n > s.out_n) {
         if (s.h_out) { cudaFreeHost(s.h_out); cudaFree(s.d_out); }
@@ -190,14 +202,15 @@ cudaEvent_t get_event(kq_ctx *c) {
     if (!c->ev_pool.empty()) { cudaEvent_t e = c->ev_pool.back(); c->ev_pool.pop_back(); return e; }
     cudaEvent_t e = nullptr; cudaEventCreate(&e); return e;
 }
-void time_begin(kq_ctx *c, int which) {
-    if (!c->timing) return;
+// CUDA-event bracket on the launching stream; returns the index of the open range or -1
+int time_begin(kq_ctx *c, int which) {
+    if (!c->timing) return -1;
     TimedRange r{get_event(c), get_event(c), which};
     cudaEventRecord(r.a, c->stream); c->ranges.push_back(r);
+    return (int)c->ranges.size() - 1;
 }
-void time_end(kq_ctx *c) {
-    if (!c->timing) return;
-    cudaEventRecord(c->ranges.back().b, c->stream);
+void time_end(kq_ctx *c, int idx) {
+    if (idx >= 0) cudaEventRecord(c->ranges[idx].b, c->stream);
 }
 void time_collect(kq_ctx *c) {
     for (auto &r : c->ranges) {
@@ -206,6 +219,156 @@ void time_collect(kq_ctx *c) {
         c->ev_pool.push_back(r.a); c->ev_pool.push_back(r.b);
     }
     c->ranges.clear();
+}
+
+}  // namespace
+
+// ---- count pipeline -------------------------------------------------------------------------------------
+
+namespace {
+
+int pipeline_scratch(kq_ctx *c, uint64_t tuples) {
+    if (c->hist_cap < c->nslices) {
+        cudaFree(c->d_hist); cudaFree(c->d_cursor); c->d_hist = c->d_cursor = nullptr; c->hist_cap = 0;
+        CU(cudaMalloc(&c->d_hist, c->nslices * 8)); CU(cudaMalloc(&c->d_cursor, c->nslices * 8));
+        c->hist_cap = c->nslices;
+    }
+    if (!c->d_ovf) CU(cudaMalloc(&c->d_ovf, OVF_CAP * 16));
+    if (c->tup_cap < tuples) {
+        cudaFree(c->d_tuples); c->d_tuples = nullptr; c->tup_cap = 0;
+        CU(cudaMalloc(&c->d_tuples, tuples * 8 * tuple_words(c->k)));
+        c->tup_cap = tuples;
+    }
+    return KQ_OK;
+}
+
+// After a synchronisation: put the tuples back whose slice was full (after doubling the table), and
+// grow when the table got fuller than planned.
+int settle(kq_ctx *c) {
+    uint64_t occ[3];
+    int rc = read_occ(c, occ); if (rc) return rc;
+    rc = check_device_error(c); if (rc) return rc;
+    c->occ_bound = occ[0];
+    if ((double)occ[1] > 0.5 * (double)c->rcap) { rc = grow_side(c, 1, c->rcap * 4); if (rc) return rc; }
+    if (!c->ovf_pending) return KQ_OK;
+    c->ovf_pending = false;
+    unsigned long long n = 0;
+    CU(cudaMemcpyAsync(&n, c->d_ovf_n, 8, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    if (!n) return KQ_OK;
+    if (n > OVF_CAP)
+        return fail(c, KQ_ENOMEM, "k-mer table too small for the batch (" + std::to_string(n) +
+                                  " instances found their slice full): pass a larger expected_distinct to kq_create / kq_reserve");
+    rc = grow_table(c, std::max<uint64_t>(2 * table_slots(c), (uint64_t)((double)(occ[0] + n) / TARGET_LOAD))); if (rc) return rc;
+    CU(cudaMemsetAsync(c->d_ovf_n, 0, 8, c->stream));
+    CU(cudaMemcpyAsync(c->d_nsrc, &n, 8, cudaMemcpyHostToDevice, c->stream));
+    rc = pipeline_scratch(c, OVF_CAP); if (rc) return rc;
+    CU(launch_insert_tuples(c->stream, view(c), c->d_ovf, c->d_nsrc, n, c->d_tuples, c->tup_cap, c->d_ovf_n, &c->launches));
+    CU(cudaMemcpyAsync(&n, c->d_ovf_n, 8, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    if (n) return fail(c, KQ_ENOMEM, "k-mer table full after growing");
+    rc = read_occ(c, occ); if (rc) return rc;
+    c->occ_bound = occ[0];
+    return KQ_OK;
+}
+
+// one batch of the pipeline: every instance of src goes into the table
+int run_batch(kq_ctx *c, Source src) {
+    const uint64_t bound = src.tuples ? src.ntuples_max : src.npos;
+    if (!bound) return KQ_OK;
+    const TableView tv = view(c);
+    const int tw = tuple_words(c->k);
+    const int cap = c->nslices > 1 ? scatter_pick_cap(c->nslices, tw) : 0;
+    { int rc = pipeline_scratch(c, 0); if (rc) return rc; }
+    const int t0 = time_begin(c, 0);
+    // a sweep over the table pays off once the batch touches a good part of it
+    if (c->nslices == 1 || cap == 0 || (double)bound < 0.25 * (double)table_slots(c)) {
+        if (src.tuples) {
+            CU(launch_insert_tuples(c->stream, tv, src.tuples, src.ntuples, bound, c->d_ovf, OVF_CAP, c->d_ovf_n, &c->launches));
+            c->ovf_pending = true;
+        } else {
+            CU(launch_count_direct(c->stream, tv, src, c->d_inst, c->d_ovf, OVF_CAP, c->d_ovf_n, &c->launches));
+            c->ovf_pending = true;
+        }
+        time_end(c, t0);
+        return KQ_OK;
+    }
+    int rc = pipeline_scratch(c, bound); if (rc) return rc;
+    const int t3 = time_begin(c, 3);
+    CU(cudaMemsetAsync(c->d_hist, 0, c->nslices * 8, c->stream));
+    CU(launch_slice_hist(c->stream, tv, src, c->d_hist, &c->launches));
+    CU(launch_slice_offsets(c->stream, c->nslices, c->d_hist, c->d_cursor, c->d_total,
+                            src.tuples ? nullptr : c->d_inst, &c->launches));
+    CU(launch_slice_scatter(c->stream, tv, src, c->d_tuples, c->d_cursor, cap, &c->launches));
+    time_end(c, t3);
+    const int t2 = time_begin(c, 2);
+    CU(launch_insert_tuples(c->stream, tv, c->d_tuples, c->d_total, bound, c->d_ovf, OVF_CAP, c->d_ovf_n, &c->launches));
+    time_end(c, t2);
+    c->ovf_pending = true;
+    time_end(c, t0);
+    return KQ_OK;
+}
+
+// Count the k-mers of start positions [pos0, pos0+npos) of a packed device-resident sequence (or of
+// ntuples tuples).  Batches are planned so that the table cannot overfill: without a size hint a
+// batch brings at most as many instances as there is room below MAX_LOAD (every instance could be a
+// new key); with a hint (kq_create / kq_reserve) four times that, backed by the overflow list.
+int count_source(kq_ctx *c, Source src) {
+    uint64_t left = src.tuples ? src.ntuples_max : src.npos;
+    while (left) {
+        if (c->ovf_pending || c->occ_bound != c->occ_known) { int rc = settle(c); if (rc) return rc; }
+        int64_t room = (int64_t)(MAX_LOAD * (double)table_slots(c)) - (int64_t)c->occ_known;
+        const int64_t want = (int64_t)std::min<uint64_t>(left, 1ull << 20);
+        if (room < want || (double)c->occ_known > 0.6 * (double)table_slots(c)) {
+            int rc = grow_table(c, std::max<uint64_t>(2 * table_slots(c), (uint64_t)((double)(c->occ_known + want) / TARGET_LOAD)));
+            if (rc) return rc;
+            continue;
+        }
+        uint64_t nb = c->optimistic ? (uint64_t)room * 4 : (uint64_t)room;
+        nb = std::min(nb, left);
+        Source b = src;
+        if (!src.tuples) { b.pos0 = src.pos0 + (src.npos - left); b.npos = nb; }
+        else {
+            b.tuples = src.tuples + (src.ntuples_max - left) * tuple_words(c->k); b.ntuples_max = nb; b.ntuples = c->d_nsrc;
+            const unsigned long long v = nb;
+            CU(cudaMemcpyAsync(c->d_nsrc, &v, 8, cudaMemcpyHostToDevice, c->stream));
+        }
+        int rc = run_batch(c, b); if (rc) return rc;
+        c->occ_bound = c->occ_known + nb;
+        left -= nb;
+    }
+    return KQ_OK;
+}
+
+int pending_reserve(kq_ctx *c, uint64_t bases) {
+    if (bases <= c->pend_cap) return KQ_OK;
+    const uint64_t cap = (std::max<uint64_t>(std::max<uint64_t>(bases, 2 * c->pend_cap), 1ull << 26) + 63) & ~63ull;
+    uint64_t *nb = nullptr, *ni = nullptr;
+    const size_t bw = cap / 32 + 16, iw = cap / 64 + 16;
+    CU(cudaMalloc(&nb, bw * 8)); CU(cudaMalloc(&ni, iw * 8));
+    CU(cudaMemsetAsync(nb, 0, bw * 8, c->stream));
+    CU(cudaMemsetAsync(ni, 0xFF, iw * 8, c->stream));                // everything not written is "not ACGT"
+    if (c->pend_len) {
+        CU(cudaMemcpyAsync(nb, c->d_pb, (c->pend_len / 32) * 8, cudaMemcpyDeviceToDevice, c->stream));
+        CU(cudaMemcpyAsync(ni, c->d_pi, (c->pend_len / 64) * 8, cudaMemcpyDeviceToDevice, c->stream));
+    }
+    CU(cudaStreamSynchronize(c->stream));
+    cudaFree(c->d_pb); cudaFree(c->d_pi);
+    c->d_pb = nb; c->d_pi = ni; c->pend_cap = cap;
+    return KQ_OK;
+}
+
+// run the pipeline over everything pending
+int pending_flush(kq_ctx *c) {
+    if (!c->pend_len) return KQ_OK;
+    const uint64_t len = c->pend_len;
+    if (len >= (uint64_t)c->k) {
+        Source src{c->d_pb, c->d_pi, 0, len - c->k + 1, nullptr, nullptr, 0};
+        int rc = count_source(c, src); if (rc) return rc;
+    }
+    CU(cudaMemsetAsync(c->d_pi, 0xFF, (len / 64 + 1) * 8, c->stream));
+    c->pend_len = 0;
+    return KQ_OK;
 }
 
 }  // namespace
@@ -231,19 +394,25 @@ extern "C" int kq_create(kq_ctx **out, int k, int device, uint64_t expected_dist
                       return bail(e_ == cudaErrorMemoryAllocation ? KQ_ENOMEM : KQ_ENODEV); } } while (0)
     CC(cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
     ctx->stream = ctx->own_stream;
-    CC(cudaMalloc(&ctx->d_occ, 2 * sizeof(unsigned long long)));
+    CC(cudaMalloc(&ctx->d_occ, 3 * sizeof(unsigned long long)));
     CC(cudaMalloc(&ctx->d_inst, sizeof(unsigned long long)));
     CC(cudaMalloc(&ctx->d_acc, 3 * sizeof(unsigned long long)));
+    CC(cudaMalloc(&ctx->d_total, sizeof(unsigned long long)));
+    CC(cudaMalloc(&ctx->d_nsrc, sizeof(unsigned long long)));
+    CC(cudaMalloc(&ctx->d_ovf_n, sizeof(unsigned long long)));
     CC(cudaMalloc(&ctx->d_err, sizeof(int)));
-    CC(cudaMemsetAsync(ctx->d_occ, 0, 2 * sizeof(unsigned long long), ctx->stream));
+    CC(cudaMemsetAsync(ctx->d_occ, 0, 3 * sizeof(unsigned long long), ctx->stream));
     CC(cudaMemsetAsync(ctx->d_inst, 0, sizeof(unsigned long long), ctx->stream));
     CC(cudaMemsetAsync(ctx->d_acc, 0, 3 * sizeof(unsigned long long), ctx->stream));
+    CC(cudaMemsetAsync(ctx->d_ovf_n, 0, sizeof(unsigned long long), ctx->stream));
     CC(cudaMemsetAsync(ctx->d_err, 0, sizeof(int), ctx->stream));
     for (auto &s : ctx->st) CC(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
 #undef CC
+    ctx->optimistic = expected_distinct != 0;
     const uint64_t want = expected_distinct ? (uint64_t)((double)expected_distinct / TARGET_LOAD) : (1ull << 20);
     int rc = grow_table(ctx, want); if (rc) return bail(rc);
-    rc = grow_side(ctx, MIN_SCAP);  if (rc) return bail(rc);
+    rc = grow_side(ctx, 1, MIN_SCAP); if (rc) return bail(rc);
+    rc = grow_side(ctx, 2, MIN_SCAP); if (rc) return bail(rc);
     if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) { ctx->err = "stream sync failed"; return bail(KQ_ECUDA); }
     *out = ctx;
     return KQ_OK;
@@ -254,13 +423,16 @@ extern "C" void kq_destroy(kq_ctx *c) {
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     for (auto &s : c->st) {
-        if (s.h_bases) { cudaFreeHost(s.h_bases); cudaFreeHost(s.h_inv); cudaFree(s.d_bases); cudaFree(s.d_inv); }
+        if (s.h_bases) { cudaFreeHost(s.h_bases); cudaFreeHost(s.h_inv); }
+        if (s.d_bases) { cudaFree(s.d_bases); cudaFree(s.d_inv); }
         if (s.h_out) { cudaFreeHost(s.h_out); cudaFree(s.d_out); }
         if (s.done) cudaEventDestroy(s.done);
     }
     for (auto &r : c->ranges) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
     for (auto e : c->ev_pool) cudaEventDestroy(e);
-    cudaFree(c->T); cudaFree(c->S); cudaFree(c->d_occ); cudaFree(c->d_inst); cudaFree(c->d_acc); cudaFree(c->d_err);
+    cudaFree(c->T); cudaFree(c->R); cudaFree(c->M); cudaFree(c->d_occ); cudaFree(c->d_inst); cudaFree(c->d_acc); cudaFree(c->d_err);
+    cudaFree(c->d_pb); cudaFree(c->d_pi); cudaFree(c->d_tuples); cudaFree(c->d_hist); cudaFree(c->d_cursor);
+    cudaFree(c->d_total); cudaFree(c->d_nsrc); cudaFree(c->d_ovf); cudaFree(c->d_ovf_n);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     delete c;
 }
@@ -277,12 +449,14 @@ extern "C" int kq_set_stream(kq_ctx *c, void *stream) {
     return KQ_OK;
 }
 
+// flush pending reads, wait, settle the table
 extern "C" int kq_sync(kq_ctx *c) {
     if (!c) return KQ_EINVAL;
     CU(cudaSetDevice(c->device));
+    int rc = pending_flush(c); if (rc) return rc;
     CU(cudaStreamSynchronize(c->stream));
     for (auto &s : c->st) s.busy = false;
-    return check_device_error(c);
+    return settle(c);
 }
 
 extern "C" int kq_owner_of(uint64_t key, int nranks) {
@@ -301,7 +475,7 @@ extern "C" int kq_set_shard(kq_ctx *c, int rank, int nranks) {
 extern "C" int kq_set_timing(kq_ctx *c, int on) { if (!c) return KQ_EINVAL; c->timing = on != 0; return KQ_OK; }
 
 extern "C" int kq_kernel_time_ms(kq_ctx *c, int which, double *ms, uint64_t *launches, int reset) {
-    if (!c || which < 0 || which > 1) return KQ_EINVAL;
+    if (!c || which < 0 || which >= NTIMERS) return KQ_EINVAL;
     CU(cudaSetDevice(c->device));
     time_collect(c);
     if (ms) *ms = c->time_ms[which];
@@ -321,24 +495,32 @@ extern "C" int kq_counters(kq_ctx *c, uint64_t *kernel_launches, uint64_t *h2d_b
 extern "C" int kq_reserve(kq_ctx *c, uint64_t extra) {
     if (!c) return KQ_EINVAL;
     CU(cudaSetDevice(c->device));
-    uint64_t occ[2];
-    int rc = read_occ(c, occ); if (rc) return rc;
-    c->occ_bound = occ[0];
-    if ((double)(occ[0] + extra) > TARGET_LOAD * (double)c->cap) {
-        rc = grow_table(c, (uint64_t)((double)(occ[0] + extra) / TARGET_LOAD)); if (rc) return rc;
+    int rc = kq_sync(c); if (rc) return rc;
+    c->optimistic = true;
+    if ((double)(c->occ_known + extra) > TARGET_LOAD * (double)table_slots(c)) {
+        rc = grow_table(c, (uint64_t)((double)(c->occ_known + extra) / TARGET_LOAD)); if (rc) return rc;
     }
+    return KQ_OK;
+}
+
+extern "C" int kq_set_flush_positions(kq_ctx *c, uint64_t positions) {
+    if (!c) return KQ_EINVAL;
+    c->flush_positions = positions ? positions : DEFAULT_FLUSH;
     return KQ_OK;
 }
 
 extern "C" int kq_clear(kq_ctx *c) {
     if (!c) return KQ_EINVAL;
     CU(cudaSetDevice(c->device));
-    CU(cudaMemsetAsync(c->T, 0, c->cap * sizeof(Slot), c->stream));
-    CU(cudaMemsetAsync(c->S, 0, c->scap * sizeof(SideSlot), c->stream));
-    CU(cudaMemsetAsync(c->d_occ, 0, 2 * sizeof(unsigned long long), c->stream));
+    if (c->pend_len) { CU(cudaMemsetAsync(c->d_pi, 0xFF, (c->pend_len / 64 + 1) * 8, c->stream)); c->pend_len = 0; }
+    CU(cudaMemsetAsync(c->T, 0, table_slots(c) * sizeof(Slot), c->stream));
+    CU(cudaMemsetAsync(c->R, 0, c->rcap * sizeof(SideSlot), c->stream));
+    CU(cudaMemsetAsync(c->M, 0, c->mcap * sizeof(SideSlot), c->stream));
+    CU(cudaMemsetAsync(c->d_occ, 0, 3 * sizeof(unsigned long long), c->stream));
     CU(cudaMemsetAsync(c->d_inst, 0, sizeof(unsigned long long), c->stream));
+    CU(cudaMemsetAsync(c->d_ovf_n, 0, sizeof(unsigned long long), c->stream));
     CU(cudaMemsetAsync(c->d_err, 0, sizeof(int), c->stream));
-    c->occ_bound = 0; c->loaded_db = false;
+    c->occ_known = c->occ_bound = 0; c->inst_tuples = 0; c->ovf_pending = false; c->loaded_db = false;
     return KQ_OK;
 }
 
@@ -355,31 +537,26 @@ extern "C" int kq_pack_host(const char *ascii, size_t len, uint64_t *bases, uint
 extern "C" int kq_count_push(kq_ctx *c, const char *ascii, size_t len) {
     if (!c || (!ascii && len)) return KQ_EINVAL;
     if (c->loaded_db) return fail(c, KQ_ESTATE, "kq_count_push: the table holds a loaded/merged database");
-    const uint64_t k = (uint64_t)c->k;
-    if (len < k) return KQ_OK;                                         // src/graph-builder.cpp:60-64
+    if (len < (size_t)c->k) return KQ_OK;                              // src/graph-builder.cpp:60-64
     CU(cudaSetDevice(c->device));
-    const uint64_t P = len - k + 1;                                    // k-mer start positions
-    for (uint64_t c0 = 0; c0 < P; c0 += CHUNK) {
-        const uint64_t npos = std::min(CHUNK, P - c0);
-        int rc = ensure_capacity(c, npos); if (rc) return rc;
-        // slice of the batch this chunk needs: one base before c0 (64-aligned down) .. k bases after the last start
-        const uint64_t a0 = c0 == 0 ? 0 : ((c0 - 1) & ~63ull);
-        const uint64_t a1 = std::min<uint64_t>(len, c0 + npos + k);
-        const size_t words = packed_words(a1 - a0);
+    if (c->pend_len && c->pend_len + len >= c->flush_positions) { int rc = pending_flush(c); if (rc) return rc; }
+    int rc = pending_reserve(c, c->pend_len + len + 128); if (rc) return rc;
+    // the batch goes to the end of the pending stream, 64-base aligned; at least one invalid position
+    // separates it from the next batch (== the '\0' / no-previous-base cases of graph-builder.cpp:98-112)
+    const uint64_t at = c->pend_len;
+    for (uint64_t c0 = 0; c0 < len; c0 += CHUNK) {
+        const uint64_t n = std::min<uint64_t>(CHUNK, len - c0);
         Stage &s = c->st[c->next_stage]; c->next_stage = (c->next_stage + 1) % NBUF;
         rc = stage_acquire(c, s); if (rc) return rc;
-        rc = stage_reserve(c, s, packed_words(CHUNK + k + 64), 0); if (rc) return rc;
-        pack_sequence(ascii + a0, a1 - a0, s.h_bases, s.h_inv, &global_pool());
-        // a1 < len means real bases follow: the padding after the slice must not read as "end of batch"
-        // for the last window's next base -- it cannot, because the slice extends k bases past the last start.
-        CU(cudaMemcpyAsync(s.d_bases, s.h_bases, words * 8, cudaMemcpyHostToDevice, c->stream));
-        CU(cudaMemcpyAsync(s.d_inv, s.h_inv, (words / 2 + 1) * 8, cudaMemcpyHostToDevice, c->stream));
-        c->h2d += words * 8 + (words / 2 + 1) * 8;
-        time_begin(c, 0);
-        CU(launch_count_packed(c->stream, view(c), s.d_bases, s.d_inv, c0 - a0, npos, c->d_inst, &c->launches));
-        time_end(c);
+        rc = stage_reserve(c, s, packed_words(CHUNK), 0, 0); if (rc) return rc;
+        pack_sequence(ascii + c0, n, s.h_bases, s.h_inv, &global_pool());
+        const size_t bw = (n + 31) / 32, iw = (n + 63) / 64;
+        CU(cudaMemcpyAsync(c->d_pb + (at + c0) / 32, s.h_bases, bw * 8, cudaMemcpyHostToDevice, c->stream));
+        CU(cudaMemcpyAsync(c->d_pi + (at + c0) / 64, s.h_inv, iw * 8, cudaMemcpyHostToDevice, c->stream));
+        c->h2d += (bw + iw) * 8;
         CU(cudaEventRecord(s.done, c->stream)); s.busy = true;
     }
+    c->pend_len = (at + len + 64) & ~63ull;                            // next 64-aligned position strictly after the end
     return KQ_OK;
 }
 
@@ -388,58 +565,57 @@ extern "C" int kq_count_finish(kq_ctx *c) { return kq_sync(c); }
 extern "C" int kq_count_instances(kq_ctx *c, uint64_t *n) {
     if (!c || !n) return KQ_EINVAL;
     CU(cudaSetDevice(c->device));
+    int rc = pending_flush(c); if (rc) return rc;
     unsigned long long v = 0;
     CU(cudaMemcpyAsync(&v, c->d_inst, sizeof v, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
-    *n = v;
+    *n = v + c->inst_tuples;
     return KQ_OK;
 }
 
 extern "C" int kq_distinct(kq_ctx *c, uint64_t *n) {
     if (!c || !n) return KQ_EINVAL;
-    CU(cudaSetDevice(c->device));
-    uint64_t occ[2]; int rc = read_occ(c, occ); if (rc) return rc;
-    *n = occ[0];
+    int rc = kq_sync(c); if (rc) return rc;
+    *n = c->occ_known;
     return KQ_OK;
 }
 
 extern "C" int kq_dev_count_packed(kq_ctx *c, const uint64_t *d_bases, const uint64_t *d_invalid,
                                    uint64_t len, uint64_t pos0, uint64_t npos) {
     if (!c || !d_bases || !d_invalid) return KQ_EINVAL;
+    if (c->loaded_db) return fail(c, KQ_ESTATE, "kq_dev_count_packed: the table holds a loaded/merged database");
     if (len < (uint64_t)c->k) return KQ_OK;
     if (pos0 + npos > len - c->k + 1) return fail(c, KQ_EINVAL, "kq_dev_count_packed: positions beyond len-k+1");
     CU(cudaSetDevice(c->device));
-    int rc = ensure_capacity(c, npos); if (rc) return rc;
-    time_begin(c, 0);
-    CU(launch_count_packed(c->stream, view(c), d_bases, d_invalid, pos0, npos, c->d_inst, &c->launches));
-    time_end(c);
-    return KQ_OK;
+    int rc = pending_flush(c); if (rc) return rc;
+    return count_source(c, Source{d_bases, d_invalid, pos0, npos, nullptr, nullptr, 0});
 }
+
+extern "C" int kq_tuple_bytes(kq_ctx *c) { return c ? 8 * tuple_words(c->k) : KQ_EINVAL; }
 
 extern "C" int kq_dev_extract_route(kq_ctx *c, const uint64_t *d_bases, const uint64_t *d_invalid,
                                     uint64_t len, uint64_t pos0, uint64_t npos,
-                                    uint64_t *d_keys, uint8_t *d_edges, uint64_t cap_per_rank,
-                                    unsigned long long *d_counts) {
-    if (!c || !d_bases || !d_invalid || !d_keys || !d_edges || !d_counts) return KQ_EINVAL;
+                                    void *d_tuples, uint64_t cap_per_rank, unsigned long long *d_counts) {
+    if (!c || !d_bases || !d_invalid || !d_tuples || !d_counts) return KQ_EINVAL;
     if (len < (uint64_t)c->k) return KQ_OK;
     if (pos0 + npos > len - c->k + 1) return fail(c, KQ_EINVAL, "kq_dev_extract_route: positions beyond len-k+1");
     CU(cudaSetDevice(c->device));
-    int rc = ensure_capacity(c, npos); if (rc) return rc;
     const TableView tv = view(c);
-    RouteArgs ra{d_keys, d_edges, cap_per_rank, d_counts, c->nranks, c->rank, tv.shard_shift};
-    time_begin(c, 0);
-    CU(launch_extract_route(c->stream, tv, d_bases, d_invalid, pos0, npos, ra, c->d_inst, &c->launches));
-    time_end(c);
+    RouteArgs ra{static_cast<uint64_t *>(d_tuples), cap_per_rank, d_counts, c->nranks, tv.shard_shift};
+    const int t = time_begin(c, 3);
+    CU(launch_extract_route(c->stream, tv, Source{d_bases, d_invalid, pos0, npos, nullptr, nullptr, 0}, ra, &c->launches));
+    time_end(c, t);
     return KQ_OK;
 }
 
-extern "C" int kq_dev_insert_tuples(kq_ctx *c, const uint64_t *d_keys, const uint8_t *d_edges, uint64_t n) {
-    if (!c || (n && (!d_keys || !d_edges))) return KQ_EINVAL;
+extern "C" int kq_dev_insert_tuples(kq_ctx *c, const void *d_tuples, uint64_t n) {
+    if (!c || (n && !d_tuples)) return KQ_EINVAL;
+    if (c->loaded_db) return fail(c, KQ_ESTATE, "kq_dev_insert_tuples: the table holds a loaded/merged database");
+    if (!n) return KQ_OK;
     CU(cudaSetDevice(c->device));
-    int rc = ensure_capacity(c, n); if (rc) return rc;
-    time_begin(c, 0);
-    CU(launch_insert_tuples(c->stream, view(c), d_keys, d_edges, n, c->d_inst, &c->launches));
-    time_end(c);
+    int rc = pending_flush(c); if (rc) return rc;
+    rc = count_source(c, Source{nullptr, nullptr, 0, 0, static_cast<const uint64_t *>(d_tuples), c->d_nsrc, n}); if (rc) return rc;
+    c->inst_tuples += n;
     return KQ_OK;
 }
 
@@ -456,11 +632,12 @@ extern "C" int kq_dev_validate_packed(kq_ctx *c, const uint64_t *d_bases, const 
                                       uint64_t len, uint32_t cutoff, kq_base *d_out, kq_qv *d_acc) {
     if (!c || !d_bases || !d_invalid || !d_out || !d_acc) return KQ_EINVAL;
     CU(cudaSetDevice(c->device));
+    if (c->pend_len || c->ovf_pending) { int rc = kq_sync(c); if (rc) return rc; }
     const uint64_t kcount = len >= (uint64_t)c->k ? len - c->k + 1 : 0;
-    time_begin(c, 1);
+    const int t = time_begin(c, 1);
     CU(launch_validate(c->stream, view(c), d_bases, d_invalid, 0, 0, len, kcount, cutoff,
                        reinterpret_cast<Base *>(d_out), reinterpret_cast<unsigned long long *>(d_acc), &c->launches));
-    time_end(c);
+    time_end(c, t);
     return KQ_OK;
 }
 
@@ -468,6 +645,7 @@ extern "C" int kq_validate_segment(kq_ctx *c, const char *seq, uint64_t len, uin
     if (!c || (!seq && len) || (!out && len) || !acc) return KQ_EINVAL;
     if (len == 0) return KQ_OK;
     CU(cudaSetDevice(c->device));
+    if (c->pend_len || c->ovf_pending) { int rc = kq_sync(c); if (rc) return rc; }
     const uint64_t k = (uint64_t)c->k;
     const uint64_t kcount = len >= k ? len - k + 1 : 0;                // src/kreeq.cpp:123-126
     CU(cudaMemsetAsync(c->d_acc, 0, 3 * sizeof(unsigned long long), c->stream));
@@ -489,7 +667,9 @@ extern "C" int kq_validate_segment(kq_ctx *c, const char *seq, uint64_t len, uin
         if (npend == NBUF) { int rc = drain_one(pend[0]); if (rc) return rc; for (int i = 1; i < NBUF; ++i) pend[i - 1] = pend[i]; --npend; }
         Stage &s = c->st[c->next_stage]; c->next_stage = (c->next_stage + 1) % NBUF;
         int rc = stage_acquire(c, s); if (rc) return rc;
-        rc = stage_reserve(c, s, packed_words(std::max(CHUNK, VCH) + k + 64), VCH); if (rc) return rc;
+        const size_t need = packed_words(std::max(CHUNK, VCH + k + 128));
+        rc = stage_reserve(c, s, need, need, VCH); if (rc) return rc;
+        // slice of the segment this chunk needs: one base before c0 (64-aligned down) .. k bases after the last start
         const uint64_t a0 = c0 == 0 ? 0 : ((c0 - 1) & ~63ull);
         const uint64_t a1 = std::min<uint64_t>(len, c0 + n + k);
         const size_t words = packed_words(a1 - a0);
@@ -497,9 +677,9 @@ extern "C" int kq_validate_segment(kq_ctx *c, const char *seq, uint64_t len, uin
         CU(cudaMemcpyAsync(s.d_bases, s.h_bases, words * 8, cudaMemcpyHostToDevice, c->stream));
         CU(cudaMemcpyAsync(s.d_inv, s.h_inv, (words / 2 + 1) * 8, cudaMemcpyHostToDevice, c->stream));
         c->h2d += words * 8 + (words / 2 + 1) * 8;
-        time_begin(c, 1);
+        const int t = time_begin(c, 1);
         CU(launch_validate(c->stream, view(c), s.d_bases, s.d_inv, a0, c0, n, kcount, cutoff, s.d_out, c->d_acc, &c->launches));
-        time_end(c);
+        time_end(c, t);
         CU(cudaMemcpyAsync(s.h_out, s.d_out, n * sizeof(Base), cudaMemcpyDeviceToHost, c->stream));
         c->d2h += n * sizeof(Base);
         CU(cudaEventRecord(s.done, c->stream)); s.busy = true;
@@ -519,6 +699,7 @@ extern "C" int kq_lookup_batch(kq_ctx *c, const uint64_t *keys, size_t n, kq_rec
     if (!c || (n && (!keys || !rec || !found))) return KQ_EINVAL;
     if (!n) return KQ_OK;
     CU(cudaSetDevice(c->device));
+    if (c->pend_len || c->ovf_pending) { int rc = kq_sync(c); if (rc) return rc; }
     uint64_t *dk = nullptr; Rec32 *dr = nullptr; uint8_t *df = nullptr;
     CU(cudaMalloc(&dk, n * 8)); CU(cudaMalloc(&dr, n * sizeof(Rec32))); CU(cudaMalloc(&df, n));
     CU(cudaMemcpyAsync(dk, keys, n * 8, cudaMemcpyHostToDevice, c->stream));
@@ -537,12 +718,12 @@ extern "C" int kq_lookup_batch(kq_ctx *c, const uint64_t *keys, size_t n, kq_rec
 
 namespace {
 
-// copy the side table to the host
-int fetch_side(kq_ctx *c, std::vector<SideSlot> &side) {
-    side.resize(c->scap);
-    CU(cudaMemcpyAsync(side.data(), c->S, c->scap * sizeof(SideSlot), cudaMemcpyDeviceToHost, c->stream));
+// copy the literal maps32 table to the host
+int fetch_map32(kq_ctx *c, std::vector<SideSlot> &side) {
+    side.resize(c->mcap);
+    CU(cudaMemcpyAsync(side.data(), c->M, c->mcap * sizeof(SideSlot), cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
-    c->d2h += c->scap * sizeof(SideSlot);
+    c->d2h += c->mcap * sizeof(SideSlot);
     return KQ_OK;
 }
 
@@ -552,9 +733,9 @@ struct FullStats { kq_stats s; std::vector<std::pair<uint64_t, uint64_t>> hist; 
 
 // DBG::summary over all maps + DBG::DBstats, src/graph-builder.cpp:240-295
 int compute_stats(kq_ctx *c, FullStats &fs) {
-    CU(cudaSetDevice(c->device));
+    int rc = kq_sync(c); if (rc) return rc;
     DevStats *d_ds = nullptr; unsigned long long *d_hist = nullptr, *d_big = nullptr;
-    const unsigned long long big_cap = c->scap;
+    const unsigned long long big_cap = c->rcap + 16;                  // a coverage >= 65536 has a remainder record
     CU(cudaMalloc(&d_ds, sizeof(DevStats))); CU(cudaMalloc(&d_hist, HIST_BINS * 8)); CU(cudaMalloc(&d_big, big_cap * 8));
     CU(cudaMemsetAsync(d_ds, 0, sizeof(DevStats), c->stream));
     CU(cudaMemsetAsync(d_hist, 0, HIST_BINS * 8, c->stream));
@@ -573,9 +754,9 @@ int compute_stats(kq_ctx *c, FullStats &fs) {
     uint64_t total = ds.total, uniq = ds.unique, distinct = ds.distinct, edges = ds.edges;
     for (auto v : big) { total += v; extra.emplace_back(v, 1); }
     // every maps32 entry counts (src/graph-builder.cpp:259-266)
-    std::vector<SideSlot> side; int rc = fetch_side(c, side); if (rc) return rc;
+    std::vector<SideSlot> side; rc = fetch_map32(c, side); if (rc) return rc;
     for (const auto &q : side) {
-        if (!q.tag || !(q.kind & KQ_SIDE_MAP32)) continue;
+        if (!q.tag) continue;
         const uint32_t cov = clamp_u32(q.cov);
         for (int w = 0; w < 4; ++w) edges += (q.fw[w] > 0 || q.bw[w] > 0);
         ++distinct; total += cov;
@@ -590,12 +771,11 @@ int compute_stats(kq_ctx *c, FullStats &fs) {
     return KQ_OK;
 }
 
-// all occupied T slots as XRec (unsorted) + the side table
+// all occupied T slots as XRec (unsorted) + the literal maps32 table
 int fetch_records(kq_ctx *c, std::vector<XRec> &recs, std::vector<SideSlot> &side) {
-    CU(cudaSetDevice(c->device));
-    uint64_t occ[2]; int rc = read_occ(c, occ); if (rc) return rc;
+    int rc = kq_sync(c); if (rc) return rc;
     XRec *d_out = nullptr; unsigned long long *d_n = nullptr;
-    const unsigned long long cap = occ[0] + 1;
+    const unsigned long long cap = c->occ_known + 1;
     CU(cudaMalloc(&d_out, cap * sizeof(XRec))); CU(cudaMalloc(&d_n, 8));
     CU(cudaMemsetAsync(d_n, 0, 8, c->stream));
     CU(launch_export(c->stream, view(c), d_out, cap, d_n, &c->launches));
@@ -607,7 +787,7 @@ int fetch_records(kq_ctx *c, std::vector<XRec> &recs, std::vector<SideSlot> &sid
     if (n) CU(cudaMemcpy(recs.data(), d_out, n * sizeof(XRec), cudaMemcpyDeviceToHost));
     cudaFree(d_out); cudaFree(d_n);
     c->d2h += n * sizeof(XRec);
-    return fetch_side(c, side);
+    return fetch_map32(c, side);
 }
 
 const SideSlot *host_side_find(const std::vector<SideSlot> &side, uint64_t key) {
@@ -625,6 +805,7 @@ const SideSlot *host_side_find(const std::vector<SideSlot> &side, uint64_t key) 
 
 extern "C" int kq_stats_get(kq_ctx *c, kq_stats *out) {
     if (!c || !out) return KQ_EINVAL;
+    CU(cudaSetDevice(c->device));
     FullStats fs; int rc = compute_stats(c, fs); if (rc) return rc;
     *out = fs.s;
     return KQ_OK;
@@ -632,6 +813,7 @@ extern "C" int kq_stats_get(kq_ctx *c, kq_stats *out) {
 
 extern "C" int kq_hist(kq_ctx *c, uint64_t *cov, uint64_t *n, size_t *len) {
     if (!c || !len) return KQ_EINVAL;
+    CU(cudaSetDevice(c->device));
     FullStats fs; int rc = compute_stats(c, fs); if (rc) return rc;
     const size_t cap = *len; *len = fs.hist.size();
     if (cov && n) for (size_t i = 0; i < fs.hist.size() && i < cap; ++i) { cov[i] = fs.hist[i].first; n[i] = fs.hist[i].second; }
@@ -640,6 +822,7 @@ extern "C" int kq_hist(kq_ctx *c, uint64_t *cov, uint64_t *n, size_t *len) {
 
 extern "C" int kq_export(kq_ctx *c, uint64_t *keys, kq_rec32 *recs, size_t *n) {
     if (!c || !n) return KQ_EINVAL;
+    CU(cudaSetDevice(c->device));
     std::vector<XRec> xs; std::vector<SideSlot> side;
     int rc = fetch_records(c, xs, side); if (rc) return rc;
     std::sort(xs.begin(), xs.end(), [](const XRec &a, const XRec &b) { return a.key < b.key; });
@@ -648,7 +831,7 @@ extern "C" int kq_export(kq_ctx *c, uint64_t *keys, kq_rec32 *recs, size_t *n) {
         Rec32 r = x.r;
         if (x.flags & F_PLACEHOLDER) {                                 // resolve through maps32 (src/kreeq.cpp:158-166)
             const SideSlot *q = host_side_find(side, x.key);
-            if (!q || !(q->kind & KQ_SIDE_MAP32)) return fail(c, KQ_ECORRUPT, "Error: int32 map missing 255 value from int8 map");
+            if (!q) return fail(c, KQ_ECORRUPT, "Error: int32 map missing 255 value from int8 map");
             for (int w = 0; w < 4; ++w) { r.fw[w] = clamp_u32(q->fw[w]); r.bw[w] = clamp_u32(q->bw[w]); }
             r.cov = clamp_u32(q->cov);
         }
@@ -676,18 +859,17 @@ int gather_for_save(kq_ctx *c, std::vector<std::vector<Rec8Entry>> &maps, std::v
         if (!(x.flags & F_PLACEHOLDER) && x.r.cov <= 254) {            // exact 8-bit record
             for (int w = 0; w < 4; ++w) { e.fw[w] = (uint8_t)x.r.fw[w]; e.bw[w] = (uint8_t)x.r.bw[w]; }
             e.cov = (uint8_t)x.r.cov;
-        } else if (x.flags & F_PLACEHOLDER) {                          // literal placeholder of a loaded database
-            for (int w = 0; w < 4; ++w) { e.fw[w] = (uint8_t)x.r.fw[w]; e.bw[w] = (uint8_t)x.r.bw[w]; }
-            e.cov = 255;
-        } else {                                                       // >= 255 instances: placeholder + 32-bit record
+        } else {                                                       // cov == 255 placeholder (fw/bw unobservable: zeros)
             std::memset(e.fw, 0, 4); std::memset(e.bw, 0, 4); e.cov = 255;
-            Rec32Entry h; h.key = x.key; std::memcpy(h.fw, x.r.fw, 16); std::memcpy(h.bw, x.r.bw, 16); h.cov = x.r.cov;
-            hc.push_back(h);
+            if (!(x.flags & F_PLACEHOLDER)) {                          // >= 255 instances counted here: 32-bit record
+                Rec32Entry h; h.key = x.key; std::memcpy(h.fw, x.r.fw, 16); std::memcpy(h.bw, x.r.bw, 16); h.cov = x.r.cov;
+                hc.push_back(h);
+            }
         }
         maps[x.key % 128].push_back(e);
     }
-    for (const auto &q : side) {
-        if (!q.tag || !(q.kind & KQ_SIDE_MAP32)) continue;
+    for (const auto &q : side) {                                       // literal maps32 entries of a loaded / merged database
+        if (!q.tag) continue;
         Rec32Entry h; h.key = q.tag - 1;
         for (int w = 0; w < 4; ++w) { h.fw[w] = clamp_u32(q.fw[w]); h.bw[w] = clamp_u32(q.bw[w]); }
         h.cov = clamp_u32(q.cov);
@@ -709,6 +891,7 @@ int write_hc_part(kq_ctx *c, const std::string &dir, const std::vector<Rec32Entr
 
 int save_impl(kq_ctx *c, const char *dir_c, bool maps_too) {
     if (!c || !dir_c) return KQ_EINVAL;
+    CU(cudaSetDevice(c->device));
     const std::string dir(dir_c);
     mkdir(dir.c_str(), 0777);
     std::vector<std::vector<Rec8Entry>> maps; std::vector<Rec32Entry> hc;
@@ -727,7 +910,7 @@ int save_impl(kq_ctx *c, const char *dir_c, bool maps_too) {
     return write_hc_part(c, dir, hc);
 }
 
-// upload literal maps32 entries as the side table
+// upload literal maps32 entries as side table M
 int upload_map32(kq_ctx *c, const std::vector<Rec32Entry> &hc, uint64_t min_scap) {
     uint64_t scap = std::max<uint64_t>(min_scap, MIN_SCAP);
     while (scap < 4 * hc.size()) scap *= 2;
@@ -737,14 +920,14 @@ int upload_map32(kq_ctx *c, const std::vector<Rec32Entry> &hc, uint64_t min_scap
         uint64_t i = (uint64_t)(((unsigned __int128)mix64(h.key ^ 0x9E3779B97F4A7C15ULL) * scap) >> 64);
         while (side[i].tag && side[i].tag != h.key + 1) if (++i == scap) i = 0;
         SideSlot &q = side[i];
-        q.tag = h.key + 1; q.kind = KQ_SIDE_MAP32; q.cov = h.cov;
+        q.tag = h.key + 1; q.cov = h.cov;
         for (int w = 0; w < 4; ++w) { q.fw[w] = h.fw[w]; q.bw[w] = h.bw[w]; }
     }
-    CU(cudaFree(c->S)); c->S = nullptr;
-    CU(cudaMalloc(&c->S, scap * sizeof(SideSlot))); c->scap = scap;
-    CU(cudaMemcpyAsync(c->S, side.data(), scap * sizeof(SideSlot), cudaMemcpyHostToDevice, c->stream));
+    CU(cudaFree(c->M)); c->M = nullptr;
+    CU(cudaMalloc(&c->M, scap * sizeof(SideSlot))); c->mcap = scap;
+    CU(cudaMemcpyAsync(c->M, side.data(), scap * sizeof(SideSlot), cudaMemcpyHostToDevice, c->stream));
     const unsigned long long n = hc.size();
-    CU(cudaMemcpyAsync(c->d_occ + 1, &n, 8, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(c->d_occ + 2, &n, 8, cudaMemcpyHostToDevice, c->stream));
     CU(cudaStreamSynchronize(c->stream));
     c->h2d += scap * sizeof(SideSlot);
     return KQ_OK;
@@ -774,7 +957,7 @@ int read_owned_hc(kq_ctx *c, const std::string &dir, std::vector<Rec32Entry> &hc
 enum class Feed { Put, MergeRef, AddLogical };
 
 // stream host records through a device buffer into one of the table kernels, in sub-batches small
-// enough that the side table can never fill up inside a launch
+// enough that neither the table nor a side table can fill up inside a launch
 int feed_records(kq_ctx *c, const std::vector<XRec> &xs, Feed mode) {
     if (xs.empty()) return KQ_OK;
     XRec *d = nullptr;
@@ -782,12 +965,14 @@ int feed_records(kq_ctx *c, const std::vector<XRec> &xs, Feed mode) {
     CU(cudaMalloc(&d, std::min<uint64_t>(xs.size(), max_batch) * sizeof(XRec)));
     for (uint64_t off = 0; off < xs.size();) {
         uint64_t n = std::min<uint64_t>(xs.size() - off, max_batch);
-        if (mode != Feed::Put) {
-            uint64_t occ[2]; int rc = read_occ(c, occ); if (rc) { cudaFree(d); return rc; }
-            if (occ[1] * 4 > c->scap) { rc = grow_side(c, c->scap * 4); if (rc) { cudaFree(d); return rc; } }
-            n = std::min<uint64_t>(n, c->scap / 4);
+        uint64_t occ[3]; int rc = read_occ(c, occ); if (rc) { cudaFree(d); return rc; }
+        if (occ[1] * 4 > c->rcap) { rc = grow_side(c, 1, c->rcap * 4); if (rc) { cudaFree(d); return rc; } }
+        if (occ[2] * 4 > c->mcap) { rc = grow_side(c, 2, c->mcap * 4); if (rc) { cudaFree(d); return rc; } }
+        n = std::min<uint64_t>(n, std::min(c->rcap, c->mcap) / 4);
+        if ((double)(occ[0] + n) > MAX_LOAD * (double)table_slots(c)) {
+            rc = grow_table(c, std::max<uint64_t>(2 * table_slots(c), (uint64_t)((double)(occ[0] + n) / TARGET_LOAD)));
+            if (rc) { cudaFree(d); return rc; }
         }
-        int rc = ensure_capacity(c, n); if (rc) { cudaFree(d); return rc; }
         CU(cudaMemcpyAsync(d, xs.data() + off, n * sizeof(XRec), cudaMemcpyHostToDevice, c->stream));
         c->h2d += n * sizeof(XRec);
         const TableView tv = view(c);
@@ -799,6 +984,8 @@ int feed_records(kq_ctx *c, const std::vector<XRec> &xs, Feed mode) {
         off += n;
     }
     cudaFree(d);
+    uint64_t occ[3]; int rc = read_occ(c, occ); if (rc) return rc;
+    c->occ_bound = occ[0];
     return check_device_error(c);
 }
 
@@ -840,6 +1027,7 @@ extern "C" int kq_db_read_k(const char *dir) {
 
 extern "C" int kq_db_load(kq_ctx *c, const char *dir_c) {
     if (!c || !dir_c) return KQ_EINVAL;
+    CU(cudaSetDevice(c->device));
     const std::string dir(dir_c);
     const int k = read_index_k(dir);
     if (k < 0) return fail(c, KQ_EIO, "Cannot load DBG input. Exiting.");          // src/input.cpp:70-72
@@ -853,7 +1041,9 @@ extern "C" int kq_db_load(kq_ctx *c, const char *dir_c) {
         const size_t b = t << 20, e = std::min(all.size(), b + (1 << 20));
         for (size_t i = b; i < e; ++i) xs[i] = raw_xrec(all[i]);
     });
-    rc = kq_reserve(c, xs.size()); if (rc) return rc;
+    if ((double)xs.size() > TARGET_LOAD * (double)table_slots(c)) {
+        rc = grow_table(c, (uint64_t)((double)xs.size() / TARGET_LOAD)); if (rc) return rc;
+    }
     rc = feed_records(c, xs, Feed::Put); if (rc) return rc;
     c->loaded_db = true;
     return KQ_OK;
@@ -886,7 +1076,7 @@ extern "C" int kq_union(kq_ctx *c, const char *const *dirs, int n, int ref_compa
                 d.cov = sat(d.cov, h.cov);
             } else m32.push_back(h);
         }
-        rc = upload_map32(c, m32, 1ull << 20); if (rc) return rc;
+        rc = upload_map32(c, m32, 1ull << 16); if (rc) return rc;
         // 2. DB0's 8-bit maps raw (kmer.h:668-672), 3. later databases in order (kmer.h:674-686)
         for (int i = 0; i < n; ++i) {
             std::vector<Rec8Entry> all; rc = read_owned_maps(c, dirs[i], all); if (rc) return rc;
@@ -900,7 +1090,6 @@ extern "C" int kq_union(kq_ctx *c, const char *const *dirs, int n, int ref_compa
     }
 
     // exact mode: saturating sum of every database's lookup-visible records
-    rc = grow_side(c, std::max<uint64_t>(c->scap, 1ull << 20)); if (rc) return rc;
     for (int i = 0; i < n; ++i) {
         std::vector<Rec32Entry> hc; rc = read_owned_hc(c, dirs[i], hc); if (rc) return rc;
         std::sort(hc.begin(), hc.end(), [](const Rec32Entry &a, const Rec32Entry &b) { return a.key < b.key; });
@@ -915,6 +1104,7 @@ extern "C" int kq_union(kq_ctx *c, const char *const *dirs, int n, int ref_compa
         }
         rc = feed_records(c, xs, Feed::AddLogical); if (rc) return rc;
     }
+    c->loaded_db = true;
     return KQ_OK;
 }
 

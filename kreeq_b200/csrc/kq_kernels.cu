@@ -1,22 +1,27 @@
-// kq_kernels.cu -- hand-written sm_100a kernels of the kreeq k-mer hot path.
+// kq_kernels.cu -- hand-written sm_100a kernels of the kreeq k-mer hot path: count pipeline,
+// validate, point lookups.  (Table maintenance kernels are in kq_table_kernels.cu.)
 //
-// All kernels are HBM-bound integer work (random 32-byte sector traffic on the table); no tensor
-// cores are involved.  Grids are sized as a multiple of the SM count (148 on B200) times the
-// resident CTAs per SM and loop grid-stride, so every SM keeps its full complement of warps in
-// flight to cover the DRAM latency of the dependent probe -> atomic chain.
+// Nothing here is a dense contraction; no tensor cores.  What bounds these kernels on B200 is the
+// number of random table touches the memory system can serve (profiles/r01_gups_*.log): ~36 G loads/s
+// and ~20 G atomics/s when the touched footprint is far larger than L2, but ~290 G loads/s and
+// ~45 G (load + CAS)/s when it is <= 64 MB.  The count path therefore never touches the table at
+// random in HBM: tuples are first scattered into slice order with coalesced 256-byte flushes
+// (slice = 32 MiB of table), then inserted slice after slice while that slice sits in L2.
 //
 // Reference semantics each kernel follows (paths relative to the reference tree):
-//   count_packed / extract_route : DBG::hashSequences   src/graph-builder.cpp:62-113
-//   insert (accumulate)          : DBG::processBuffers  src/graph-builder.cpp:160-206 (closed form)
-//   validate                     : DBG::evaluateSegment src/kreeq.cpp:143-219
-//   stats_scan                   : DBG::summary         src/graph-builder.cpp:240-282
-//   merge_ref                    : DBG::mergeSubMaps    src/graph-builder.cpp:353-432
+//   extraction (all count kernels) : DBG::hashSequences   src/graph-builder.cpp:62-113
+//   insert                         : DBG::processBuffers  src/graph-builder.cpp:160-206 (closed form)
+//   validate                       : DBG::evaluateSegment src/kreeq.cpp:143-219
 #include "kq_kernels.h"
+
+#include <algorithm>
 
 namespace kq {
 
-constexpr int TPB = 256;          // threads per CTA
-constexpr int CTAS_PER_SM = 6;    // 1536 resident threads per SM, 40 registers each
+constexpr int TPB = 256;          // threads per CTA of the grid-stride kernels
+constexpr int CTAS_PER_SM = 6;
+constexpr int RUN = 8;            // consecutive k-mer start positions one thread extracts per round
+constexpr int SC_THREADS = 512;   // scatter kernel: one CTA per SM, most of the shared memory as bins
 
 int sm_count() {
     static int n = 0;
@@ -28,138 +33,289 @@ int sm_count() {
     return n;
 }
 
-static inline unsigned grid_for(uint64_t n) {
+static inline unsigned grid_for(uint64_t n, int per_thread = 1) {
     const uint64_t full = (uint64_t)sm_count() * CTAS_PER_SM;
-    const uint64_t need = (n + TPB - 1) / TPB;
+    const uint64_t need = (n + (uint64_t)TPB * per_thread - 1) / ((uint64_t)TPB * per_thread);
     return (unsigned)(need < full ? (need ? need : 1) : full);
 }
 
-// block-wide sum of per-thread counters, one global atomic per CTA
+// block-wide sum of per-thread counters (< 2^32 per thread), one global atomic per CTA
 __device__ __forceinline__ void block_add(unsigned long long v, unsigned long long *dst, unsigned long long *sh) {
-    v = __reduce_add_sync(0xffffffffu, (unsigned)v);   // per-thread partial sums stay < 2^32 (see callers)
+    v = __reduce_add_sync(0xffffffffu, (unsigned)v);
     if ((threadIdx.x & 31) == 0 && v) atomicAdd(sh, v);
     __syncthreads();
     if (threadIdx.x == 0 && *sh) atomicAdd(dst, *sh);
 }
 
-// one k-mer instance -> table (src/graph-builder.cpp:160-206)
-__device__ __forceinline__ bool insert_instance(const TableView &tv, uint64_t key, uint32_t e) {
-    bool is_new;
-    Slot *s = find_or_claim(tv, key, &is_new);
-    if (!s) return false;
-    uint32_t fwi[4], bwi[4];
-#pragma unroll
-    for (int w = 0; w < 4; ++w) { fwi[w] = (e >> (7 - w)) & 1u; bwi[w] = (e >> (3 - w)) & 1u; }
-    accumulate(tv, s, key, 1u, fwi, bwi);
-    return is_new;
+// ---- extraction ---------------------------------------------------------------------------------------
+
+// 64 bits at bit offset o (< 128) of the 192-bit little-endian value {w0, w1, w2}
+__device__ __forceinline__ uint64_t bits3(uint64_t w0, uint64_t w1, uint64_t w2, uint32_t o) {
+    const uint64_t lo = o < 64 ? w0 : w1, hi = o < 64 ? w1 : w2;
+    const uint32_t s = o & 63u;
+    return s ? (lo >> s) | (hi << (64 - s)) : lo;
 }
 
-// ---- count: fused extract + insert ----------------------------------------------------------
+// k-mers starting at positions p0 .. p0+cnt-1 (cnt <= RUN) of a packed sequence: 5 word loads for the
+// whole run instead of 6 per position.  Returns the mask of valid windows.
+__device__ __forceinline__ uint32_t extract_run(const uint64_t *__restrict__ B, const uint64_t *__restrict__ M,
+                                                uint64_t p0, uint32_t cnt, int k, uint64_t key[RUN], uint32_t e[RUN]) {
+    const uint64_t bw = p0 >> 5; const uint32_t bs = (uint32_t)(2 * p0) & 63u;
+    const uint64_t b0 = __ldg(B + bw), b1 = __ldg(B + bw + 1), b2 = __ldg(B + bw + 2);
+    const uint64_t iw = p0 >> 6; const uint32_t is = (uint32_t)p0 & 63u;
+    const uint64_t i0 = __ldg(M + iw), i1 = __ldg(M + iw + 1);
+    uint32_t prv = (p0 == 0 || invalid_at(M, p0 - 1)) ? 4u : base_at(B, p0 - 1);
+    uint32_t mask = 0;
+#pragma unroll
+    for (int i = 0; i < RUN; ++i) {
+        const uint32_t o = bs + 2 * i;                               // <= 62 + 14
+        const uint64_t win = bits3(b0, b1, b2, o);
+        const uint32_t oi = is + i;                                  // <= 63 + 7; k + 1 more bits are needed
+        const uint64_t inv = oi < 64 ? ((i0 >> oi) | (oi ? i1 << (64 - oi) : 0)) : (i1 >> (oi - 64));
+        const uint32_t on = o + 2 * k;                               // bit offset of the base after the window
+        const uint64_t wn = on < 64 ? b0 : on < 128 ? b1 : b2;
+        const uint32_t nxt = ((inv >> k) & 1) ? 4u : (uint32_t)(wn >> (on & 63u)) & 3u;
+        const Kmer km = kmer_from_window(win, inv, nxt, prv, k);
+        if ((uint32_t)i < cnt && km.valid) { key[i] = km.key; e[i] = edge_byte(km); mask |= 1u << i; }
+        prv = (inv & 1) ? 4u : (uint32_t)win & 3u;
+    }
+    return mask;
+}
 
-__global__ void __launch_bounds__(TPB, CTAS_PER_SM)
-count_packed_kernel(TableView tv, const uint64_t *__restrict__ B, const uint64_t *__restrict__ M,
-                    uint64_t pos0, uint64_t npos, unsigned long long *instances) {
+template <int TW> __device__ __forceinline__ void tuple_unpack(const uint64_t *t, uint64_t i, uint64_t &key, uint32_t &e) {
+    if (TW == 1) { const uint64_t w = __ldcs(t + i); key = w >> 8; e = (uint32_t)w & 255u; }
+    else { const ulonglong2 w = __ldcs(reinterpret_cast<const ulonglong2 *>(t) + i); key = w.x; e = (uint32_t)w.y & 255u; }
+}
+template <int TW> __device__ __forceinline__ void tuple_store(uint64_t *t, uint64_t i, uint64_t key, uint32_t e) {
+    if (TW == 1) t[i] = (key << 8) | e;
+    else reinterpret_cast<ulonglong2 *>(t)[i] = make_ulonglong2(key, e);
+}
+
+// One round of a CTA over its tile: every thread produces up to RUN (key, edge) pairs.
+// Sequence source: tile = nthreads * RUN consecutive positions, thread t takes RUN consecutive ones.
+// Tuple source: tile = nthreads * RUN tuples, element i of thread t is tile + i * nthreads + t (coalesced).
+template <int TW>
+__device__ __forceinline__ uint32_t produce(const Source &src, const TableView &tv, uint64_t tile, uint64_t total,
+                                            uint64_t key[RUN], uint32_t e[RUN]) {
+    if (src.tuples == nullptr) {
+        const uint64_t first = tile + (uint64_t)threadIdx.x * RUN;
+        if (first >= total) return 0;
+        const uint32_t cnt = (uint32_t)min((uint64_t)RUN, total - first);
+        uint32_t m = extract_run(src.bases, src.invalid, src.pos0 + first, cnt, tv.k, key, e);
+        if (tv.shard_rank >= 0) {
+#pragma unroll
+            for (int i = 0; i < RUN; ++i) if ((m >> i & 1u) && !owns(tv, key[i])) m &= ~(1u << i);
+        }
+        return m;
+    }
+    uint32_t m = 0;
+#pragma unroll
+    for (int i = 0; i < RUN; ++i) {
+        const uint64_t j = tile + (uint64_t)i * blockDim.x + threadIdx.x;
+        if (j < total) { tuple_unpack<TW>(src.tuples, j, key[i], e[i]); m |= 1u << i; }
+    }
+    return m;
+}
+
+__device__ __forceinline__ uint64_t source_total(const Source &src) {
+    return src.tuples ? (uint64_t)*src.ntuples : src.npos;
+}
+
+// ---- count: fused extract + insert (single-slice tables, small inputs) ------------------------------
+
+template <int TW>
+__global__ void __launch_bounds__(TPB, 4)
+count_direct_kernel(TableView tv, Source src, unsigned long long *instances,
+                    uint64_t *ovf, unsigned long long ovf_cap, unsigned long long *ovf_n) {
     __shared__ unsigned long long sh[2];
     if (threadIdx.x < 2) sh[threadIdx.x] = 0;
     __syncthreads();
     unsigned long long inst = 0, fresh = 0;
-    const uint64_t stride = (uint64_t)gridDim.x * TPB;
-    for (uint64_t i = (uint64_t)blockIdx.x * TPB + threadIdx.x; i < npos; i += stride) {
-        const Kmer km = kmer_at(B, M, pos0 + i, tv.k);
-        if (!km.valid || !owns(tv, km.key)) continue;
-        ++inst;
-        fresh += insert_instance(tv, km.key, edge_byte(km));
+    const uint64_t total = source_total(src), per = (uint64_t)TPB * RUN;
+    for (uint64_t tile = (uint64_t)blockIdx.x * per; tile < total; tile += (uint64_t)gridDim.x * per) {
+        uint64_t key[RUN]; uint32_t e[RUN];
+        const uint32_t m = produce<TW>(src, tv, tile, total, key, e);
+#pragma unroll
+        for (int i = 0; i < RUN; ++i) {
+            if (!(m >> i & 1u)) continue;
+            const int r = insert_instance(tv, key[i], e[i]);
+            ++inst;
+            if (r < 0) {                                              // table full: keep the tuple for after a grow
+                const unsigned long long j = atomicAdd(ovf_n, 1ULL);
+                if (j < ovf_cap) tuple_store<TW>(ovf, j, key[i], e[i]);
+            } else fresh += r;
+        }
     }
     block_add(inst, instances, &sh[0]);
     block_add(fresh, &tv.occ[0], &sh[1]);
 }
 
-// ---- count: extract with routing (multi-GPU) --------------------------------------------------
+// ---- count, step 1: tuples per slice -----------------------------------------------------------------
 
-__global__ void __launch_bounds__(TPB, CTAS_PER_SM)
-extract_route_kernel(TableView tv, const uint64_t *__restrict__ B, const uint64_t *__restrict__ M,
-                     uint64_t pos0, uint64_t npos, RouteArgs ra, unsigned long long *instances) {
-    __shared__ unsigned long long sh[2];
-    if (threadIdx.x < 2) sh[threadIdx.x] = 0;
+template <int TW>
+__global__ void __launch_bounds__(TPB, 4)
+slice_hist_kernel(TableView tv, Source src, unsigned long long *hist) {
+    extern __shared__ unsigned int h[];
+    for (unsigned i = threadIdx.x; i < tv.nslices; i += TPB) h[i] = 0;
     __syncthreads();
-    unsigned long long inst = 0, fresh = 0;
-    const uint64_t stride = (uint64_t)gridDim.x * TPB;
-    const uint64_t rounds = (npos + stride - 1) / stride;        // warp-uniform trip count
-    const unsigned lane = threadIdx.x & 31;
-    for (uint64_t r = 0; r < rounds; ++r) {
-        const uint64_t i = r * stride + (uint64_t)blockIdx.x * TPB + threadIdx.x;
-        int dest = -1; uint64_t key = 0; uint32_t e = 0;
-        if (i < npos) {
-            const Kmer km = kmer_at(B, M, pos0 + i, tv.k);
-            if (km.valid) {
-                key = km.key; e = edge_byte(km);
-                dest = (int)((key & 127) >> ra.shift);
-                if (dest == ra.my_rank) {                        // fused local insert
-                    ++inst; fresh += insert_instance(tv, key, e); dest = -1;
-                }
-            }
+    const uint64_t total = source_total(src), per = (uint64_t)TPB * RUN;
+    for (uint64_t tile = (uint64_t)blockIdx.x * per; tile < total; tile += (uint64_t)gridDim.x * per) {
+        uint64_t key[RUN]; uint32_t e[RUN];
+        const uint32_t m = produce<TW>(src, tv, tile, total, key, e);
+#pragma unroll
+        for (int i = 0; i < RUN; ++i)
+            if (m >> i & 1u) atomicAdd(&h[slice_of(tv, mix64(key[i]))], 1u);
+    }
+    __syncthreads();
+    for (unsigned i = threadIdx.x; i < tv.nslices; i += TPB)
+        if (h[i]) atomicAdd(&hist[i], (unsigned long long)h[i]);
+}
+
+// ---- count, step 2: exclusive scan of the slice histogram (one CTA) ------------------------------------
+
+__global__ void __launch_bounds__(1024, 1)
+slice_offsets_kernel(unsigned long long nslices, const unsigned long long *hist, unsigned long long *cursor,
+                     unsigned long long *total, unsigned long long *instances) {
+    __shared__ unsigned long long part[1024];
+    const unsigned long long per = (nslices + 1023) / 1024;
+    const unsigned long long b = threadIdx.x * per, e = min(nslices, b + per);
+    unsigned long long s = 0;
+    for (unsigned long long i = b; i < e; ++i) s += hist[i];
+    part[threadIdx.x] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long run = 0;
+        for (int i = 0; i < 1024; ++i) { const unsigned long long v = part[i]; part[i] = run; run += v; }
+        *total = run; if (instances) *instances += run;
+    }
+    __syncthreads();
+    s = part[threadIdx.x];
+    for (unsigned long long i = b; i < e; ++i) { cursor[i] = s; s += hist[i]; }
+}
+
+// ---- count, step 3: scatter into slice order -------------------------------------------------------------
+
+// Shared memory: nslices bins of `cap` tuples + one fill counter per bin.  A tuple is appended to its
+// bin with one shared-memory atomic; a bin that reaches `cap` entries is flushed by one warp as ONE
+// coalesced cap * 8 * TW byte store (256 B for cap = 32) at a position reserved with one global atomic
+// on the slice's cursor.  Random 256-byte stores run at ~5.4 TB/s on B200 (r01_gups_footprint_sweep.log).
+template <int TW>
+__global__ void __launch_bounds__(SC_THREADS, 1)
+slice_scatter_kernel(TableView tv, Source src, uint64_t *__restrict__ out, unsigned long long *cursor, int cap) {
+    extern __shared__ uint64_t sm[];
+    const unsigned P = (unsigned)tv.nslices;
+    uint64_t *bins = sm;
+    unsigned int *fill = reinterpret_cast<unsigned int *>(bins + (size_t)P * cap * TW);
+    for (unsigned i = threadIdx.x; i < P; i += SC_THREADS) fill[i] = 0;
+    __syncthreads();
+    const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = SC_THREADS / 32;
+    const uint64_t total = source_total(src), per = (uint64_t)SC_THREADS * RUN;
+    for (uint64_t tile = (uint64_t)blockIdx.x * per; tile < total; tile += (uint64_t)gridDim.x * per) {
+        uint64_t key[RUN]; uint32_t e[RUN]; unsigned bin[RUN], slot[RUN];
+        uint32_t m = produce<TW>(src, tv, tile, total, key, e);
+        bool filled = false;
+#pragma unroll
+        for (int i = 0; i < RUN; ++i) {
+            if (!(m >> i & 1u)) continue;
+            bin[i] = (unsigned)slice_of(tv, mix64(key[i]));
+            slot[i] = atomicAdd(&fill[bin[i]], 1u);
+            filled |= slot[i] >= (unsigned)cap - 1;
         }
-        // warp-aggregated append: one atomic per (warp, destination)
-        const unsigned peers = __match_any_sync(0xffffffffu, dest);
-        if (dest >= 0) {
+        for (;;) {
+#pragma unroll
+            for (int i = 0; i < RUN; ++i) {
+                if (!(m >> i & 1u) || slot[i] >= (unsigned)cap) continue;
+                tuple_store<TW>(bins, (size_t)bin[i] * cap + slot[i], key[i], e[i]);
+                m &= ~(1u << i);
+            }
+            if (!__syncthreads_or(filled)) break;                    // no bin reached cap in this round
+            for (unsigned b = warp; b < P; b += nwarps) {
+                const unsigned f = fill[b];
+                if (f < (unsigned)cap) continue;
+                unsigned long long g = 0;
+                if (lane == 0) g = atomicAdd(&cursor[b], (unsigned long long)cap);
+                g = __shfl_sync(0xffffffffu, g, 0);
+                const uint64_t *srcw = bins + (size_t)b * cap * TW;
+                uint64_t *dst = out + g * TW;
+                for (unsigned w = lane; w < (unsigned)cap * TW; w += 32) __stcs(dst + w, srcw[w]);
+                __syncwarp();
+                if (lane == 0) fill[b] = f - cap;
+            }
+            __syncthreads();
+            filled = false;
+#pragma unroll
+            for (int i = 0; i < RUN; ++i) {
+                if (!(m >> i & 1u)) continue;
+                slot[i] -= cap;                                      // the first cap entries of the bin are gone
+                filled = true;                                       // something is still waiting: go round again
+            }
+            if (!__syncthreads_or(filled)) break;
+        }
+    }
+    __syncthreads();
+    for (unsigned b = warp; b < P; b += nwarps) {                     // what is left in the bins
+        const unsigned f = fill[b];
+        if (!f) continue;
+        unsigned long long g = 0;
+        if (lane == 0) g = atomicAdd(&cursor[b], (unsigned long long)f);
+        g = __shfl_sync(0xffffffffu, g, 0);
+        const uint64_t *srcw = bins + (size_t)b * cap * TW;
+        uint64_t *dst = out + g * TW;
+        for (unsigned w = lane; w < f * TW; w += 32) __stcs(dst + w, srcw[w]);
+    }
+}
+
+// ---- count, step 4: insert slice-ordered tuples -----------------------------------------------------------
+
+// Consecutive CTAs work on consecutive tuples, i.e. on the same one or two slices at a time, so the
+// slot loads and CASes below hit L2.  Tuples are streamed with evict-first loads to keep L2 for the table.
+template <int TW>
+__global__ void __launch_bounds__(TPB, CTAS_PER_SM)
+insert_tuples_kernel(TableView tv, const uint64_t *__restrict__ tuples, const unsigned long long *n_ptr,
+                     uint64_t *ovf, unsigned long long ovf_cap, unsigned long long *ovf_n) {
+    __shared__ unsigned long long sh[1];
+    if (threadIdx.x == 0) sh[0] = 0;
+    __syncthreads();
+    unsigned long long fresh = 0;
+    const uint64_t n = *n_ptr, stride = (uint64_t)gridDim.x * TPB;
+    for (uint64_t i = (uint64_t)blockIdx.x * TPB + threadIdx.x; i < n; i += stride) {
+        uint64_t key; uint32_t e;
+        tuple_unpack<TW>(tuples, i, key, e);
+        const int r = insert_instance(tv, key, e);
+        if (r < 0) {                                                  // slice full: keep the tuple for after a grow
+            const unsigned long long j = atomicAdd(ovf_n, 1ULL);
+            if (j < ovf_cap) tuple_store<TW>(ovf, j, key, e);
+        } else fresh += r;
+    }
+    block_add(fresh, &tv.occ[0], &sh[0]);
+}
+
+// ---- count: extract with routing (multi-GPU) ------------------------------------------------------------
+
+template <int TW>
+__global__ void __launch_bounds__(TPB, 4)
+extract_route_kernel(TableView tv, Source src, RouteArgs ra) {
+    const uint64_t total = src.npos, per = (uint64_t)TPB * RUN;
+    const unsigned lane = threadIdx.x & 31;
+    tv.shard_rank = -1;                                               // every window is routed, none dropped
+    for (uint64_t tile = (uint64_t)blockIdx.x * per; tile < total; tile += (uint64_t)gridDim.x * per) {
+        uint64_t key[RUN]; uint32_t e[RUN];
+        const uint32_t m = produce<TW>(src, tv, tile, total, key, e);
+#pragma unroll
+        for (int i = 0; i < RUN; ++i) {
+            const int dest = (m >> i & 1u) ? (int)((key[i] & 127) >> ra.shift) : -1;
+            // warp-aggregated append: one atomic per (warp, destination)
+            const unsigned peers = __match_any_sync(0xffffffffu, dest);
+            if (dest < 0) continue;
             const unsigned leader = __ffs(peers) - 1;
             unsigned long long base = 0;
             if (lane == leader) base = atomicAdd(&ra.counts[dest], (unsigned long long)__popc(peers));
             base = __shfl_sync(peers, base, leader);
             const unsigned long long slot = base + __popc(peers & ((1u << lane) - 1));
-            if (slot < ra.cap_per_rank) {
-                ra.keys[(unsigned long long)dest * ra.cap_per_rank + slot] = key;
-                ra.edges[(unsigned long long)dest * ra.cap_per_rank + slot] = (uint8_t)e;
-            } else {
-                atomicOr(tv.err, 8);
-            }
+            if (slot < ra.cap_per_rank) tuple_store<TW>(ra.tuples, (unsigned long long)dest * ra.cap_per_rank + slot, key[i], e[i]);
+            else atomicOr(tv.err, 8);
         }
     }
-    block_add(inst, instances, &sh[0]);
-    block_add(fresh, &tv.occ[0], &sh[1]);
-}
-
-// ---- count: insert routed tuples ---------------------------------------------------------------
-
-__global__ void __launch_bounds__(TPB, CTAS_PER_SM)
-insert_tuples_kernel(TableView tv, const uint64_t *__restrict__ keys, const uint8_t *__restrict__ edges,
-                     uint64_t n, unsigned long long *instances) {
-    __shared__ unsigned long long sh[2];
-    if (threadIdx.x < 2) sh[threadIdx.x] = 0;
-    __syncthreads();
-    unsigned long long inst = 0, fresh = 0;
-    const uint64_t stride = (uint64_t)gridDim.x * TPB;
-    for (uint64_t i = (uint64_t)blockIdx.x * TPB + threadIdx.x; i < n; i += stride) {
-        ++inst;
-        fresh += insert_instance(tv, __ldg(keys + i), __ldg(edges + i));
-    }
-    block_add(inst, instances, &sh[0]);
-    block_add(fresh, &tv.occ[0], &sh[1]);
-}
-
-cudaError_t launch_count_packed(cudaStream_t st, const TableView &tv, const uint64_t *B, const uint64_t *M,
-                                uint64_t pos0, uint64_t npos, unsigned long long *instances, uint64_t *launches) {
-    if (!npos) return cudaSuccess;
-    count_packed_kernel<<<grid_for(npos), TPB, 0, st>>>(tv, B, M, pos0, npos, instances);
-    ++*launches;
-    return cudaGetLastError();
-}
-
-cudaError_t launch_extract_route(cudaStream_t st, const TableView &tv, const uint64_t *B, const uint64_t *M,
-                                 uint64_t pos0, uint64_t npos, RouteArgs ra, unsigned long long *instances,
-                                 uint64_t *launches) {
-    if (!npos) return cudaSuccess;
-    extract_route_kernel<<<grid_for(npos), TPB, 0, st>>>(tv, B, M, pos0, npos, ra, instances);
-    ++*launches;
-    return cudaGetLastError();
-}
-
-cudaError_t launch_insert_tuples(cudaStream_t st, const TableView &tv, const uint64_t *keys, const uint8_t *edges,
-                                 uint64_t n, unsigned long long *instances, uint64_t *launches) {
-    if (!n) return cudaSuccess;
-    insert_tuples_kernel<<<grid_for(n), TPB, 0, st>>>(tv, keys, edges, n, instances);
-    ++*launches;
-    return cudaGetLastError();
 }
 
 // ---- validate ------------------------------------------------------------------------------------
@@ -205,7 +361,7 @@ validate_kernel(TableView tv, const uint64_t *__restrict__ B, const uint64_t *__
                 ++counted;
             }
         }
-        reinterpret_cast<uint4 *>(out)[i] = o;                  // one coalesced 16-byte store per base
+        __stcs(reinterpret_cast<uint4 *>(out) + i, o);          // one coalesced 16-byte store per base
     }
     block_add(missing, &acc3[0], &sh[0]);
     block_add(counted, &acc3[1], &sh[1]);
@@ -223,6 +379,97 @@ lookup_kernel(TableView tv, const uint64_t *__restrict__ keys, uint64_t n, Rec32
     }
 }
 
+// ---- launchers ---------------------------------------------------------------------------------------
+
+size_t scatter_smem_bytes(unsigned long long nslices, int cap, int tw) {
+    return (size_t)nslices * cap * tw * 8 + (size_t)nslices * 4;
+}
+
+int scatter_pick_cap(unsigned long long nslices, int tw) {
+    static int max_smem = 0;
+    if (!max_smem) {
+        int dev = 0; cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+        if (max_smem <= 0) max_smem = 227 * 1024;
+    }
+    for (int cap : {32, 16, 8})
+        if (scatter_smem_bytes(nslices, cap, tw) <= (size_t)max_smem - 1024) return cap;
+    return 0;
+}
+
+static inline uint64_t source_bound(const Source &src) { return src.tuples ? src.ntuples_max : src.npos; }
+
+#define KQ_TW_DISPATCH(tw, CALL) do { if ((tw) == 1) { constexpr int TW = 1; CALL; } else { constexpr int TW = 2; CALL; } } while (0)
+
+cudaError_t launch_count_direct(cudaStream_t st, const TableView &tv, const Source &src,
+                                unsigned long long *instances, uint64_t *ovf, unsigned long long ovf_cap,
+                                unsigned long long *ovf_n, uint64_t *launches) {
+    const uint64_t n = source_bound(src);
+    if (!n) return cudaSuccess;
+    const unsigned grid = std::min<uint64_t>((n + TPB * RUN - 1) / (TPB * RUN), (uint64_t)sm_count() * 4);
+    KQ_TW_DISPATCH(tuple_words(tv.k), (count_direct_kernel<TW><<<grid, TPB, 0, st>>>(tv, src, instances, ovf, ovf_cap, ovf_n)));
+    ++*launches;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_slice_hist(cudaStream_t st, const TableView &tv, const Source &src, unsigned long long *hist,
+                              uint64_t *launches) {
+    const uint64_t n = source_bound(src);
+    if (!n) return cudaSuccess;
+    const unsigned grid = std::min<uint64_t>((n + TPB * RUN - 1) / (TPB * RUN), (uint64_t)sm_count() * 4);
+    const size_t smem = (size_t)tv.nslices * 4;
+    KQ_TW_DISPATCH(tuple_words(tv.k), (slice_hist_kernel<TW><<<grid, TPB, smem, st>>>(tv, src, hist)));
+    ++*launches;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_slice_offsets(cudaStream_t st, unsigned long long nslices, const unsigned long long *hist,
+                                 unsigned long long *cursor, unsigned long long *total, unsigned long long *instances,
+                                 uint64_t *launches) {
+    slice_offsets_kernel<<<1, 1024, 0, st>>>(nslices, hist, cursor, total, instances);
+    ++*launches;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_slice_scatter(cudaStream_t st, const TableView &tv, const Source &src, uint64_t *out,
+                                 unsigned long long *cursor, int cap, uint64_t *launches) {
+    const uint64_t n = source_bound(src);
+    if (!n) return cudaSuccess;
+    const int tw = tuple_words(tv.k);
+    const size_t smem = scatter_smem_bytes(tv.nslices, cap, tw);
+    const unsigned grid = std::min<uint64_t>((n + SC_THREADS * RUN - 1) / (SC_THREADS * RUN), (uint64_t)sm_count());
+    cudaError_t e;
+    if (tw == 1) {
+        e = cudaFuncSetAttribute(slice_scatter_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        slice_scatter_kernel<1><<<grid, SC_THREADS, smem, st>>>(tv, src, out, cursor, cap);
+    } else {
+        e = cudaFuncSetAttribute(slice_scatter_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        slice_scatter_kernel<2><<<grid, SC_THREADS, smem, st>>>(tv, src, out, cursor, cap);
+    }
+    ++*launches;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_insert_tuples(cudaStream_t st, const TableView &tv, const uint64_t *tuples,
+                                 const unsigned long long *n, uint64_t n_max, uint64_t *ovf,
+                                 unsigned long long ovf_cap, unsigned long long *ovf_n, uint64_t *launches) {
+    if (!n_max) return cudaSuccess;
+    KQ_TW_DISPATCH(tuple_words(tv.k), (insert_tuples_kernel<TW><<<grid_for(n_max), TPB, 0, st>>>(tv, tuples, n, ovf, ovf_cap, ovf_n)));
+    ++*launches;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_extract_route(cudaStream_t st, const TableView &tv, const Source &src, RouteArgs ra,
+                                 uint64_t *launches) {
+    if (!src.npos) return cudaSuccess;
+    const unsigned grid = std::min<uint64_t>((src.npos + TPB * RUN - 1) / (TPB * RUN), (uint64_t)sm_count() * 4);
+    KQ_TW_DISPATCH(tuple_words(tv.k), (extract_route_kernel<TW><<<grid, TPB, 0, st>>>(tv, src, ra)));
+    ++*launches;
+    return cudaGetLastError();
+}
+
 cudaError_t launch_validate(cudaStream_t st, const TableView &tv, const uint64_t *B, const uint64_t *M,
                             uint64_t base0, uint64_t c0, uint64_t n, uint64_t kcount, uint32_t cutoff,
                             Base *out, unsigned long long *acc3, uint64_t *launches) {
@@ -236,273 +483,6 @@ cudaError_t launch_lookup(cudaStream_t st, const TableView &tv, const uint64_t *
                           uint8_t *found, uint64_t *launches) {
     if (!n) return cudaSuccess;
     lookup_kernel<<<grid_for(n), TPB, 0, st>>>(tv, keys, n, rec, found);
-    ++*launches;
-    return cudaGetLastError();
-}
-
-// ---- stats / export ----------------------------------------------------------------------------------
-
-// logical record of an occupied, non-placeholder slot
-__device__ __forceinline__ void slot_logical(const TableView &tv, const Slot &s, Rec32 &r) {
-    unsigned long long c = s.cov, f[4], b[4];
-#pragma unroll
-    for (int w = 0; w < 4; ++w) { f[w] = (s.fw >> (16 * w)) & 0xFFFF; b[w] = (s.bw >> (16 * w)) & 0xFFFF; }
-    if (s.flags & F_HAS_SIDE) {
-        const SideSlot *q = side_find(tv, s.tag - 1);
-        if (q) {
-            c += q->cov;
-#pragma unroll
-            for (int w = 0; w < 4; ++w) { f[w] += q->fw[w]; b[w] += q->bw[w]; }
-        }
-    }
-#pragma unroll
-    for (int w = 0; w < 4; ++w) { r.fw[w] = clamp32(f[w]); r.bw[w] = clamp32(b[w]); }
-    r.cov = clamp32(c);
-}
-
-// DBG::summary src/graph-builder.cpp:240-257 over the 8-bit side of the database
-__global__ void __launch_bounds__(TPB, CTAS_PER_SM)
-stats_kernel(TableView tv, DevStats *ds, unsigned long long *hist, unsigned long long *big, unsigned long long big_cap) {
-    __shared__ unsigned long long sh[4];
-    if (threadIdx.x < 4) sh[threadIdx.x] = 0;
-    __syncthreads();
-    unsigned long long total = 0, uniq = 0, distinct = 0, edges = 0;
-    const uint64_t stride = (uint64_t)gridDim.x * TPB;
-    for (uint64_t i = (uint64_t)blockIdx.x * TPB + threadIdx.x; i < tv.cap; i += stride) {
-        const Slot s = tv.T[i];
-        if (s.tag == 0 || (s.flags & F_PLACEHOLDER)) continue;          // :246-247
-        Rec32 r; slot_logical(tv, s, r);
-        uniq += r.cov == 1;
-#pragma unroll
-        for (int w = 0; w < 4; ++w) edges += (r.fw[w] > 0 || r.bw[w] > 0);   // precedence quirk :253-254
-        ++distinct;
-        if (r.cov < (uint32_t)HIST_BINS) { atomicAdd(&hist[r.cov], 1ULL); total += r.cov; }
-        else {
-            const unsigned long long j = atomicAdd(&ds->big_n, 1ULL);
-            if (j < big_cap) big[j] = r.cov;
-        }
-    }
-    // per-thread totals can exceed 32 bits: add them directly, one atomic per warp
-    for (int o = 16; o; o >>= 1) total += __shfl_xor_sync(0xffffffffu, total, o);
-    if ((threadIdx.x & 31) == 0 && total) atomicAdd(&ds->total, total);
-    block_add(uniq, &ds->unique, &sh[1]);
-    block_add(distinct, &ds->distinct, &sh[2]);
-    block_add(edges, &ds->edges, &sh[3]);
-}
-
-__global__ void __launch_bounds__(TPB, CTAS_PER_SM)
-export_kernel(TableView tv, XRec *out, unsigned long long cap, unsigned long long *n_out) {
-    const uint64_t stride = (uint64_t)gridDim.x * TPB;
-    const unsigned lane = threadIdx.x & 31;
-    const uint64_t rounds = (tv.cap + stride - 1) / stride;
-    for (uint64_t r = 0; r < rounds; ++r) {
-        const uint64_t i = r * stride + (uint64_t)blockIdx.x * TPB + threadIdx.x;
-        Slot s; s.tag = 0;
-        if (i < tv.cap) s = tv.T[i];
-        const bool have = s.tag != 0;
-        const unsigned m = __ballot_sync(0xffffffffu, have);
-        if (!m) continue;
-        unsigned long long base = 0;
-        if (lane == 0) base = atomicAdd(n_out, (unsigned long long)__popc(m));
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (!have) continue;
-        const unsigned long long j = base + __popc(m & ((1u << lane) - 1));
-        if (j >= cap) continue;
-        XRec x; x.key = s.tag - 1; x.flags = s.flags;
-        if (s.flags & F_PLACEHOLDER) {
-#pragma unroll
-            for (int w = 0; w < 4; ++w) { x.r.fw[w] = (uint32_t)(s.fw >> (16 * w)) & 0xFFFF; x.r.bw[w] = (uint32_t)(s.bw >> (16 * w)) & 0xFFFF; }
-            x.r.cov = s.cov;
-        } else {
-            slot_logical(tv, s, x.r);
-        }
-        out[j] = x;
-    }
-}
-
-cudaError_t launch_stats(cudaStream_t st, const TableView &tv, DevStats *ds, unsigned long long *hist,
-                         unsigned long long *big, unsigned long long big_cap, uint64_t *launches) {
-    stats_kernel<<<grid_for(tv.cap), TPB, 0, st>>>(tv, ds, hist, big, big_cap);
-    ++*launches;
-    return cudaGetLastError();
-}
-
-cudaError_t launch_export(cudaStream_t st, const TableView &tv, XRec *out, unsigned long long cap,
-                          unsigned long long *n_out, uint64_t *launches) {
-    export_kernel<<<grid_for(tv.cap), TPB, 0, st>>>(tv, out, cap, n_out);
-    ++*launches;
-    return cudaGetLastError();
-}
-
-// ---- grow / load / union -----------------------------------------------------------------------------
-
-// move every occupied slot of the old table into tv.T (keys are unique: claim, then plain stores)
-__global__ void __launch_bounds__(TPB, CTAS_PER_SM)
-rehash_kernel(TableView tv, const Slot *__restrict__ from, unsigned long long from_cap) {
-    const uint64_t stride = (uint64_t)gridDim.x * TPB;
-    for (uint64_t i = (uint64_t)blockIdx.x * TPB + threadIdx.x; i < from_cap; i += stride) {
-        const Slot s = from[i];
-        if (s.tag == 0) continue;
-        bool is_new; Slot *d = find_or_claim(tv, s.tag - 1, &is_new);
-        if (!d) continue;
-        d->cov = s.cov; d->flags = s.flags; d->fw = s.fw; d->bw = s.bw;
-    }
-}
-
-__global__ void __launch_bounds__(TPB, CTAS_PER_SM)
-side_rehash_kernel(TableView tv, const SideSlot *__restrict__ from, unsigned long long from_cap) {
-    const uint64_t stride = (uint64_t)gridDim.x * TPB;
-    for (uint64_t i = (uint64_t)blockIdx.x * TPB + threadIdx.x; i < from_cap; i += stride) {
-        const SideSlot s = from[i];
-        if (s.tag == 0) continue;
-        SideSlot *d = side_find_or_claim(tv, s.tag - 1);
-        if (!d) continue;
-        d->kind = s.kind; d->cov = s.cov;
-#pragma unroll
-        for (int w = 0; w < 4; ++w) { d->fw[w] = s.fw[w]; d->bw[w] = s.bw[w]; }
-    }
-}
-
-__device__ __forceinline__ unsigned long long pack16(const uint32_t v[4]) {
-    return (unsigned long long)v[0] | ((unsigned long long)v[1] << 16) | ((unsigned long long)v[2] << 32) |
-           ((unsigned long long)v[3] << 48);
-}
-
-// raw entries of an 8-bit map (Kmap::loadMap kmer.h:592-602): unique keys, values <= 255
-__global__ void __launch_bounds__(TPB, CTAS_PER_SM)
-put_kernel(TableView tv, const XRec *__restrict__ in, uint64_t n) {
-    __shared__ unsigned long long sh[1];
-    if (threadIdx.x == 0) sh[0] = 0;
-    __syncthreads();
-    unsigned long long fresh = 0;
-    const uint64_t stride = (uint64_t)gridDim.x * TPB;
-    for (uint64_t i = (uint64_t)blockIdx.x * TPB + threadIdx.x; i < n; i += stride) {
-        const XRec x = in[i];
-        bool is_new; Slot *d = find_or_claim(tv, x.key, &is_new);
-        if (!d) continue;
-        fresh += is_new;
-        d->cov = x.r.cov; d->flags = x.flags; d->fw = pack16(x.r.fw); d->bw = pack16(x.r.bw);
-    }
-    block_add(fresh, &tv.occ[0], &sh[0]);
-}
-
-// exact union: add the logical record x.r of a key (keys unique within one launch)
-__global__ void __launch_bounds__(TPB, CTAS_PER_SM)
-add_records_kernel(TableView tv, const XRec *__restrict__ in, uint64_t n) {
-    __shared__ unsigned long long sh[1];
-    if (threadIdx.x == 0) sh[0] = 0;
-    __syncthreads();
-    unsigned long long fresh = 0;
-    const uint64_t stride = (uint64_t)gridDim.x * TPB;
-    for (uint64_t i = (uint64_t)blockIdx.x * TPB + threadIdx.x; i < n; i += stride) {
-        const XRec x = in[i];
-        bool is_new; Slot *d = find_or_claim(tv, x.key, &is_new);
-        if (!d) continue;
-        fresh += is_new;
-        // the slot takes what fits its 16-bit lanes, the side table the rest
-        const uint32_t room = d->cov >= KQ_LIMIT ? 0u : KQ_LIMIT - d->cov;
-        const uint32_t m = min(x.r.cov, room);
-        uint32_t fm[4], bm[4]; bool spill = m < x.r.cov;
-#pragma unroll
-        for (int w = 0; w < 4; ++w) {
-            fm[w] = min(x.r.fw[w], m); bm[w] = min(x.r.bw[w], m);
-            spill |= fm[w] < x.r.fw[w] || bm[w] < x.r.bw[w];
-        }
-        d->cov += m; d->fw += pack16(fm); d->bw += pack16(bm);
-        if (spill) {
-            SideSlot *q = side_find_or_claim(tv, x.key);
-            if (!q) continue;
-            q->kind |= KQ_SIDE_REMAINDER;
-            q->cov += x.r.cov - m;
-#pragma unroll
-            for (int w = 0; w < 4; ++w) { q->fw[w] += x.r.fw[w] - fm[w]; q->bw[w] += x.r.bw[w] - bm[w]; }
-            d->flags |= F_HAS_SIDE;
-        }
-    }
-    block_add(fresh, &tv.occ[0], &sh[0]);
-}
-
-// DBG::mergeSubMaps src/graph-builder.cpp:353-432: one (key, a) of a later database's 8-bit map
-// against the merged table (T = "submap2", S/KQ_SIDE_MAP32 = maps32[m]).  Keys are unique within
-// one launch and launches follow the database order, so the result is the reference's.
-__global__ void __launch_bounds__(TPB, CTAS_PER_SM)
-merge_ref_kernel(TableView tv, const XRec *__restrict__ in, uint64_t n) {
-    __shared__ unsigned long long sh[1];
-    if (threadIdx.x == 0) sh[0] = 0;
-    __syncthreads();
-    unsigned long long fresh = 0;
-    const uint64_t stride = (uint64_t)gridDim.x * TPB;
-    for (uint64_t i = (uint64_t)blockIdx.x * TPB + threadIdx.x; i < n; i += stride) {
-        const XRec a = in[i];
-        if (a.r.cov == 255) continue;                                        // :367-368
-        SideSlot *q = side_find(tv, a.key);
-        bool overflow = false;
-        Slot *d = nullptr;
-        if (q && (q->kind & KQ_SIDE_MAP32)) {                                // :370-372
-            overflow = true;
-        } else {
-            bool is_new; d = find_or_claim(tv, a.key, &is_new);
-            if (!d) continue;
-            if (is_new) {                                                    // :375-377
-                ++fresh;
-                d->cov = a.r.cov; d->flags = 0; d->fw = pack16(a.r.fw); d->bw = pack16(a.r.bw);
-            } else {
-                uint32_t bf[4], bb[4];
-#pragma unroll
-                for (int w = 0; w < 4; ++w) { bf[w] = (uint32_t)(d->fw >> (16 * w)) & 0xFFFF; bb[w] = (uint32_t)(d->bw >> (16 * w)) & 0xFFFF; }
-                if (255 - (int)d->cov <= (int)a.r.cov) overflow = true;      // :382-383
-#pragma unroll
-                for (int w = 0; w < 4; ++w)                                  // :385-391
-                    if (255 - (int)bf[w] <= (int)a.r.fw[w] || 255 - (int)bb[w] <= (int)a.r.bw[w]) overflow = true;
-                if (!overflow) {                                             // :393-400
-                    d->cov += a.r.cov; d->fw += pack16(a.r.fw); d->bw += pack16(a.r.bw);
-                } else {                                                     // :404-412 first spill of this key
-                    q = side_find_or_claim(tv, a.key);
-                    if (!q) continue;
-                    q->kind |= KQ_SIDE_MAP32;
-                    q->cov = d->cov;
-#pragma unroll
-                    for (int w = 0; w < 4; ++w) { q->fw[w] = bf[w]; q->bw[w] = bb[w]; }
-                    d->cov = 255; d->flags |= F_PLACEHOLDER;
-                }
-            }
-        }
-        if (overflow) {                                                      // :414-427 (clamped on read)
-            q->cov += a.r.cov;
-#pragma unroll
-            for (int w = 0; w < 4; ++w) { q->fw[w] += a.r.fw[w]; q->bw[w] += a.r.bw[w]; }
-        }
-    }
-    block_add(fresh, &tv.occ[0], &sh[0]);
-}
-
-cudaError_t launch_rehash(cudaStream_t st, const TableView &tv, const Slot *from, unsigned long long from_cap,
-                          uint64_t *launches) {
-    rehash_kernel<<<grid_for(from_cap), TPB, 0, st>>>(tv, from, from_cap);
-    ++*launches;
-    return cudaGetLastError();
-}
-cudaError_t launch_side_rehash(cudaStream_t st, const TableView &tv, const SideSlot *from,
-                               unsigned long long from_cap, uint64_t *launches) {
-    side_rehash_kernel<<<grid_for(from_cap), TPB, 0, st>>>(tv, from, from_cap);
-    ++*launches;
-    return cudaGetLastError();
-}
-cudaError_t launch_put(cudaStream_t st, const TableView &tv, const XRec *in, uint64_t n, uint64_t *launches) {
-    if (!n) return cudaSuccess;
-    put_kernel<<<grid_for(n), TPB, 0, st>>>(tv, in, n);
-    ++*launches;
-    return cudaGetLastError();
-}
-cudaError_t launch_add_records(cudaStream_t st, const TableView &tv, const XRec *in, uint64_t n, uint64_t *launches) {
-    if (!n) return cudaSuccess;
-    add_records_kernel<<<grid_for(n), TPB, 0, st>>>(tv, in, n);
-    ++*launches;
-    return cudaGetLastError();
-}
-cudaError_t launch_merge_ref(cudaStream_t st, const TableView &tv, const XRec *in, uint64_t n, uint64_t *launches) {
-    if (!n) return cudaSuccess;
-    merge_ref_kernel<<<grid_for(n), TPB, 0, st>>>(tv, in, n);
     ++*launches;
     return cudaGetLastError();
 }

@@ -1,4 +1,4 @@
-// kq_kernels.h -- host-callable launchers of the sm_100a kernels (kq_kernels.cu).
+// kq_kernels.h -- host-callable launchers of the sm_100a kernels (kq_kernels.cu, kq_table_kernels.cu).
 // Every launcher enqueues on `st`, returns the cudaError_t of the launch and adds the
 // number of kernels it launched to *launches.
 #pragma once
@@ -9,6 +9,7 @@
 namespace kq {
 
 // record as moved between host and device by load / save / union (48 bytes)
+constexpr uint32_t F_PLACEHOLDER = 2u;       // XRec.flags: the 8-bit map entry is a cov == 255 placeholder
 struct XRec { uint64_t key; Rec32 r; uint32_t flags; };
 static_assert(sizeof(XRec) == 48, "XRec layout");
 
@@ -19,41 +20,72 @@ struct DevStats {
     unsigned long long big_n;                            // entries with cov >= HIST_BINS appended to big[]
 };
 
+// (key, edgeBit) tuples in device memory: one 64-bit word (key << 8 | edge) while 2k + 8 <= 64,
+// otherwise two words {key, edge}.
+__host__ __device__ inline int tuple_words(int k) { return 2 * k + 8 <= 64 ? 1 : 2; }
+
+// where the count pipeline takes its k-mer instances from
+struct Source {
+    const uint64_t *bases, *invalid;   // packed sequence (tuples == nullptr) ...
+    uint64_t pos0, npos;               // ... k-mer start positions [pos0, pos0 + npos)
+    const uint64_t *tuples;            // or tuples already extracted (multi-GPU: received from peers)
+    const unsigned long long *ntuples; // device pointer to their number
+    uint64_t ntuples_max;              // host-side upper bound of *ntuples (grid sizing)
+};
+
 struct RouteArgs {           // destination of extracted tuples (multi-GPU count)
-    uint64_t *keys; uint8_t *edges; unsigned long long cap_per_rank; unsigned long long *counts;
-    int nranks, my_rank, shift;   // owner = (key & 127) >> shift; my_rank < 0: route everything
+    uint64_t *tuples; unsigned long long cap_per_rank; unsigned long long *counts;
+    int nranks, shift;       // owner = (key & 127) >> shift
 };
 
 int sm_count();   // multiprocessors of the current device (cached)
+// shared memory the scatter kernel needs for `nslices` bins of `cap` tuples; 0 if it cannot fit
+size_t scatter_smem_bytes(unsigned long long nslices, int cap, int tw);
+int scatter_pick_cap(unsigned long long nslices, int tw);       // largest of 32/16/8 that fits, 0 = none
 
-// A2+A3 fused: positions [pos0,pos0+npos) of a packed sequence -> table (owned keys only)
-cudaError_t launch_count_packed(cudaStream_t st, const TableView &tv, const uint64_t *B, const uint64_t *M,
-                                uint64_t pos0, uint64_t npos, unsigned long long *instances, uint64_t *launches);
-// A2 with routing: owned tuples are inserted in place, the others appended per owner rank
-cudaError_t launch_extract_route(cudaStream_t st, const TableView &tv, const uint64_t *B, const uint64_t *M,
-                                 uint64_t pos0, uint64_t npos, RouteArgs ra, unsigned long long *instances,
+// ---- count pipeline (rows A2 + A3) -------------------------------------------------------------------
+// single-slice tables / small inputs: fused extract + insert
+cudaError_t launch_count_direct(cudaStream_t st, const TableView &tv, const Source &src,
+                                unsigned long long *instances, uint64_t *ovf, unsigned long long ovf_cap,
+                                unsigned long long *ovf_n, uint64_t *launches);
+// 1. tuples per slice -> hist[nslices]
+cudaError_t launch_slice_hist(cudaStream_t st, const TableView &tv, const Source &src, unsigned long long *hist,
+                              uint64_t *launches);
+// 2. exclusive scan: cursor[p] = first tuple index of slice p; *total = number of tuples; *instances += total
+cudaError_t launch_slice_offsets(cudaStream_t st, unsigned long long nslices, const unsigned long long *hist,
+                                 unsigned long long *cursor, unsigned long long *total, unsigned long long *instances,
                                  uint64_t *launches);
-// A3: (key, edgeBit) tuples -> table
-cudaError_t launch_insert_tuples(cudaStream_t st, const TableView &tv, const uint64_t *keys, const uint8_t *edges,
-                                 uint64_t n, unsigned long long *instances, uint64_t *launches);
-// A5: positions [c0, c0+n) of a segment with kcount windows; the packed arrays start at segment
+// 3. scatter tuples into slice order (out holds *total tuples afterwards)
+cudaError_t launch_slice_scatter(cudaStream_t st, const TableView &tv, const Source &src, uint64_t *out,
+                                 unsigned long long *cursor, int cap, uint64_t *launches);
+// 4. insert slice-ordered tuples; tuples whose slice is full are appended to ovf (capacity ovf_cap,
+//    ovf_n counts every failure, also those that did not fit)
+cudaError_t launch_insert_tuples(cudaStream_t st, const TableView &tv, const uint64_t *tuples,
+                                 const unsigned long long *n, uint64_t n_max, uint64_t *ovf,
+                                 unsigned long long ovf_cap, unsigned long long *ovf_n, uint64_t *launches);
+// multi-GPU: extract every valid window and append its tuple to the slab of its owner rank
+cudaError_t launch_extract_route(cudaStream_t st, const TableView &tv, const Source &src, RouteArgs ra,
+                                 uint64_t *launches);
+
+// ---- validate / lookups (rows A5, host consumers) ------------------------------------------------------
+// positions [c0, c0+n) of a segment with kcount windows; the packed arrays start at segment
 // position `base0` (so bit position of c is c-base0); out is indexed by c-c0.
 cudaError_t launch_validate(cudaStream_t st, const TableView &tv, const uint64_t *B, const uint64_t *M,
                             uint64_t base0, uint64_t c0, uint64_t n, uint64_t kcount, uint32_t cutoff,
                             Base *out, unsigned long long *acc3, uint64_t *launches);
-// point lookups (host consumers)
 cudaError_t launch_lookup(cudaStream_t st, const TableView &tv, const uint64_t *keys, uint64_t n, Rec32 *rec,
                           uint8_t *found, uint64_t *launches);
-// A3s: scan T
+
+// ---- table maintenance (rows A3s, A4, A8) ----------------------------------------------------------------
 cudaError_t launch_stats(cudaStream_t st, const TableView &tv, DevStats *ds, unsigned long long *hist,
                          unsigned long long *big, unsigned long long big_cap, uint64_t *launches);
-// export occupied slots (logical record, or raw lanes + F_PLACEHOLDER) in arbitrary order
+// export occupied slots (logical record, or F_PLACEHOLDER) in arbitrary order
 cudaError_t launch_export(cudaStream_t st, const TableView &tv, XRec *out, unsigned long long cap,
                           unsigned long long *n_out, uint64_t *launches);
-// move every slot of `from` into tv (grow)
+// move every slot of the old table into tv (grow)
 cudaError_t launch_rehash(cudaStream_t st, const TableView &tv, const Slot *from, unsigned long long from_cap,
                           uint64_t *launches);
-cudaError_t launch_side_rehash(cudaStream_t st, const TableView &tv, const SideSlot *from,
+cudaError_t launch_side_rehash(cudaStream_t st, const TableView &tv, int which, const SideSlot *from,
                                unsigned long long from_cap, uint64_t *launches);
 // load: unique keys, raw 8-bit-map entries (flags carry F_PLACEHOLDER) -> T
 cudaError_t launch_put(cudaStream_t st, const TableView &tv, const XRec *in, uint64_t n, uint64_t *launches);

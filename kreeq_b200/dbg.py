@@ -68,6 +68,9 @@ class DBG:
         check(lib().kq_clear(self._h), self._h)
         self.tot_missing = self.tot_kcount = self.tot_edge_missing = 0
 
+    def set_flush_positions(self, positions):
+        check(lib().kq_set_flush_positions(self._h, int(positions)), self._h)
+
     def reserve(self, extra_distinct):
         check(lib().kq_reserve(self._h, int(extra_distinct)), self._h)
 

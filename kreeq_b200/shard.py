@@ -30,33 +30,48 @@ def exchange_counts(send_counts, group=None):
     return torch.stack(rows)[:, rank].contiguous()
 
 
-def exchange_tuples(send_keys, send_edges, send_counts_host, recv_counts_host, recv_keys, recv_edges, group=None):
+def exchange_tuples(send, send_counts_host, recv_counts_host, recv, group=None):
     """Route tuples to their owners: one grouped send/recv per peer (ncclGroupStart ... ncclSend/ncclRecv
     ... ncclGroupEnd under NCCL; plain point-to-point under gloo in the CPU tests).
 
-    send_keys [nranks, cap] int64 / send_edges [nranks, cap] uint8 hold, for destination r, the first
-    send_counts_host[r] tuples of slab r.  Received tuples are packed back to back into recv_keys /
-    recv_edges (1-D, large enough); returns the number received."""
+    send [nranks, cap, tuple_bytes] uint8 holds, for destination r, the first send_counts_host[r] tuples of
+    slab r (the layout kq_dev_extract_route writes).  Received tuples are packed back to back into
+    recv [N, tuple_bytes] (large enough); returns the number received."""
     n = len(send_counts_host)
     me = dist.get_rank(group)
     offs = np.concatenate(([0], np.cumsum(recv_counts_host))).astype(np.int64)
     ops = []
     for r in range(n):
         sc, rc = int(send_counts_host[r]), int(recv_counts_host[r])
-        dst_k, dst_e = recv_keys[int(offs[r]):int(offs[r + 1])], recv_edges[int(offs[r]):int(offs[r + 1])]
+        dst = recv[int(offs[r]):int(offs[r + 1])]
         if r == me:
-            dst_k.copy_(send_keys[r, :sc]); dst_e.copy_(send_edges[r, :sc])
+            dst.copy_(send[r, :sc])
             continue
         if sc:
-            ops.append(dist.P2POp(dist.isend, send_keys[r, :sc], r, group))
-            ops.append(dist.P2POp(dist.isend, send_edges[r, :sc], r, group))
+            ops.append(dist.P2POp(dist.isend, send[r, :sc], r, group))
         if rc:
-            ops.append(dist.P2POp(dist.irecv, dst_k, r, group))
-            ops.append(dist.P2POp(dist.irecv, dst_e, r, group))
+            ops.append(dist.P2POp(dist.irecv, dst, r, group))
     if ops:
         for w in dist.batch_isend_irecv(ops):
             w.wait()
     return int(offs[-1])
+
+
+def pack_tuples(keys, edges, k):
+    """numpy (keys u64, edges u8) -> [n, tuple_bytes] uint8 in the device tuple format (kq_tuple_bytes)."""
+    keys = np.asarray(keys, dtype=np.uint64); edges = np.asarray(edges, dtype=np.uint64)
+    if 2 * k + 8 <= 64:
+        return ((keys << np.uint64(8)) | edges).view(np.uint8).reshape(-1, 8)
+    return np.stack((keys, edges), axis=1).view(np.uint8).reshape(-1, 16)
+
+
+def unpack_tuples(raw, k):
+    raw = np.ascontiguousarray(raw)
+    if 2 * k + 8 <= 64:
+        w = raw.view(np.uint64).reshape(-1)
+        return w >> np.uint64(8), (w & np.uint64(255)).astype(np.uint8)
+    w = raw.view(np.uint64).reshape(-1, 2)
+    return w[:, 0].copy(), w[:, 1].astype(np.uint8)
 
 
 class RoutedCounter:
@@ -65,13 +80,12 @@ class RoutedCounter:
 
     def __init__(self, dbg, rank, nranks, round_pos, device, slack=1.25):
         self.g, self.rank, self.n, self.round_pos = dbg, rank, nranks, int(round_pos)
+        self.tb = lib().kq_tuple_bytes(dbg.handle)
         self.cap = int(self.round_pos / nranks * slack) + 1024          # tuples per destination per round
-        self.send_keys = torch.empty((nranks, self.cap), dtype=torch.int64, device=device)
-        self.send_edges = torch.empty((nranks, self.cap), dtype=torch.uint8, device=device)
+        self.send = torch.empty((nranks, self.cap, self.tb), dtype=torch.uint8, device=device)
         self.counts = torch.zeros(nranks, dtype=torch.int64, device=device)
         rcap = int(self.round_pos * slack) + 1024 * nranks
-        self.recv_keys = torch.empty(rcap, dtype=torch.int64, device=device)
-        self.recv_edges = torch.empty(rcap, dtype=torch.uint8, device=device)
+        self.recv = torch.empty((rcap, self.tb), dtype=torch.uint8, device=device)
         self.a2a_bytes = 0
 
     def count(self, d_bases, d_invalid, length):
@@ -85,15 +99,13 @@ class RoutedCounter:
             npos = min(self.round_pos, total - p0)
             self.counts.zero_()
             check(L.kq_dev_extract_route(g.handle, C.c_void_p(d_bases.data_ptr()), C.c_void_p(d_invalid.data_ptr()),
-                                         length, p0, npos, C.c_void_p(self.send_keys.data_ptr()),
-                                         C.c_void_p(self.send_edges.data_ptr()), self.cap,
+                                         length, p0, npos, C.c_void_p(self.send.data_ptr()), self.cap,
                                          C.c_void_p(self.counts.data_ptr())), g.handle)
             recv_counts = exchange_counts(self.counts)
             sc = self.counts.cpu().numpy()
             rc = recv_counts.cpu().numpy()
-            if sc.max() > self.cap or rc.sum() > self.recv_keys.numel():
+            if sc.max() > self.cap or rc.sum() > self.recv.shape[0]:
                 raise RuntimeError("route buffers too small: %s > %d" % (sc, self.cap))
-            nrecv = exchange_tuples(self.send_keys, self.send_edges, sc, rc, self.recv_keys, self.recv_edges)
-            self.a2a_bytes += int(sc.sum()) * 9
-            check(L.kq_dev_insert_tuples(g.handle, C.c_void_p(self.recv_keys.data_ptr()),
-                                         C.c_void_p(self.recv_edges.data_ptr()), nrecv), g.handle)
+            nrecv = exchange_tuples(self.send, sc, rc, self.recv)
+            self.a2a_bytes += (int(sc.sum()) - int(sc[self.rank])) * self.tb
+            check(L.kq_dev_insert_tuples(g.handle, C.c_void_p(self.recv.data_ptr()), nrecv), g.handle)

@@ -187,3 +187,108 @@ def test_find_lookup_batch(mods):
         assert rec[:500].tobytes() == rr[:500].tobytes()
         present = np.isin(q[500:], rk)
         assert np.array_equal(found[500:], present)
+
+
+@pytest.mark.parametrize("k,hint", [(21, 6_000_000), (31, 6_000_000), (21, 0)])
+def test_partitioned_pipeline_multi_slice(mods, k, hint):
+    """Table of several 32 MiB slices: histogram -> scatter -> L2-resident insert (8- and 16-byte tuples),
+    with a size hint (one big batch) and without (planned batches + growth)."""
+    kb, ko = mods
+    rng = np.random.default_rng(51 + k)
+    genome = random_genome(rng, 2_500_000)
+    batches = [sample_reads(rng, genome, 50_000, 150, err=0.01) for _ in range(2)]
+    ref = ko.Table(k); n_ref = sum(ref.count_batch(b) for b in batches)
+    with kb.DBG(k=k, expected_distinct=hint) as g:
+        for b in batches:
+            g.traverseInReads(b)
+        g.finalize()
+        assert g.instances() == n_ref
+        assert_same_records(g.export(), ref.export())
+        assert g.stats() == ref.stats()
+        out = g.evaluateSegment(genome.tobytes()[:1_000_000])
+        rc, rout, racc = ref.validate_segment(genome.tobytes()[:1_000_000])
+        assert out.tobytes() == rout.tobytes()
+        assert (g.tot_missing, g.tot_kcount, g.tot_edge_missing) == racc
+
+
+def test_wrong_size_hint_overflow_list(mods):
+    """A size hint that is too small: slices fill up, the tuples that found no room are kept, the
+    table is doubled and they are inserted afterwards -- nothing may be lost or counted twice."""
+    kb, ko = mods
+    k = 21
+    rng = np.random.default_rng(61)
+    genome = random_genome(rng, 2_600_000)
+    batch = sample_reads(rng, genome, 70_000, 150, err=0.01)
+    ref = ko.Table(k); n_ref = ref.count_batch(batch)
+    with kb.DBG(k=k, expected_distinct=2_000_000) as g:           # ~4.4 M distinct arrive
+        g.traverseInReads(batch); g.finalize()
+        assert g.instances() == n_ref
+        assert_same_records(g.export(), ref.export())
+    with kb.DBG(k=k, expected_distinct=300_000) as g:             # single-slice table, fused kernel
+        g.traverseInReads(batch[:151 * 20000]); g.finalize()
+        ref2 = ko.Table(k); ref2.count_batch(batch[:151 * 20000])
+        assert_same_records(g.export(), ref2.export())
+
+
+def test_small_pushes_accumulate(mods):
+    """Many small pushes join the pending stream (64-base aligned, invalid separators) and are counted
+    together; a low flush threshold forces several pipeline runs."""
+    kb, ko = mods
+    k = 21
+    rng = np.random.default_rng(71)
+    genome = random_genome(rng, 50_000)
+    ref = ko.Table(k)
+    with kb.DBG(k=k) as g:
+        g.set_flush_positions(200_000)
+        n_ref = 0
+        for i in range(40):
+            n_reads = int(rng.integers(1, 300)); L = int(rng.integers(21, 200))
+            b = sample_reads(rng, genome, n_reads, L, err=0.01, n_rate=0.001)
+            if i % 7 == 0:
+                b = b[:-1]                                          # batch without the trailing 'N'
+            if i % 5 == 0:
+                b = b[:(len(b) // 64) * 64] if len(b) >= 64 else b  # length a multiple of 64
+            n_ref += ref.count_batch(b)
+            g.traverseInReads(b)
+        g.finalize()
+        assert g.instances() == n_ref
+        assert_same_records(g.export(), ref.export())
+        assert g.stats() == ref.stats()
+
+
+def test_routed_tuples_two_shards_one_gpu(mods):
+    """kq_dev_extract_route -> (exchange stand-in) -> kq_dev_insert_tuples with two sharded handles."""
+    import ctypes as C
+    import torch
+    kb, ko = mods
+    from kreeq_b200._lib import check, lib
+    L = lib()
+    for k in (21, 31):
+        rng = np.random.default_rng(81 + k)
+        genome = random_genome(rng, 200_000)
+        batch = sample_reads(rng, genome, 8000, 150, err=0.01)
+        ref = ko.Table(k); ref.count_batch(batch)
+        rk, rr = ref.export()
+        bases, inv = kb.pack_host(batch)
+        d_b = torch.from_numpy(bases.view(np.int64)).cuda(); d_i = torch.from_numpy(inv.view(np.int64)).cuda()
+        npos = len(batch) - k + 1
+        nr = 2
+        gs = [kb.DBG(k=k, rank=r, nranks=nr) for r in range(nr)]
+        tb = L.kq_tuple_bytes(gs[0].handle)
+        assert tb == (8 if k <= 28 else 16)
+        cap = npos
+        slabs = torch.zeros((nr, cap, tb), dtype=torch.uint8, device="cuda")
+        counts = torch.zeros(nr, dtype=torch.int64, device="cuda")
+        check(L.kq_dev_extract_route(gs[0].handle, C.c_void_p(d_b.data_ptr()), C.c_void_p(d_i.data_ptr()), len(batch), 0, npos,
+                                     C.c_void_p(slabs.data_ptr()), cap, C.c_void_p(counts.data_ptr())), gs[0].handle)
+        gs[0].sync()
+        cnt = counts.cpu().numpy()
+        ks, rs = [], []
+        for r in range(nr):
+            check(L.kq_dev_insert_tuples(gs[r].handle, C.c_void_p(slabs[r].data_ptr()), int(cnt[r])), gs[r].handle)
+            gs[r].finalize()
+            assert gs[r].instances() == cnt[r]
+            kk, rec = gs[r].export(); ks.append(kk); rs.append(rec)
+            gs[r].close()
+        kk = np.concatenate(ks); rec = np.concatenate(rs); o = np.argsort(kk)
+        assert np.array_equal(kk[o], rk) and rec[o].tobytes() == rr.tobytes()

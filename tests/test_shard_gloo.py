@@ -36,17 +36,18 @@ def _worker(rank, world, port, out_dir):
     keys, edges = ko.extract(k, batches[rank])
     owner = shard.owner_of(keys, world)
     cap = int(max(np.bincount(owner, minlength=world))) + 8
-    send_k = torch.zeros((world, cap), dtype=torch.int64); send_e = torch.zeros((world, cap), dtype=torch.uint8)
+    raw = shard.pack_tuples(keys, edges, k)                       # the layout kq_dev_extract_route writes
+    send = torch.zeros((world, cap, raw.shape[1]), dtype=torch.uint8)
     counts = torch.zeros(world, dtype=torch.int64)
     for r in range(world):
         sel = owner == r
         n = int(sel.sum()); counts[r] = n
-        send_k[r, :n] = torch.from_numpy(keys[sel].view(np.int64)); send_e[r, :n] = torch.from_numpy(edges[sel])
+        send[r, :n] = torch.from_numpy(raw[sel])
     recv_counts = shard.exchange_counts(counts)
-    recv_k = torch.zeros(int(recv_counts.sum()) + 4, dtype=torch.int64); recv_e = torch.zeros(recv_k.numel(), dtype=torch.uint8)
-    n = shard.exchange_tuples(send_k, send_e, counts.numpy(), recv_counts.numpy(), recv_k, recv_e)
+    recv = torch.zeros((int(recv_counts.sum()) + 4, raw.shape[1]), dtype=torch.uint8)
+    n = shard.exchange_tuples(send, counts.numpy(), recv_counts.numpy(), recv)
     assert n == int(recv_counts.sum())
-    rk = recv_k[:n].numpy().view(np.uint64); re_ = recv_e[:n].numpy()
+    rk, re_ = shard.unpack_tuples(recv[:n].numpy(), k)
     assert np.all(shard.owner_of(rk, world) == rank)
     t = ko.Table(k)
     t.insert_tuples(rk, re_)

@@ -133,6 +133,40 @@ __global__ void __launch_bounds__(256) window(Slot16 *T, uint64_t slice_slots, u
     if (acc == 0x123456789abcdefULL) *sink = acc;
 }
 
+// faithful insert: keys drawn from 0.47 * slice_slots distinct keys per slice, linear probing, claim of an
+// empty slot by CLAIM = 0: one 128-bit CAS, 1: 64-bit CAS on the tag then 64-bit CAS on the counters;
+// STREAM: also stream an 8-byte tuple per op (ld.cs) like the real kernel
+template <int CLAIM, bool STREAM>
+__global__ void __launch_bounds__(256) window_insert(Slot16 *T, uint64_t slice_slots, uint64_t nslices, uint64_t nops,
+                                                     const uint64_t *tuples, unsigned long long *sink) {
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    const uint64_t per = (nops + nslices - 1) / nslices, mask = slice_slots - 1, distinct = slice_slots * 47 / 100;
+    unsigned long long acc = 0;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nops; i += stride) {
+        const uint64_t sl = i / per;
+        uint64_t r = mix64(i);
+        if (STREAM) r ^= __ldcs(tuples + i);
+        const uint64_t keyid = __umul64hi(r, distinct), tag = (sl << 32 | keyid) + 1;
+        Slot16 *base = T + sl * slice_slots;
+        uint64_t j = mix64(tag) & mask;
+        for (int n = 0; n < 4096; ++n) {
+            Slot16 *p = base + j;
+            uint4 v = ld16(p);
+            unsigned long long t = ((unsigned long long)v.y << 32) | v.x, c = ((unsigned long long)v.w << 32) | v.z;
+            if (t == 0) {
+                if (CLAIM == 0) { unsigned long long olo, ohi; cas128(p, 0, 0, tag, 1, olo, ohi); if (olo == 0) break; t = olo; c = ohi; }
+                else { const unsigned long long o = atomicCAS(&p->tag, 0ULL, tag); t = o == 0 ? tag : o; c = 0; }
+            }
+            if (t == tag) {
+                for (int q = 0; q < 64; ++q) { const unsigned long long o = atomicCAS(&p->cnt, c, c + 1); if (o == c) break; c = o; }
+                acc += c; break;
+            }
+            j = (j + 1) & mask;
+        }
+    }
+    if (acc == 0x123456789abcdefULL) *sink = acc;
+}
+
 // each warp stores CH bytes (coalesced) at a random CH-aligned offset: the scatter kernel's flushes
 template <int CH>
 __global__ void __launch_bounds__(256) chunk_write(uint64_t *T, uint64_t nchunks_table, uint64_t nchunks) {
@@ -181,14 +215,28 @@ int main(int argc, char **argv) {
             run<0, 1>("ld16 (footprint sweep)", T, bytes, nops, 8, sink);
             run<2, 1>("red64 (footprint sweep)", T, bytes, nops, 8, sink);
         }
-        for (int log2s : {20, 21, 22, 23}) {
-            const uint64_t slice_slots = 1ull << log2s, nsl = max_bytes / 16 / slice_slots, n = 1ull << 30;
+        for (int log2s : {16, 18, 20, 21, 22, 23}) {
+            // 2 GiB table swept once with 2.25 ops per slot (the count pipeline's insert phase on C2)
+            const uint64_t slice_slots = 1ull << log2s, nsl = (2ull << 30) / 16 / slice_slots, n = 300ull << 20;
             CK(cudaEventRecord(a)); window<0><<<148 * 8, 256>>>(T, slice_slots, nsl, n, sink); CK(cudaEventRecord(b)); CK(cudaEventSynchronize(b));
             CK(cudaEventElapsedTime(&ms, a, b)); printf("window ld16+cas64  slice %4llu MiB x %llu : %8.2f G ops/s\n", (unsigned long long)(slice_slots >> 16), (unsigned long long)nsl, n / (ms * 1e-3) / 1e9);
             CK(cudaEventRecord(a)); window<1><<<148 * 8, 256>>>(T, slice_slots, nsl, n, sink); CK(cudaEventRecord(b)); CK(cudaEventSynchronize(b));
             CK(cudaEventElapsedTime(&ms, a, b)); printf("window ld16+atom64 slice %4llu MiB x %llu : %8.2f G ops/s\n", (unsigned long long)(slice_slots >> 16), (unsigned long long)nsl, n / (ms * 1e-3) / 1e9);
             CK(cudaEventRecord(a)); window<2><<<148 * 6, 256>>>(T, slice_slots, nsl, n, sink); CK(cudaEventRecord(b)); CK(cudaEventSynchronize(b));
             CK(cudaEventElapsedTime(&ms, a, b)); printf("window 32B recipe  slice %4llu MiB x %llu : %8.2f G ops/s\n", (unsigned long long)(slice_slots >> 16), (unsigned long long)nsl, n / (ms * 1e-3) / 1e9);
+        }
+        {
+            uint64_t *tup; const uint64_t n = 300ull << 20; CK(cudaMalloc(&tup, n * 8)); CK(cudaMemset(tup, 1, n * 8));
+            for (int log2s : {18, 21}) {
+                const uint64_t slice_slots = 1ull << log2s, nsl = (2ull << 30) / 16 / slice_slots;
+                #define RUNW(NAME, ...) CK(cudaMemset(T, 0, 2ull << 30)); CK(cudaEventRecord(a)); __VA_ARGS__; CK(cudaEventRecord(b)); CK(cudaEventSynchronize(b)); \
+                    CK(cudaEventElapsedTime(&ms, a, b)); printf("winsert %-28s slice %4llu MiB : %8.2f G ops/s\n", NAME, (unsigned long long)(slice_slots >> 16), n / (ms * 1e-3) / 1e9);
+                RUNW("cas128 claim", (window_insert<0, false><<<148 * 6, 256>>>(T, slice_slots, nsl, n, tup, sink)))
+                RUNW("cas64+cas64 claim", (window_insert<1, false><<<148 * 6, 256>>>(T, slice_slots, nsl, n, tup, sink)))
+                RUNW("cas128 claim + tuple stream", (window_insert<0, true><<<148 * 6, 256>>>(T, slice_slots, nsl, n, tup, sink)))
+                RUNW("cas64+cas64 + tuple stream", (window_insert<1, true><<<148 * 6, 256>>>(T, slice_slots, nsl, n, tup, sink)))
+            }
+            CK(cudaFree(tup));
         }
         const uint64_t tb = 16ull << 30;
         CK(cudaEventRecord(a)); chunk_write<128><<<148 * 8, 256>>>((uint64_t *)T, tb / 128, tb / 128); CK(cudaEventRecord(b)); CK(cudaEventSynchronize(b));
