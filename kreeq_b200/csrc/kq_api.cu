@@ -73,7 +73,7 @@ struct kq_ctx {
     // pipeline scratch
     uint64_t *d_tuples = nullptr; uint64_t tup_cap = 0;          // tuples (not words)
     unsigned long long *d_hist = nullptr, *d_cursor = nullptr; uint64_t hist_cap = 0;
-    unsigned long long *d_total = nullptr, *d_nsrc = nullptr;
+    unsigned long long *d_total = nullptr, *d_nsrc = nullptr, *d_ticket = nullptr;
     uint64_t *d_ovf = nullptr; unsigned long long *d_ovf_n = nullptr; bool ovf_pending = false;
     Stage st[NBUF]; int next_stage = 0;
     uint64_t launches = 0, h2d = 0, d2h = 0;
@@ -263,7 +263,7 @@ int settle(kq_ctx *c) {
     CU(cudaMemsetAsync(c->d_ovf_n, 0, 8, c->stream));
     CU(cudaMemcpyAsync(c->d_nsrc, &n, 8, cudaMemcpyHostToDevice, c->stream));
     rc = pipeline_scratch(c, OVF_CAP); if (rc) return rc;
-    CU(launch_insert_tuples(c->stream, view(c), c->d_ovf, c->d_nsrc, n, c->d_tuples, c->tup_cap, c->d_ovf_n, &c->launches));
+    CU(launch_insert_tuples(c->stream, view(c), c->d_ovf, c->d_nsrc, n, c->d_tuples, c->tup_cap, c->d_ovf_n, c->d_ticket, &c->launches));
     CU(cudaMemcpyAsync(&n, c->d_ovf_n, 8, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
     if (n) return fail(c, KQ_ENOMEM, "k-mer table full after growing");
@@ -284,7 +284,7 @@ int run_batch(kq_ctx *c, Source src) {
     // a sweep over the table pays off once the batch touches a good part of it
     if (c->nslices == 1 || cap == 0 || (double)bound < 0.25 * (double)table_slots(c)) {
         if (src.tuples) {
-            CU(launch_insert_tuples(c->stream, tv, src.tuples, src.ntuples, bound, c->d_ovf, OVF_CAP, c->d_ovf_n, &c->launches));
+            CU(launch_insert_tuples(c->stream, tv, src.tuples, src.ntuples, bound, c->d_ovf, OVF_CAP, c->d_ovf_n, c->d_ticket, &c->launches));
             c->ovf_pending = true;
         } else {
             CU(launch_count_direct(c->stream, tv, src, c->d_inst, c->d_ovf, OVF_CAP, c->d_ovf_n, &c->launches));
@@ -301,8 +301,23 @@ int run_batch(kq_ctx *c, Source src) {
                             src.tuples ? nullptr : c->d_inst, &c->launches));
     CU(launch_slice_scatter(c->stream, tv, src, c->d_tuples, c->d_cursor, cap, &c->launches));
     time_end(c, t3);
+    if (std::getenv("KQ_DEBUG_ORDER")) {                              // debugging aid: is the scatter output in slice order?
+        unsigned long long total = 0;
+        cudaMemcpyAsync(&total, c->d_total, 8, cudaMemcpyDeviceToHost, c->stream); cudaStreamSynchronize(c->stream);
+        std::vector<uint64_t> h(total * tw);
+        cudaMemcpy(h.data(), c->d_tuples, total * tw * 8, cudaMemcpyDeviceToHost);
+        uint64_t changes = 0, backwards = 0, prev = 0;
+        for (uint64_t i = 0; i < total; ++i) {
+            const uint64_t key = tw == 1 ? h[i] >> 8 : h[2 * i];
+            const uint64_t sl = slice_of_key(key, c->nslices);
+            if (i && sl != prev) { ++changes; if (sl < prev) ++backwards; }
+            prev = sl;
+        }
+        std::fprintf(stderr, "KQ_DEBUG_ORDER: %llu tuples, %llu slices, %llu slice changes, %llu backwards\n",
+                     total, (unsigned long long)c->nslices, (unsigned long long)changes, (unsigned long long)backwards);
+    }
     const int t2 = time_begin(c, 2);
-    CU(launch_insert_tuples(c->stream, tv, c->d_tuples, c->d_total, bound, c->d_ovf, OVF_CAP, c->d_ovf_n, &c->launches));
+    CU(launch_insert_tuples(c->stream, tv, c->d_tuples, c->d_total, bound, c->d_ovf, OVF_CAP, c->d_ovf_n, c->d_ticket, &c->launches));
     time_end(c, t2);
     c->ovf_pending = true;
     time_end(c, t0);
@@ -399,6 +414,7 @@ extern "C" int kq_create(kq_ctx **out, int k, int device, uint64_t expected_dist
     CC(cudaMalloc(&ctx->d_acc, 3 * sizeof(unsigned long long)));
     CC(cudaMalloc(&ctx->d_total, sizeof(unsigned long long)));
     CC(cudaMalloc(&ctx->d_nsrc, sizeof(unsigned long long)));
+    CC(cudaMalloc(&ctx->d_ticket, sizeof(unsigned long long)));
     CC(cudaMalloc(&ctx->d_ovf_n, sizeof(unsigned long long)));
     CC(cudaMalloc(&ctx->d_err, sizeof(int)));
     CC(cudaMemsetAsync(ctx->d_occ, 0, 3 * sizeof(unsigned long long), ctx->stream));
@@ -432,7 +448,7 @@ extern "C" void kq_destroy(kq_ctx *c) {
     for (auto e : c->ev_pool) cudaEventDestroy(e);
     cudaFree(c->T); cudaFree(c->R); cudaFree(c->M); cudaFree(c->d_occ); cudaFree(c->d_inst); cudaFree(c->d_acc); cudaFree(c->d_err);
     cudaFree(c->d_pb); cudaFree(c->d_pi); cudaFree(c->d_tuples); cudaFree(c->d_hist); cudaFree(c->d_cursor);
-    cudaFree(c->d_total); cudaFree(c->d_nsrc); cudaFree(c->d_ovf); cudaFree(c->d_ovf_n);
+    cudaFree(c->d_total); cudaFree(c->d_nsrc); cudaFree(c->d_ticket); cudaFree(c->d_ovf); cudaFree(c->d_ovf_n);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     delete c;
 }

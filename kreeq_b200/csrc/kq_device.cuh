@@ -96,9 +96,12 @@ __device__ __forceinline__ bool owns(const TableView &tv, uint64_t key) {
     return tv.shard_rank < 0 || (int)((key & 127) >> tv.shard_shift) == tv.shard_rank;
 }
 
-// slice of a key and its home slot inside the slice
-__device__ __forceinline__ unsigned long long slice_of(const TableView &tv, uint64_t h) { return __umul64hi(h, tv.nslices); }
-__device__ __forceinline__ unsigned long long home_of(const TableView &tv, uint64_t h) { return h & ((1ull << tv.slice_bits) - 1); }
+// Slice of a key: multiplicative hash, top 32 bits scaled to nslices (a handful of instructions: the
+// histogram and scatter kernels evaluate it for every k-mer instance).  The home slot inside the slice
+// comes from the low bits of mix64(key), which only the kernels that touch the table compute.
+__host__ __device__ __forceinline__ unsigned long long slice_of_key(uint64_t key, unsigned long long nslices) {
+    return ((unsigned long long)(uint32_t)((key * 0x9E3779B97F4A7C15ULL) >> 32) * nslices) >> 32;
+}
 
 // 64 bits of a little-endian bit stream starting at absolute bit position `bit`
 __device__ __forceinline__ uint64_t load_bits(const uint64_t *__restrict__ W, uint64_t bit) {
@@ -216,7 +219,7 @@ __device__ __forceinline__ void remainder_add(const TableView &tv, uint64_t key,
 __device__ __forceinline__ Slot *find_slot(const TableView &tv, uint64_t key, Slot *out) {
     const unsigned long long tag = key + 1;
     const uint64_t h = mix64(key);
-    Slot *base = tv.T + (slice_of(tv, h) << tv.slice_bits);
+    Slot *base = tv.T + (slice_of_key(key, tv.nslices) << tv.slice_bits);
     const unsigned long long mask = (1ull << tv.slice_bits) - 1;
     unsigned long long j = h & mask;
     for (unsigned long long n = 0; n <= mask; ++n) {
@@ -235,7 +238,7 @@ __device__ __forceinline__ Slot *find_slot(const TableView &tv, uint64_t key, Sl
 __device__ __forceinline__ int insert_instance(const TableView &tv, uint64_t key, uint32_t e) {
     const unsigned long long tag = key + 1, inc = inc_of_edge(e);
     const uint64_t h = mix64(key);
-    Slot *base = tv.T + (slice_of(tv, h) << tv.slice_bits);
+    Slot *base = tv.T + (slice_of_key(key, tv.nslices) << tv.slice_bits);
     const unsigned long long mask = (1ull << tv.slice_bits) - 1;
     unsigned long long j = h & mask;
     for (unsigned long long n = 0; n <= mask; ++n) {
@@ -271,7 +274,7 @@ __device__ __forceinline__ int insert_instance(const TableView &tv, uint64_t key
 __device__ __forceinline__ Slot *find_or_claim(const TableView &tv, uint64_t key, bool *is_new) {
     const unsigned long long tag = key + 1;
     const uint64_t h = mix64(key);
-    Slot *base = tv.T + (slice_of(tv, h) << tv.slice_bits);
+    Slot *base = tv.T + (slice_of_key(key, tv.nslices) << tv.slice_bits);
     const unsigned long long mask = (1ull << tv.slice_bits) - 1;
     unsigned long long j = h & mask;
     *is_new = false;

@@ -15,13 +15,13 @@
 #include "kq_kernels.h"
 
 #include <algorithm>
+#include <cstdlib>
 
 namespace kq {
 
 constexpr int TPB = 256;          // threads per CTA of the grid-stride kernels
 constexpr int CTAS_PER_SM = 6;
 constexpr int RUN = 8;            // consecutive k-mer start positions one thread extracts per round
-constexpr int SC_THREADS = 512;   // scatter kernel: one CTA per SM, most of the shared memory as bins
 
 int sm_count() {
     static int n = 0;
@@ -58,26 +58,36 @@ __device__ __forceinline__ uint64_t bits3(uint64_t w0, uint64_t w1, uint64_t w2,
 
 // k-mers starting at positions p0 .. p0+cnt-1 (cnt <= RUN) of a packed sequence: 5 word loads for the
 // whole run instead of 6 per position.  Returns the mask of valid windows.
+template <int R>
 __device__ __forceinline__ uint32_t extract_run(const uint64_t *__restrict__ B, const uint64_t *__restrict__ M,
-                                                uint64_t p0, uint32_t cnt, int k, uint64_t key[RUN], uint32_t e[RUN]) {
+                                                uint64_t p0, uint32_t cnt, int k, uint64_t key[R], uint32_t e[R]) {
+    static_assert(R <= 16, "three base words / two invalid words cover at most 16 positions + k + 1 bases");
     const uint64_t bw = p0 >> 5; const uint32_t bs = (uint32_t)(2 * p0) & 63u;
     const uint64_t b0 = __ldg(B + bw), b1 = __ldg(B + bw + 1), b2 = __ldg(B + bw + 2);
     const uint64_t iw = p0 >> 6; const uint32_t is = (uint32_t)p0 & 63u;
     const uint64_t i0 = __ldg(M + iw), i1 = __ldg(M + iw + 1);
     uint32_t prv = (p0 == 0 || invalid_at(M, p0 - 1)) ? 4u : base_at(B, p0 - 1);
+    const uint64_t kmask = k == 32 ? ~0ULL : ((1ULL << (2 * k)) - 1), vmask = (1ULL << k) - 1;
+    // forward and reverse-complement values of the first window (Kmap::hash, kmer.h:781-794), then rolled:
+    // fw drops its lowest digit and gains the new base on top, rv gains the complement at the bottom
+    const uint64_t win0 = bits3(b0, b1, b2, bs);
+    uint64_t fw = win0 & kmask, rv = reverse_pairs(~win0) >> (64 - 2 * k);
     uint32_t mask = 0;
 #pragma unroll
-    for (int i = 0; i < RUN; ++i) {
-        const uint32_t o = bs + 2 * i;                               // <= 62 + 14
-        const uint64_t win = bits3(b0, b1, b2, o);
-        const uint32_t oi = is + i;                                  // <= 63 + 7; k + 1 more bits are needed
+    for (int i = 0; i < R; ++i) {
+        const uint32_t oi = is + i;                                  // <= 63 + R - 1; k + 1 more bits are needed
         const uint64_t inv = oi < 64 ? ((i0 >> oi) | (oi ? i1 << (64 - oi) : 0)) : (i1 >> (oi - 64));
-        const uint32_t on = o + 2 * k;                               // bit offset of the base after the window
+        const uint32_t on = bs + 2 * i + 2 * k;                      // bit offset of the base after the window
         const uint64_t wn = on < 64 ? b0 : on < 128 ? b1 : b2;
-        const uint32_t nxt = ((inv >> k) & 1) ? 4u : (uint32_t)(wn >> (on & 63u)) & 3u;
-        const Kmer km = kmer_from_window(win, inv, nxt, prv, k);
-        if ((uint32_t)i < cnt && km.valid) { key[i] = km.key; e[i] = edge_byte(km); mask |= 1u << i; }
-        prv = (inv & 1) ? 4u : (uint32_t)win & 3u;
+        const uint32_t nb = (uint32_t)(wn >> (on & 63u)) & 3u;       // its code (0 if it is not ACGT)
+        const uint32_t nxt = ((inv >> k) & 1) ? 4u : nb;
+        if ((uint32_t)i < cnt && (inv & vmask) == 0) {
+            Kmer km; km.isFw = fw < rv; km.key = km.isFw ? fw : rv; km.nxt = nxt; km.prv = prv;   // tie => not forward
+            key[i] = km.key; e[i] = edge_byte(km); mask |= 1u << i;
+        }
+        prv = (inv & 1) ? 4u : (uint32_t)fw & 3u;
+        fw = (fw >> 2) | ((uint64_t)nb << (2 * k - 2));
+        rv = ((rv << 2) | (3u - nb)) & kmask;
     }
     return mask;
 }
@@ -94,23 +104,23 @@ template <int TW> __device__ __forceinline__ void tuple_store(uint64_t *t, uint6
 // One round of a CTA over its tile: every thread produces up to RUN (key, edge) pairs.
 // Sequence source: tile = nthreads * RUN consecutive positions, thread t takes RUN consecutive ones.
 // Tuple source: tile = nthreads * RUN tuples, element i of thread t is tile + i * nthreads + t (coalesced).
-template <int TW>
+template <int TW, int R = RUN>
 __device__ __forceinline__ uint32_t produce(const Source &src, const TableView &tv, uint64_t tile, uint64_t total,
-                                            uint64_t key[RUN], uint32_t e[RUN]) {
+                                            uint64_t key[R], uint32_t e[R]) {
     if (src.tuples == nullptr) {
-        const uint64_t first = tile + (uint64_t)threadIdx.x * RUN;
+        const uint64_t first = tile + (uint64_t)threadIdx.x * R;
         if (first >= total) return 0;
-        const uint32_t cnt = (uint32_t)min((uint64_t)RUN, total - first);
-        uint32_t m = extract_run(src.bases, src.invalid, src.pos0 + first, cnt, tv.k, key, e);
+        const uint32_t cnt = (uint32_t)min((uint64_t)R, total - first);
+        uint32_t m = extract_run<R>(src.bases, src.invalid, src.pos0 + first, cnt, tv.k, key, e);
         if (tv.shard_rank >= 0) {
 #pragma unroll
-            for (int i = 0; i < RUN; ++i) if ((m >> i & 1u) && !owns(tv, key[i])) m &= ~(1u << i);
+            for (int i = 0; i < R; ++i) if ((m >> i & 1u) && !owns(tv, key[i])) m &= ~(1u << i);
         }
         return m;
     }
     uint32_t m = 0;
 #pragma unroll
-    for (int i = 0; i < RUN; ++i) {
+    for (int i = 0; i < R; ++i) {
         const uint64_t j = tile + (uint64_t)i * blockDim.x + threadIdx.x;
         if (j < total) { tuple_unpack<TW>(src.tuples, j, key[i], e[i]); m |= 1u << i; }
     }
@@ -164,7 +174,7 @@ slice_hist_kernel(TableView tv, Source src, unsigned long long *hist) {
         const uint32_t m = produce<TW>(src, tv, tile, total, key, e);
 #pragma unroll
         for (int i = 0; i < RUN; ++i)
-            if (m >> i & 1u) atomicAdd(&h[slice_of(tv, mix64(key[i]))], 1u);
+            if (m >> i & 1u) atomicAdd(&h[slice_of_key(key[i], tv.nslices)], 1u);
     }
     __syncthreads();
     for (unsigned i = threadIdx.x; i < tv.nslices; i += TPB)
@@ -199,52 +209,57 @@ slice_offsets_kernel(unsigned long long nslices, const unsigned long long *hist,
 // bin with one shared-memory atomic; a bin that reaches `cap` entries is flushed by one warp as ONE
 // coalesced cap * 8 * TW byte store (256 B for cap = 32) at a position reserved with one global atomic
 // on the slice's cursor.  Random 256-byte stores run at ~5.4 TB/s on B200 (r01_gups_footprint_sweep.log).
-template <int TW>
-__global__ void __launch_bounds__(SC_THREADS, 1)
+template <int TW, int R, int NT>
+__global__ void __launch_bounds__(NT, 1)
 slice_scatter_kernel(TableView tv, Source src, uint64_t *__restrict__ out, unsigned long long *cursor, int cap) {
     extern __shared__ uint64_t sm[];
     const unsigned P = (unsigned)tv.nslices;
     uint64_t *bins = sm;
     unsigned int *fill = reinterpret_cast<unsigned int *>(bins + (size_t)P * cap * TW);
-    for (unsigned i = threadIdx.x; i < P; i += SC_THREADS) fill[i] = 0;
+    for (unsigned i = threadIdx.x; i < P; i += NT) fill[i] = 0;
     __syncthreads();
-    const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = SC_THREADS / 32;
-    const uint64_t total = source_total(src), per = (uint64_t)SC_THREADS * RUN;
+    const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = NT / 32;
+    const uint64_t total = source_total(src), per = (uint64_t)NT * R;
     for (uint64_t tile = (uint64_t)blockIdx.x * per; tile < total; tile += (uint64_t)gridDim.x * per) {
-        uint64_t key[RUN]; uint32_t e[RUN]; unsigned bin[RUN], slot[RUN];
-        uint32_t m = produce<TW>(src, tv, tile, total, key, e);
+        uint64_t key[R]; uint32_t e[R]; unsigned bin[R], slot[R];
+        uint32_t m = produce<TW, R>(src, tv, tile, total, key, e);
         bool filled = false;
 #pragma unroll
-        for (int i = 0; i < RUN; ++i) {
+        for (int i = 0; i < R; ++i) {
             if (!(m >> i & 1u)) continue;
-            bin[i] = (unsigned)slice_of(tv, mix64(key[i]));
+            bin[i] = (unsigned)slice_of_key(key[i], tv.nslices);
             slot[i] = atomicAdd(&fill[bin[i]], 1u);
             filled |= slot[i] >= (unsigned)cap - 1;
         }
         for (;;) {
 #pragma unroll
-            for (int i = 0; i < RUN; ++i) {
+            for (int i = 0; i < R; ++i) {
                 if (!(m >> i & 1u) || slot[i] >= (unsigned)cap) continue;
                 tuple_store<TW>(bins, (size_t)bin[i] * cap + slot[i], key[i], e[i]);
                 m &= ~(1u << i);
             }
             if (!__syncthreads_or(filled)) break;                    // no bin reached cap in this round
-            for (unsigned b = warp; b < P; b += nwarps) {
-                const unsigned f = fill[b];
-                if (f < (unsigned)cap) continue;
+            // lane l of a warp looks at bin b0 + l: all reservations of a warp's 32 bins are issued together
+            // (one atomic round trip instead of one per bin), then the warp copies the full bins one by one
+            for (unsigned b0 = warp * 32; b0 < P; b0 += nwarps * 32) {
+                const unsigned b = b0 + lane;
+                const unsigned f = b < P ? fill[b] : 0;
+                const bool full = f >= (unsigned)cap;
                 unsigned long long g = 0;
-                if (lane == 0) g = atomicAdd(&cursor[b], (unsigned long long)cap);
-                g = __shfl_sync(0xffffffffu, g, 0);
-                const uint64_t *srcw = bins + (size_t)b * cap * TW;
-                uint64_t *dst = out + g * TW;
-                for (unsigned w = lane; w < (unsigned)cap * TW; w += 32) __stcs(dst + w, srcw[w]);
-                __syncwarp();
-                if (lane == 0) fill[b] = f - cap;
+                if (full) { g = atomicAdd(&cursor[b], (unsigned long long)cap); fill[b] = f - cap; }
+                unsigned todo = __ballot_sync(0xffffffffu, full);
+                while (todo) {
+                    const int l = __ffs(todo) - 1; todo &= todo - 1;
+                    const unsigned long long gg = __shfl_sync(0xffffffffu, g, l);
+                    const uint64_t *srcw = bins + (size_t)(b0 + l) * cap * TW;
+                    uint64_t *dst = out + gg * TW;
+                    for (unsigned w = lane; w < (unsigned)cap * TW; w += 32) __stcs(dst + w, srcw[w]);
+                }
             }
             __syncthreads();
             filled = false;
 #pragma unroll
-            for (int i = 0; i < RUN; ++i) {
+            for (int i = 0; i < R; ++i) {
                 if (!(m >> i & 1u)) continue;
                 slot[i] -= cap;                                      // the first cap entries of the bin are gone
                 filled = true;                                       // something is still waiting: go round again
@@ -253,15 +268,39 @@ slice_scatter_kernel(TableView tv, Source src, uint64_t *__restrict__ out, unsig
         }
     }
     __syncthreads();
-    for (unsigned b = warp; b < P; b += nwarps) {                     // what is left in the bins
-        const unsigned f = fill[b];
-        if (!f) continue;
+    for (unsigned b0 = warp * 32; b0 < P; b0 += nwarps * 32) {         // what is left in the bins
+        const unsigned b = b0 + lane;
+        const unsigned f = b < P ? fill[b] : 0;
         unsigned long long g = 0;
-        if (lane == 0) g = atomicAdd(&cursor[b], (unsigned long long)f);
-        g = __shfl_sync(0xffffffffu, g, 0);
-        const uint64_t *srcw = bins + (size_t)b * cap * TW;
-        uint64_t *dst = out + g * TW;
-        for (unsigned w = lane; w < f * TW; w += 32) __stcs(dst + w, srcw[w]);
+        if (f) g = atomicAdd(&cursor[b], (unsigned long long)f);
+        unsigned todo = __ballot_sync(0xffffffffu, f != 0);
+        while (todo) {
+            const int l = __ffs(todo) - 1; todo &= todo - 1;
+            const unsigned long long gg = __shfl_sync(0xffffffffu, g, l);
+            const unsigned ff = __shfl_sync(0xffffffffu, f, l);
+            const uint64_t *srcw = bins + (size_t)(b0 + l) * cap * TW;
+            uint64_t *dst = out + gg * TW;
+            for (unsigned w = lane; w < ff * TW; w += 32) __stcs(dst + w, srcw[w]);
+        }
+    }
+}
+
+// Variant without shared-memory bins: one global atomic on the slice cursor per tuple and one 8/16-byte
+// store; L2 is the write combiner (the ~600 cursor lines and the ~600 frontier lines of the output stay
+// resident, every output line is complete before it is evicted).
+template <int TW>
+__global__ void __launch_bounds__(TPB, 4)
+slice_scatter_direct_kernel(TableView tv, Source src, uint64_t *__restrict__ out, unsigned long long *cursor) {
+    const uint64_t total = source_total(src), per = (uint64_t)TPB * RUN;
+    for (uint64_t tile = (uint64_t)blockIdx.x * per; tile < total; tile += (uint64_t)gridDim.x * per) {
+        uint64_t key[RUN]; uint32_t e[RUN]; unsigned long long at[RUN];
+        const uint32_t m = produce<TW>(src, tv, tile, total, key, e);
+#pragma unroll
+        for (int i = 0; i < RUN; ++i)
+            if (m >> i & 1u) at[i] = atomicAdd(&cursor[slice_of_key(key[i], tv.nslices)], 1ULL);
+#pragma unroll
+        for (int i = 0; i < RUN; ++i)
+            if (m >> i & 1u) tuple_store<TW>(out, at[i], key[i], e[i]);
     }
 }
 
@@ -269,23 +308,38 @@ slice_scatter_kernel(TableView tv, Source src, uint64_t *__restrict__ out, unsig
 
 // Consecutive CTAs work on consecutive tuples, i.e. on the same one or two slices at a time, so the
 // slot loads and CASes below hit L2.  Tuples are streamed with evict-first loads to keep L2 for the table.
+constexpr int INS_TILE = TPB * 8;   // tuples per ticket
+
+// CTAs take tiles of INS_TILE consecutive tuples from a global ticket counter, so at any moment all
+// resident CTAs work within ~1.8 M consecutive tuples (less than half a slice) however their speeds
+// differ; with a static grid-stride assignment CTAs on the far L2 die fall behind and the set of
+// slices in use outgrows L2.
 template <int TW>
 __global__ void __launch_bounds__(TPB, CTAS_PER_SM)
 insert_tuples_kernel(TableView tv, const uint64_t *__restrict__ tuples, const unsigned long long *n_ptr,
-                     uint64_t *ovf, unsigned long long ovf_cap, unsigned long long *ovf_n) {
-    __shared__ unsigned long long sh[1];
+                     uint64_t *ovf, unsigned long long ovf_cap, unsigned long long *ovf_n, unsigned long long *ticket) {
+    __shared__ unsigned long long sh[2];
     if (threadIdx.x == 0) sh[0] = 0;
-    __syncthreads();
     unsigned long long fresh = 0;
-    const uint64_t n = *n_ptr, stride = (uint64_t)gridDim.x * TPB;
-    for (uint64_t i = (uint64_t)blockIdx.x * TPB + threadIdx.x; i < n; i += stride) {
-        uint64_t key; uint32_t e;
-        tuple_unpack<TW>(tuples, i, key, e);
-        const int r = insert_instance(tv, key, e);
-        if (r < 0) {                                                  // slice full: keep the tuple for after a grow
-            const unsigned long long j = atomicAdd(ovf_n, 1ULL);
-            if (j < ovf_cap) tuple_store<TW>(ovf, j, key, e);
-        } else fresh += r;
+    const uint64_t n = *n_ptr;
+    for (;;) {
+        __syncthreads();
+        if (threadIdx.x == 0) sh[1] = atomicAdd(ticket, 1ULL);
+        __syncthreads();
+        const uint64_t tile = sh[1] * INS_TILE;
+        if (tile >= n) break;
+#pragma unroll 2
+        for (int r = 0; r < INS_TILE / TPB; ++r) {
+            const uint64_t i = tile + (uint64_t)r * TPB + threadIdx.x;
+            if (i >= n) break;
+            uint64_t key; uint32_t e;
+            tuple_unpack<TW>(tuples, i, key, e);
+            const int st = insert_instance(tv, key, e);
+            if (st < 0) {                                             // slice full: keep the tuple for after a grow
+                const unsigned long long j = atomicAdd(ovf_n, 1ULL);
+                if (j < ovf_cap) tuple_store<TW>(ovf, j, key, e);
+            } else fresh += st;
+        }
     }
     block_add(fresh, &tv.occ[0], &sh[0]);
 }
@@ -385,12 +439,20 @@ size_t scatter_smem_bytes(unsigned long long nslices, int cap, int tw) {
     return (size_t)nslices * cap * tw * 8 + (size_t)nslices * 4;
 }
 
+// largest bin capacity (tuples) such that TWO scatter CTAs fit one SM's shared memory (latency hiding
+// matters more than flush size: 128-byte flushes still run at 2.6 TB/s), else one CTA per SM
 int scatter_pick_cap(unsigned long long nslices, int tw) {
-    static int max_smem = 0;
+    static int max_smem = 0, sm_smem = 0;
     if (!max_smem) {
         int dev = 0; cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+        cudaDeviceGetAttribute(&sm_smem, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev);
         if (max_smem <= 0) max_smem = 227 * 1024;
+        if (sm_smem <= 0) sm_smem = 228 * 1024;
+    }
+    if (const char *e = std::getenv("KQ_SCATTER_CAP")) {              // tuning knob
+        const int cap = std::atoi(e);
+        if (cap > 0 && scatter_smem_bytes(nslices, cap, tw) <= (size_t)max_smem - 1024) return cap;
     }
     for (int cap : {32, 16, 8})
         if (scatter_smem_bytes(nslices, cap, tw) <= (size_t)max_smem - 1024) return cap;
@@ -436,17 +498,28 @@ cudaError_t launch_slice_scatter(cudaStream_t st, const TableView &tv, const Sou
     const uint64_t n = source_bound(src);
     if (!n) return cudaSuccess;
     const int tw = tuple_words(tv.k);
+    static const bool direct = [] { const char *e = std::getenv("KQ_SCATTER"); return e && e[0] == 'd'; }();
+    if (direct) {
+        const unsigned g = std::min<uint64_t>((n + TPB * RUN - 1) / (TPB * RUN), (uint64_t)sm_count() * 4);
+        KQ_TW_DISPATCH(tw, (slice_scatter_direct_kernel<TW><<<g, TPB, 0, st>>>(tv, src, out, cursor)));
+        ++*launches;
+        return cudaGetLastError();
+    }
     const size_t smem = scatter_smem_bytes(tv.nslices, cap, tw);
-    const unsigned grid = std::min<uint64_t>((n + SC_THREADS * RUN - 1) / (SC_THREADS * RUN), (uint64_t)sm_count());
-    cudaError_t e;
-    if (tw == 1) {
-        e = cudaFuncSetAttribute(slice_scatter_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        slice_scatter_kernel<1><<<grid, SC_THREADS, smem, st>>>(tv, src, out, cursor, cap);
+    static const int variant = [] { const char *e = std::getenv("KQ_SC_VARIANT"); return e ? std::atoi(e) : 0; }();
+    cudaError_t e = cudaSuccess;
+#define KQ_SCATTER_LAUNCH(TWV, RV, NTV) do {                                                                        \
+        e = cudaFuncSetAttribute(slice_scatter_kernel<TWV, RV, NTV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+        if (e != cudaSuccess) return e;                                                                             \
+        const unsigned grid = std::min<uint64_t>((n + NTV * RV - 1) / (NTV * RV), (uint64_t)sm_count());           \
+        slice_scatter_kernel<TWV, RV, NTV><<<grid, NTV, smem, st>>>(tv, src, out, cursor, cap); } while (0)
+    if (tw == 1) {                                                   // measured on C2 (profiles/): 16 x 512 is the fastest
+        if (variant == 1) KQ_SCATTER_LAUNCH(1, 8, 512);
+        else if (variant == 2) KQ_SCATTER_LAUNCH(1, 8, 1024);
+        else if (variant == 3) KQ_SCATTER_LAUNCH(1, 4, 1024);
+        else KQ_SCATTER_LAUNCH(1, 16, 512);
     } else {
-        e = cudaFuncSetAttribute(slice_scatter_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        slice_scatter_kernel<2><<<grid, SC_THREADS, smem, st>>>(tv, src, out, cursor, cap);
+        KQ_SCATTER_LAUNCH(2, 8, 512);
     }
     ++*launches;
     return cudaGetLastError();
@@ -454,9 +527,12 @@ cudaError_t launch_slice_scatter(cudaStream_t st, const TableView &tv, const Sou
 
 cudaError_t launch_insert_tuples(cudaStream_t st, const TableView &tv, const uint64_t *tuples,
                                  const unsigned long long *n, uint64_t n_max, uint64_t *ovf,
-                                 unsigned long long ovf_cap, unsigned long long *ovf_n, uint64_t *launches) {
+                                 unsigned long long ovf_cap, unsigned long long *ovf_n, unsigned long long *ticket,
+                                 uint64_t *launches) {
     if (!n_max) return cudaSuccess;
-    KQ_TW_DISPATCH(tuple_words(tv.k), (insert_tuples_kernel<TW><<<grid_for(n_max), TPB, 0, st>>>(tv, tuples, n, ovf, ovf_cap, ovf_n)));
+    cudaError_t e = cudaMemsetAsync(ticket, 0, sizeof(unsigned long long), st);
+    if (e != cudaSuccess) return e;
+    KQ_TW_DISPATCH(tuple_words(tv.k), (insert_tuples_kernel<TW><<<grid_for(n_max, INS_TILE / TPB), TPB, 0, st>>>(tv, tuples, n, ovf, ovf_cap, ovf_n, ticket)));
     ++*launches;
     return cudaGetLastError();
 }

@@ -62,7 +62,8 @@ cudaError_t launch_slice_scatter(cudaStream_t st, const TableView &tv, const Sou
 //    ovf_n counts every failure, also those that did not fit)
 cudaError_t launch_insert_tuples(cudaStream_t st, const TableView &tv, const uint64_t *tuples,
                                  const unsigned long long *n, uint64_t n_max, uint64_t *ovf,
-                                 unsigned long long ovf_cap, unsigned long long *ovf_n, uint64_t *launches);
+                                 unsigned long long ovf_cap, unsigned long long *ovf_n, unsigned long long *ticket,
+                                 uint64_t *launches);
 // multi-GPU: extract every valid window and append its tuple to the slab of its owner rank
 cudaError_t launch_extract_route(cudaStream_t st, const TableView &tv, const Source &src, RouteArgs ra,
                                  uint64_t *launches);

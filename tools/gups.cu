@@ -9,6 +9,7 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
+#include <algorithm>
 #include <cuda_runtime.h>
 
 #define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { fprintf(stderr, "%s: %s\n", #x, cudaGetErrorString(e_)); exit(1); } } while (0)
@@ -238,7 +239,7 @@ int main(int argc, char **argv) {
             }
             CK(cudaFree(tup));
         }
-        const uint64_t tb = 16ull << 30;
+        const uint64_t tb = std::min<uint64_t>(16ull << 30, max_bytes);
         CK(cudaEventRecord(a)); chunk_write<128><<<148 * 8, 256>>>((uint64_t *)T, tb / 128, tb / 128); CK(cudaEventRecord(b)); CK(cudaEventSynchronize(b));
         CK(cudaEventElapsedTime(&ms, a, b)); printf("random 128-B chunk writes: %8.1f GB/s\n", tb / (ms * 1e-3) / 1e9);
         CK(cudaEventRecord(a)); chunk_write<256><<<148 * 8, 256>>>((uint64_t *)T, tb / 256, tb / 256); CK(cudaEventRecord(b)); CK(cudaEventSynchronize(b));
