@@ -16,7 +16,7 @@ def pytest_configure(config):
 def _build_once():
     import __graft_entry__ as g
     lib = os.path.join(ROOT, "kreeq_b200", "libkreeq_b200.so")
-    if not os.path.exists(lib):
+    if not os.path.exists(lib) or not os.path.exists(os.path.join(ROOT, "kreeq_b200", "kreeq")):
         g.build()
 
 

@@ -188,3 +188,22 @@ def test_reference_binary_loads_our_database(kb, tmp_path):
     import gzip
     with open(os.path.join(GOLD, "ref_runs", "repeat1_k21.kwig.gz"), "rb") as f:
         assert open(tmp_path / "r.kwig", "rb").read() == gzip.decompress(f.read())
+
+
+def test_cli_binary_usage_and_no_cpu_fallback(tmp_path):
+    """kreeq_b200/kreeq is the reference's command line over the C-ABI: usage text works anywhere, a run
+    without a CUDA device fails loudly instead of computing on the CPU."""
+    import subprocess
+    import torch
+    exe = os.path.join(ROOT, "kreeq_b200", "kreeq")
+    assert os.path.exists(exe)
+    p = subprocess.run([exe], capture_output=True)
+    assert p.returncode == 0 and b"validate" in p.stdout and b"union" in p.stdout
+    p = subprocess.run([exe, "validate", "-h"], capture_output=True)
+    assert p.returncode == 0 and b"--input-reads" in p.stdout and b"--coverage-cutoff" in p.stdout
+    p = subprocess.run([exe, "union", "-d", os.path.join(GOLD, "inputs", "random1.fastq")], capture_output=True)
+    assert p.returncode != 0 and b"At least two databases required (-d)." in p.stderr
+    if not torch.cuda.is_available():
+        reads = os.path.join(GOLD, "inputs", "random1.fastq")
+        p = subprocess.run([exe, "validate", "-r", reads], capture_output=True, cwd=str(tmp_path))
+        assert p.returncode != 0 and p.stdout == b"" and p.stderr.strip()

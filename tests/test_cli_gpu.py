@@ -1,0 +1,132 @@
+"""The `kreeq` command line (kreeq_b200/kreeq, C++ over the C-ABI) against the reference's own outputs:
+its 36 stdout goldens (validateFiles/test.0-35.tst, commands unchanged apart from the input directory) and
+the committed reference-binary runs (database content, stdout, .kwig / .bed / .bkwig bytes, union orders).
+Nothing here reads /root/reference; everything runs on the GPU through libkreeq_b200.so."""
+import gzip
+import json
+import os
+import shlex
+import subprocess
+import tarfile
+
+import numpy as np
+import pytest
+
+import kreeq_oracle as ko
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLD = os.path.join(ROOT, "tests", "golden")
+EXE = os.path.join(ROOT, "kreeq_b200", "kreeq")
+
+with open(os.path.join(GOLD, "ref_golden.json")) as f:
+    REF = json.load(f)
+with open(os.path.join(GOLD, "ref_runs.json")) as f:
+    RUNS = json.load(f)
+
+
+def run(args, cwd):
+    p = subprocess.run([EXE] + args, cwd=cwd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, timeout=600)
+    assert p.returncode == 0, p.stderr.decode()
+    return p.stdout.decode()
+
+
+def _gz(rel):
+    with open(os.path.join(GOLD, rel), "rb") as f:
+        return gzip.decompress(f.read())
+
+
+@pytest.fixture(scope="module")
+def fixture_dbs(tmp_path_factory):
+    d = tmp_path_factory.mktemp("fixture_dbs")
+    with tarfile.open(os.path.join(GOLD, "fixture_dbs.tar.gz")) as tar:
+        tar.extractall(d)
+    return str(d)
+
+
+@pytest.mark.parametrize("name", sorted(REF, key=lambda s: int(s.split(".")[1])))
+def test_reference_goldens_through_the_cli(name, fixture_dbs, tmp_path):
+    """Same command lines as validateFiles/test.N.tst; stdout must be byte-identical."""
+    args = shlex.split(REF[name]["cmd"])[1:]
+    fixed = []
+    for a in args:
+        if a.startswith("testFiles/") and a.endswith(".kreeq"):
+            a = os.path.join(fixture_dbs, a[len("testFiles/"):])
+        elif a.startswith("testFiles/"):
+            a = os.path.join(GOLD, "inputs", a[len("testFiles/"):])
+        fixed.append(a)
+    assert run(fixed, str(tmp_path)) == REF[name]["stdout"]
+
+
+def _db_arrays(path):
+    t = ko.read_db(path, check=True)
+    return t.dump8() + t.dump32()
+
+
+@pytest.mark.parametrize("name", [n for n in sorted(RUNS) if n != "union"])
+def test_reference_binary_runs_through_the_cli(name, tmp_path):
+    """count -> .kreeq (decoded records equal the reference's), then validate from that database into
+    .kwig / .bed / .bkwig: stdout and file bytes equal the reference binary's."""
+    r = RUNS[name]
+    k, cutoff = r["k"], r["cutoff"]
+    reads = [os.path.join(GOLD, p) for p in r["reads"]]
+    asm = os.path.join(GOLD, r["asm"])
+    db = str(tmp_path / "db.kreeq")
+    assert run(["validate", "-r"] + reads + ["-k", str(k), "-o", db], str(tmp_path)) == r["count_stdout"]
+    k8, r8, k32, r32 = _db_arrays(db)
+    gold = np.load(os.path.join(GOLD, "ref_runs", name + ".db.npz"))
+    assert np.array_equal(k8, gold["k8"]) and np.array_equal(k32, gold["k32"])
+    live = r8["cov"] != 255
+    assert r8[live].tobytes() == gold["r8"][live].tobytes()
+    assert r32.tobytes() == gold["r32"].tobytes()
+    for ext in ("kwig", "bed", "bkwig"):
+        out = str(tmp_path / ("x." + ext))
+        stdout = run(["validate", "-f", asm, "-d", db, "-k", str(k), "-c", str(cutoff), "-o", out], str(tmp_path))
+        assert stdout == r["validate_stdout"]
+        with open(out, "rb") as f:
+            assert f.read() == _gz("ref_runs/%s.%s.gz" % (name, ext)), ext
+    # one-shot form (reads + assembly in one call) prints the same two blocks
+    assert run(["validate", "-f", asm, "-r"] + reads + ["-k", str(k), "-c", str(cutoff)], str(tmp_path)) == r["validate_stdout"]
+
+
+@pytest.fixture(scope="module")
+def union_inputs(tmp_path_factory):
+    d = tmp_path_factory.mktemp("union_inputs")
+    with tarfile.open(os.path.join(GOLD, "ref_runs", "union_inputs.tar.gz")) as tar:
+        tar.extractall(d)
+    return str(d)
+
+
+@pytest.mark.parametrize("tag", sorted(RUNS["union"]))
+def test_union_orders_through_the_cli(union_inputs, tag, tmp_path):
+    """`kreeq union` is order dependent for high-copy keys: all three orders."""
+    g = RUNS["union"][tag]
+    dbs = [os.path.join(union_inputs, "u%d.kreeq" % i) for i in g["order"]]
+    out = str(tmp_path / "u.kreeq")
+    assert run(["union", "-d"] + dbs + ["-o", out], str(tmp_path)) == g["stdout"]
+    k8, r8, k32, r32 = _db_arrays(out)
+    gold = np.load(os.path.join(GOLD, "ref_runs", "union%s.db.npz" % tag))
+    assert np.array_equal(k8, gold["k8"]) and np.array_equal(k32, gold["k32"])
+    assert r32.tobytes() == gold["r32"].tobytes()
+    live = r8["cov"] != 255
+    assert r8[live].tobytes() == gold["r8"][live].tobytes()
+    kwig = str(tmp_path / "u.kwig")
+    asm = os.path.join(GOLD, "inputs", "repeat1.fasta")
+    assert run(["validate", "-f", asm, "-d", out, "-o", kwig], str(tmp_path)) == g["validate_stdout"]
+    with open(kwig) as f:
+        assert f.read() == g["kwig"]
+
+
+def test_hist_and_errors(tmp_path):
+    reads = os.path.join(GOLD, "inputs", "random1.fastq")
+    hist = str(tmp_path / "x.hist")
+    run(["validate", "-r", reads, "-o", hist], str(tmp_path))
+    rows = [tuple(map(int, ln.split("\t"))) for ln in open(hist).read().splitlines()]
+    assert rows == sorted(rows) and sum(c * n for c, n in rows) == 172 and sum(n for _, n in rows) == 96
+    p = subprocess.run([EXE, "validate", "-r", reads, "-k", "33"], cwd=str(tmp_path), capture_output=True)
+    assert p.returncode != 0 and b"Invalid kmer length." in p.stderr
+    p = subprocess.run([EXE, "union", "-d", reads], cwd=str(tmp_path), capture_output=True)
+    assert p.returncode != 0 and b"At least two databases required (-d)." in p.stderr
+    p = subprocess.run([EXE, "frobnicate", "-x", "y"], cwd=str(tmp_path), capture_output=True)
+    assert p.returncode != 0 and b"does not exist" in p.stderr
