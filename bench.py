@@ -270,7 +270,15 @@ def main_ours(args):
     stream = torch.cuda.Stream(dev)
     torch.cuda.set_stream(stream)
     g.set_stream(stream.cuda_stream)
-    router = shard.RoutedCounter(g, rank, world, 512 << 20, dev) if world > 1 else None
+    # multi-GPU count: tuples go to their owner inside the scatter kernel (peer stores over NVLink);
+    # KQ_TRANSPORT=nccl selects the staged all-to-all (extract -> ncclSend/Recv -> second scatter) instead
+    transport = os.environ.get("KQ_TRANSPORT", "peer") if world > 1 else None
+    if transport == "peer":
+        router = shard.PeerRoutedCounter(g, rank, world, 512 << 20, dev, stream=stream)
+    elif transport == "nccl":
+        router = shard.RoutedCounter(g, rank, world, 512 << 20, dev)
+    else:
+        router = None
 
     def count_resident():
         total = reads_np.size - K + 1
@@ -366,7 +374,7 @@ def main_ours(args):
     line = {"metric": "kmers_counted_per_sec", "value": value, "unit": "k-mers/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": res["count_ms"] + res["validate_ms"],
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-            "config": dict(cfg, parallelism="keyshard%d" % world, kmer_instances_per_step=inst_total,
+            "config": dict(cfg, parallelism="keyshard%d" % world, exchange=transport, kmer_instances_per_step=inst_total,
                            assembly_kmers_per_step=asm_k, distinct_kmers=None,
                            l2="no flush needed: table (%.1f GB/GPU) and inputs (%.2f GB/GPU) are far larger than the 126 MB L2"
                               % (est_distinct / 0.5 * 16 / 1e9, reads_np.size * 0.375 / 1e9)),

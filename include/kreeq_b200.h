@@ -173,6 +173,32 @@ int  kq_dev_extract_route(kq_ctx *ctx, const uint64_t *d_bases, const uint64_t *
                           void *d_tuples, uint64_t cap_per_rank, unsigned long long *d_counts);
 /* insert n tuples (row A3) already resident on the device (all owned by this shard) */
 int  kq_dev_insert_tuples(kq_ctx *ctx, const void *d_tuples, uint64_t n);
+/* ---- routed count over peer memory (count's exchange step) -----------------------
+ * One process per GPU, handles sharded with kq_set_shard.  The all-to-all of (key, edgeBit) tuples the
+ * reference design calls for (8e "Collective") is fused into the scatter kernel: every rank writes the
+ * tuples a peer owns straight into that peer's receive slab (peer-mapped memory, NVLink), in slice order,
+ * and the peer only runs the insert kernel over its slab.  Per round of k-mer start positions:
+ *   kq_route_hist      tuples this rank sends into every (owner, hash range) bin -> d_hist[kq_route_bins]
+ *   (caller)           all-gather the histograms of all ranks: d_all_hist[nranks][bins]; this collective
+ *                      also orders the round after every rank's previous kq_route_insert
+ *   kq_route_scatter   offsets from d_all_hist, capacity check (same verdict on every rank), scatter into
+ *                      the owners' slabs; *nrecv = tuples this rank receives
+ *   (caller)           barrier on the stream (all slabs complete)
+ *   kq_route_insert    count the nrecv tuples of the local slab (row A3)
+ * Set-up: kq_route_setup allocates the slab (slab_tuples tuples; nb_bits = log2 hash ranges per owner,
+ * nranks << nb_bits bins must fit shared memory: <= 2048) and returns its device pointer and a 64-byte
+ * CUDA IPC handle; peers open it with kq_route_open; kq_route_connect takes the nranks slab pointers
+ * (own slab at index rank).  Within one process pass the pointers directly. */
+int  kq_route_setup(kq_ctx *ctx, uint64_t slab_tuples, int nb_bits, void **d_slab, void *ipc_handle64);
+int  kq_route_open(kq_ctx *ctx, const void *ipc_handle64, void **d_ptr);
+int  kq_route_connect(kq_ctx *ctx, void *const *slabs);
+int  kq_route_bins(kq_ctx *ctx);
+int  kq_route_hist(kq_ctx *ctx, const uint64_t *d_bases, const uint64_t *d_invalid, uint64_t len,
+                   uint64_t pos0, uint64_t npos, unsigned long long *d_hist);
+int  kq_route_scatter(kq_ctx *ctx, const uint64_t *d_bases, const uint64_t *d_invalid, uint64_t len,
+                      uint64_t pos0, uint64_t npos, const unsigned long long *d_all_hist, uint64_t *nrecv);
+int  kq_route_insert(kq_ctx *ctx, uint64_t n);
+
 /* probe positions [0, len-k+1) of one packed device-resident segment;
  * d_out (len entries) and d_acc (kq_qv, accumulates) are device memory. */
 int  kq_dev_validate_packed(kq_ctx *ctx, const uint64_t *d_bases, const uint64_t *d_invalid,
@@ -190,7 +216,7 @@ int  kq_set_flush_positions(kq_ctx *ctx, uint64_t positions);
 int  kq_counters(kq_ctx *ctx, uint64_t *kernel_launches, uint64_t *h2d_bytes, uint64_t *d2h_bytes);
 /* CUDA-event time (ms) on the launching stream since the last call with reset=1:
  * which = 0 whole count pipeline (per batch), 1 validate/probe kernel, 2 insert kernel,
- * 3 slice histogram + scatter (or extract_route).  Only measured when kq_set_timing(ctx,1). */
+ * 3 slice histogram + scatter (or extract_route / kq_route_hist + kq_route_scatter).  Only measured when kq_set_timing(ctx,1). */
 int  kq_set_timing(kq_ctx *ctx, int on);
 int  kq_kernel_time_ms(kq_ctx *ctx, int which, double *ms, uint64_t *launches, int reset);
 

@@ -72,6 +72,13 @@ PROTOTYPES = {
     "kq_dev_extract_route": (_i, [_vp, _vp, _vp, _u64, _u64, _u64, _vp, _u64, _vp]),
     "kq_dev_insert_tuples": (_i, [_vp, _vp, _u64]),
     "kq_set_flush_positions": (_i, [_vp, _u64]),
+    "kq_route_setup": (_i, [_vp, _u64, _i, C.POINTER(_vp), _vp]),
+    "kq_route_open": (_i, [_vp, _vp, C.POINTER(_vp)]),
+    "kq_route_connect": (_i, [_vp, C.POINTER(_vp)]),
+    "kq_route_bins": (_i, [_vp]),
+    "kq_route_hist": (_i, [_vp, _vp, _vp, _u64, _u64, _u64, _vp]),
+    "kq_route_scatter": (_i, [_vp, _vp, _vp, _u64, _u64, _u64, _vp, C.POINTER(_u64)]),
+    "kq_route_insert": (_i, [_vp, _u64]),
     "kq_dev_validate_packed": (_i, [_vp, _vp, _vp, _u64, C.c_uint32, _vp, _vp]),
     "kq_reserve": (_i, [_vp, _u64]),
     "kq_counters": (_i, [_vp, C.POINTER(_u64), C.POINTER(_u64), C.POINTER(_u64)]),

@@ -75,6 +75,11 @@ struct kq_ctx {
     unsigned long long *d_hist = nullptr, *d_cursor = nullptr; uint64_t hist_cap = 0;
     unsigned long long *d_total = nullptr, *d_nsrc = nullptr, *d_ticket = nullptr;
     uint64_t *d_ovf = nullptr; unsigned long long *d_ovf_n = nullptr; bool ovf_pending = false;
+    // routed (multi-GPU) pipeline: receive slab the owners' tuples are written into by every rank
+    uint64_t *d_slab = nullptr; uint64_t slab_cap = 0;          // tuples
+    RouteMap route{}; bool route_ready = false;
+    std::vector<void *> ipc_opened;
+    unsigned long long *d_rcursor = nullptr, *d_rtotals = nullptr;
     Stage st[NBUF]; int next_stage = 0;
     uint64_t launches = 0, h2d = 0, d2h = 0;
     bool timing = false; std::vector<TimedRange> ranges; std::vector<cudaEvent_t> ev_pool;
@@ -204,7 +209,7 @@ cudaEvent_t get_event(kq_ctx *c) {
 }
 // CUDA-event bracket on the launching stream; returns the index of the open range or -1
 int time_begin(kq_ctx *c, int which) {
-    if (!c->timing) return -1;
+    if (!c->timing || which < 0) return -1;
     TimedRange r{get_event(c), get_event(c), which};
     cudaEventRecord(r.a, c->stream); c->ranges.push_back(r);
     return (int)c->ranges.size() - 1;
@@ -282,9 +287,11 @@ int run_batch(kq_ctx *c, Source src) {
     { int rc = pipeline_scratch(c, 0); if (rc) return rc; }
     const int t0 = time_begin(c, 0);
     // a sweep over the table pays off once the batch touches a good part of it
-    if (c->nslices == 1 || cap == 0 || (double)bound < 0.25 * (double)table_slots(c)) {
+    if (src.ordered || c->nslices == 1 || cap == 0 || (double)bound < 0.25 * (double)table_slots(c)) {
         if (src.tuples) {
+            const int t2 = time_begin(c, src.ordered ? 2 : -1);
             CU(launch_insert_tuples(c->stream, tv, src.tuples, src.ntuples, bound, c->d_ovf, OVF_CAP, c->d_ovf_n, c->d_ticket, &c->launches));
+            time_end(c, t2);
             c->ovf_pending = true;
         } else {
             CU(launch_count_direct(c->stream, tv, src, c->d_inst, c->d_ovf, OVF_CAP, c->d_ovf_n, &c->launches));
@@ -449,6 +456,8 @@ extern "C" void kq_destroy(kq_ctx *c) {
     cudaFree(c->T); cudaFree(c->R); cudaFree(c->M); cudaFree(c->d_occ); cudaFree(c->d_inst); cudaFree(c->d_acc); cudaFree(c->d_err);
     cudaFree(c->d_pb); cudaFree(c->d_pi); cudaFree(c->d_tuples); cudaFree(c->d_hist); cudaFree(c->d_cursor);
     cudaFree(c->d_total); cudaFree(c->d_nsrc); cudaFree(c->d_ticket); cudaFree(c->d_ovf); cudaFree(c->d_ovf_n);
+    for (void *p : c->ipc_opened) cudaIpcCloseMemHandle(p);
+    cudaFree(c->d_slab); cudaFree(c->d_rcursor); cudaFree(c->d_rtotals);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     delete c;
 }
@@ -631,6 +640,116 @@ extern "C" int kq_dev_insert_tuples(kq_ctx *c, const void *d_tuples, uint64_t n)
     CU(cudaSetDevice(c->device));
     int rc = pending_flush(c); if (rc) return rc;
     rc = count_source(c, Source{nullptr, nullptr, 0, 0, static_cast<const uint64_t *>(d_tuples), c->d_nsrc, n}); if (rc) return rc;
+    c->inst_tuples += n;
+    return KQ_OK;
+}
+
+// ---- routed count over peer memory (row E) ---------------------------------------------------------------
+// One process per GPU.  Every rank owns a receive slab; the scatter kernel of every rank writes the tuples
+// a slab's owner must count straight into it (peer-mapped pointers, NVLink), already in slice order, so
+// the all-to-all is the scatter kernel's own stores and the receiver only runs the insert kernel.
+
+extern "C" int kq_route_setup(kq_ctx *c, uint64_t slab_tuples, int nb_bits, void **d_slab, void *ipc_handle) {
+    if (!c || !slab_tuples || nb_bits < 0 || nb_bits > 12) return KQ_EINVAL;
+    if (c->nranks > KQ_MAX_RANKS) return fail(c, KQ_EINVAL, "kq_route_setup: too many ranks");
+    CU(cudaSetDevice(c->device));
+    const int tw = tuple_words(c->k);
+    if (scatter_pick_cap((unsigned long long)c->nranks << nb_bits, tw) == 0)
+        return fail(c, KQ_EINVAL, "kq_route_setup: nranks << nb_bits bins do not fit shared memory");
+    CU(cudaStreamSynchronize(c->stream));
+    for (void *p : c->ipc_opened) cudaIpcCloseMemHandle(p);
+    c->ipc_opened.clear();
+    cudaFree(c->d_slab); c->d_slab = nullptr; c->slab_cap = 0; c->route_ready = false;
+    CU(cudaMalloc(&c->d_slab, slab_tuples * 8 * tw));
+    c->slab_cap = slab_tuples;
+    if (!c->d_rcursor) {
+        CU(cudaMalloc(&c->d_rcursor, (size_t)KQ_MAX_RANKS * 4096 * 8));
+        CU(cudaMalloc(&c->d_rtotals, KQ_MAX_RANKS * 8));
+    }
+    c->route = RouteMap{};
+    c->route.nranks = c->nranks; c->route.nb_bits = nb_bits;
+    c->route.shift = view(c).shard_shift;
+    if (d_slab) *d_slab = c->d_slab;
+    if (ipc_handle) {
+        cudaIpcMemHandle_t h;
+        CU(cudaIpcGetMemHandle(&h, c->d_slab));
+        static_assert(sizeof h == 64, "CUDA IPC handles are 64 bytes");
+        std::memcpy(ipc_handle, &h, sizeof h);
+    }
+    return KQ_OK;
+}
+
+extern "C" int kq_route_open(kq_ctx *c, const void *ipc_handle, void **d_ptr) {
+    if (!c || !ipc_handle || !d_ptr) return KQ_EINVAL;
+    CU(cudaSetDevice(c->device));
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, ipc_handle, sizeof h);
+    void *p = nullptr;
+    CU(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    c->ipc_opened.push_back(p);
+    *d_ptr = p;
+    return KQ_OK;
+}
+
+extern "C" int kq_route_connect(kq_ctx *c, void *const *slabs) {
+    if (!c || !slabs || !c->d_slab) return KQ_EINVAL;
+    for (int r = 0; r < c->nranks; ++r) {
+        if (!slabs[r]) return fail(c, KQ_EINVAL, "kq_route_connect: NULL slab pointer");
+        c->route.out[r] = static_cast<uint64_t *>(slabs[r]);
+    }
+    if (c->route.out[c->rank] != c->d_slab) return fail(c, KQ_EINVAL, "kq_route_connect: slabs[rank] is not this handle's slab");
+    c->route_ready = true;
+    return KQ_OK;
+}
+
+extern "C" int kq_route_bins(kq_ctx *c) { return c && c->d_slab ? c->nranks << c->route.nb_bits : KQ_EINVAL; }
+
+extern "C" int kq_route_hist(kq_ctx *c, const uint64_t *d_bases, const uint64_t *d_invalid, uint64_t len,
+                             uint64_t pos0, uint64_t npos, unsigned long long *d_hist) {
+    if (!c || !d_bases || !d_invalid || !d_hist) return KQ_EINVAL;
+    if (!c->d_slab) return fail(c, KQ_ESTATE, "kq_route_hist: call kq_route_setup first");
+    if (len < (uint64_t)c->k) npos = 0;
+    else if (pos0 + npos > len - c->k + 1) return fail(c, KQ_EINVAL, "kq_route_hist: positions beyond len-k+1");
+    CU(cudaSetDevice(c->device));
+    const int t = time_begin(c, 3);
+    CU(launch_route_hist(c->stream, view(c), Source{d_bases, d_invalid, pos0, npos, nullptr, nullptr, 0, 0}, c->route, d_hist, &c->launches));
+    time_end(c, t);
+    return KQ_OK;
+}
+
+extern "C" int kq_route_scatter(kq_ctx *c, const uint64_t *d_bases, const uint64_t *d_invalid, uint64_t len,
+                                uint64_t pos0, uint64_t npos, const unsigned long long *d_all_hist, uint64_t *nrecv) {
+    if (!c || !d_bases || !d_invalid || !d_all_hist || !nrecv) return KQ_EINVAL;
+    if (!c->route_ready) return fail(c, KQ_ESTATE, "kq_route_scatter: call kq_route_connect first");
+    if (len < (uint64_t)c->k) npos = 0;
+    else if (pos0 + npos > len - c->k + 1) return fail(c, KQ_EINVAL, "kq_route_scatter: positions beyond len-k+1");
+    CU(cudaSetDevice(c->device));
+    const int t = time_begin(c, 3);
+    CU(launch_route_offsets(c->stream, c->route, c->rank, d_all_hist, c->d_rcursor, c->d_rtotals, &c->launches));
+    unsigned long long totals[KQ_MAX_RANKS];
+    CU(cudaMemcpyAsync(totals, c->d_rtotals, c->nranks * 8, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    for (int r = 0; r < c->nranks; ++r)                  // every rank sees the same totals and takes the same decision
+        if (totals[r] > c->slab_cap) {
+            time_end(c, t);
+            return fail(c, KQ_ENOMEM, "kq_route_scatter: rank " + std::to_string(r) + " would receive " + std::to_string(totals[r]) +
+                                      " tuples, its slab holds " + std::to_string(c->slab_cap) + " (smaller rounds or a larger slab)");
+        }
+    const int tw = tuple_words(c->k);
+    const int cap = scatter_pick_cap((unsigned long long)c->nranks << c->route.nb_bits, tw);
+    CU(launch_route_scatter(c->stream, view(c), Source{d_bases, d_invalid, pos0, npos, nullptr, nullptr, 0, 0}, c->route, c->d_rcursor, cap, &c->launches));
+    time_end(c, t);
+    *nrecv = totals[c->rank];
+    return KQ_OK;
+}
+
+extern "C" int kq_route_insert(kq_ctx *c, uint64_t n) {
+    if (!c || !c->d_slab || n > c->slab_cap) return KQ_EINVAL;
+    if (c->loaded_db) return fail(c, KQ_ESTATE, "kq_route_insert: the table holds a loaded/merged database");
+    if (!n) return KQ_OK;
+    CU(cudaSetDevice(c->device));
+    int rc = pending_flush(c); if (rc) return rc;
+    rc = count_source(c, Source{nullptr, nullptr, 0, 0, c->d_slab, c->d_nsrc, n, 1}); if (rc) return rc;
     c->inst_tuples += n;
     return KQ_OK;
 }

@@ -162,11 +162,27 @@ count_direct_kernel(TableView tv, Source src, unsigned long long *instances,
 
 // ---- count, step 1: tuples per slice -----------------------------------------------------------------
 
-template <int TW>
+// Bin of a key: its slice in the local pipeline; in the routed (multi-GPU) pipeline the owner rank in the
+// high bits and 2^nb_bits equal ranges of the slice hash below.  Both are monotone in the slice hash, so
+// tuples in bin order are in slice order on the table that receives them, whatever its geometry.
+template <bool RT>
+__device__ __forceinline__ unsigned bin_of_key(const TableView &tv, const RouteMap &rt, uint64_t key) {
+    if (!RT) return (unsigned)slice_of_key(key, tv.nslices);
+    const unsigned owner = (unsigned)(key & 127u) >> rt.shift;
+    const uint64_t h = (uint32_t)((key * 0x9E3779B97F4A7C15ULL) >> 32);
+    return (owner << rt.nb_bits) | (unsigned)(h >> (32 - rt.nb_bits));
+}
+template <bool RT>
+__device__ __forceinline__ unsigned bin_count(const TableView &tv, const RouteMap &rt) {
+    return RT ? (unsigned)rt.nranks << rt.nb_bits : (unsigned)tv.nslices;
+}
+
+template <int TW, bool RT>
 __global__ void __launch_bounds__(TPB, 4)
-slice_hist_kernel(TableView tv, Source src, unsigned long long *hist) {
+slice_hist_kernel(TableView tv, Source src, unsigned long long *hist, RouteMap rt) {
     extern __shared__ unsigned int h[];
-    for (unsigned i = threadIdx.x; i < tv.nslices; i += TPB) h[i] = 0;
+    const unsigned P = bin_count<RT>(tv, rt);
+    for (unsigned i = threadIdx.x; i < P; i += TPB) h[i] = 0;
     __syncthreads();
     const uint64_t total = source_total(src), per = (uint64_t)TPB * RUN;
     for (uint64_t tile = (uint64_t)blockIdx.x * per; tile < total; tile += (uint64_t)gridDim.x * per) {
@@ -174,10 +190,10 @@ slice_hist_kernel(TableView tv, Source src, unsigned long long *hist) {
         const uint32_t m = produce<TW>(src, tv, tile, total, key, e);
 #pragma unroll
         for (int i = 0; i < RUN; ++i)
-            if (m >> i & 1u) atomicAdd(&h[slice_of_key(key[i], tv.nslices)], 1u);
+            if (m >> i & 1u) atomicAdd(&h[bin_of_key<RT>(tv, rt, key[i])], 1u);
     }
     __syncthreads();
-    for (unsigned i = threadIdx.x; i < tv.nslices; i += TPB)
+    for (unsigned i = threadIdx.x; i < P; i += TPB)
         if (h[i]) atomicAdd(&hist[i], (unsigned long long)h[i]);
 }
 
@@ -203,17 +219,54 @@ slice_offsets_kernel(unsigned long long nslices, const unsigned long long *hist,
     for (unsigned long long i = b; i < e; ++i) { cursor[i] = s; s += hist[i]; }
 }
 
+// Routed pipeline: H[s][b] = tuples rank s sends into global bin b = (owner d, j).  Destination d lays its
+// receive slab out bin by bin and, inside a bin, sender by sender; CTA d computes where THIS rank's (me)
+// tuples for each of d's bins start, and how many tuples d receives in total.
+__global__ void __launch_bounds__(1024, 1)
+route_offsets_kernel(int nranks, unsigned nb, int me, const unsigned long long *H, unsigned long long *cursor,
+                     unsigned long long *recv_totals) {
+    __shared__ unsigned long long part[1024];
+    const unsigned d = blockIdx.x, P = (unsigned)nranks * nb;
+    const unsigned per = (nb + 1023) / 1024;
+    const unsigned b = threadIdx.x * per, e = min(nb, b + per);
+    unsigned long long s = 0;
+    for (unsigned j = b; j < e; ++j)
+        for (int r = 0; r < nranks; ++r) s += H[(size_t)r * P + d * nb + j];
+    part[threadIdx.x] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long run = 0;
+        for (int i = 0; i < 1024; ++i) { const unsigned long long v = part[i]; part[i] = run; run += v; }
+        recv_totals[d] = run;
+    }
+    __syncthreads();
+    s = part[threadIdx.x];
+    for (unsigned j = b; j < e; ++j) {
+        unsigned long long before = 0, all = 0;
+        for (int r = 0; r < nranks; ++r) {
+            const unsigned long long v = H[(size_t)r * P + d * nb + j];
+            if (r < me) before += v;
+            all += v;
+        }
+        cursor[d * nb + j] = s + before;
+        s += all;
+    }
+}
+
 // ---- count, step 3: scatter into slice order -------------------------------------------------------------
 
 // Shared memory: nslices bins of `cap` tuples + one fill counter per bin.  A tuple is appended to its
 // bin with one shared-memory atomic; a bin that reaches `cap` entries is flushed by one warp as ONE
 // coalesced cap * 8 * TW byte store (256 B for cap = 32) at a position reserved with one global atomic
 // on the slice's cursor.  Random 256-byte stores run at ~5.4 TB/s on B200 (r01_gups_footprint_sweep.log).
-template <int TW, int R, int NT>
+// Routed form (RT): bins are (owner rank, hash range) and a bin's tuples go to the receive slab of its owner
+// -- rt.out[owner], a peer-mapped pointer -- so the flush below IS the all-to-all: 64..256-byte stores
+// straight over NVLink, overlapped with the extraction of the next tuples.
+template <int TW, int R, int NT, bool RT>
 __global__ void __launch_bounds__(NT, 1)
-slice_scatter_kernel(TableView tv, Source src, uint64_t *__restrict__ out, unsigned long long *cursor, int cap) {
+slice_scatter_kernel(TableView tv, Source src, uint64_t *__restrict__ out, unsigned long long *cursor, int cap, RouteMap rt) {
     extern __shared__ uint64_t sm[];
-    const unsigned P = (unsigned)tv.nslices;
+    const unsigned P = bin_count<RT>(tv, rt);
     uint64_t *bins = sm;
     unsigned int *fill = reinterpret_cast<unsigned int *>(bins + (size_t)P * cap * TW);
     for (unsigned i = threadIdx.x; i < P; i += NT) fill[i] = 0;
@@ -227,7 +280,7 @@ slice_scatter_kernel(TableView tv, Source src, uint64_t *__restrict__ out, unsig
 #pragma unroll
         for (int i = 0; i < R; ++i) {
             if (!(m >> i & 1u)) continue;
-            bin[i] = (unsigned)slice_of_key(key[i], tv.nslices);
+            bin[i] = bin_of_key<RT>(tv, rt, key[i]);
             slot[i] = atomicAdd(&fill[bin[i]], 1u);
             filled |= slot[i] >= (unsigned)cap - 1;
         }
@@ -252,7 +305,7 @@ slice_scatter_kernel(TableView tv, Source src, uint64_t *__restrict__ out, unsig
                     const int l = __ffs(todo) - 1; todo &= todo - 1;
                     const unsigned long long gg = __shfl_sync(0xffffffffu, g, l);
                     const uint64_t *srcw = bins + (size_t)(b0 + l) * cap * TW;
-                    uint64_t *dst = out + gg * TW;
+                    uint64_t *dst = (RT ? rt.out[(b0 + l) >> rt.nb_bits] : out) + gg * TW;
                     for (unsigned w = lane; w < (unsigned)cap * TW; w += 32) __stcs(dst + w, srcw[w]);
                 }
             }
@@ -279,7 +332,7 @@ slice_scatter_kernel(TableView tv, Source src, uint64_t *__restrict__ out, unsig
             const unsigned long long gg = __shfl_sync(0xffffffffu, g, l);
             const unsigned ff = __shfl_sync(0xffffffffu, f, l);
             const uint64_t *srcw = bins + (size_t)(b0 + l) * cap * TW;
-            uint64_t *dst = out + gg * TW;
+            uint64_t *dst = (RT ? rt.out[(b0 + l) >> rt.nb_bits] : out) + gg * TW;
             for (unsigned w = lane; w < ff * TW; w += 32) __stcs(dst + w, srcw[w]);
         }
     }
@@ -480,7 +533,48 @@ cudaError_t launch_slice_hist(cudaStream_t st, const TableView &tv, const Source
     if (!n) return cudaSuccess;
     const unsigned grid = std::min<uint64_t>((n + TPB * RUN - 1) / (TPB * RUN), (uint64_t)sm_count() * 4);
     const size_t smem = (size_t)tv.nslices * 4;
-    KQ_TW_DISPATCH(tuple_words(tv.k), (slice_hist_kernel<TW><<<grid, TPB, smem, st>>>(tv, src, hist)));
+    KQ_TW_DISPATCH(tuple_words(tv.k), (slice_hist_kernel<TW, false><<<grid, TPB, smem, st>>>(tv, src, hist, RouteMap{})));
+    ++*launches;
+    return cudaGetLastError();
+}
+
+// ---- routed (multi-GPU) pipeline: the same histogram and scatter kernels over (owner, hash range) bins ----
+
+static TableView unsharded(const TableView &tv) { TableView v = tv; v.shard_rank = -1; return v; }   // route every k-mer
+
+cudaError_t launch_route_hist(cudaStream_t st, const TableView &tv, const Source &src, const RouteMap &rt,
+                              unsigned long long *hist, uint64_t *launches) {
+    const uint64_t n = source_bound(src);
+    const unsigned P = (unsigned)rt.nranks << rt.nb_bits;
+    cudaError_t e = cudaMemsetAsync(hist, 0, (size_t)P * 8, st);
+    if (e != cudaSuccess || !n) return e;
+    const unsigned grid = std::min<uint64_t>((n + TPB * RUN - 1) / (TPB * RUN), (uint64_t)sm_count() * 4);
+    KQ_TW_DISPATCH(tuple_words(tv.k), (slice_hist_kernel<TW, true><<<grid, TPB, (size_t)P * 4, st>>>(unsharded(tv), src, hist, rt)));
+    ++*launches;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_route_offsets(cudaStream_t st, const RouteMap &rt, int me, const unsigned long long *H,
+                                 unsigned long long *cursor, unsigned long long *recv_totals, uint64_t *launches) {
+    route_offsets_kernel<<<rt.nranks, 1024, 0, st>>>(rt.nranks, 1u << rt.nb_bits, me, H, cursor, recv_totals);
+    ++*launches;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_route_scatter(cudaStream_t st, const TableView &tv, const Source &src, const RouteMap &rt,
+                                 unsigned long long *cursor, int cap, uint64_t *launches) {
+    const uint64_t n = source_bound(src);
+    if (!n) return cudaSuccess;
+    const int tw = tuple_words(tv.k);
+    const size_t smem = scatter_smem_bytes((unsigned long long)rt.nranks << rt.nb_bits, cap, tw);
+    const TableView v = unsharded(tv);
+    cudaError_t e = cudaSuccess;
+#define KQ_ROUTE_LAUNCH(TWV, RV, NTV) do {                                                                           \
+        e = cudaFuncSetAttribute(slice_scatter_kernel<TWV, RV, NTV, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+        if (e != cudaSuccess) return e;                                                                             \
+        const unsigned grid = std::min<uint64_t>((n + NTV * RV - 1) / (NTV * RV), (uint64_t)sm_count());           \
+        slice_scatter_kernel<TWV, RV, NTV, true><<<grid, NTV, smem, st>>>(v, src, nullptr, cursor, cap, rt); } while (0)
+    if (tw == 1) KQ_ROUTE_LAUNCH(1, 16, 512); else KQ_ROUTE_LAUNCH(2, 8, 512);
     ++*launches;
     return cudaGetLastError();
 }
@@ -509,10 +603,10 @@ cudaError_t launch_slice_scatter(cudaStream_t st, const TableView &tv, const Sou
     static const int variant = [] { const char *e = std::getenv("KQ_SC_VARIANT"); return e ? std::atoi(e) : 0; }();
     cudaError_t e = cudaSuccess;
 #define KQ_SCATTER_LAUNCH(TWV, RV, NTV) do {                                                                        \
-        e = cudaFuncSetAttribute(slice_scatter_kernel<TWV, RV, NTV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+        e = cudaFuncSetAttribute(slice_scatter_kernel<TWV, RV, NTV, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
         if (e != cudaSuccess) return e;                                                                             \
         const unsigned grid = std::min<uint64_t>((n + NTV * RV - 1) / (NTV * RV), (uint64_t)sm_count());           \
-        slice_scatter_kernel<TWV, RV, NTV><<<grid, NTV, smem, st>>>(tv, src, out, cursor, cap); } while (0)
+        slice_scatter_kernel<TWV, RV, NTV, false><<<grid, NTV, smem, st>>>(tv, src, out, cursor, cap, RouteMap{}); } while (0)
     if (tw == 1) {                                                   // measured on C2 (profiles/): 16 x 512 is the fastest
         if (variant == 1) KQ_SCATTER_LAUNCH(1, 8, 512);
         else if (variant == 2) KQ_SCATTER_LAUNCH(1, 8, 1024);

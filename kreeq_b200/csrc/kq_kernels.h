@@ -31,11 +31,20 @@ struct Source {
     const uint64_t *tuples;            // or tuples already extracted (multi-GPU: received from peers)
     const unsigned long long *ntuples; // device pointer to their number
     uint64_t ntuples_max;              // host-side upper bound of *ntuples (grid sizing)
+    int ordered;                       // host side: the tuples already are in slice order (routed pipeline)
 };
 
 struct RouteArgs {           // destination of extracted tuples (multi-GPU count)
     uint64_t *tuples; unsigned long long cap_per_rank; unsigned long long *counts;
     int nranks, shift;       // owner = (key & 127) >> shift
+};
+
+// routed (multi-GPU) scatter: bins are (owner rank, 2^nb_bits equal ranges of the slice hash); the tuples of
+// owner d go to out[d], the receive slab of rank d (peer-mapped; out[me] is the local one)
+constexpr int KQ_MAX_RANKS = 16;
+struct RouteMap {
+    int nranks, shift, nb_bits;          // owner = (key & 127) >> shift
+    uint64_t *out[KQ_MAX_RANKS];
 };
 
 int sm_count();   // multiprocessors of the current device (cached)
@@ -64,7 +73,16 @@ cudaError_t launch_insert_tuples(cudaStream_t st, const TableView &tv, const uin
                                  const unsigned long long *n, uint64_t n_max, uint64_t *ovf,
                                  unsigned long long ovf_cap, unsigned long long *ovf_n, unsigned long long *ticket,
                                  uint64_t *launches);
-// multi-GPU: extract every valid window and append its tuple to the slab of its owner rank
+// routed pipeline, steps 1-3: hist[nranks << nb_bits] of this rank's tuples; from the all-gathered
+// histograms H[nranks][P] the start of this rank's tuples inside every destination bin (cursor[P]) and what
+// every rank receives (recv_totals[nranks]); scatter straight into the owners' receive slabs
+cudaError_t launch_route_hist(cudaStream_t st, const TableView &tv, const Source &src, const RouteMap &rt,
+                              unsigned long long *hist, uint64_t *launches);
+cudaError_t launch_route_offsets(cudaStream_t st, const RouteMap &rt, int me, const unsigned long long *H,
+                                 unsigned long long *cursor, unsigned long long *recv_totals, uint64_t *launches);
+cudaError_t launch_route_scatter(cudaStream_t st, const TableView &tv, const Source &src, const RouteMap &rt,
+                                 unsigned long long *cursor, int cap, uint64_t *launches);
+// multi-GPU, NCCL transport: extract every valid window and append its tuple to the slab of its owner rank
 cudaError_t launch_extract_route(cudaStream_t st, const TableView &tv, const Source &src, RouteArgs ra,
                                  uint64_t *launches);
 

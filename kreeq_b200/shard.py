@@ -88,14 +88,16 @@ class RoutedCounter:
         self.recv = torch.empty((rcap, self.tb), dtype=torch.uint8, device=device)
         self.a2a_bytes = 0
 
-    def count(self, d_bases, d_invalid, length):
-        """d_bases / d_invalid: int64 device tensors holding the packed sequence of `length` bases."""
+    def count(self, d_bases, d_invalid, length, rounds=None):
+        """d_bases / d_invalid: int64 device tensors holding the packed sequence of `length` bases.
+        Collective: every rank must run the same number of rounds (pass `rounds` when inputs differ)."""
         g, L = self.g, lib()
         k = g.k
-        if length < k:
-            return
-        total = length - k + 1
-        for p0 in range(0, total, self.round_pos):
+        total = max(0, length - k + 1)
+        if rounds is None:
+            rounds = (total + self.round_pos - 1) // self.round_pos
+        for r in range(rounds):
+            p0 = min(r * self.round_pos, total)
             npos = min(self.round_pos, total - p0)
             self.counts.zero_()
             check(L.kq_dev_extract_route(g.handle, C.c_void_p(d_bases.data_ptr()), C.c_void_p(d_invalid.data_ptr()),
@@ -109,3 +111,71 @@ class RoutedCounter:
             nrecv = exchange_tuples(self.send, sc, rc, self.recv)
             self.a2a_bytes += (int(sc.sum()) - int(sc[self.rank])) * self.tb
             check(L.kq_dev_insert_tuples(g.handle, C.c_void_p(self.recv.data_ptr()), nrecv), g.handle)
+
+
+class PeerRoutedCounter:
+    """Same job as RoutedCounter with the exchange fused into the scatter kernel: every rank's scatter
+    writes the tuples a peer owns straight into that peer's receive slab (CUDA IPC peer mapping, NVLink),
+    already in slice order, so a round is  histogram -> all-gather of the histograms (tiny) -> scatter
+    over peer memory -> barrier -> insert;  no tuple ever goes through a send buffer or a second scatter.
+
+    `stream` is the torch stream both the library's kernels and the NCCL collectives are ordered on."""
+
+    def __init__(self, dbg, rank, nranks, round_pos, device, slack=1.3, nb_bits=None, stream=None, group=None):
+        L = lib()
+        self.g, self.rank, self.n, self.round_pos, self.group = dbg, rank, nranks, int(round_pos), group
+        self.device = device
+        self.stream = stream if stream is not None else torch.cuda.Stream(device)
+        dbg.set_stream(self.stream.cuda_stream)
+        if nb_bits is None:                       # 1024 bins in all: 128-byte flushes (2048 for >= 4 ranks: 64-byte)
+            nb_bits = ((1024 if nranks <= 2 else 2048) // nranks).bit_length() - 1
+        self.slab_cap = int(self.round_pos * slack) + 4096
+        slab, handle = C.c_void_p(), (C.c_ubyte * 64)()
+        check(L.kq_route_setup(dbg.handle, self.slab_cap, nb_bits, C.byref(slab), handle), dbg.handle)
+        with torch.cuda.stream(self.stream):
+            mine = torch.tensor(list(handle), dtype=torch.uint8, device=device)
+            handles = torch.empty(nranks * 64, dtype=torch.uint8, device=device)
+            dist.all_gather_into_tensor(handles, mine, group=group)
+            handles = handles.cpu().numpy().reshape(nranks, 64)
+        ptrs = (C.c_void_p * nranks)()
+        for r in range(nranks):
+            if r == rank:
+                ptrs[r] = slab.value
+            else:
+                p = C.c_void_p()
+                check(L.kq_route_open(dbg.handle, C.c_void_p(handles[r].ctypes.data), C.byref(p)), dbg.handle)
+                ptrs[r] = p.value
+        check(L.kq_route_connect(dbg.handle, ptrs), dbg.handle)
+        self.bins = L.kq_route_bins(dbg.handle)
+        self.hist = torch.zeros(self.bins, dtype=torch.int64, device=device)
+        self.all_hist = torch.zeros(nranks * self.bins, dtype=torch.int64, device=device)
+        self.flag = torch.zeros(1, dtype=torch.int32, device=device)
+        self.rounds = torch.zeros(1, dtype=torch.int64, device=device)
+        self.a2a_bytes = 0
+        self.tb = L.kq_tuple_bytes(dbg.handle)
+
+    def count(self, d_bases, d_invalid, length):
+        """Collective: every rank calls it (ranks with fewer rounds take part with empty ones)."""
+        g, L = self.g, lib()
+        total = max(0, length - g.k + 1)
+        mine = (total + self.round_pos - 1) // self.round_pos
+        caller = torch.cuda.current_stream(self.device)
+        self.stream.wait_stream(caller)
+        with torch.cuda.stream(self.stream):
+            self.rounds.fill_(mine)
+            dist.all_reduce(self.rounds, op=dist.ReduceOp.MAX, group=self.group)
+            rounds = int(self.rounds.item())
+            pb, pi = C.c_void_p(d_bases.data_ptr()), C.c_void_p(d_invalid.data_ptr())
+            for r in range(rounds):
+                p0 = min(r * self.round_pos, total)
+                npos = min(self.round_pos, total - p0)
+                check(L.kq_route_hist(g.handle, pb, pi, length, p0, npos, C.c_void_p(self.hist.data_ptr())), g.handle)
+                # also orders this round after every rank's previous insert: the slabs are free again
+                dist.all_gather_into_tensor(self.all_hist, self.hist, group=self.group)
+                nrecv = C.c_uint64()
+                check(L.kq_route_scatter(g.handle, pb, pi, length, p0, npos, C.c_void_p(self.all_hist.data_ptr()),
+                                         C.byref(nrecv)), g.handle)
+                dist.all_reduce(self.flag, group=self.group)         # barrier on the stream: every slab is complete
+                check(L.kq_route_insert(g.handle, nrecv.value), g.handle)
+                self.a2a_bytes += nrecv.value * self.tb
+        caller.wait_stream(self.stream)

@@ -292,3 +292,94 @@ def test_routed_tuples_two_shards_one_gpu(mods):
             gs[r].close()
         kk = np.concatenate(ks); rec = np.concatenate(rs); o = np.argsort(kk)
         assert np.array_equal(kk[o], rk) and rec[o].tobytes() == rr.tobytes()
+
+
+@pytest.mark.parametrize("k,nr,hint", [(21, 2, 0), (31, 4, 0), (21, 4, 2_000_000)])
+def test_peer_routed_pipeline_shards_one_gpu(mods, k, nr, hint):
+    """kq_route_hist -> (all-gather stand-in) -> kq_route_scatter into every owner's slab -> kq_route_insert,
+    with nr sharded handles in one process (slab pointers passed directly instead of through CUDA IPC).
+    Every "rank" routes its own read batch, in two rounds; the union of the shards equals the oracle."""
+    import ctypes as C
+    import torch
+    kb, ko = mods
+    from kreeq_b200._lib import check, lib
+    L = lib()
+    rng = np.random.default_rng(500 + k + nr)
+    genome = random_genome(rng, 300_000)
+    batches = [sample_reads(rng, genome, 6000, 150, err=0.01) for _ in range(nr)]
+    ref = ko.Table(k)
+    for b in batches:
+        ref.count_batch(b)
+    rk, rr = ref.export()
+    gs = [kb.DBG(k=k, rank=r, nranks=nr, expected_distinct=hint) for r in range(nr)]
+    dev = []
+    for b in batches:
+        bases, inv = kb.pack_host(b)
+        dev.append((torch.from_numpy(bases.view(np.int64)).cuda(), torch.from_numpy(inv.view(np.int64)).cuda(), len(b)))
+    slab_cap = 2 * max(len(b) for b in batches)
+    ptrs = (C.c_void_p * nr)()
+    for r in range(nr):
+        p = C.c_void_p()
+        check(L.kq_route_setup(gs[r].handle, slab_cap, 6, C.byref(p), None), gs[r].handle)
+        ptrs[r] = p.value
+    for r in range(nr):
+        check(L.kq_route_connect(gs[r].handle, ptrs), gs[r].handle)
+    P = L.kq_route_bins(gs[0].handle)
+    assert P == nr << 6
+    H = torch.zeros((nr, P), dtype=torch.int64, device="cuda")
+    sent = 0
+    for rnd in range(2):
+        spans = []
+        for r in range(nr):
+            d_b, d_i, n = dev[r]
+            total = n - k + 1
+            p0 = rnd * (total // 2)
+            npos = total // 2 if rnd == 0 else total - p0
+            spans.append((p0, npos))
+            check(L.kq_route_hist(gs[r].handle, C.c_void_p(d_b.data_ptr()), C.c_void_p(d_i.data_ptr()), n, p0, npos,
+                                  C.c_void_p(H[r].data_ptr())), gs[r].handle)
+        for g in gs:
+            g.sync()
+        nrecv = []
+        for r in range(nr):
+            d_b, d_i, n = dev[r]
+            out = C.c_uint64()
+            check(L.kq_route_scatter(gs[r].handle, C.c_void_p(d_b.data_ptr()), C.c_void_p(d_i.data_ptr()), n, spans[r][0], spans[r][1],
+                                     C.c_void_p(H.data_ptr()), C.byref(out)), gs[r].handle)
+            nrecv.append(out.value)
+        for g in gs:
+            g.sync()
+        Hh = H.cpu().numpy().reshape(nr, nr, P // nr)
+        assert nrecv == [int(Hh[:, r, :].sum()) for r in range(nr)]
+        sent += int(Hh.sum())
+        for r in range(nr):
+            check(L.kq_route_insert(gs[r].handle, nrecv[r]), gs[r].handle)
+        for g in gs:
+            g.sync()
+    ks, rs = [], []
+    for g in gs:
+        g.finalize()
+        kk, rec = g.export(); ks.append(kk); rs.append(rec)
+    assert sum(g.instances() for g in gs) == sent == int(ref.stats()["total"])
+    for g in gs:
+        g.close()
+    kk = np.concatenate(ks); rec = np.concatenate(rs); o = np.argsort(kk)
+    assert np.array_equal(kk[o], rk) and rec[o].tobytes() == rr.tobytes()
+    # a slab that is too small is refused on every rank before anything is written
+    g2 = [kb.DBG(k=k, rank=r, nranks=2) for r in range(2)]
+    p2 = (C.c_void_p * 2)()
+    for r in range(2):
+        p = C.c_void_p()
+        check(L.kq_route_setup(g2[r].handle, 1000, 4, C.byref(p), None), g2[r].handle)
+        p2[r] = p.value
+    H2 = torch.zeros((2, 32), dtype=torch.int64, device="cuda")
+    d_b, d_i, n = dev[0]
+    for r in range(2):
+        check(L.kq_route_connect(g2[r].handle, p2), g2[r].handle)
+    check(L.kq_route_hist(g2[0].handle, C.c_void_p(d_b.data_ptr()), C.c_void_p(d_i.data_ptr()), n, 0, n - k + 1,
+                          C.c_void_p(H2[0].data_ptr())), g2[0].handle)
+    out = C.c_uint64()
+    assert L.kq_route_scatter(g2[0].handle, C.c_void_p(d_b.data_ptr()), C.c_void_p(d_i.data_ptr()), n, 0, n - k + 1,
+                              C.c_void_p(H2.data_ptr()), C.byref(out)) == -4
+    for g in g2:
+        g.close()
