@@ -199,6 +199,18 @@ int  kq_route_scatter(kq_ctx *ctx, const uint64_t *d_bases, const uint64_t *d_in
                       uint64_t pos0, uint64_t npos, const unsigned long long *d_all_hist, uint64_t *nrecv);
 int  kq_route_insert(kq_ctx *ctx, uint64_t n);
 
+/* ---- validate against every rank's shard over peer memory (validate's exchange step) ----------
+ * Instead of routing (key, origin) queries to the owners and the answers back, a rank probes the owner's
+ * table directly: kq_peer_export publishes this shard (CUDA IPC handles of its tables + geometry, 256
+ * bytes; the tables then stay put until kq_peer_disconnect), kq_peer_connect takes the nranks blobs in rank
+ * order.  While connected, kq_validate_segment / kq_dev_validate_packed answer EVERY position (not only the
+ * ones this shard owns), so segments can be dealt to ranks and only the three QV counters are summed. */
+#define KQ_PEER_BLOB 256
+int  kq_peer_export(kq_ctx *ctx, void *blob256);
+int  kq_peer_connect(kq_ctx *ctx, const void *blobs);
+int  kq_peer_connect_local(kq_ctx *ctx, kq_ctx *const *handles);   /* shards held by this process */
+int  kq_peer_disconnect(kq_ctx *ctx);
+
 /* probe positions [0, len-k+1) of one packed device-resident segment;
  * d_out (len entries) and d_acc (kq_qv, accumulates) are device memory. */
 int  kq_dev_validate_packed(kq_ctx *ctx, const uint64_t *d_bases, const uint64_t *d_invalid,

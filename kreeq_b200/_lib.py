@@ -79,6 +79,10 @@ PROTOTYPES = {
     "kq_route_hist": (_i, [_vp, _vp, _vp, _u64, _u64, _u64, _vp]),
     "kq_route_scatter": (_i, [_vp, _vp, _vp, _u64, _u64, _u64, _vp, C.POINTER(_u64)]),
     "kq_route_insert": (_i, [_vp, _u64]),
+    "kq_peer_export": (_i, [_vp, _vp]),
+    "kq_peer_connect": (_i, [_vp, _vp]),
+    "kq_peer_connect_local": (_i, [_vp, C.POINTER(_vp)]),
+    "kq_peer_disconnect": (_i, [_vp]),
     "kq_dev_validate_packed": (_i, [_vp, _vp, _vp, _u64, C.c_uint32, _vp, _vp]),
     "kq_reserve": (_i, [_vp, _u64]),
     "kq_counters": (_i, [_vp, C.POINTER(_u64), C.POINTER(_u64), C.POINTER(_u64)]),

@@ -65,6 +65,7 @@ struct kq_ctx {
     int *d_err = nullptr;
     uint64_t occ_known = 0;                      // T occupancy at the last synchronisation
     uint64_t occ_bound = 0;                      // upper bound of it including batches in flight
+    uint64_t r_bound = 0;                        // upper bound of R's occupancy (a key needs 128 instances to get there)
     bool optimistic = false;                     // the caller sized the table (kq_create / kq_reserve)
     int rank = 0, nranks = 1;
     bool loaded_db = false;                      // table holds literal database entries (load/union)
@@ -80,6 +81,8 @@ struct kq_ctx {
     RouteMap route{}; bool route_ready = false;
     std::vector<void *> ipc_opened;
     unsigned long long *d_rcursor = nullptr, *d_rtotals = nullptr;
+    // peer tables (multi-GPU validate): views of every rank's shard, mapped into this process
+    TableView *d_peers = nullptr; std::vector<void *> peer_opened; bool exported = false;
     Stage st[NBUF]; int next_stage = 0;
     uint64_t launches = 0, h2d = 0, d2h = 0;
     bool timing = false; std::vector<TimedRange> ranges; std::vector<cudaEvent_t> ev_pool;
@@ -145,6 +148,7 @@ void table_geometry(uint64_t need, uint64_t &nslices, int &slice_bits) {
 }
 
 int grow_table(kq_ctx *c, uint64_t need) {
+    if (c->exported) return fail(c, KQ_ESTATE, "the table is mapped by peers (kq_peer_export): call kq_peer_disconnect first");
     Slot *old = c->T; const uint64_t old_slots = table_slots(c);
     uint64_t ns; int sb; table_geometry(need, ns, sb);
     Slot *nt = nullptr;
@@ -160,6 +164,7 @@ int grow_table(kq_ctx *c, uint64_t need) {
 }
 
 int grow_side(kq_ctx *c, int which, uint64_t new_scap) {
+    if (c->exported) return fail(c, KQ_ESTATE, "the table is mapped by peers (kq_peer_export): call kq_peer_disconnect first");
     SideSlot *&S = which == 1 ? c->R : c->M; uint64_t &cap = which == 1 ? c->rcap : c->mcap;
     SideSlot *old = S; const uint64_t old_cap = cap;
     SideSlot *ns = nullptr;
@@ -254,6 +259,7 @@ int settle(kq_ctx *c) {
     int rc = read_occ(c, occ); if (rc) return rc;
     rc = check_device_error(c); if (rc) return rc;
     c->occ_bound = occ[0];
+    c->r_bound = occ[1];
     if ((double)occ[1] > 0.5 * (double)c->rcap) { rc = grow_side(c, 1, c->rcap * 4); if (rc) return rc; }
     if (!c->ovf_pending) return KQ_OK;
     c->ovf_pending = false;
@@ -354,6 +360,11 @@ int count_source(kq_ctx *c, Source src) {
             b.tuples = src.tuples + (src.ntuples_max - left) * tuple_words(c->k); b.ntuples_max = nb; b.ntuples = c->d_nsrc;
             const unsigned long long v = nb;
             CU(cudaMemcpyAsync(c->d_nsrc, &v, 8, cudaMemcpyHostToDevice, c->stream));
+        }
+        // R cannot overflow inside the batch: a key reaches it with its 128th instance at the earliest
+        c->r_bound += nb / 128 + 1;
+        if ((double)c->r_bound * 1.25 + 4096 > (double)c->rcap) {
+            int rc = grow_side(c, 1, std::max<uint64_t>(2 * c->rcap, (uint64_t)((double)c->r_bound * 1.5) + 8192)); if (rc) return rc;
         }
         int rc = run_batch(c, b); if (rc) return rc;
         c->occ_bound = c->occ_known + nb;
@@ -457,6 +468,8 @@ extern "C" void kq_destroy(kq_ctx *c) {
     cudaFree(c->d_pb); cudaFree(c->d_pi); cudaFree(c->d_tuples); cudaFree(c->d_hist); cudaFree(c->d_cursor);
     cudaFree(c->d_total); cudaFree(c->d_nsrc); cudaFree(c->d_ticket); cudaFree(c->d_ovf); cudaFree(c->d_ovf_n);
     for (void *p : c->ipc_opened) cudaIpcCloseMemHandle(p);
+    for (void *p : c->peer_opened) cudaIpcCloseMemHandle(p);
+    cudaFree(c->d_peers);
     cudaFree(c->d_slab); cudaFree(c->d_rcursor); cudaFree(c->d_rtotals);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     delete c;
@@ -545,7 +558,7 @@ extern "C" int kq_clear(kq_ctx *c) {
     CU(cudaMemsetAsync(c->d_inst, 0, sizeof(unsigned long long), c->stream));
     CU(cudaMemsetAsync(c->d_ovf_n, 0, sizeof(unsigned long long), c->stream));
     CU(cudaMemsetAsync(c->d_err, 0, sizeof(int), c->stream));
-    c->occ_known = c->occ_bound = 0; c->inst_tuples = 0; c->ovf_pending = false; c->loaded_db = false;
+    c->occ_known = c->occ_bound = 0; c->r_bound = 0; c->inst_tuples = 0; c->ovf_pending = false; c->loaded_db = false;
     return KQ_OK;
 }
 
@@ -754,6 +767,87 @@ extern "C" int kq_route_insert(kq_ctx *c, uint64_t n) {
     return KQ_OK;
 }
 
+// ---- peer tables: validate against every rank's shard over NVLink (row E) ----------------------------------
+
+namespace {
+struct PeerBlob {                     // what a rank publishes about its shard (kq_peer_export)
+    cudaIpcMemHandle_t T, R, M;
+    unsigned long long nslices, rcap, mcap; int slice_bits, k, rank, nranks;
+};
+static_assert(sizeof(PeerBlob) <= 256, "PeerBlob fits KQ_PEER_BLOB bytes");
+
+int peers_install(kq_ctx *c, const std::vector<TableView> &views) {
+    if (!c->d_peers) CU(cudaMalloc(&c->d_peers, KQ_MAX_RANKS * sizeof(TableView)));
+    CU(cudaMemcpyAsync(c->d_peers, views.data(), views.size() * sizeof(TableView), cudaMemcpyHostToDevice, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return KQ_OK;
+}
+}  // namespace
+
+extern "C" int kq_peer_export(kq_ctx *c, void *blob) {
+    if (!c || !blob) return KQ_EINVAL;
+    CU(cudaSetDevice(c->device));
+    int rc = kq_sync(c); if (rc) return rc;
+    PeerBlob b{};
+    CU(cudaIpcGetMemHandle(&b.T, c->T)); CU(cudaIpcGetMemHandle(&b.R, c->R)); CU(cudaIpcGetMemHandle(&b.M, c->M));
+    b.nslices = c->nslices; b.rcap = c->rcap; b.mcap = c->mcap; b.slice_bits = c->slice_bits;
+    b.k = c->k; b.rank = c->rank; b.nranks = c->nranks;
+    std::memset(blob, 0, 256); std::memcpy(blob, &b, sizeof b);
+    c->exported = true;               // the tables must stay where they are until kq_peer_disconnect
+    return KQ_OK;
+}
+
+extern "C" int kq_peer_connect(kq_ctx *c, const void *blobs) {
+    if (!c || !blobs) return KQ_EINVAL;
+    if (c->nranks > KQ_MAX_RANKS) return fail(c, KQ_EINVAL, "kq_peer_connect: too many ranks");
+    CU(cudaSetDevice(c->device));
+    std::vector<TableView> views(c->nranks, view(c));
+    for (int r = 0; r < c->nranks; ++r) {
+        if (r == c->rank) continue;
+        PeerBlob b; std::memcpy(&b, static_cast<const char *>(blobs) + (size_t)r * 256, sizeof b);
+        if (b.k != c->k || b.rank != r || b.nranks != c->nranks) return fail(c, KQ_EINVAL, "kq_peer_connect: blob " + std::to_string(r) + " does not describe rank " + std::to_string(r));
+        void *T = nullptr, *R = nullptr, *M = nullptr;
+        CU(cudaIpcOpenMemHandle(&T, b.T, cudaIpcMemLazyEnablePeerAccess)); c->peer_opened.push_back(T);
+        CU(cudaIpcOpenMemHandle(&R, b.R, cudaIpcMemLazyEnablePeerAccess)); c->peer_opened.push_back(R);
+        CU(cudaIpcOpenMemHandle(&M, b.M, cudaIpcMemLazyEnablePeerAccess)); c->peer_opened.push_back(M);
+        TableView &v = views[r];
+        v.T = static_cast<Slot *>(T); v.R = static_cast<SideSlot *>(R); v.M = static_cast<SideSlot *>(M);
+        v.nslices = b.nslices; v.rcap = b.rcap; v.mcap = b.mcap; v.slice_bits = b.slice_bits;
+    }
+    return peers_install(c, views);
+}
+
+// same-process form: the other shards are handles of this process (tests; several GPUs driven by one process)
+extern "C" int kq_peer_connect_local(kq_ctx *c, kq_ctx *const *handles) {
+    if (!c || !handles) return KQ_EINVAL;
+    if (c->nranks > KQ_MAX_RANKS) return fail(c, KQ_EINVAL, "kq_peer_connect_local: too many ranks");
+    CU(cudaSetDevice(c->device));
+    std::vector<TableView> views(c->nranks, view(c));
+    for (int r = 0; r < c->nranks; ++r) {
+        kq_ctx *o = handles[r];
+        if (!o || o->k != c->k || o->rank != r || o->nranks != c->nranks) return fail(c, KQ_EINVAL, "kq_peer_connect_local: handle " + std::to_string(r) + " is not rank " + std::to_string(r));
+        if (o == c) continue;
+        int rc = kq_sync(o); if (rc) return fail(c, rc, kq_last_error(o));
+        CU(cudaSetDevice(c->device));
+        if (o->device != c->device) { cudaError_t e = cudaDeviceEnablePeerAccess(o->device, 0); if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) CU(e); cudaGetLastError(); }
+        TableView &v = views[r];
+        v.T = o->T; v.R = o->R; v.M = o->M; v.nslices = o->nslices; v.rcap = o->rcap; v.mcap = o->mcap; v.slice_bits = o->slice_bits;
+        o->exported = true;
+    }
+    return peers_install(c, views);
+}
+
+extern "C" int kq_peer_disconnect(kq_ctx *c) {
+    if (!c) return KQ_EINVAL;
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    for (void *p : c->peer_opened) cudaIpcCloseMemHandle(p);
+    c->peer_opened.clear();
+    cudaFree(c->d_peers); c->d_peers = nullptr;
+    c->exported = false;
+    return KQ_OK;
+}
+
 // ---- validate -----------------------------------------------------------------------------------------------
 
 extern "C" double kq_error_rate(uint64_t missing, uint64_t total, int k) {      // src/kreeq.cpp:36-40
@@ -771,7 +865,7 @@ extern "C" int kq_dev_validate_packed(kq_ctx *c, const uint64_t *d_bases, const 
     const uint64_t kcount = len >= (uint64_t)c->k ? len - c->k + 1 : 0;
     const int t = time_begin(c, 1);
     CU(launch_validate(c->stream, view(c), d_bases, d_invalid, 0, 0, len, kcount, cutoff,
-                       reinterpret_cast<Base *>(d_out), reinterpret_cast<unsigned long long *>(d_acc), &c->launches));
+                       reinterpret_cast<Base *>(d_out), reinterpret_cast<unsigned long long *>(d_acc), c->d_peers, c->nranks, &c->launches));
     time_end(c, t);
     return KQ_OK;
 }
@@ -813,7 +907,7 @@ extern "C" int kq_validate_segment(kq_ctx *c, const char *seq, uint64_t len, uin
         CU(cudaMemcpyAsync(s.d_inv, s.h_inv, (words / 2 + 1) * 8, cudaMemcpyHostToDevice, c->stream));
         c->h2d += words * 8 + (words / 2 + 1) * 8;
         const int t = time_begin(c, 1);
-        CU(launch_validate(c->stream, view(c), s.d_bases, s.d_inv, a0, c0, n, kcount, cutoff, s.d_out, c->d_acc, &c->launches));
+        CU(launch_validate(c->stream, view(c), s.d_bases, s.d_inv, a0, c0, n, kcount, cutoff, s.d_out, c->d_acc, c->d_peers, c->nranks, &c->launches));
         time_end(c, t);
         CU(cudaMemcpyAsync(s.h_out, s.d_out, n * sizeof(Base), cudaMemcpyDeviceToHost, c->stream));
         c->d2h += n * sizeof(Base);

@@ -21,6 +21,7 @@
 namespace kq {
 
 constexpr uint32_t KQ_LANE_MAX = 127u;         // a slot lane counts to 127, the rest lives in R
+constexpr uint32_t KQ_REM_FLOOR = 64u;         // counted slots that own a remainder never drop below this coverage
 constexpr uint32_t KQ_LARGEST = 4294967295u;   // LARGEST, include/kreeq.h:68
 constexpr int KQ_MAX_SLICE_BITS = 21;          // 2^21 slots x 16 B = 32 MiB per slice
 
@@ -64,9 +65,11 @@ __host__ __device__ __forceinline__ uint64_t mix64(uint64_t x) {
 
 __host__ __device__ __forceinline__ uint32_t cnt_cov(unsigned long long c) { return (uint32_t)(c >> 56) & 127u; }
 __host__ __device__ __forceinline__ uint32_t cnt_lane(unsigned long long c, int i) { return (uint32_t)(c >> (7 * i)) & 127u; }
-// true if any of the nine 7-bit fields is saturated (a remainder may exist)
+// true if a remainder record may exist: the count path moves 63 of a full slot's 127 to R at a time and so
+// never leaves such a slot below KQ_REM_FLOOR; load / union fill fields to 127 and put the rest in R
 __host__ __device__ __forceinline__ bool cnt_saturated(unsigned long long c) {
     c &= ~CNT_PLACEHOLDER;
+    if (cnt_cov(c) >= KQ_REM_FLOOR) return true;
     unsigned long long t = c & (c >> 1); t &= t >> 2; t &= (t >> 3) & (c >> 6);    // bit 7i set iff bits 7i..7i+6 all set
     return (t & 0x0102040810204081ULL) != 0;
 }
@@ -252,12 +255,21 @@ __device__ __forceinline__ int insert_instance(const TableView &tv, uint64_t key
         if (s.tag == tag) {
             unsigned long long cur = s.cnt;
             for (;;) {
-                if (cnt_cov(cur) >= KQ_LANE_MAX) {                  // slot is full: the instance goes to the remainder
+                if (cnt_cov(cur) >= KQ_LANE_MAX) {
+                    // slot is full: move 63 of the coverage and up to 63 of every lane to the remainder in
+                    // the same CAS that counts this instance -- R is touched once per 63 instances of a
+                    // high-copy k-mer, and the slot stays >= KQ_REM_FLOOR so readers know to look there
                     uint32_t fw[4], bw[4];
+                    unsigned long long take = 63ull << 56;
 #pragma unroll
-                    for (int w = 0; w < 4; ++w) { fw[w] = (e >> (7 - w)) & 1u; bw[w] = (e >> (3 - w)) & 1u; }
-                    remainder_add(tv, key, 1, fw, bw);
-                    return 0;
+                    for (int w = 0; w < 4; ++w) {
+                        fw[w] = min(cnt_lane(cur, w), 63u); bw[w] = min(cnt_lane(cur, 4 + w), 63u);
+                        take |= (unsigned long long)fw[w] << (7 * w) | (unsigned long long)bw[w] << (7 * (4 + w));
+                    }
+                    const unsigned long long old = atomicCAS(&p->cnt, cur, cur - take + inc);
+                    if (old == cur) { remainder_add(tv, key, 63, fw, bw); return 0; }
+                    cur = old;
+                    continue;
                 }
                 // lanes <= cov < 127 for counted records, so cur + inc cannot carry between lanes
                 const unsigned long long old = atomicCAS(&p->cnt, cur, cur + inc);

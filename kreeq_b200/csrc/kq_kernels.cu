@@ -431,9 +431,17 @@ extract_route_kernel(TableView tv, Source src, RouteArgs ra) {
 __global__ void __launch_bounds__(TPB, CTAS_PER_SM)
 validate_kernel(TableView tv, const uint64_t *__restrict__ B, const uint64_t *__restrict__ M,
                 uint64_t base0, uint64_t c0, uint64_t n, uint64_t kcount, uint32_t cutoff,
-                Base *__restrict__ out, unsigned long long *acc3) {
+                Base *__restrict__ out, unsigned long long *acc3, const TableView *__restrict__ peers, int npeers) {
     __shared__ unsigned long long sh[3];
+    // Multi-GPU: peers[r] describes the shard of rank r (its T / R / M mapped into this process); every
+    // position is probed in the table of its key's owner, over NVLink when that is another GPU.
+    __shared__ TableView pv[KQ_MAX_RANKS];
     if (threadIdx.x < 3) sh[threadIdx.x] = 0;
+    if (peers) {
+        const unsigned words = (unsigned)(npeers * sizeof(TableView) / 4);
+        for (unsigned i = threadIdx.x; i < words; i += TPB)
+            reinterpret_cast<uint32_t *>(pv)[i] = reinterpret_cast<const uint32_t *>(peers)[i];
+    }
     __syncthreads();
     unsigned long long missing = 0, counted = 0, edge_missing = 0;
     const uint64_t stride = (uint64_t)gridDim.x * TPB;
@@ -444,10 +452,10 @@ validate_kernel(TableView tv, const uint64_t *__restrict__ B, const uint64_t *__
             const Kmer km = kmer_at(B, M, c - base0, tv.k);
             // a window holding a non-ACGT byte can never be found; it still counts (kreeq.cpp:216),
             // on shard 0 only so that the per-shard counters add up
-            if (km.valid ? owns(tv, km.key) : tv.shard_rank <= 0) {
+            if (peers || (km.valid ? owns(tv, km.key) : tv.shard_rank <= 0)) {
                 Rec32 kh; int found = 0;
                 if (km.valid) {
-                    found = lookup(tv, km.key, kh);
+                    found = lookup(peers ? pv[(km.key & 127) >> tv.shard_shift] : tv, km.key, kh);
                     if (found < 0) { atomicOr(tv.err, 4); found = 0; }
                 }
                 if (found) { o.z = kh.cov; o.w = km.isFw ? 1u : 0u; }                // :168-169
@@ -642,9 +650,9 @@ cudaError_t launch_extract_route(cudaStream_t st, const TableView &tv, const Sou
 
 cudaError_t launch_validate(cudaStream_t st, const TableView &tv, const uint64_t *B, const uint64_t *M,
                             uint64_t base0, uint64_t c0, uint64_t n, uint64_t kcount, uint32_t cutoff,
-                            Base *out, unsigned long long *acc3, uint64_t *launches) {
+                            Base *out, unsigned long long *acc3, const TableView *peers, int npeers, uint64_t *launches) {
     if (!n) return cudaSuccess;
-    validate_kernel<<<grid_for(n), TPB, 0, st>>>(tv, B, M, base0, c0, n, kcount, cutoff, out, acc3);
+    validate_kernel<<<grid_for(n), TPB, 0, st>>>(tv, B, M, base0, c0, n, kcount, cutoff, out, acc3, peers, npeers);
     ++*launches;
     return cudaGetLastError();
 }

@@ -87,11 +87,12 @@ cudaError_t launch_extract_route(cudaStream_t st, const TableView &tv, const Sou
                                  uint64_t *launches);
 
 // ---- validate / lookups (rows A5, host consumers) ------------------------------------------------------
+// peers != nullptr (device array of npeers views, one per rank): probe every position in its owner's shard.
 // positions [c0, c0+n) of a segment with kcount windows; the packed arrays start at segment
 // position `base0` (so bit position of c is c-base0); out is indexed by c-c0.
 cudaError_t launch_validate(cudaStream_t st, const TableView &tv, const uint64_t *B, const uint64_t *M,
                             uint64_t base0, uint64_t c0, uint64_t n, uint64_t kcount, uint32_t cutoff,
-                            Base *out, unsigned long long *acc3, uint64_t *launches);
+                            Base *out, unsigned long long *acc3, const TableView *peers, int npeers, uint64_t *launches);
 cudaError_t launch_lookup(cudaStream_t st, const TableView &tv, const uint64_t *keys, uint64_t n, Rec32 *rec,
                           uint8_t *found, uint64_t *launches);
 

@@ -179,3 +179,61 @@ class PeerRoutedCounter:
                 check(L.kq_route_insert(g.handle, nrecv.value), g.handle)
                 self.a2a_bytes += nrecv.value * self.tb
         caller.wait_stream(self.stream)
+
+
+class PeerTables:
+    """`with PeerTables(dbg, nranks, device):` -- inside the block every rank's validate calls answer all
+    positions, probing each k-mer in its owner's shard over peer memory (kq_peer_export / kq_peer_connect).
+    Entry and exit are collective.  With keep=True the peer mappings stay open after the block (mapping a
+    peer's tables costs milliseconds; a pipeline maps them once): the tables may then be cleared and counted
+    into again between blocks as long as they do not have to grow (the library refuses to move an exported
+    table: KQ_ESTATE), and disconnect() must be called by every rank at the end.
+
+    The library's stream must be torch's current stream: the collectives order the kernels of all ranks."""
+
+    def __init__(self, dbg, nranks, device, keep=False, group=None):
+        self.g, self.n, self.device, self.keep, self.group = dbg, nranks, device, keep, group
+        self.connected = False
+        self.flag = torch.zeros(1, dtype=torch.int32, device=device)
+        self.connect_ms = 0.0
+
+    def _stream_barrier(self):
+        dist.all_reduce(self.flag, group=self.group)
+
+    def connect(self):
+        import time
+        L = lib()
+        t0 = time.perf_counter()
+        blob = (C.c_ubyte * 256)()
+        check(L.kq_peer_export(self.g.handle, blob), self.g.handle)
+        mine = torch.tensor(list(blob), dtype=torch.uint8, device=self.device)
+        blobs = torch.empty(self.n * 256, dtype=torch.uint8, device=self.device)
+        dist.all_gather_into_tensor(blobs, mine, group=self.group)      # also: every rank's table is complete
+        self._blobs = blobs.cpu().numpy()
+        check(L.kq_peer_connect(self.g.handle, C.c_void_p(self._blobs.ctypes.data)), self.g.handle)
+        self.connected = True
+        self.connect_ms = (time.perf_counter() - t0) * 1e3
+
+    def disconnect(self):
+        if not self.connected:
+            return
+        torch.cuda.current_stream(self.device).synchronize()
+        dist.barrier(group=self.group)                   # nobody is still probing this rank's tables
+        check(lib().kq_peer_disconnect(self.g.handle), self.g.handle)
+        dist.barrier(group=self.group)
+        self.connected = False
+
+    def __enter__(self):
+        if self.connected:
+            check(lib().kq_sync(self.g.handle), self.g.handle)          # pending reads counted
+            self._stream_barrier()                       # every rank's table is complete before anyone probes
+        else:
+            self.connect()
+        return self
+
+    def __exit__(self, *exc):
+        if self.keep and exc[0] is None:
+            self._stream_barrier()                       # nobody still probes before a table changes again
+        else:
+            self.disconnect()
+        return False

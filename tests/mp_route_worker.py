@@ -27,7 +27,8 @@ def main():
     k = 21
     genome = random_genome(np.random.default_rng(11), 400_000)
     # ranks bring different amounts of reads: the round counts differ and the short ranks join empty rounds
-    batches = [sample_reads(np.random.default_rng(100 + r), genome, 6000 + 3000 * r, 150, err=0.01) for r in range(world)]
+    batches = [sample_reads(np.random.default_rng(100 + r), genome, 6000 + 3000 * r, 150, err=0.01) +
+               (genome[1000 * r:1000 * r + 400].tobytes() + b"N") * 200 for r in range(world)]      # + a high-copy stretch each
     ref = ko.Table(k)
     for b in batches:
         ref.count_batch(b)
@@ -57,6 +58,16 @@ def main():
     t = torch.tensor([g.instances()], dtype=torch.int64, device=dev)
     dist.all_reduce(t)
     assert int(t.item()) == int(ref.stats()["total"])
+    # validate: every rank takes its own slice of the assembly and probes the owners' shards over peer memory
+    span = len(genome) // world
+    seg = genome[rank * span:(rank + 1) * span].tobytes()
+    _, rout, racc = ref.validate_segment(seg, cutoff=2)
+    with shard.PeerTables(g, world, dev):
+        out = g.evaluateSegment(seg, cov_cutoff=2)
+    assert out.tobytes() == rout.tobytes(), "rank %d: per-base validate output differs" % rank
+    assert (g.tot_missing, g.tot_kcount, g.tot_edge_missing) == racc
+    # the handle is usable for counting again after the block
+    g.traverseInReads(batches[rank][:1510]); g.finalize()
     g.close()
     dist.barrier()
     if rank == 0:

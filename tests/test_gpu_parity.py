@@ -383,3 +383,59 @@ def test_peer_routed_pipeline_shards_one_gpu(mods, k, nr, hint):
                               C.c_void_p(H2.data_ptr()), C.byref(out)) == -4
     for g in g2:
         g.close()
+
+
+@pytest.mark.parametrize("hint", [0, 400_000])
+def test_every_kmer_high_copy(mods, hint):
+    """300x coverage: every genomic k-mer passes 127 (slot lanes move to the remainder table 63 at a time)
+    and most pass 254 (the reference's 32-bit spill); counted in one large batch so the remainder table
+    must have been sized before the kernels ran."""
+    kb, ko = mods
+    k = 21
+    rng = np.random.default_rng(4242)
+    genome = random_genome(rng, 60_000)
+    batch = sample_reads(rng, genome, 120_000, 150, err=0.002)
+    ref = ko.Table(k); ref.count_batch(batch)
+    with kb.DBG(k=k, expected_distinct=hint) as g:
+        g.traverseInReads(batch)
+        g.finalize()
+        assert_same_records(g.export(), ref.export())
+        assert g.stats() == ref.stats()
+        out = g.evaluateSegment(genome.tobytes())
+        _, rout, racc = ref.validate_segment(genome.tobytes())
+        assert out.tobytes() == rout.tobytes()
+        assert (g.tot_missing, g.tot_kcount, g.tot_edge_missing) == racc
+
+
+def test_peer_tables_validate_shards_one_gpu(mods):
+    """kq_peer_connect_local: a sharded handle answers every position of a segment by probing the shard that
+    owns each k-mer (high-copy keys included: remainder table of the owner), equal to the oracle."""
+    import ctypes as C
+    kb, ko = mods
+    from kreeq_b200._lib import check, lib
+    L = lib()
+    k, nr = 21, 4
+    rng = np.random.default_rng(77)
+    genome = random_genome(rng, 150_000)
+    batch = sample_reads(rng, genome, 20_000, 150, err=0.01) + (genome[:300].tobytes() + b"N") * 400
+    ref = ko.Table(k); ref.count_batch(batch)
+    gs = [kb.DBG(k=k, rank=r, nranks=nr) for r in range(nr)]
+    for g in gs:
+        g.traverseInReads(batch); g.finalize()
+    arr = (C.c_void_p * nr)(*[g.handle for g in gs])
+    seg = genome.tobytes()
+    _, rout, racc = ref.validate_segment(seg, cutoff=2)
+    for r in (0, 3):
+        check(L.kq_peer_connect_local(gs[r].handle, arr), gs[r].handle)
+        out = gs[r].evaluateSegment(seg, cov_cutoff=2)
+        assert out.tobytes() == rout.tobytes()
+        assert (gs[r].tot_missing, gs[r].tot_kcount, gs[r].tot_edge_missing) == racc
+    with pytest.raises(kb.KreeqError):                     # an exported table must not be counted into (it could move)
+        gs[1].traverseInReads(sample_reads(rng, random_genome(rng, 3_000_000), 40_000, 150, err=0.0)); gs[1].finalize()
+    for g in gs:
+        check(L.kq_peer_disconnect(g.handle), g.handle)
+    # without peers a sharded handle only answers what it owns
+    own = gs[0].evaluateSegment(seg, cov_cutoff=2)
+    assert own.tobytes() != rout.tobytes()
+    for g in gs:
+        g.close()
