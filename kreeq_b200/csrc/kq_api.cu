@@ -80,7 +80,7 @@ struct kq_ctx {
     uint64_t *d_slab = nullptr; uint64_t slab_cap = 0;          // tuples
     RouteMap route{}; bool route_ready = false;
     std::vector<void *> ipc_opened;
-    unsigned long long *d_rcursor = nullptr, *d_rtotals = nullptr;
+    unsigned long long *d_rcursor = nullptr, *d_rback = nullptr, *d_rtotals = nullptr; uint64_t route_real = 0;
     // peer tables (multi-GPU validate): views of every rank's shard, mapped into this process
     TableView *d_peers = nullptr; std::vector<void *> peer_opened; bool exported = false;
     Stage st[NBUF]; int next_stage = 0;
@@ -470,7 +470,7 @@ extern "C" void kq_destroy(kq_ctx *c) {
     for (void *p : c->ipc_opened) cudaIpcCloseMemHandle(p);
     for (void *p : c->peer_opened) cudaIpcCloseMemHandle(p);
     cudaFree(c->d_peers);
-    cudaFree(c->d_slab); cudaFree(c->d_rcursor); cudaFree(c->d_rtotals);
+    cudaFree(c->d_slab); cudaFree(c->d_rcursor); cudaFree(c->d_rback); cudaFree(c->d_rtotals);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     delete c;
 }
@@ -677,7 +677,8 @@ extern "C" int kq_route_setup(kq_ctx *c, uint64_t slab_tuples, int nb_bits, void
     c->slab_cap = slab_tuples;
     if (!c->d_rcursor) {
         CU(cudaMalloc(&c->d_rcursor, (size_t)KQ_MAX_RANKS * 4096 * 8));
-        CU(cudaMalloc(&c->d_rtotals, KQ_MAX_RANKS * 8));
+        CU(cudaMalloc(&c->d_rback, (size_t)KQ_MAX_RANKS * 4096 * 8));
+        CU(cudaMalloc(&c->d_rtotals, 2 * KQ_MAX_RANKS * 8));
     }
     c->route = RouteMap{};
     c->route.nranks = c->nranks; c->route.nb_bits = nb_bits;
@@ -738,9 +739,13 @@ extern "C" int kq_route_scatter(kq_ctx *c, const uint64_t *d_bases, const uint64
     else if (pos0 + npos > len - c->k + 1) return fail(c, KQ_EINVAL, "kq_route_scatter: positions beyond len-k+1");
     CU(cudaSetDevice(c->device));
     const int t = time_begin(c, 3);
-    CU(launch_route_offsets(c->stream, c->route, c->rank, d_all_hist, c->d_rcursor, c->d_rtotals, &c->launches));
-    unsigned long long totals[KQ_MAX_RANKS];
-    CU(cudaMemcpyAsync(totals, c->d_rtotals, c->nranks * 8, cudaMemcpyDeviceToHost, c->stream));
+    const int tw = tuple_words(c->k);
+    const int cap = scatter_pick_cap((unsigned long long)c->nranks << c->route.nb_bits, tw);
+    unsigned long long totals[2 * KQ_MAX_RANKS];
+    // the padding sentinels go to the peers' slabs from this kernel: like the scatter, it runs after the
+    // all-gather that ordered this round behind every rank's previous insert
+    CU(launch_route_offsets(c->stream, c->route, c->rank, cap, tw, c->slab_cap, d_all_hist, c->d_rcursor, c->d_rback, c->d_rtotals, &c->launches));
+    CU(cudaMemcpyAsync(totals, c->d_rtotals, 2 * c->nranks * 8, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
     for (int r = 0; r < c->nranks; ++r)                  // every rank sees the same totals and takes the same decision
         if (totals[r] > c->slab_cap) {
@@ -748,10 +753,9 @@ extern "C" int kq_route_scatter(kq_ctx *c, const uint64_t *d_bases, const uint64
             return fail(c, KQ_ENOMEM, "kq_route_scatter: rank " + std::to_string(r) + " would receive " + std::to_string(totals[r]) +
                                       " tuples, its slab holds " + std::to_string(c->slab_cap) + " (smaller rounds or a larger slab)");
         }
-    const int tw = tuple_words(c->k);
-    const int cap = scatter_pick_cap((unsigned long long)c->nranks << c->route.nb_bits, tw);
-    CU(launch_route_scatter(c->stream, view(c), Source{d_bases, d_invalid, pos0, npos, nullptr, nullptr, 0, 0}, c->route, c->d_rcursor, cap, &c->launches));
+    CU(launch_route_scatter(c->stream, view(c), Source{d_bases, d_invalid, pos0, npos, nullptr, nullptr, 0, 0}, c->route, c->d_rcursor, c->d_rback, cap, &c->launches));
     time_end(c, t);
+    c->route_real = totals[c->nranks + c->rank];
     *nrecv = totals[c->rank];
     return KQ_OK;
 }
@@ -763,7 +767,7 @@ extern "C" int kq_route_insert(kq_ctx *c, uint64_t n) {
     CU(cudaSetDevice(c->device));
     int rc = pending_flush(c); if (rc) return rc;
     rc = count_source(c, Source{nullptr, nullptr, 0, 0, c->d_slab, c->d_nsrc, n, 1}); if (rc) return rc;
-    c->inst_tuples += n;
+    c->inst_tuples += c->route_real;                     // n is the slab extent including the alignment padding
     return KQ_OK;
 }
 

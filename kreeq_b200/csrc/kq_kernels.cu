@@ -220,37 +220,45 @@ slice_offsets_kernel(unsigned long long nslices, const unsigned long long *hist,
 }
 
 // Routed pipeline: H[s][b] = tuples rank s sends into global bin b = (owner d, j).  Destination d lays its
-// receive slab out bin by bin and, inside a bin, sender by sender; CTA d computes where THIS rank's (me)
-// tuples for each of d's bins start, and how many tuples d receives in total.
+// receive slab out bin by bin and, inside a bin, sender by sender; every (sender, bin) region is padded to
+// a multiple of `cap` tuples so that all full-bin flushes are aligned cap * 8 * TW byte stores (one NVLink
+// packet, whole sectors).  CTA d computes, for THIS rank (me): front[b] = start of its region in bin b of d,
+// back[b] = its end (partial flushes are taken from the back so the front stays aligned), the extent of
+// d's slab (recv[d]) and the number of real tuples in it (recv[nranks + d]); it also writes the sentinel
+// tuples (all ones: no k-mer instance has edge byte 0xFF) into the padding behind its own regions.
 __global__ void __launch_bounds__(1024, 1)
-route_offsets_kernel(int nranks, unsigned nb, int me, const unsigned long long *H, unsigned long long *cursor,
-                     unsigned long long *recv_totals) {
-    __shared__ unsigned long long part[1024];
-    const unsigned d = blockIdx.x, P = (unsigned)nranks * nb;
+route_offsets_kernel(RouteMap rt, int me, int cap, int tw, unsigned long long slab_cap, const unsigned long long *H,
+                     unsigned long long *front, unsigned long long *back, unsigned long long *recv) {
+    __shared__ unsigned long long part[1024], real[1024];
+    __shared__ bool fits;
+    const int nranks = rt.nranks;
+    const unsigned nb = 1u << rt.nb_bits, d = blockIdx.x, P = (unsigned)nranks * nb;
     const unsigned per = (nb + 1023) / 1024;
     const unsigned b = threadIdx.x * per, e = min(nb, b + per);
-    unsigned long long s = 0;
+    const unsigned long long c1 = (unsigned long long)cap - 1;
+    unsigned long long s = 0, rl = 0;
     for (unsigned j = b; j < e; ++j)
-        for (int r = 0; r < nranks; ++r) s += H[(size_t)r * P + d * nb + j];
-    part[threadIdx.x] = s;
+        for (int r = 0; r < nranks; ++r) { const unsigned long long v = H[(size_t)r * P + d * nb + j]; s += (v + c1) / cap * cap; rl += v; }
+    part[threadIdx.x] = s; real[threadIdx.x] = rl;
     __syncthreads();
     if (threadIdx.x == 0) {
-        unsigned long long run = 0;
-        for (int i = 0; i < 1024; ++i) { const unsigned long long v = part[i]; part[i] = run; run += v; }
-        recv_totals[d] = run;
+        unsigned long long run = 0, rr = 0;
+        for (int i = 0; i < 1024; ++i) { const unsigned long long v = part[i]; part[i] = run; run += v; rr += real[i]; }
+        recv[d] = run; recv[nranks + d] = rr;
+        fits = run <= slab_cap;                                      // else the host refuses the round: write nothing
     }
     __syncthreads();
     s = part[threadIdx.x];
-    for (unsigned j = b; j < e; ++j) {
-        unsigned long long before = 0, all = 0;
+    for (unsigned j = b; j < e; ++j)
         for (int r = 0; r < nranks; ++r) {
-            const unsigned long long v = H[(size_t)r * P + d * nb + j];
-            if (r < me) before += v;
-            all += v;
+            const unsigned long long v = H[(size_t)r * P + d * nb + j], L = (v + c1) / cap * cap;
+            if (r == me) {
+                front[d * nb + j] = s; back[d * nb + j] = s + v;
+                uint64_t *pad = rt.out[d] + (s + v) * tw;
+                if (fits) for (unsigned long long w = 0; w < (L - v) * tw; ++w) pad[w] = ~0ULL;
+            }
+            s += L;
         }
-        cursor[d * nb + j] = s + before;
-        s += all;
-    }
 }
 
 // ---- count, step 3: scatter into slice order -------------------------------------------------------------
@@ -264,7 +272,8 @@ route_offsets_kernel(int nranks, unsigned nb, int me, const unsigned long long *
 // straight over NVLink, overlapped with the extraction of the next tuples.
 template <int TW, int R, int NT, bool RT>
 __global__ void __launch_bounds__(NT, 1)
-slice_scatter_kernel(TableView tv, Source src, uint64_t *__restrict__ out, unsigned long long *cursor, int cap, RouteMap rt) {
+slice_scatter_kernel(TableView tv, Source src, uint64_t *__restrict__ out, unsigned long long *cursor, int cap, RouteMap rt,
+                     unsigned long long *back) {
     extern __shared__ uint64_t sm[];
     const unsigned P = bin_count<RT>(tv, rt);
     uint64_t *bins = sm;
@@ -272,6 +281,8 @@ slice_scatter_kernel(TableView tv, Source src, uint64_t *__restrict__ out, unsig
     for (unsigned i = threadIdx.x; i < P; i += NT) fill[i] = 0;
     __syncthreads();
     const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = NT / 32;
+    const unsigned lpb = min(32u, (unsigned)cap * TW);                 // lanes that copy one bin (cap is 8, 16 or 32)
+    const unsigned sub = lane / lpb;
     const uint64_t total = source_total(src), per = (uint64_t)NT * R;
     for (uint64_t tile = (uint64_t)blockIdx.x * per; tile < total; tile += (uint64_t)gridDim.x * per) {
         uint64_t key[R]; uint32_t e[R]; unsigned bin[R], slot[R];
@@ -301,12 +312,17 @@ slice_scatter_kernel(TableView tv, Source src, uint64_t *__restrict__ out, unsig
                 unsigned long long g = 0;
                 if (full) { g = atomicAdd(&cursor[b], (unsigned long long)cap); fill[b] = f - cap; }
                 unsigned todo = __ballot_sync(0xffffffffu, full);
+                // a bin is copied by min(32, words) lanes, so a warp moves 32 / that many full bins at a time
                 while (todo) {
-                    const int l = __ffs(todo) - 1; todo &= todo - 1;
-                    const unsigned long long gg = __shfl_sync(0xffffffffu, g, l);
-                    const uint64_t *srcw = bins + (size_t)(b0 + l) * cap * TW;
-                    uint64_t *dst = (RT ? rt.out[(b0 + l) >> rt.nb_bits] : out) + gg * TW;
-                    for (unsigned w = lane; w < (unsigned)cap * TW; w += 32) __stcs(dst + w, srcw[w]);
+                    const unsigned l = lpb == 32 ? (unsigned)__ffs(todo) - 1 : __fns(todo, 0, (int)sub + 1);   // the sub-th bin still to do
+#pragma unroll 1
+                    for (unsigned i = 0; i < 32 / lpb && todo; ++i) todo &= todo - 1;
+                    const unsigned long long gg = __shfl_sync(0xffffffffu, g, l & 31u);
+                    if (l < 32) {
+                        const uint64_t *srcw = bins + (size_t)(b0 + l) * cap * TW;
+                        uint64_t *dst = (RT ? rt.out[(b0 + l) >> rt.nb_bits] : out) + gg * TW;
+                        for (unsigned w = lane & (lpb - 1); w < (unsigned)cap * TW; w += lpb) __stcs(dst + w, srcw[w]);
+                    }
                 }
             }
             __syncthreads();
@@ -325,7 +341,8 @@ slice_scatter_kernel(TableView tv, Source src, uint64_t *__restrict__ out, unsig
         const unsigned b = b0 + lane;
         const unsigned f = b < P ? fill[b] : 0;
         unsigned long long g = 0;
-        if (f) g = atomicAdd(&cursor[b], (unsigned long long)f);
+        // routed: what is left goes to the END of this rank's region of the bin, the aligned front is for full bins
+        if (f) g = RT ? atomicAdd(&back[b], 0ULL - f) - f : atomicAdd(&cursor[b], (unsigned long long)f);
         unsigned todo = __ballot_sync(0xffffffffu, f != 0);
         while (todo) {
             const int l = __ffs(todo) - 1; todo &= todo - 1;
@@ -387,6 +404,7 @@ insert_tuples_kernel(TableView tv, const uint64_t *__restrict__ tuples, const un
             if (i >= n) break;
             uint64_t key; uint32_t e;
             tuple_unpack<TW>(tuples, i, key, e);
+            if (e == 255u) continue;                                  // padding of the routed layout (no instance has all 8 edges)
             const int st = insert_instance(tv, key, e);
             if (st < 0) {                                             // slice full: keep the tuple for after a grow
                 const unsigned long long j = atomicAdd(ovf_n, 1ULL);
@@ -562,15 +580,16 @@ cudaError_t launch_route_hist(cudaStream_t st, const TableView &tv, const Source
     return cudaGetLastError();
 }
 
-cudaError_t launch_route_offsets(cudaStream_t st, const RouteMap &rt, int me, const unsigned long long *H,
-                                 unsigned long long *cursor, unsigned long long *recv_totals, uint64_t *launches) {
-    route_offsets_kernel<<<rt.nranks, 1024, 0, st>>>(rt.nranks, 1u << rt.nb_bits, me, H, cursor, recv_totals);
+cudaError_t launch_route_offsets(cudaStream_t st, const RouteMap &rt, int me, int cap, int tw, unsigned long long slab_cap,
+                                 const unsigned long long *H, unsigned long long *front, unsigned long long *back,
+                                 unsigned long long *recv, uint64_t *launches) {
+    route_offsets_kernel<<<rt.nranks, 1024, 0, st>>>(rt, me, cap, tw, slab_cap, H, front, back, recv);
     ++*launches;
     return cudaGetLastError();
 }
 
 cudaError_t launch_route_scatter(cudaStream_t st, const TableView &tv, const Source &src, const RouteMap &rt,
-                                 unsigned long long *cursor, int cap, uint64_t *launches) {
+                                 unsigned long long *cursor, unsigned long long *back, int cap, uint64_t *launches) {
     const uint64_t n = source_bound(src);
     if (!n) return cudaSuccess;
     const int tw = tuple_words(tv.k);
@@ -581,8 +600,15 @@ cudaError_t launch_route_scatter(cudaStream_t st, const TableView &tv, const Sou
         e = cudaFuncSetAttribute(slice_scatter_kernel<TWV, RV, NTV, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
         if (e != cudaSuccess) return e;                                                                             \
         const unsigned grid = std::min<uint64_t>((n + NTV * RV - 1) / (NTV * RV), (uint64_t)sm_count());           \
-        slice_scatter_kernel<TWV, RV, NTV, true><<<grid, NTV, smem, st>>>(v, src, nullptr, cursor, cap, rt); } while (0)
-    if (tw == 1) KQ_ROUTE_LAUNCH(1, 16, 512); else KQ_ROUTE_LAUNCH(2, 8, 512);
+        slice_scatter_kernel<TWV, RV, NTV, true><<<grid, NTV, smem, st>>>(v, src, nullptr, cursor, cap, rt, back); } while (0)
+    static const int variant = [] { const char *e = std::getenv("KQ_RT_VARIANT"); return e ? std::atoi(e) : 0; }();   // tuning knob
+    if (tw == 1) {
+        if (variant == 1) KQ_ROUTE_LAUNCH(1, 8, 1024);
+        else if (variant == 2) KQ_ROUTE_LAUNCH(1, 8, 512);
+        else KQ_ROUTE_LAUNCH(1, 16, 512);
+    } else {
+        KQ_ROUTE_LAUNCH(2, 8, 512);
+    }
     ++*launches;
     return cudaGetLastError();
 }
@@ -614,7 +640,7 @@ cudaError_t launch_slice_scatter(cudaStream_t st, const TableView &tv, const Sou
         e = cudaFuncSetAttribute(slice_scatter_kernel<TWV, RV, NTV, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
         if (e != cudaSuccess) return e;                                                                             \
         const unsigned grid = std::min<uint64_t>((n + NTV * RV - 1) / (NTV * RV), (uint64_t)sm_count());           \
-        slice_scatter_kernel<TWV, RV, NTV, false><<<grid, NTV, smem, st>>>(tv, src, out, cursor, cap, RouteMap{}); } while (0)
+        slice_scatter_kernel<TWV, RV, NTV, false><<<grid, NTV, smem, st>>>(tv, src, out, cursor, cap, RouteMap{}, nullptr); } while (0)
     if (tw == 1) {                                                   // measured on C2 (profiles/): 16 x 512 is the fastest
         if (variant == 1) KQ_SCATTER_LAUNCH(1, 8, 512);
         else if (variant == 2) KQ_SCATTER_LAUNCH(1, 8, 1024);

@@ -75,13 +75,15 @@ cudaError_t launch_insert_tuples(cudaStream_t st, const TableView &tv, const uin
                                  uint64_t *launches);
 // routed pipeline, steps 1-3: hist[nranks << nb_bits] of this rank's tuples; from the all-gathered
 // histograms H[nranks][P] the start of this rank's tuples inside every destination bin (cursor[P]) and what
-// every rank receives (recv_totals[nranks]); scatter straight into the owners' receive slabs
+// every rank receives (recv[d] = extent of d's slab with the alignment padding, recv[nranks + d] = real
+// tuples in it); scatter straight into the owners' receive slabs
 cudaError_t launch_route_hist(cudaStream_t st, const TableView &tv, const Source &src, const RouteMap &rt,
                               unsigned long long *hist, uint64_t *launches);
-cudaError_t launch_route_offsets(cudaStream_t st, const RouteMap &rt, int me, const unsigned long long *H,
-                                 unsigned long long *cursor, unsigned long long *recv_totals, uint64_t *launches);
+cudaError_t launch_route_offsets(cudaStream_t st, const RouteMap &rt, int me, int cap, int tw, unsigned long long slab_cap,
+                                 const unsigned long long *H, unsigned long long *front, unsigned long long *back,
+                                 unsigned long long *recv, uint64_t *launches);
 cudaError_t launch_route_scatter(cudaStream_t st, const TableView &tv, const Source &src, const RouteMap &rt,
-                                 unsigned long long *cursor, int cap, uint64_t *launches);
+                                 unsigned long long *cursor, unsigned long long *back, int cap, uint64_t *launches);
 // multi-GPU, NCCL transport: extract every valid window and append its tuple to the slab of its owner rank
 cudaError_t launch_extract_route(cudaStream_t st, const TableView &tv, const Source &src, RouteArgs ra,
                                  uint64_t *launches);

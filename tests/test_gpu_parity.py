@@ -350,7 +350,9 @@ def test_peer_routed_pipeline_shards_one_gpu(mods, k, nr, hint):
         for g in gs:
             g.sync()
         Hh = H.cpu().numpy().reshape(nr, nr, P // nr)
-        assert nrecv == [int(Hh[:, r, :].sum()) for r in range(nr)]
+        for r in range(nr):                    # slab extent = real tuples + alignment padding (< 32 per sender and bin)
+            real = int(Hh[:, r, :].sum())
+            assert real <= nrecv[r] <= real + 32 * P
         sent += int(Hh.sum())
         for r in range(nr):
             check(L.kq_route_insert(gs[r].handle, nrecv[r]), gs[r].handle)
