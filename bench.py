@@ -405,8 +405,18 @@ def main_ours(args):
         per_launch_s = res["kt_count"] * 1e-3 / res["kn_count"]
         units_per_launch = inst_per_rank * args.steps / res["kn_count"]
         ach = ALG_BYTES_COUNT * units_per_launch / per_launch_s / 1e9
+        traffic, traffic_src = None, None
+        try:                                        # dram__bytes_read+write of this kernel from the committed ncu --set full capture
+            with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+                t = json.load(f)["insert_tuples_kernel"]
+            traffic = t["dram_bytes_per_tuple"] * units_per_launch
+            traffic_src = "%s: %.1f B/tuple at %d tuples per launch, scaled to this run's tuples per launch" % (
+                t["summary"], t["dram_bytes_per_tuple"], t["tuples_per_launch"])
+        except Exception:
+            pass
         line["roofline"] = {"bound": "hbm", "kernel": "insert_tuples_kernel",
-                            "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+                            "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": traffic,
+                            "traffic_source": traffic_src,
                             "peak_source": peak_src, "algorithmic_bytes_per_kmer": ALG_BYTES_COUNT,
                             "sector_bound_frac": SECTOR_BYTES_COUNT * units_per_launch / per_launch_s / 1e9 / peak,
                             "avg_launch_ms": per_launch_s * 1e3, "launches_timed": res["kn_count"],
