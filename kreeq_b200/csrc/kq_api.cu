@@ -65,6 +65,7 @@ struct kq_ctx {
     int *d_err = nullptr;
     uint64_t occ_known = 0;                      // T occupancy at the last synchronisation
     uint64_t occ_bound = 0;                      // upper bound of it including batches in flight
+    uint64_t big_seen = 0;                       // records fed by load / union that could own a side-table entry
     uint64_t r_bound = 0;                        // upper bound of R's occupancy (a key needs 128 instances to get there)
     bool optimistic = false;                     // the caller sized the table (kq_create / kq_reserve)
     int rank = 0, nranks = 1;
@@ -558,7 +559,7 @@ extern "C" int kq_clear(kq_ctx *c) {
     CU(cudaMemsetAsync(c->d_inst, 0, sizeof(unsigned long long), c->stream));
     CU(cudaMemsetAsync(c->d_ovf_n, 0, sizeof(unsigned long long), c->stream));
     CU(cudaMemsetAsync(c->d_err, 0, sizeof(int), c->stream));
-    c->occ_known = c->occ_bound = 0; c->r_bound = 0; c->inst_tuples = 0; c->ovf_pending = false; c->loaded_db = false;
+    c->occ_known = c->occ_bound = 0; c->r_bound = 0; c->big_seen = 0; c->inst_tuples = 0; c->ovf_pending = false; c->loaded_db = false;
     return KQ_OK;
 }
 
@@ -1122,19 +1123,39 @@ int write_hc_part(kq_ctx *c, const std::string &dir, const std::vector<Rec32Entr
     return ok ? KQ_OK : fail(c, KQ_EIO, "short write on " + hc_part_path(dir, c->rank));
 }
 
+int save_maps_gpu(kq_ctx *c, const std::string &dir, std::vector<Rec32Entry> &hc);
+int load_maps_gpu(kq_ctx *c, const std::string &dir, XRec **d_xs, uint64_t *n_out);
+
+// KQ_DB_HOST=1 keeps the file codec on the host (the first implementation; useful to cross-check the device one)
+bool db_on_host() { static const bool v = [] { const char *e = std::getenv("KQ_DB_HOST"); return e && e[0] == '1'; }(); return v; }
+
 int save_impl(kq_ctx *c, const char *dir_c, bool maps_too) {
     if (!c || !dir_c) return KQ_EINVAL;
     CU(cudaSetDevice(c->device));
     const std::string dir(dir_c);
     mkdir(dir.c_str(), 0777);
-    std::vector<std::vector<Rec8Entry>> maps; std::vector<Rec32Entry> hc;
-    int rc = gather_for_save(c, maps, hc); if (rc) return rc;
-    if (maps_too) {
-        int lo, hi; owned_maps(c, lo, hi);
-        std::vector<std::string> errs(128);
-        global_pool().parallel_for((size_t)(hi - lo), [&](size_t i) { errs[lo + i] = write_map8(map_path(dir, lo + (int)i), maps[lo + i]); });
-        for (const auto &e : errs) if (!e.empty()) return fail(c, KQ_EIO, e);
+    std::vector<Rec32Entry> hc;
+    if (maps_too && !db_on_host()) {
+        int rc = save_maps_gpu(c, dir, hc); if (rc) return rc;
+        std::vector<SideSlot> side; rc = fetch_map32(c, side); if (rc) return rc;
+        for (const auto &q : side) {                                   // literal maps32 entries of a loaded / merged database
+            if (!q.tag) continue;
+            Rec32Entry h; h.key = q.tag - 1;
+            for (int w = 0; w < 4; ++w) { h.fw[w] = clamp_u32(q.fw[w]); h.bw[w] = clamp_u32(q.bw[w]); }
+            h.cov = clamp_u32(q.cov);
+            hc.push_back(h);
+        }
         if (c->rank == 0) { const std::string e = write_index(dir, c->k); if (!e.empty()) return fail(c, KQ_EIO, e); }
+    } else {
+        std::vector<std::vector<Rec8Entry>> maps;
+        int rc = gather_for_save(c, maps, hc); if (rc) return rc;
+        if (maps_too) {
+            int lo, hi; owned_maps(c, lo, hi);
+            std::vector<std::string> errs(128);
+            global_pool().parallel_for((size_t)(hi - lo), [&](size_t i) { errs[lo + i] = write_map8(map_path(dir, lo + (int)i), maps[lo + i]); });
+            for (const auto &e : errs) if (!e.empty()) return fail(c, KQ_EIO, e);
+            if (c->rank == 0) { const std::string e = write_index(dir, c->k); if (!e.empty()) return fail(c, KQ_EIO, e); }
+        }
     }
     if (c->nranks == 1 && maps_too) {
         const std::string e = write_map32(dir + "/.map.hc.bin", hc);
@@ -1187,7 +1208,234 @@ int read_owned_hc(kq_ctx *c, const std::string &dir, std::vector<Rec32Entry> &hc
     return KQ_OK;
 }
 
+
+// ---- .kreeq files through device-built images -------------------------------------------------------
+
+// per-thread pinned staging buffer + stream for the file <-> device copies of the pool workers
+struct FileStage { char *buf = nullptr; cudaStream_t st = nullptr; int device = -1; };
+constexpr size_t FILE_CHUNK = 32u << 20;
+constexpr uint64_t kDumpVersion = 0xFFFFFFFFFFFFFFF5ULL;              // SIZE_MAX - 10, phmap_dump.h:47-48
+FileStage *file_stage(int device) {
+    thread_local FileStage s;
+    if (s.device != device) {
+        if (cudaSetDevice(device) != cudaSuccess) return nullptr;
+        if (s.buf) { cudaFreeHost(s.buf); cudaStreamDestroy(s.st); s.buf = nullptr; }
+        if (cudaHostAlloc(&s.buf, FILE_CHUNK, cudaHostAllocDefault) != cudaSuccess) { s.buf = nullptr; return nullptr; }
+        if (cudaStreamCreateWithFlags(&s.st, cudaStreamNonBlocking) != cudaSuccess) { cudaFreeHost(s.buf); s.buf = nullptr; return nullptr; }
+        s.device = device;
+    }
+    return &s;
+}
+
+// occupied slots of the table as records, left on the device
+int export_device(kq_ctx *c, XRec **d_xs, uint64_t *n_out) {
+    int rc = kq_sync(c); if (rc) return rc;
+    unsigned long long *d_n = nullptr;
+    const unsigned long long cap = c->occ_known + 1;
+    CU(cudaMalloc(d_xs, cap * sizeof(XRec))); CU(cudaMalloc(&d_n, 8));
+    CU(cudaMemsetAsync(d_n, 0, 8, c->stream));
+    CU(launch_export(c->stream, view(c), *d_xs, cap, d_n, &c->launches));
+    unsigned long long n = 0;
+    CU(cudaMemcpyAsync(&n, d_n, 8, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    cudaFree(d_n);
+    if (n > cap) { cudaFree(*d_xs); *d_xs = nullptr; return fail(c, KQ_ECUDA, "export: occupancy counter out of sync"); }
+    *n_out = n;
+    return KQ_OK;
+}
+
+// byte layout of the owned .map.<m>.bin files inside one device image (each file starts 256-byte aligned)
+struct ImageLayout { std::vector<DbBucket> buckets; std::vector<uint64_t> file_off, file_size; uint64_t total = 0; };
+
+void layout_from_counts(const std::vector<unsigned long long> &counts, int lo, int hi, ImageLayout &L) {
+    L.buckets.assign(128 * 256, DbBucket{0, 0, 0, 0, 0});
+    L.file_off.assign(128, 0); L.file_size.assign(128, 0);
+    uint64_t at = 0;
+    for (int m = lo; m < hi; ++m) {
+        L.file_off[m] = at;
+        uint64_t cur = 8;                                              // u64 submap count
+        for (int s = 0; s < 256; ++s) {
+            DbBucket &b = L.buckets[(size_t)m * 256 + s];
+            b.n = counts[(size_t)m * 256 + s];
+            b.hdr_off = at + cur; cur += 24;
+            if (b.n) {
+                b.cap = db_capacity_for(b.n);
+                b.ctrl_off = at + cur; cur += b.cap + 17;
+                b.slot_off = at + cur; cur += b.cap * 24 + 8;           // slots + growth_left
+            }
+        }
+        L.file_size[m] = cur;
+        at = (at + cur + 255) & ~255ull;
+    }
+    L.total = at;
+}
+
+// write the 8-bit maps this shard owns from a device-built image; hc receives the 32-bit spill records
+int save_maps_gpu(kq_ctx *c, const std::string &dir, std::vector<Rec32Entry> &hc) {
+    XRec *d_xs = nullptr; uint64_t n = 0;
+    int rc = export_device(c, &d_xs, &n); if (rc) return rc;
+    int lo, hi; owned_maps(c, lo, hi);
+    unsigned long long *d_counts = nullptr, *d_hc_n = nullptr, *d_pos = nullptr; XRec *d_hc = nullptr;
+    unsigned char *d_img = nullptr; DbBucket *d_buckets = nullptr;
+    auto cleanup = [&] { cudaFree(d_xs); cudaFree(d_counts); cudaFree(d_hc_n); cudaFree(d_pos); cudaFree(d_hc); cudaFree(d_img); cudaFree(d_buckets); };
+#define CUX(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { cleanup(); return fail(c, e_ == cudaErrorMemoryAllocation ? KQ_ENOMEM : KQ_ECUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); } } while (0)
+    CUX(cudaMalloc(&d_counts, 128 * 256 * 8)); CUX(cudaMalloc(&d_hc_n, 8));
+    std::vector<unsigned long long> counts(128 * 256);
+    unsigned long long hc_cap = std::min<unsigned long long>(n + 1, 1ull << 20), hc_n = 0;
+    for (;;) {                                                          // second pass only if the spill list was too small
+        cudaFree(d_hc); d_hc = nullptr;
+        CUX(cudaMalloc(&d_hc, hc_cap * sizeof(XRec)));
+        CUX(cudaMemsetAsync(d_counts, 0, 128 * 256 * 8, c->stream)); CUX(cudaMemsetAsync(d_hc_n, 0, 8, c->stream));
+        CUX(launch_db_count(c->stream, d_xs, n, lo, hi, d_counts, d_hc, hc_cap, d_hc_n, &c->launches));
+        CUX(cudaMemcpyAsync(counts.data(), d_counts, 128 * 256 * 8, cudaMemcpyDeviceToHost, c->stream));
+        CUX(cudaMemcpyAsync(&hc_n, d_hc_n, 8, cudaMemcpyDeviceToHost, c->stream));
+        CUX(cudaStreamSynchronize(c->stream));
+        if (hc_n <= hc_cap) break;
+        hc_cap = hc_n;
+    }
+    if (hc_n) {
+        std::vector<XRec> h(hc_n);
+        CUX(cudaMemcpy(h.data(), d_hc, hc_n * sizeof(XRec), cudaMemcpyDeviceToHost));
+        for (const auto &x : h) { Rec32Entry e; e.key = x.key; std::memcpy(e.fw, x.r.fw, 16); std::memcpy(e.bw, x.r.bw, 16); e.cov = x.r.cov; hc.push_back(e); }
+    }
+    ImageLayout L; layout_from_counts(counts, lo, hi, L);
+    CUX(cudaMalloc(&d_img, std::max<uint64_t>(L.total, 256)));
+    CUX(cudaMemsetAsync(d_img, 0, std::max<uint64_t>(L.total, 256), c->stream));
+    CUX(cudaMalloc(&d_buckets, L.buckets.size() * sizeof(DbBucket)));
+    CUX(cudaMemcpyAsync(d_buckets, L.buckets.data(), L.buckets.size() * sizeof(DbBucket), cudaMemcpyHostToDevice, c->stream));
+    CUX(cudaMalloc(&d_pos, (n + 1) * 8));
+    CUX(launch_db_build(c->stream, d_xs, n, lo, hi, d_img, d_buckets, d_pos, &c->launches));
+    CUX(cudaStreamSynchronize(c->stream));
+#undef CUX
+    rc = check_device_error(c); if (rc) { cleanup(); return rc; }
+    // one pool task per file: device image -> pinned chunk -> fwrite
+    std::vector<std::string> errs((size_t)(hi - lo));
+    const int device = c->device;
+    global_pool().parallel_for((size_t)(hi - lo), [&](size_t i) {
+        const int m = lo + (int)i;
+        FileStage *fs = file_stage(device);
+        if (!fs) { errs[i] = "cannot allocate a pinned staging buffer"; return; }
+        const std::string path = map_path(dir, m);
+        FILE *f = std::fopen(path.c_str(), "wb");
+        if (!f) { errs[i] = "cannot open " + path + " for writing"; return; }
+        for (uint64_t off = 0; off < L.file_size[m]; off += FILE_CHUNK) {
+            const size_t len = (size_t)std::min<uint64_t>(FILE_CHUNK, L.file_size[m] - off);
+            if (cudaMemcpyAsync(fs->buf, d_img + L.file_off[m] + off, len, cudaMemcpyDeviceToHost, fs->st) != cudaSuccess ||
+                cudaStreamSynchronize(fs->st) != cudaSuccess) { errs[i] = "device to host copy failed for " + path; break; }
+            if (std::fwrite(fs->buf, 1, len, f) != len) { errs[i] = "short write on " + path; break; }
+        }
+        if (std::fclose(f) != 0 && errs[i].empty()) errs[i] = "short write on " + path;
+    });
+    c->d2h += L.total;
+    cleanup();
+    for (const auto &e : errs) if (!e.empty()) return fail(c, KQ_EIO, e);
+    return KQ_OK;
+}
+
+// upload the owned .map.<m>.bin files of a database and decode them on the device into raw records
+int load_maps_gpu(kq_ctx *c, const std::string &dir, XRec **d_xs, uint64_t *n_out) {
+    int lo, hi; owned_maps(c, lo, hi);
+    *d_xs = nullptr; *n_out = 0;
+    std::vector<uint64_t> file_off(128, 0), file_size(128, 0);
+    uint64_t total = 0;
+    for (int m = lo; m < hi; ++m) {
+        struct stat st;
+        if (stat(map_path(dir, m).c_str(), &st) != 0) return fail(c, KQ_EIO, "cannot open " + map_path(dir, m));
+        file_off[m] = total; file_size[m] = (uint64_t)st.st_size;
+        total = (total + file_size[m] + 255) & ~255ull;
+    }
+    unsigned char *d_img = nullptr; DbBucket *d_buckets = nullptr; unsigned long long *d_n = nullptr;
+    CU(cudaMalloc(&d_img, std::max<uint64_t>(total, 256)));
+    std::vector<DbBucket> buckets((size_t)(hi - lo) * 256, DbBucket{0, 0, 0, 0, 0});
+    std::vector<std::string> errs((size_t)(hi - lo));
+    const int device = c->device;
+    global_pool().parallel_for((size_t)(hi - lo), [&](size_t i) {
+        const int m = lo + (int)i;
+        const std::string path = map_path(dir, m);
+        FileStage *fs = file_stage(device);
+        if (!fs) { errs[i] = "cannot allocate a pinned staging buffer"; return; }
+        FILE *f = std::fopen(path.c_str(), "rb");
+        if (!f) { errs[i] = "cannot open " + path; return; }
+        // submap directory: three or four u64 per submap, the rest is skipped (phmap_dump.h:60-104)
+        auto rd64 = [&](uint64_t at, uint64_t &v) { return at + 8 <= file_size[m] && fseeko(f, (off_t)at, SEEK_SET) == 0 && std::fread(&v, 8, 1, f) == 1; };
+        uint64_t cur = 0, nsub = 0;
+        if (!rd64(cur, nsub) || nsub != 256) { errs[i] = path + ": submap count is not 256"; std::fclose(f); return; }
+        cur += 8;
+        for (int s = 0; s < 256 && errs[i].empty(); ++s) {
+            uint64_t ver = 0, n = 0, cap = 0;
+            bool ok = rd64(cur, ver); cur += 8;
+            if (ok && ver < kDumpVersion) n = ver; else { ok = ok && rd64(cur, n); cur += 8; }   // phmap_dump.h:77-83
+            ok = ok && rd64(cur, cap); cur += 8;
+            if (!ok) { errs[i] = path + ": truncated"; break; }
+            DbBucket &b = buckets[i * 256 + s];
+            b.n = n; b.cap = cap;
+            if (!n) continue;
+            b.ctrl_off = file_off[m] + cur; cur += cap + 17;
+            b.slot_off = file_off[m] + cur; cur += cap * 24 + (ver >= kDumpVersion ? 8 : 0);
+            if (cur > file_size[m]) errs[i] = path + ": truncated submap";
+        }
+        if (errs[i].empty() && fseeko(f, 0, SEEK_SET) != 0) errs[i] = "cannot read " + path;
+        for (uint64_t off = 0; off < file_size[m] && errs[i].empty(); off += FILE_CHUNK) {
+            const size_t len = (size_t)std::min<uint64_t>(FILE_CHUNK, file_size[m] - off);
+            if (std::fread(fs->buf, 1, len, f) != len) { errs[i] = "cannot read " + path; break; }
+            if (cudaMemcpyAsync(d_img + file_off[m] + off, fs->buf, len, cudaMemcpyHostToDevice, fs->st) != cudaSuccess ||
+                cudaStreamSynchronize(fs->st) != cudaSuccess) errs[i] = "host to device copy failed for " + path;
+        }
+        std::fclose(f);
+    });
+    for (const auto &e : errs) if (!e.empty()) { cudaFree(d_img); return fail(c, KQ_EIO, e); }
+    c->h2d += total;
+    uint64_t n = 0; for (const auto &b : buckets) n += b.n;
+    auto cleanup = [&] { cudaFree(d_img); cudaFree(d_buckets); cudaFree(d_n); };
+#define CUX(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { cleanup(); cudaFree(*d_xs); *d_xs = nullptr; return fail(c, e_ == cudaErrorMemoryAllocation ? KQ_ENOMEM : KQ_ECUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); } } while (0)
+    CUX(cudaMalloc(&d_buckets, buckets.size() * sizeof(DbBucket))); CUX(cudaMalloc(&d_n, 8));
+    CUX(cudaMalloc(d_xs, (n + 1) * sizeof(XRec)));
+    CUX(cudaMemcpyAsync(d_buckets, buckets.data(), buckets.size() * sizeof(DbBucket), cudaMemcpyHostToDevice, c->stream));
+    CUX(cudaMemsetAsync(d_n, 0, 8, c->stream));
+    CUX(launch_db_decode(c->stream, d_img, d_buckets, (unsigned)buckets.size(), *d_xs, n, d_n, &c->launches));
+    unsigned long long got = 0;
+    CUX(cudaMemcpyAsync(&got, d_n, 8, cudaMemcpyDeviceToHost, c->stream));
+    CUX(cudaStreamSynchronize(c->stream));
+#undef CUX
+    cleanup();
+    if (got != n) { cudaFree(*d_xs); *d_xs = nullptr; return fail(c, KQ_EIO, dir + ": submap sizes do not match their control bytes"); }
+    *n_out = n;
+    return KQ_OK;
+}
+
 enum class Feed { Put, MergeRef, AddLogical };
+
+// run device-resident records through one of the table kernels, in sub-batches small enough that neither
+// the table nor a side table can fill up inside a launch
+int feed_device(kq_ctx *c, const XRec *d, uint64_t total, Feed mode) {
+    for (uint64_t off = 0; off < total;) {
+        const uint64_t n = std::min<uint64_t>(total - off, 64ull << 20);
+        // only records with a field above a slot lane (or placeholders) can create side-table entries, and a
+        // merge can spill at most those plus the keys that already own a remainder: size R and M for that
+        CU(cudaMemsetAsync(c->d_total, 0, 8, c->stream));
+        CU(launch_db_count_big(c->stream, d + off, n, c->d_total, &c->launches));
+        unsigned long long big = 0;
+        CU(cudaMemcpyAsync(&big, c->d_total, 8, cudaMemcpyDeviceToHost, c->stream));
+        uint64_t occ[3]; int rc = read_occ(c, occ); if (rc) return rc;
+        c->big_seen += big;
+        const uint64_t need_r = occ[1] + big, need_m = occ[2] + c->big_seen;
+        if (need_r * 2 > c->rcap) { rc = grow_side(c, 1, std::max<uint64_t>(4 * c->rcap, 4 * need_r)); if (rc) return rc; }
+        if (mode != Feed::Put && need_m * 2 > c->mcap) { rc = grow_side(c, 2, std::max<uint64_t>(4 * c->mcap, 4 * need_m)); if (rc) return rc; }
+        if ((double)(occ[0] + n) > MAX_LOAD * (double)table_slots(c)) {
+            rc = grow_table(c, std::max<uint64_t>(2 * table_slots(c), (uint64_t)((double)(occ[0] + n) / TARGET_LOAD)));
+            if (rc) return rc;
+        }
+        const TableView tv = view(c);
+        cudaError_t e = mode == Feed::Put ? launch_put(c->stream, tv, d + off, n, &c->launches)
+                      : mode == Feed::MergeRef ? launch_merge_ref(c->stream, tv, d + off, n, &c->launches)
+                                               : launch_add_records(c->stream, tv, d + off, n, &c->launches);
+        if (e != cudaSuccess) return fail(c, KQ_ECUDA, cudaGetErrorString(e));
+        off += n;
+    }
+    uint64_t occ[3]; int rc = read_occ(c, occ); if (rc) return rc;
+    c->occ_bound = occ[0];
+    return check_device_error(c);
+}
 
 // stream host records through a device buffer into one of the table kernels, in sub-batches small
 // enough that neither the table nor a side table can fill up inside a launch
@@ -1266,9 +1514,19 @@ extern "C" int kq_db_load(kq_ctx *c, const char *dir_c) {
     if (k < 0) return fail(c, KQ_EIO, "Cannot load DBG input. Exiting.");          // src/input.cpp:70-72
     if (k != c->k) return fail(c, KQ_EINVAL, "database k-mer length " + std::to_string(k) + " differs from the handle's " + std::to_string(c->k));
     int rc = kq_clear(c); if (rc) return rc;
-    std::vector<Rec8Entry> all; rc = read_owned_maps(c, dir, all); if (rc) return rc;
     std::vector<Rec32Entry> hc; rc = read_owned_hc(c, dir, hc); if (rc) return rc;
     rc = upload_map32(c, hc, MIN_SCAP); if (rc) return rc;
+    if (!db_on_host()) {
+        XRec *d_xs = nullptr; uint64_t n = 0;
+        rc = load_maps_gpu(c, dir, &d_xs, &n); if (rc) return rc;
+        if ((double)n > TARGET_LOAD * (double)table_slots(c)) rc = grow_table(c, (uint64_t)((double)n / TARGET_LOAD));
+        if (!rc) rc = feed_device(c, d_xs, n, Feed::Put);
+        cudaFree(d_xs);
+        if (rc) return rc;
+        c->loaded_db = true;
+        return KQ_OK;
+    }
+    std::vector<Rec8Entry> all; rc = read_owned_maps(c, dir, all); if (rc) return rc;
     std::vector<XRec> xs(all.size());
     global_pool().parallel_for((all.size() + (1 << 20) - 1) >> 20, [&](size_t t) {
         const size_t b = t << 20, e = std::min(all.size(), b + (1 << 20));
@@ -1312,6 +1570,14 @@ extern "C" int kq_union(kq_ctx *c, const char *const *dirs, int n, int ref_compa
         rc = upload_map32(c, m32, 1ull << 16); if (rc) return rc;
         // 2. DB0's 8-bit maps raw (kmer.h:668-672), 3. later databases in order (kmer.h:674-686)
         for (int i = 0; i < n; ++i) {
+            if (!db_on_host()) {
+                XRec *d_xs = nullptr; uint64_t nx = 0;
+                rc = load_maps_gpu(c, dirs[i], &d_xs, &nx); if (rc) return rc;
+                rc = feed_device(c, d_xs, nx, i == 0 ? Feed::Put : Feed::MergeRef);
+                cudaFree(d_xs);
+                if (rc) return rc;
+                continue;
+            }
             std::vector<Rec8Entry> all; rc = read_owned_maps(c, dirs[i], all); if (rc) return rc;
             std::vector<XRec> xs(all.size());
             for (size_t j = 0; j < all.size(); ++j) xs[j] = raw_xrec(all[j]);

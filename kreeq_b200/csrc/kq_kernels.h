@@ -116,4 +116,21 @@ cudaError_t launch_add_records(cudaStream_t st, const TableView &tv, const XRec 
 // reference-compatible union: DBG::mergeSubMaps for the 8-bit entries of one later database
 cudaError_t launch_merge_ref(cudaStream_t st, const TableView &tv, const XRec *in, uint64_t n, uint64_t *launches);
 
+// ---- .kreeq file images on the device (row A8 / N1, kq_db_kernels.cu) -----------------------------------------
+// one submap of one .map.<m>.bin inside a device image: byte offsets of its header, control bytes and slots
+struct DbBucket { unsigned long long hdr_off, ctrl_off, slot_off, cap, n; };
+unsigned long long db_capacity_for(unsigned long long n);
+// records per (map, submap) bucket (counts[128 * 256]) of the maps [lo, hi); 32-bit spill records -> hc
+cudaError_t launch_db_count(cudaStream_t st, const XRec *xs, unsigned long long n, int lo, int hi,
+                            unsigned long long *counts, XRec *hc, unsigned long long hc_cap, unsigned long long *hc_n,
+                            uint64_t *launches);
+// lay out headers + control bytes, place every record (phmap probe order), write the slots; img is zeroed
+cudaError_t launch_db_build(cudaStream_t st, const XRec *xs, unsigned long long n, int lo, int hi, unsigned char *img,
+                            const DbBucket *buckets, unsigned long long *pos_scratch, uint64_t *launches);
+// *out += records that can create a remainder / maps32 entry (a field above a slot lane, or a placeholder)
+cudaError_t launch_db_count_big(cudaStream_t st, const XRec *xs, unsigned long long n, unsigned long long *out, uint64_t *launches);
+// uploaded file images -> raw records
+cudaError_t launch_db_decode(cudaStream_t st, const unsigned char *img, const DbBucket *buckets, unsigned nbuckets,
+                             XRec *out, unsigned long long cap_out, unsigned long long *n_out, uint64_t *launches);
+
 }  // namespace kq

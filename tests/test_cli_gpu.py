@@ -130,3 +130,48 @@ def test_hist_and_errors(tmp_path):
     assert p.returncode != 0 and b"At least two databases required (-d)." in p.stderr
     p = subprocess.run([EXE, "frobnicate", "-x", "y"], cwd=str(tmp_path), capture_output=True)
     assert p.returncode != 0 and b"does not exist" in p.stderr
+
+
+REF_BIN = os.path.join(ROOT, "oracle", "_ref", "kreeq")
+
+
+@pytest.mark.skipif(not os.path.exists(REF_BIN), reason="oracle/_ref/kreeq not built")
+@pytest.mark.parametrize("name", ["synthA_k21", "synthC_k32_c3", "random1x2_k21"])
+def test_reference_binary_reads_gpu_written_database(name, tmp_path):
+    """The .map.<m>.bin images are laid out by CUDA kernels (kq_db_kernels.cu); the UNMODIFIED reference must
+    load them and print what it prints for its own database (checker use of oracle/_ref only)."""
+    r = RUNS[name]
+    k, cutoff = r["k"], r["cutoff"]
+    reads = [os.path.join(GOLD, p) for p in r["reads"]]
+    asm = os.path.join(GOLD, r["asm"])
+    db = str(tmp_path / "db.kreeq")
+    run(["validate", "-r"] + reads + ["-k", str(k), "-o", db], str(tmp_path))
+    out = str(tmp_path / "x.kwig")
+    p = subprocess.run([REF_BIN, "validate", "-f", asm, "-d", db, "-k", str(k), "-c", str(cutoff), "-o", out, "-j", "2"],
+                       cwd=str(tmp_path), stdout=subprocess.PIPE, stderr=subprocess.PIPE, timeout=600)
+    assert p.returncode == 0, p.stderr.decode()
+    assert p.stdout.decode() == r["validate_stdout"]
+    with open(out, "rb") as f:
+        assert f.read() == _gz("ref_runs/%s.kwig.gz" % name)
+
+
+def test_host_and_device_codecs_agree(tmp_path):
+    """KQ_DB_HOST=1 selects the host implementation of the file codec: both write databases that decode to
+    the same records, and each loads what the other wrote."""
+    r = RUNS["synthB_k31"]
+    reads = [os.path.join(GOLD, p) for p in r["reads"]]
+    asm = os.path.join(GOLD, r["asm"])
+    dbs = {}
+    for mode in ("0", "1"):
+        env = dict(os.environ, KQ_DB_HOST=mode)
+        db = str(tmp_path / ("db%s.kreeq" % mode))
+        p = subprocess.run([EXE, "validate", "-r"] + reads + ["-k", "31", "-o", db], cwd=str(tmp_path), env=env, capture_output=True)
+        assert p.returncode == 0 and p.stdout.decode() == r["count_stdout"]
+        dbs[mode] = db
+    a, b = _db_arrays(dbs["0"]), _db_arrays(dbs["1"])
+    for x, y in zip(a, b):
+        assert x.tobytes() == y.tobytes()
+    for writer, reader in (("0", "1"), ("1", "0")):
+        env = dict(os.environ, KQ_DB_HOST=reader)
+        p = subprocess.run([EXE, "validate", "-f", asm, "-d", dbs[writer], "-k", "31"], cwd=str(tmp_path), env=env, capture_output=True)
+        assert p.returncode == 0 and p.stdout.decode() == r["validate_stdout"]
