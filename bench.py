@@ -43,6 +43,7 @@ def parse_args():
     ap.add_argument("--coverage", type=float, default=30.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-union", action="store_true", help="skip the database rows (save / union / load timing)")
     ap.add_argument("--ref-sample-reads", type=int, default=1_500_000)
     return ap.parse_args()
 
@@ -157,13 +158,26 @@ def run_reference_once(fq, fa, workdir, threads):
     db = os.path.join(workdir, "db.kreeq")
     shutil.rmtree(db, ignore_errors=True)
     t0 = time.perf_counter()
-    subprocess.check_call([REF_BIN, "validate", "-r", fq, "-k", str(K), "-o", db, "-j", str(threads)],
-                          cwd=workdir, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    out = subprocess.run([REF_BIN, "validate", "-r", fq, "-k", str(K), "-o", db, "-j", str(threads)],
+                         cwd=workdir, stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, check=True).stdout.decode()
     t1 = time.perf_counter()
     subprocess.check_call([REF_BIN, "validate", "-f", fa, "-d", db, "-o", os.path.join(workdir, "out.kwig"), "-j", str(threads)],
                           cwd=workdir, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
     t2 = time.perf_counter()
-    return t1 - t0, t2 - t1
+    distinct = [int(ln.split(":")[1]) for ln in out.splitlines() if ln.startswith("Distinct kmers")]
+    return t1 - t0, t2 - t1, (distinct[0] if distinct else 0)
+
+
+def run_reference_union(workdir, threads):
+    """`kreeq union -d db.kreeq db.kreeq -o u.kreeq`: the sample database merged with itself (row A4)."""
+    db = os.path.join(workdir, "db.kreeq"); u = os.path.join(workdir, "u.kreeq")
+    shutil.rmtree(u, ignore_errors=True)
+    t0 = time.perf_counter()
+    subprocess.check_call([REF_BIN, "union", "-d", db, db, "-o", u, "-j", str(threads)],
+                          cwd=workdir, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    dt = time.perf_counter() - t0
+    shutil.rmtree(u, ignore_errors=True)
+    return dt
 
 
 def cpu_baseline(args, steps, warmup):
@@ -175,13 +189,17 @@ def cpu_baseline(args, steps, warmup):
     workdir = tempfile.mkdtemp(prefix="kreeq_ref_", dir=base)
     try:
         fq, fa, inst, asm_k = reference_sample(args, workdir)
-        tc, tv = [], []
+        tc, tv, distinct = [], [], 0
         for i in range(warmup + steps):
-            c, v = run_reference_once(fq, fa, workdir, threads)
+            c, v, distinct = run_reference_once(fq, fa, workdir, threads)
             if i >= warmup:
                 tc.append(c); tv.append(v)
         c = sum(tc) / len(tc); v = sum(tv) / len(tv)
-        return {"value": inst / c, "unit": "k-mers/s", "cores": threads, "kind": "reference",
+        union = {}
+        if not getattr(args, "no_union", False) and distinct:
+            us = run_reference_union(workdir, threads)
+            union = {"union_value": 2 * distinct / us, "union_unit": "input records/s", "union_s": us, "union_records_in": 2 * distinct}
+        return {**union, "value": inst / c, "unit": "k-mers/s", "cores": threads, "kind": "reference",
                 "sample": "%d reads x %d bp of the same C2 generator (%d k-mer instances) counted by `kreeq validate -r -o db.kreeq -j %d`; "
                           "validate: first %d bp of the genome vs that DB" % (args.ref_sample_reads // 2 * 2, READ_LEN, inst, threads, asm_k + K - 1),
                 "count_s": c, "validate_value": asm_k / v, "validate_s": v}
@@ -331,6 +349,8 @@ def main_ours(args):
         e0, e1, e2 = ev(), ev(), ev()
         e0.record(stream)
         g.clear()
+        if os.environ.get("KQ_E2E_FLUSH"):                     # tuning knob: pending positions that start the pipeline
+            g.set_flush_positions(int(os.environ["KQ_E2E_FLUSH"]))
         B = 64 * (READ_LEN + 1) * 10000                       # ~97 MB pushes, cut at read boundaries
         if world > 1:
             for o in range(0, reads_np.size, B):
@@ -439,6 +459,17 @@ def main_ours(args):
                        "d2h_bytes_per_step": e["d2h"], "count_ms": e["count_ms"], "validate_ms": e["validate_ms"],
                        "validate_value": asm_k * world / (e["validate_ms"] * 1e-3),
                        "host_input_bytes_per_step": int(reads_np.size + asm_np.size), "steps": min(args.steps, 2)}
+    if world == 1 and not args.no_union:
+        # database rows (A4 / A8): 2 x 5.8e7-record databases of a 10 Mbp genome saved, merged, saved, loaded
+        from kreeq_b200.dbbench import union_rows
+        try:
+            u = union_rows(10.0, 30.0, None, local)
+            line["union"] = {"metric": "union_input_records_per_sec", "value": u["union_input_records_per_s"], "unit": "records/s",
+                             "save_records_per_sec": u["save_records_per_s"], "load_records_per_sec": u["load_records_per_s"],
+                             "records_in": u["records_in"], "records_out": u["records_out"], "db_bytes": u["db_bytes"],
+                             "files_on": u["files_on"], "mode": "reference-compatible (kq_union ..., 1)"}
+        except Exception as ex:                       # never lose the main line to the side measurement
+            line["union"] = {"error": str(ex)[:200]}
     if peers is not None:
         line["validate"]["peer_connect_ms"] = peers.connect_ms
         peers.disconnect()
