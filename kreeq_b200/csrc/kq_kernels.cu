@@ -384,8 +384,8 @@ constexpr int INS_TILE = TPB * 8;   // tuples per ticket
 // resident CTAs work within ~1.8 M consecutive tuples (less than half a slice) however their speeds
 // differ; with a static grid-stride assignment CTAs on the far L2 die fall behind and the set of
 // slices in use outgrows L2.
-template <int TW>
-__global__ void __launch_bounds__(TPB, CTAS_PER_SM)
+template <int TW, int CPS>
+__global__ void __launch_bounds__(TPB, CPS)
 insert_tuples_kernel(TableView tv, const uint64_t *__restrict__ tuples, const unsigned long long *n_ptr,
                      uint64_t *ovf, unsigned long long ovf_cap, unsigned long long *ovf_n, unsigned long long *ticket) {
     __shared__ unsigned long long sh[2];
@@ -446,7 +446,8 @@ extract_route_kernel(TableView tv, Source src, RouteArgs ra) {
 // ---- validate ------------------------------------------------------------------------------------
 
 // DBG::evaluateSegment src/kreeq.cpp:143-219 for positions [c0, c0+n) of one segment.
-__global__ void __launch_bounds__(TPB, CTAS_PER_SM)
+template <int CPS>
+__global__ void __launch_bounds__(TPB, CPS)
 validate_kernel(TableView tv, const uint64_t *__restrict__ B, const uint64_t *__restrict__ M,
                 uint64_t base0, uint64_t c0, uint64_t n, uint64_t kcount, uint32_t cutoff,
                 Base *__restrict__ out, unsigned long long *acc3, const TableView *__restrict__ peers, int npeers) {
@@ -660,7 +661,12 @@ cudaError_t launch_insert_tuples(cudaStream_t st, const TableView &tv, const uin
     if (!n_max) return cudaSuccess;
     cudaError_t e = cudaMemsetAsync(ticket, 0, sizeof(unsigned long long), st);
     if (e != cudaSuccess) return e;
-    KQ_TW_DISPATCH(tuple_words(tv.k), (insert_tuples_kernel<TW><<<grid_for(n_max, INS_TILE / TPB), TPB, 0, st>>>(tv, tuples, n, ovf, ovf_cap, ovf_n, ticket)));
+    // 8 CTAs of 256 threads = every thread slot of the SM (32 registers, a few spilled words): the kernel waits on
+    // L2 round trips and its rate follows the warps in flight (3/4/5/6/7/8 CTAs: 125/101/86/76/70/67 ms on C2)
+    static const int ctas = [] { const char *e = std::getenv("KQ_INSERT_CTAS"); const int v = e ? std::atoi(e) : 0; return v >= 1 && v <= 8 ? v : 8; }();   // tuning knob
+    const unsigned grid = (unsigned)std::min<uint64_t>((n_max + INS_TILE - 1) / INS_TILE, (uint64_t)sm_count() * ctas);
+    if (ctas > CTAS_PER_SM) KQ_TW_DISPATCH(tuple_words(tv.k), (insert_tuples_kernel<TW, 8><<<grid, TPB, 0, st>>>(tv, tuples, n, ovf, ovf_cap, ovf_n, ticket)));
+    else KQ_TW_DISPATCH(tuple_words(tv.k), (insert_tuples_kernel<TW, CTAS_PER_SM><<<grid, TPB, 0, st>>>(tv, tuples, n, ovf, ovf_cap, ovf_n, ticket)));
     ++*launches;
     return cudaGetLastError();
 }
@@ -678,7 +684,10 @@ cudaError_t launch_validate(cudaStream_t st, const TableView &tv, const uint64_t
                             uint64_t base0, uint64_t c0, uint64_t n, uint64_t kcount, uint32_t cutoff,
                             Base *out, unsigned long long *acc3, const TableView *peers, int npeers, uint64_t *launches) {
     if (!n) return cudaSuccess;
-    validate_kernel<<<grid_for(n), TPB, 0, st>>>(tv, B, M, base0, c0, n, kcount, cutoff, out, acc3, peers, npeers);
+    static const int ctas = [] { const char *e = std::getenv("KQ_VALIDATE_CTAS"); const int v = e ? std::atoi(e) : 0; return v >= 1 && v <= 8 ? v : 8; }();   // tuning knob (8: 0.42 ms, 6: 0.45 ms per 1e7 positions)
+    const unsigned grid = (unsigned)std::min<uint64_t>((n + TPB - 1) / TPB, (uint64_t)sm_count() * ctas);
+    if (ctas > CTAS_PER_SM) validate_kernel<8><<<grid, TPB, 0, st>>>(tv, B, M, base0, c0, n, kcount, cutoff, out, acc3, peers, npeers);
+    else validate_kernel<CTAS_PER_SM><<<grid, TPB, 0, st>>>(tv, B, M, base0, c0, n, kcount, cutoff, out, acc3, peers, npeers);
     ++*launches;
     return cudaGetLastError();
 }
