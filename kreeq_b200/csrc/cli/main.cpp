@@ -12,8 +12,12 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <condition_variable>
+#include <deque>
 #include <fstream>
 #include <iostream>
+#include <mutex>
+#include <thread>
 
 using namespace cli;
 
@@ -189,14 +193,58 @@ void print_qv(const kq_qv &qv, int k) {           // src/kreeq.cpp:78-106
     std::cout << qv.missing + qv.edge_missing << "\t" << qv.kcount << "\t" << kv << "\t" << ke << "\t" << std::to_string(k) << "\t" << "Kreeq" << std::endl;
 }
 
-struct PushSink : ReadSink {
-    kq_ctx *ctx;
-    explicit PushSink(kq_ctx *c) : ctx(c) {}
-    bool operator()(const char *data, size_t len) override {
-        CHECK(ctx, kq_count_push(ctx, data, len));
+// Read files are parsed (and gunzipped) by one producer thread each, at most four at a time; batches go
+// through a bounded queue to the caller's thread, which is the only one that talks to the library.  Counting
+// commutes, so the order in which batches of different files arrive does not change the database.
+struct BatchQueue {
+    std::mutex mu; std::condition_variable can_put, can_get;
+    std::deque<std::string> q; size_t producers = 0; std::string error;
+    static constexpr size_t kDepth = 4;
+    void put(std::string &&b) {
+        std::unique_lock<std::mutex> lk(mu);
+        can_put.wait(lk, [&] { return q.size() < kDepth; });
+        q.push_back(std::move(b)); can_get.notify_one();
+    }
+    bool get(std::string &b) {
+        std::unique_lock<std::mutex> lk(mu);
+        can_get.wait(lk, [&] { return !q.empty() || producers == 0; });
+        if (q.empty()) return false;
+        b = std::move(q.front()); q.pop_front(); can_put.notify_one();
         return true;
     }
 };
+struct QueueSink : ReadSink {
+    BatchQueue &bq;
+    explicit QueueSink(BatchQueue &b) : bq(b) {}
+    bool operator()(const char *data, size_t len) override { bq.put(std::string(data, len)); return true; }
+};
+
+bool count_files(kq_ctx *ctx, const std::vector<std::string> &files, std::string &err) {
+    BatchQueue bq;
+    std::mutex next_mu; size_t next = 0;
+    const size_t nthreads = std::min<size_t>(files.size(), 4);
+    bq.producers = nthreads;
+    std::vector<std::thread> threads;
+    for (size_t t = 0; t < nthreads; ++t)
+        threads.emplace_back([&] {
+            for (;;) {
+                size_t i;
+                { std::lock_guard<std::mutex> lk(next_mu); i = next++; }
+                if (i >= files.size()) break;
+                QueueSink sink(bq); std::string e;
+                if (!stream_reads(files[i], 128u << 20, sink, e)) { std::lock_guard<std::mutex> lk(bq.mu); if (bq.error.empty()) bq.error = e; }
+            }
+            { std::lock_guard<std::mutex> lk(bq.mu); --bq.producers; }
+            bq.can_get.notify_all();
+        });
+    std::string batch; int rc = KQ_OK;
+    while (bq.get(batch))
+        if (rc == KQ_OK) rc = kq_count_push(ctx, batch.data(), batch.size());      // keep draining after an error
+    for (auto &t : threads) t.join();
+    if (rc != KQ_OK) die(ctx, rc);
+    err = bq.error;
+    return err.empty();
+}
 
 void write_index(const std::string &dir, int k) {  // kreeq-output.cpp:88-94
     std::ofstream ofs(dir + "/.index");
@@ -253,10 +301,8 @@ int run_validate(Options &o) {                    // Input::read case 0, src/inp
         if (o.k < 1 || o.k > 32) { fprintf(stderr, "Invalid kmer length.\n"); return EXIT_FAILURE; }
         if (kq_create(&ctx, o.k, o.device, o.expected) != KQ_OK) die(nullptr, 0);
         verbose("Loading input reads.");
-        PushSink sink(ctx);
         std::string err;
-        for (const std::string &file : o.reads)
-            if (!stream_reads(file, 256u << 20, sink, err)) { fprintf(stderr, "%s\n", err.c_str()); return EXIT_FAILURE; }
+        if (!count_files(ctx, o.reads, err)) { fprintf(stderr, "%s\n", err.c_str()); return EXIT_FAILURE; }
         CHECK(ctx, kq_count_finish(ctx));
         verbose("Reads loaded.");
         if (keep_db) { make_dir(o.out); CHECK(ctx, kq_db_save(ctx, o.out.c_str())); }

@@ -5,11 +5,60 @@
 //   .bkwig             DBG::printTableCompressedBinary   src/kreeq-output.cpp:305-399
 #include "kreeq_cli.h"
 
+#include <algorithm>
+#include <atomic>
 #include <cstdio>
 #include <cstring>
+#include <functional>
+#include <thread>
 
 namespace cli {
 namespace {
+
+// Formats blocks [0, n) with fmt(block, out) on all cores, a wave at a time, and appends them to f in order.
+bool emit_blocks(FILE *f, size_t n, const std::function<void(size_t, std::string &)> &fmt) {
+    const size_t nthreads = std::max<size_t>(1, std::min<size_t>(std::thread::hardware_concurrency(), 32));
+    const size_t wave = nthreads * 2;
+    std::vector<std::string> out(wave);
+    for (size_t base = 0; base < n; base += wave) {
+        const size_t cnt = std::min(wave, n - base);
+        std::atomic<size_t> next{0};
+        auto work = [&] { for (size_t i; (i = next.fetch_add(1)) < cnt;) { out[i].clear(); fmt(base + i, out[i]); } };
+        std::vector<std::thread> th;
+        for (size_t t = 1; t < std::min(nthreads, cnt); ++t) th.emplace_back(work);
+        work();
+        for (auto &t : th) t.join();
+        for (size_t i = 0; i < cnt; ++i)
+            if (!out[i].empty() && fwrite(out[i].data(), 1, out[i].size(), f) != out[i].size()) return false;
+    }
+    return true;
+}
+
+inline void append_num(std::string &o, uint64_t v) {
+    char tmp[20];
+    int len = 0;
+    do { tmp[len++] = (char)('0' + v % 10); v /= 10; } while (v);
+    while (len) o.push_back(tmp[--len]);
+}
+
+constexpr uint64_t BLOCK = 1u << 20;               // bases per formatting task
+struct Span { const Path *path; const Component *comp; uint64_t abs_pos, from, to; };   // bases [from, to) of one segment
+
+std::vector<Span> spans_of(const Genome &g) {
+    std::vector<Span> v;
+    for (const Path &p : g.paths) {
+        uint64_t abs_pos = 0;
+        for (const Component &c : p.components) {
+            if (c.is_segment) {
+                const uint64_t len = g.bases[c.segment].size();
+                if (len == 0) v.push_back({&p, &c, abs_pos, 0, 0});
+                for (uint64_t a = 0; a < len; a += BLOCK) v.push_back({&p, &c, abs_pos, a, std::min(len, a + BLOCK)});
+            }
+            abs_pos += c.len;
+        }
+    }
+    return v;
+}
 
 struct Out {
     FILE *f;
@@ -48,25 +97,24 @@ inline void triple(const kq_base &b, uint32_t &cov, uint32_t &F, uint32_t &B) {
 } // namespace
 
 bool write_kwig(const std::string &file, int k, const Genome &g) {
-    Out o(file);
-    if (!o.ok()) return false;
-    o.num((uint64_t)k); o.put('\n');
-    for (const Path &p : g.paths) {
-        uint64_t abs_pos = 0;
-        for (const Component &c : p.components) {
-            if (c.is_segment) {
-                o.put("fixedStep chrom=", 16); o.put(p.header);
-                o.put(" start=", 7); o.num(abs_pos); o.put(" step=1\n", 8);
-                for (const kq_base &b : g.bases[c.segment]) {
-                    uint32_t cov, F, B;
-                    triple(b, cov, F, B);
-                    o.num(cov); o.put(','); o.num(F); o.put(','); o.num(B); o.put('\n');
-                }
-            }
-            abs_pos += c.len;
+    FILE *f = fopen(file.c_str(), "wb");
+    if (!f) return false;
+    fprintf(f, "%d\n", k);
+    const std::vector<Span> spans = spans_of(g);
+    const bool ok = emit_blocks(f, spans.size(), [&](size_t i, std::string &o) {
+        const Span &sp = spans[i];
+        o.reserve((sp.to - sp.from) * 12 + 128);
+        if (sp.from == 0) {
+            o += "fixedStep chrom="; o += sp.path->header; o += " start="; append_num(o, sp.abs_pos); o += " step=1\n";
         }
-    }
-    return o.close();
+        const kq_base *b = g.bases[sp.comp->segment].data();
+        for (uint64_t x = sp.from; x < sp.to; ++x) {
+            uint32_t cov, F, B;
+            triple(b[x], cov, F, B);
+            append_num(o, cov); o.push_back(','); append_num(o, F); o.push_back(','); append_num(o, B); o.push_back('\n');
+        }
+    });
+    return (fclose(f) == 0) && ok;
 }
 
 // Each line repeats the last k values of the three tracks (zeros before the segment start), so a line is
@@ -75,8 +123,8 @@ bool write_table(const std::string &file, const std::string &ext, int k, const G
     char col = ',', entry = ',';
     if (ext == "bed") { col = '\t'; entry = ':'; }
     else if (ext == "csv") { col = ','; entry = ' '; }
-    Out o(file);
-    if (!o.ok()) return false;
+    FILE *f = fopen(file.c_str(), "wb");
+    if (!f) return false;
     struct Tok { char s[11]; uint8_t len; };
     auto fmt = [](uint32_t v, Tok &t) {
         char tmp[10];
@@ -85,37 +133,39 @@ bool write_table(const std::string &file, const std::string &ext, int k, const G
         t.len = (uint8_t)len;
         for (int i = 0; i < len; ++i) t.s[i] = tmp[len - 1 - i];
     };
-    std::vector<Tok> ring[3];
-    for (auto &r : ring) r.resize((size_t)k);
-    for (const Path &p : g.paths) {
-        uint64_t abs_pos = 0;
-        for (const Component &c : p.components) {
-            if (!c.is_segment) { abs_pos += c.len; continue; }
-            for (auto &r : ring)
-                for (Tok &t : r) { t.s[0] = '0'; t.len = 1; }
-            size_t head = 0;                       // slot of the oldest value
-            for (const kq_base &b : g.bases[c.segment]) {
-                uint32_t v[3];
-                triple(b, v[0], v[1], v[2]);
-                for (int t = 0; t < 3; ++t) fmt(v[t], ring[t][head]);
-                head = (head + 1) % (size_t)k;     // the newest value is now the last of the window
-                o.put(p.header); o.put(col); o.num(abs_pos);
-                o.room(3 * (size_t)k * 12 + 8);
-                for (int t = 0; t < 3; ++t) {
-                    o.buf[o.n++] = col;
-                    for (int i = 0; i < k; ++i) {
-                        const Tok &tk = ring[t][(head + (size_t)i) % (size_t)k];
-                        memcpy(o.buf.data() + o.n, tk.s, tk.len);
-                        o.n += tk.len;
-                        if (i + 1 < k) o.buf[o.n++] = entry;
-                    }
-                }
-                o.buf[o.n++] = '\n';
-                ++abs_pos;
-            }
+    const std::vector<Span> spans = spans_of(g);
+    const bool ok = emit_blocks(f, spans.size(), [&](size_t idx, std::string &o) {
+        const Span &sp = spans[idx];
+        const kq_base *b = g.bases[sp.comp->segment].data();
+        std::vector<Tok> ring[3];
+        for (auto &r : ring) { r.resize((size_t)k); for (Tok &t : r) { t.s[0] = '0'; t.len = 1; } }
+        size_t head = 0;                            // slot of the oldest value
+        const uint64_t warm = sp.from >= (uint64_t)(k - 1) ? sp.from - (uint64_t)(k - 1) : 0;
+        for (uint64_t x = warm; x < sp.from; ++x) {   // the window a block inherits from the bases before it
+            uint32_t v[3];
+            triple(b[x], v[0], v[1], v[2]);
+            for (int t = 0; t < 3; ++t) fmt(v[t], ring[t][head]);
+            head = (head + 1) % (size_t)k;
         }
-    }
-    return o.close();
+        o.reserve((sp.to - sp.from) * (size_t)(3 * k * 3 + 32));
+        for (uint64_t x = sp.from; x < sp.to; ++x) {
+            uint32_t v[3];
+            triple(b[x], v[0], v[1], v[2]);
+            for (int t = 0; t < 3; ++t) fmt(v[t], ring[t][head]);
+            head = (head + 1) % (size_t)k;         // the newest value is now the last of the window
+            o += sp.path->header; o.push_back(col); append_num(o, sp.abs_pos + x);
+            for (int t = 0; t < 3; ++t) {
+                o.push_back(col);
+                for (int i = 0; i < k; ++i) {
+                    const Tok &tk = ring[t][(head + (size_t)i) % (size_t)k];
+                    o.append(tk.s, tk.len);
+                    if (i + 1 < k) o.push_back(entry);
+                }
+            }
+            o.push_back('\n');
+        }
+    });
+    return (fclose(f) == 0) && ok;
 }
 
 // Layout (kreeq-output.cpp:305-399): u8 k; u32 #paths; per path {u16 len, header, u32 #segments,
