@@ -175,3 +175,58 @@ def test_host_and_device_codecs_agree(tmp_path):
         env = dict(os.environ, KQ_DB_HOST=reader)
         p = subprocess.run([EXE, "validate", "-f", asm, "-d", dbs[writer], "-k", "31"], cwd=str(tmp_path), env=env, capture_output=True)
         assert p.returncode == 0 and p.stdout.decode() == r["validate_stdout"]
+
+
+@pytest.mark.skipif(not os.path.exists(REF_BIN), reason="oracle/_ref/kreeq not built")
+def test_union_with_high_copy_repeats_at_scale(tmp_path):
+    """A scaled C3: a 1 Mbp genome with 32 copies of a 5 kb repeat and a 2 kb poly-A run, four
+    13x read sets counted separately, then `union -d s0 s1 s2 s3`.  Every database and the union hold k-mers
+    beyond the 8-bit range (32-bit spill, order-dependent merge rules of row A4).  The same commands run
+    through the unmodified reference on the box; decoded databases, stdout and .kwig must be identical."""
+    import sys
+    import torch
+    sys.path.insert(0, ROOT)
+    import bench
+    from kreeq_b200 import synth
+    dev = torch.device("cuda", 0)
+    g = torch.Generator(device=dev); g.manual_seed(77)
+    genome = synth.random_genome_codes(1_000_000, 30, dev)
+    repeat = torch.randint(0, 4, (5000,), dtype=torch.uint8, device=dev, generator=g)
+    for pos in torch.randint(0, 990_000, (32,), device=dev, generator=g).tolist():
+        genome[pos:pos + 5000] = repeat
+    genome[500_000:502_000] = 0                                              # poly-A
+    asm = str(tmp_path / "asm.fasta")
+    bench.write_fasta(asm, synth.codes_to_ascii(genome).cpu().numpy())
+    L, pairs = 150, 43_500
+    ours, refs = [], []
+    for i in range(4):
+        fq = str(tmp_path / ("s%d.fastq" % i))
+        bench.write_fastq(fq, synth.paired_reads_ascii(genome, pairs, L, 0.01, 30 + i).cpu().numpy(), 2 * pairs, L)
+        o, r = str(tmp_path / ("ours%d.kreeq" % i)), str(tmp_path / ("ref%d.kreeq" % i))
+        so = run(["validate", "-r", fq, "-o", o], str(tmp_path))
+        p = subprocess.run([REF_BIN, "validate", "-r", fq, "-o", r, "-j", "8"], cwd=str(tmp_path), capture_output=True, timeout=900)
+        assert p.returncode == 0 and p.stdout.decode() == so
+        ours.append(o); refs.append(r)
+
+    def same_db(a, b):
+        ta, tb = ko.read_db(a, check=False), ko.read_db(b, check=False)
+        (ka8, ra8), (kb8, rb8) = ta.dump8(), tb.dump8()
+        (ka32, ra32), (kb32, rb32) = ta.dump32(), tb.dump32()
+        assert np.array_equal(ka8, kb8) and np.array_equal(ka32, kb32) and ka32.size > 1000
+        assert ra32.tobytes() == rb32.tobytes()
+        live = ra8["cov"] != 255
+        assert np.array_equal(live, rb8["cov"] != 255) and ra8[live].tobytes() == rb8[live].tobytes()
+
+    uo, ur, ux = str(tmp_path / "uo.kreeq"), str(tmp_path / "ur.kreeq"), str(tmp_path / "ux.kreeq")
+    so = run(["union", "-d"] + ours + ["-o", uo], str(tmp_path))
+    p = subprocess.run([REF_BIN, "union", "-d"] + refs + ["-o", ur, "-j", "8"], cwd=str(tmp_path), capture_output=True, timeout=900)
+    assert p.returncode == 0 and p.stdout.decode() == so
+    same_db(uo, ur)
+    assert run(["union", "-d"] + refs + ["-o", ux], str(tmp_path)) == so          # our union of reference-written databases
+    same_db(ux, ur)
+    ko_, kr_ = str(tmp_path / "o.kwig"), str(tmp_path / "r.kwig")
+    vo = run(["validate", "-f", asm, "-d", uo, "-c", "3", "-o", ko_], str(tmp_path))
+    p = subprocess.run([REF_BIN, "validate", "-f", asm, "-d", ur, "-k", "21", "-c", "3", "-o", kr_, "-j", "8"], cwd=str(tmp_path), capture_output=True, timeout=900)
+    assert p.returncode == 0 and p.stdout.decode() == vo
+    with open(ko_, "rb") as a, open(kr_, "rb") as b:
+        assert a.read() == b.read()
