@@ -220,7 +220,8 @@ int  kq_dev_validate_packed(kq_ctx *ctx, const uint64_t *d_bases, const uint64_t
  * large batches) */
 int  kq_reserve(kq_ctx *ctx, uint64_t extra_distinct);
 /* kq_count_push only appends the packed batch to a device-resident pending stream; the count
- * pipeline runs once this many k-mer start positions are pending (0 = default 2^31), at
+ * pipeline runs once this many k-mer start positions are pending (0 = default 2^29; the next batches are copied in
+ * while it runs), at
  * kq_count_finish / kq_sync, and before anything that reads the table. */
 int  kq_set_flush_positions(kq_ctx *ctx, uint64_t positions);
 

@@ -35,7 +35,7 @@ constexpr double TARGET_LOAD = 0.50;             // load right after a grow / re
 constexpr uint64_t MIN_SLOTS = 1ull << 12;
 constexpr uint64_t MIN_SCAP = 1ull << 12;
 constexpr uint64_t OVF_CAP = 4ull << 20;         // tuples kept when their slice is full
-constexpr uint64_t DEFAULT_FLUSH = 1ull << 31;   // pending k-mer start positions that trigger the pipeline
+constexpr uint64_t DEFAULT_FLUSH = 1ull << 29;   // pending k-mer start positions that trigger the pipeline
 constexpr int NTIMERS = 4;                       // 0 count pipeline, 1 validate, 2 insert kernel, 3 hist + scatter
 
 thread_local std::string g_create_error;
@@ -72,6 +72,12 @@ struct kq_ctx {
     bool loaded_db = false;                      // table holds literal database entries (load/union)
     // pending reads (device-resident packed stream)
     uint64_t *d_pb = nullptr, *d_pi = nullptr; uint64_t pend_cap = 0, pend_len = 0, flush_positions = DEFAULT_FLUSH;
+    // ... double-buffered: batches are copied in on copy_stream while the pipeline reads the other buffer
+    uint64_t *d_pb_alt = nullptr, *d_pi_alt = nullptr; uint64_t pend_cap_alt = 0;
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_copied = nullptr;                 // last host-to-device copy into the current buffer
+    cudaEvent_t ev_read = nullptr, ev_read_alt = nullptr;   // pipeline done with the current / the other buffer
+    bool read_armed = false, read_armed_alt = false;
     // pipeline scratch
     uint64_t *d_tuples = nullptr; uint64_t tup_cap = 0;          // tuples (not words)
     unsigned long long *d_hist = nullptr, *d_cursor = nullptr; uint64_t hist_cap = 0;
@@ -382,6 +388,7 @@ int pending_reserve(kq_ctx *c, uint64_t bases) {
     CU(cudaMalloc(&nb, bw * 8)); CU(cudaMalloc(&ni, iw * 8));
     CU(cudaMemsetAsync(nb, 0, bw * 8, c->stream));
     CU(cudaMemsetAsync(ni, 0xFF, iw * 8, c->stream));                // everything not written is "not ACGT"
+    CU(cudaStreamSynchronize(c->copy_stream));                       // copies into the old buffer have landed
     if (c->pend_len) {
         CU(cudaMemcpyAsync(nb, c->d_pb, (c->pend_len / 32) * 8, cudaMemcpyDeviceToDevice, c->stream));
         CU(cudaMemcpyAsync(ni, c->d_pi, (c->pend_len / 64) * 8, cudaMemcpyDeviceToDevice, c->stream));
@@ -396,12 +403,18 @@ int pending_reserve(kq_ctx *c, uint64_t bases) {
 int pending_flush(kq_ctx *c) {
     if (!c->pend_len) return KQ_OK;
     const uint64_t len = c->pend_len;
+    CU(cudaStreamWaitEvent(c->stream, c->ev_copied, 0));               // every batch of this buffer has arrived
     if (len >= (uint64_t)c->k) {
         Source src{c->d_pb, c->d_pi, 0, len - c->k + 1, nullptr, nullptr, 0};
         int rc = count_source(c, src); if (rc) return rc;
     }
     CU(cudaMemsetAsync(c->d_pi, 0xFF, (len / 64 + 1) * 8, c->stream));
+    CU(cudaEventRecord(c->ev_read, c->stream));                        // the buffer may be refilled after this point
+    c->read_armed = true;
     c->pend_len = 0;
+    // the next batches go to the other buffer, so their copies overlap the kernels launched above
+    std::swap(c->d_pb, c->d_pb_alt); std::swap(c->d_pi, c->d_pi_alt); std::swap(c->pend_cap, c->pend_cap_alt);
+    std::swap(c->ev_read, c->ev_read_alt); std::swap(c->read_armed, c->read_armed_alt);
     return KQ_OK;
 }
 
@@ -428,6 +441,10 @@ extern "C" int kq_create(kq_ctx **out, int k, int device, uint64_t expected_dist
                       return bail(e_ == cudaErrorMemoryAllocation ? KQ_ENOMEM : KQ_ENODEV); } } while (0)
     CC(cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
     ctx->stream = ctx->own_stream;
+    CC(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+    CC(cudaEventCreateWithFlags(&ctx->ev_copied, cudaEventDisableTiming));
+    CC(cudaEventCreateWithFlags(&ctx->ev_read, cudaEventDisableTiming));
+    CC(cudaEventCreateWithFlags(&ctx->ev_read_alt, cudaEventDisableTiming));
     CC(cudaMalloc(&ctx->d_occ, 3 * sizeof(unsigned long long)));
     CC(cudaMalloc(&ctx->d_inst, sizeof(unsigned long long)));
     CC(cudaMalloc(&ctx->d_acc, 3 * sizeof(unsigned long long)));
@@ -466,6 +483,11 @@ extern "C" void kq_destroy(kq_ctx *c) {
     for (auto &r : c->ranges) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
     for (auto e : c->ev_pool) cudaEventDestroy(e);
     cudaFree(c->T); cudaFree(c->R); cudaFree(c->M); cudaFree(c->d_occ); cudaFree(c->d_inst); cudaFree(c->d_acc); cudaFree(c->d_err);
+    if (c->copy_stream) { cudaStreamSynchronize(c->copy_stream); cudaStreamDestroy(c->copy_stream); }
+    if (c->ev_copied) cudaEventDestroy(c->ev_copied);
+    if (c->ev_read) cudaEventDestroy(c->ev_read);
+    if (c->ev_read_alt) cudaEventDestroy(c->ev_read_alt);
+    cudaFree(c->d_pb_alt); cudaFree(c->d_pi_alt);
     cudaFree(c->d_pb); cudaFree(c->d_pi); cudaFree(c->d_tuples); cudaFree(c->d_hist); cudaFree(c->d_cursor);
     cudaFree(c->d_total); cudaFree(c->d_nsrc); cudaFree(c->d_ticket); cudaFree(c->d_ovf); cudaFree(c->d_ovf_n);
     for (void *p : c->ipc_opened) cudaIpcCloseMemHandle(p);
@@ -551,7 +573,11 @@ extern "C" int kq_set_flush_positions(kq_ctx *c, uint64_t positions) {
 extern "C" int kq_clear(kq_ctx *c) {
     if (!c) return KQ_EINVAL;
     CU(cudaSetDevice(c->device));
-    if (c->pend_len) { CU(cudaMemsetAsync(c->d_pi, 0xFF, (c->pend_len / 64 + 1) * 8, c->stream)); c->pend_len = 0; }
+    if (c->pend_len) {
+        CU(cudaStreamSynchronize(c->copy_stream));                     // batches still on their way into the buffer
+        CU(cudaMemsetAsync(c->d_pi, 0xFF, (c->pend_len / 64 + 1) * 8, c->stream)); c->pend_len = 0;
+        CU(cudaEventRecord(c->ev_read, c->stream)); c->read_armed = true;
+    }
     CU(cudaMemsetAsync(c->T, 0, table_slots(c) * sizeof(Slot), c->stream));
     CU(cudaMemsetAsync(c->R, 0, c->rcap * sizeof(SideSlot), c->stream));
     CU(cudaMemsetAsync(c->M, 0, c->mcap * sizeof(SideSlot), c->stream));
@@ -583,6 +609,10 @@ extern "C" int kq_count_push(kq_ctx *c, const char *ascii, size_t len) {
     // the batch goes to the end of the pending stream, 64-base aligned; at least one invalid position
     // separates it from the next batch (== the '\0' / no-previous-base cases of graph-builder.cpp:98-112)
     const uint64_t at = c->pend_len;
+    if (at == 0 && c->read_armed) {                                    // first batch into a buffer the pipeline has read before
+        CU(cudaStreamWaitEvent(c->copy_stream, c->ev_read, 0));
+        c->read_armed = false;
+    }
     for (uint64_t c0 = 0; c0 < len; c0 += CHUNK) {
         const uint64_t n = std::min<uint64_t>(CHUNK, len - c0);
         Stage &s = c->st[c->next_stage]; c->next_stage = (c->next_stage + 1) % NBUF;
@@ -590,11 +620,12 @@ extern "C" int kq_count_push(kq_ctx *c, const char *ascii, size_t len) {
         rc = stage_reserve(c, s, packed_words(CHUNK), 0, 0); if (rc) return rc;
         pack_sequence(ascii + c0, n, s.h_bases, s.h_inv, &global_pool());
         const size_t bw = (n + 31) / 32, iw = (n + 63) / 64;
-        CU(cudaMemcpyAsync(c->d_pb + (at + c0) / 32, s.h_bases, bw * 8, cudaMemcpyHostToDevice, c->stream));
-        CU(cudaMemcpyAsync(c->d_pi + (at + c0) / 64, s.h_inv, iw * 8, cudaMemcpyHostToDevice, c->stream));
+        CU(cudaMemcpyAsync(c->d_pb + (at + c0) / 32, s.h_bases, bw * 8, cudaMemcpyHostToDevice, c->copy_stream));
+        CU(cudaMemcpyAsync(c->d_pi + (at + c0) / 64, s.h_inv, iw * 8, cudaMemcpyHostToDevice, c->copy_stream));
         c->h2d += (bw + iw) * 8;
-        CU(cudaEventRecord(s.done, c->stream)); s.busy = true;
+        CU(cudaEventRecord(s.done, c->copy_stream)); s.busy = true;
     }
+    CU(cudaEventRecord(c->ev_copied, c->copy_stream));
     c->pend_len = (at + len + 64) & ~63ull;                            // next 64-aligned position strictly after the end
     return KQ_OK;
 }
