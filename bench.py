@@ -41,11 +41,15 @@ def parse_args():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--genome-mbp", type=float, default=100.0, help="C2 genome size (default 100 Mbp)")
     ap.add_argument("--coverage", type=float, default=30.0)
+    ap.add_argument("--k", type=int, default=21, help="k-mer length (default: C2's 21; 29..32 use 16-byte tuples)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-union", action="store_true", help="skip the database rows (save / union / load timing)")
     ap.add_argument("--ref-sample-reads", type=int, default=1_500_000)
-    return ap.parse_args()
+    a = ap.parse_args()
+    global K
+    K = a.k
+    return a
 
 
 def workload(args):
@@ -161,7 +165,7 @@ def run_reference_once(fq, fa, workdir, threads):
     out = subprocess.run([REF_BIN, "validate", "-r", fq, "-k", str(K), "-o", db, "-j", str(threads)],
                          cwd=workdir, stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, check=True).stdout.decode()
     t1 = time.perf_counter()
-    subprocess.check_call([REF_BIN, "validate", "-f", fa, "-d", db, "-o", os.path.join(workdir, "out.kwig"), "-j", str(threads)],
+    subprocess.check_call([REF_BIN, "validate", "-f", fa, "-d", db, "-k", str(K), "-o", os.path.join(workdir, "out.kwig"), "-j", str(threads)],
                           cwd=workdir, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
     t2 = time.perf_counter()
     distinct = [int(ln.split(":")[1]) for ln in out.splitlines() if ln.startswith("Distinct kmers")]
@@ -240,6 +244,8 @@ def main_ours(args):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:                                    # the ranks share the host cores (packing, file codec)
+        os.environ.setdefault("KQ_THREADS", str(max(1, (os.cpu_count() or 1) // world)))
     if not torch.cuda.is_available():
         raise SystemExit("bench.py --impl ours needs a CUDA device (there is no CPU fallback)")
     torch.cuda.set_device(local)
@@ -302,6 +308,13 @@ def main_ours(args):
     # warm-up step, reported as peer_connect_ms) and stay mapped: the steady-state steps refill tables that
     # do not move
     peers = shard.PeerTables(g, world, dev, keep=True) if world > 1 else None
+    e2e_bufs = []
+    if world > 1 and not args.no_e2e:
+        words = L.kq_packed_words(5 * 64 * (READ_LEN + 1) * 10000)
+        for _ in range(2):
+            e2e_bufs.append((torch.empty(words, dtype=torch.int64, pin_memory=True), torch.empty(words, dtype=torch.int64, pin_memory=True),
+                             torch.empty(words, dtype=torch.int64, device=dev), torch.empty(words, dtype=torch.int64, device=dev),
+                             torch.cuda.Event()))
 
     def count_resident():
         total = reads_np.size - K + 1
@@ -353,9 +366,17 @@ def main_ours(args):
             g.set_flush_positions(int(os.environ["KQ_E2E_FLUSH"]))
         B = 64 * (READ_LEN + 1) * 10000                       # ~97 MB pushes, cut at read boundaries
         if world > 1:
-            for o in range(0, reads_np.size, B):
-                b, m = pack_to_device(reads_np[o:o + B])
-                router.count(b, m, min(B, reads_np.size - o))
+            # chunks of five pushes: packed on this rank's share of the host cores into pinned memory, copied in,
+            # routed as one round; the next chunk is packed while the GPUs insert this one
+            CH = 5 * B
+            for i, o in enumerate(range(0, reads_np.size, CH)):
+                n = min(CH, reads_np.size - o)
+                hb, hm, db, dm, done = e2e_bufs[i % 2]
+                done.synchronize()
+                check(L.kq_pack_host(C.c_void_p(reads_np[o:o + n].ctypes.data), n, C.c_void_p(hb.data_ptr()), C.c_void_p(hm.data_ptr()), 0))
+                db.copy_(hb, non_blocking=True); dm.copy_(hm, non_blocking=True)
+                done.record(stream)
+                router.count(db, dm, n)
         else:
             for o in range(0, reads_np.size, B):
                 g.traverseInReads(reads_np[o:o + B])
