@@ -1,9 +1,18 @@
 // File inputs of the command line: FASTQ read batching and the -f genome (FASTA / FASTQ / GFA1).
 #include "kreeq_cli.h"
 
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
 #include <zlib.h>
 
+#include <algorithm>
+#include <atomic>
+#include <cstdlib>
 #include <cstring>
+#include <mutex>
+#include <thread>
 #include <unordered_map>
 
 namespace cli {
@@ -48,29 +57,17 @@ bool read_file(const std::string &path, std::string &out, std::string &err) {
 // getKmers (functions.h:69-122) consumes, per record: the header line, the sequence line (kept), the '+'
 // line and the quality line, and only then appends the 'N' separator; if the file ends inside any of the
 // last three lines the record's bases are kept but no 'N' follows.  This state machine does the same over
-// fixed-size chunks so a file never has to be resident.
-bool stream_reads(const std::string &path, size_t batch_bytes, ReadSink &sink, std::string &err) {
-    GzReader r(path);
-    if (!r.f) { err = "cannot open " + path; return false; }
-    std::vector<char> buf(16u << 20);
-    std::string batch;
-    batch.reserve(batch_bytes + (1u << 20));
-    int line = 0;                                   // 0 header, 1 sequence, 2 plus, 3 quality
-    bool first = true;
-    for (;;) {
-        const long n = r.read(buf.data(), buf.size());
-        if (n < 0) { err = "read error in " + path; return false; }
-        if (n == 0) break;
-        if (first) {
-            first = false;
-            if (buf[0] != '@') return true;         // loadKmers only takes FASTQ (fastx.h:95-118)
-        }
-        const char *p = buf.data(), *end = p + n;
+// arbitrary pieces of the file.
+namespace {
+struct FastqState {
+    std::string batch; int line = 0; size_t batch_bytes; ReadSink &sink;
+    FastqState(size_t bb, ReadSink &s) : batch_bytes(bb), sink(s) { batch.reserve(bb + (1u << 20)); }
+    bool feed(const char *p, const char *end) {
         while (p < end) {
             const char *nl = (const char *)memchr(p, '\n', (size_t)(end - p));
             const char *stop = nl ? nl : end;
             if (line == 1) batch.append(p, (size_t)(stop - p));
-            if (!nl) break;                         // line continues in the next chunk
+            if (!nl) break;                         // line continues in the next piece
             if (line == 3) {
                 batch.push_back('N');
                 if (batch.size() >= batch_bytes) {
@@ -81,9 +78,108 @@ bool stream_reads(const std::string &path, size_t batch_bytes, ReadSink &sink, s
             line = (line + 1) & 3;
             p = nl + 1;
         }
+        return true;
     }
-    if (!batch.empty() && !sink(batch.data(), batch.size())) return false;
-    return true;
+    bool finish() { return batch.empty() || sink(batch.data(), batch.size()); }
+};
+
+// Uncompressed files are mapped and cut into one slice per core AT RECORD BOUNDARIES: newlines are counted in
+// parallel first, so the line number (mod 4) of every slice start is known exactly -- no guessing where a
+// FASTQ record starts -- and the slices are parsed concurrently.  Counting commutes, so slice order is free.
+bool stream_plain_parallel(const char *data, size_t size, size_t batch_bytes, ReadSink &sink, std::mutex *sink_mu) {
+    static const size_t slice_min = [] { const char *e = getenv("KQ_CLI_SLICE"); const long v = e ? atol(e) : 0; return v > 0 ? (size_t)v : (size_t)64 << 20; }();
+    const size_t nt = std::max<size_t>(1, std::min<size_t>({(size_t)std::thread::hardware_concurrency(), (size_t)16, size / slice_min}));
+    std::vector<size_t> cut(nt + 1), lines(nt, 0);
+    for (size_t t = 0; t <= nt; ++t) cut[t] = size / nt * t;
+    cut[nt] = size;
+    {
+        std::vector<std::thread> th;
+        for (size_t t = 0; t < nt; ++t)
+            th.emplace_back([&, t] {
+                size_t n = 0;
+                for (const char *p = data + cut[t], *e = data + cut[t + 1]; p < e;) {
+                    const char *nl = (const char *)memchr(p, '\n', (size_t)(e - p));
+                    if (!nl) break;
+                    ++n; p = nl + 1;
+                }
+                lines[t] = n;
+            });
+        for (auto &x : th) x.join();
+    }
+    // first byte of the first record that STARTS in slice t (line number divisible by four)
+    std::vector<size_t> start(nt + 1, size);
+    start[0] = 0;
+    size_t before = 0;
+    for (size_t t = 1; t < nt; ++t) {
+        before += lines[t - 1];
+        size_t need = (4 - before % 4) % 4, pos = cut[t];   // newlines to pass before a record boundary
+        if (need == 0 && pos > 0 && data[pos - 1] != '\n') need = 4;   // the slice starts inside the record's header line
+        while (need && pos < size) {
+            const char *nl = (const char *)memchr(data + pos, '\n', size - pos);
+            if (!nl) { pos = size; break; }
+            pos = (size_t)(nl - data) + 1; --need;
+        }
+        start[t] = need ? size : pos;
+    }
+    for (size_t t = nt - 1; t >= 1; --t) start[t] = std::min(start[t], start[t + 1]);   // slices without a boundary are empty
+    std::atomic<bool> ok{true};
+    struct Locked : ReadSink {                      // the caller's sink is not thread safe
+        ReadSink &inner; std::mutex &mu;
+        Locked(ReadSink &i, std::mutex &m) : inner(i), mu(m) {}
+        bool operator()(const char *d, size_t l) override { std::lock_guard<std::mutex> lk(mu); return inner(d, l); }
+    };
+    std::mutex local_mu;
+    std::vector<std::thread> th;
+    for (size_t t = 0; t < nt; ++t)
+        th.emplace_back([&, t] {
+            if (start[t] >= start[t + 1]) return;
+            Locked locked(sink, sink_mu ? *sink_mu : local_mu);
+            FastqState st(batch_bytes, locked);
+            if (!st.feed(data + start[t], data + start[t + 1]) || !st.finish()) ok = false;
+        });
+    for (auto &x : th) x.join();
+    return ok;
+}
+}  // namespace
+
+bool stream_reads(const std::string &path, size_t batch_bytes, ReadSink &sink, std::string &err) {
+    // plain file: map it and parse slices on all cores
+    {
+        const int fd = open(path.c_str(), O_RDONLY);
+        if (fd < 0) { err = "cannot open " + path; return false; }
+        struct stat st;
+        unsigned char magic[2] = {0, 0};
+        static const off_t par_min = [] { const char *e = getenv("KQ_CLI_PAR_MIN"); const long v = e ? atol(e) : 0; return v > 0 ? (off_t)v : (off_t)128 << 20; }();   // test knobs
+        const bool have = fstat(fd, &st) == 0 && st.st_size >= par_min && pread(fd, magic, 2, 0) == 2;
+        if (have && !(magic[0] == 0x1f && magic[1] == 0x8b)) {
+            if (magic[0] != '@') { close(fd); return true; }           // loadKmers only takes FASTQ (fastx.h:95-118)
+            void *m = mmap(nullptr, (size_t)st.st_size, PROT_READ, MAP_PRIVATE, fd, 0);
+            if (m != MAP_FAILED) {
+                madvise(m, (size_t)st.st_size, MADV_SEQUENTIAL);
+                const bool ok = stream_plain_parallel((const char *)m, (size_t)st.st_size, batch_bytes, sink, nullptr);
+                munmap(m, (size_t)st.st_size); close(fd);
+                if (!ok) err = "reading " + path + " was interrupted";
+                return ok;
+            }
+        }
+        close(fd);
+    }
+    GzReader r(path);
+    if (!r.f) { err = "cannot open " + path; return false; }
+    std::vector<char> buf(16u << 20);
+    FastqState st(batch_bytes, sink);
+    bool first = true;
+    for (;;) {
+        const long n = r.read(buf.data(), buf.size());
+        if (n < 0) { err = "read error in " + path; return false; }
+        if (n == 0) break;
+        if (first) {
+            first = false;
+            if (buf[0] != '@') return true;         // loadKmers only takes FASTQ (fastx.h:95-118)
+        }
+        if (!st.feed(buf.data(), buf.data() + n)) return false;
+    }
+    return st.finish();
 }
 
 namespace {

@@ -12,26 +12,46 @@
 #include <functional>
 #include <thread>
 
+#include <unistd.h>
+
 namespace cli {
 namespace {
 
-// Formats blocks [0, n) with fmt(block, out) on all cores, a wave at a time, and appends them to f in order.
+// Formats blocks [0, n) with fmt(block, out) on all cores, a wave at a time; the blocks of a wave are then
+// written at their final offsets concurrently (pwrite), which is what a tmpfs / page-cache target rewards.
 bool emit_blocks(FILE *f, size_t n, const std::function<void(size_t, std::string &)> &fmt) {
     const size_t nthreads = std::max<size_t>(1, std::min<size_t>(std::thread::hardware_concurrency(), 32));
     const size_t wave = nthreads * 2;
     std::vector<std::string> out(wave);
+    std::vector<off_t> at(wave);
+    if (fflush(f) != 0) return false;
+    const int fd = fileno(f);
+    off_t pos = lseek(fd, 0, SEEK_END);
+    if (pos < 0) return false;
+    std::atomic<bool> ok{true};
     for (size_t base = 0; base < n; base += wave) {
         const size_t cnt = std::min(wave, n - base);
-        std::atomic<size_t> next{0};
-        auto work = [&] { for (size_t i; (i = next.fetch_add(1)) < cnt;) { out[i].clear(); fmt(base + i, out[i]); } };
-        std::vector<std::thread> th;
-        for (size_t t = 1; t < std::min(nthreads, cnt); ++t) th.emplace_back(work);
-        work();
-        for (auto &t : th) t.join();
-        for (size_t i = 0; i < cnt; ++i)
-            if (!out[i].empty() && fwrite(out[i].data(), 1, out[i].size(), f) != out[i].size()) return false;
+        auto run = [&](const std::function<void(size_t)> &job) {
+            std::atomic<size_t> next{0};
+            auto work = [&] { for (size_t i; (i = next.fetch_add(1)) < cnt;) job(i); };
+            std::vector<std::thread> th;
+            for (size_t t = 1; t < std::min(nthreads, cnt); ++t) th.emplace_back(work);
+            work();
+            for (auto &t : th) t.join();
+        };
+        run([&](size_t i) { out[i].clear(); fmt(base + i, out[i]); });
+        for (size_t i = 0; i < cnt; ++i) { at[i] = pos; pos += (off_t)out[i].size(); }
+        run([&](size_t i) {
+            const char *p = out[i].data(); size_t left = out[i].size(); off_t o = at[i];
+            while (left) {
+                const ssize_t w = pwrite(fd, p, left, o);
+                if (w <= 0) { ok = false; return; }
+                p += w; left -= (size_t)w; o += w;
+            }
+        });
+        if (!ok) return false;
     }
-    return true;
+    return lseek(fd, pos, SEEK_SET) >= 0;
 }
 
 inline void append_num(std::string &o, uint64_t v) {

@@ -230,3 +230,29 @@ def test_union_with_high_copy_repeats_at_scale(tmp_path):
     assert p.returncode == 0 and p.stdout.decode() == vo
     with open(ko_, "rb") as a, open(kr_, "rb") as b:
         assert a.read() == b.read()
+
+
+@pytest.mark.parametrize("slice_bytes", ["40", "3000"])
+def test_parallel_fastq_slicing_is_exact(slice_bytes, fixture_dbs, tmp_path):
+    """Large plain FASTQ files are cut into slices at record boundaries found by counting newlines; with the
+    size thresholds lowered the reference's goldens (incl. the N-containing and two-file cases) and a file that
+    ends inside a record go through that path and must print the same text."""
+    env = dict(os.environ, KQ_CLI_PAR_MIN="1", KQ_CLI_SLICE=slice_bytes)
+    for name in ("test.1", "test.3", "test.8"):
+        args = [a.replace("testFiles/", os.path.join(GOLD, "inputs") + "/") for a in shlex.split(REF[name]["cmd"])[1:]]
+        p = subprocess.run([EXE] + args, cwd=str(tmp_path), env=env, capture_output=True, timeout=300)
+        assert p.returncode == 0 and p.stdout.decode() == REF[name]["stdout"], name
+    # truncated inputs: cut random2.fastq inside a quality line, inside a sequence line and right after a '+' line
+    with open(os.path.join(GOLD, "inputs", "random2.fastq"), "rb") as f:
+        data = f.read()
+    nl = [i for i, c in enumerate(data) if c == 10]
+    for cut in (nl[3 * 4 + 3] - 20, nl[5 * 4 + 1] - 7, nl[7 * 4 + 2] + 1):
+        fq = str(tmp_path / "cut.fastq")
+        with open(fq, "wb") as f:
+            f.write(data[:cut])
+        base = subprocess.run([EXE, "validate", "-r", fq, "-k", "15"], cwd=str(tmp_path), capture_output=True, timeout=300)
+        par = subprocess.run([EXE, "validate", "-r", fq, "-k", "15"], cwd=str(tmp_path), env=env, capture_output=True, timeout=300)
+        assert base.returncode == 0 and par.returncode == 0 and base.stdout == par.stdout and b"Total kmers" in par.stdout
+        if os.path.exists(REF_BIN):                       # and the reference agrees on the end-of-file rules
+            ref = subprocess.run([REF_BIN, "validate", "-r", fq, "-k", "15", "-o", str(tmp_path / "r.kreeq")], cwd=str(tmp_path), capture_output=True, timeout=300)
+            assert ref.stdout == par.stdout
