@@ -519,8 +519,7 @@ size_t scatter_smem_bytes(unsigned long long nslices, int cap, int tw) {
     return (size_t)nslices * cap * tw * 8 + (size_t)nslices * 4;
 }
 
-// largest bin capacity (tuples) such that TWO scatter CTAs fit one SM's shared memory (latency hiding
-// matters more than flush size: 128-byte flushes still run at 2.6 TB/s), else one CTA per SM
+// bin capacity (tuples) of the scatter kernel's shared-memory bins; one CTA per SM owns them
 int scatter_pick_cap(unsigned long long nslices, int tw) {
     static int max_smem = 0, sm_smem = 0;
     if (!max_smem) {
@@ -534,7 +533,9 @@ int scatter_pick_cap(unsigned long long nslices, int tw) {
         const int cap = std::atoi(e);
         if (cap > 0 && scatter_smem_bytes(nslices, cap, tw) <= (size_t)max_smem - 1024) return cap;
     }
-    for (int cap : {32, 16, 8})
+    // a tile brings NT * R = 8192 tuples: with few bins a small capacity would overflow several times per
+    // tile (each time costs a round of barriers), so take the largest power of two that fits
+    for (int cap : {512, 256, 128, 64, 32, 16, 8})
         if (scatter_smem_bytes(nslices, cap, tw) <= (size_t)max_smem - 1024) return cap;
     return 0;
 }
