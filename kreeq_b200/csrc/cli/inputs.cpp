@@ -1,5 +1,6 @@
 // File inputs of the command line: FASTQ read batching and the -f genome (FASTA / FASTQ / GFA1).
 #include "kreeq_cli.h"
+#include "pgzip.h"
 
 #include <fcntl.h>
 #include <sys/mman.h>
@@ -40,7 +41,57 @@ struct GzReader {
 
 } // namespace
 
+
+namespace {
+
+long env_long(const char *name, long dflt) { const char *e = getenv(name); const long v = e ? atol(e) : 0; return v > 0 ? v : dflt; }
+
+struct Mapped {                                       // read-only mapping of a whole file
+    const unsigned char *data = nullptr; size_t size = 0; int fd = -1;
+    explicit Mapped(const std::string &path) {
+        fd = open(path.c_str(), O_RDONLY);
+        struct stat st;
+        if (fd < 0 || fstat(fd, &st) != 0 || st.st_size <= 0) return;
+        void *m = mmap(nullptr, (size_t)st.st_size, PROT_READ, MAP_PRIVATE, fd, 0);
+        if (m == MAP_FAILED) return;
+        madvise(m, (size_t)st.st_size, MADV_SEQUENTIAL);
+        data = (const unsigned char *)m; size = (size_t)st.st_size;
+    }
+    ~Mapped() { if (data) munmap((void *)data, size); if (fd >= 0) close(fd); }
+};
+
+// gzip files of at least KQ_CLI_PGZ_MIN bytes (default 4 MiB) go through the parallel decoder (pgzip.h),
+// smaller ones through zlib.  KQ_CLI_PGZ_CHUNK sets the compressed chunk size (tests use tiny chunks).
+bool wants_parallel_gz(const Mapped &m) {
+    static const size_t pgz_min = (size_t)env_long("KQ_CLI_PGZ_MIN", 4 << 20);
+    return m.data && m.size >= pgz_min && pgz::is_gzip(m.data, m.size);
+}
+size_t pgz_chunk() { static const size_t c = (size_t)env_long("KQ_CLI_PGZ_CHUNK", 0); return c; }
+
+} // namespace
+
+std::atomic<int> g_feed_share{1};
+int feed_threads() {
+    static const int forced = (int)env_long("KQ_CLI_THREADS", 0);
+    if (forced) return forced;
+    const int hw = (int)std::max(1u, std::min(std::thread::hardware_concurrency(), 32u));
+    return std::max(2, hw / std::max(1, g_feed_share.load()));
+}
+
 bool read_file(const std::string &path, std::string &out, std::string &err) {
+    {
+        Mapped m(path);
+        if (wants_parallel_gz(m)) {
+            struct Append : pgz::Sink {
+                std::string &out; explicit Append(std::string &o) : out(o) {}
+                bool consume(const char *d, size_t n, bool) override { out.append(d, n); return true; }
+            } sink(out);
+            out.clear();
+            std::string e;
+            if (!pgz::inflate_parallel(m.data, m.size, feed_threads(), sink, e, nullptr, pgz_chunk())) { err = e + " in " + path; return false; }
+            return true;
+        }
+    }
     GzReader r(path);
     if (!r.f) { err = "cannot open " + path; return false; }
     out.clear();
@@ -86,8 +137,9 @@ struct FastqState {
 // Uncompressed files are mapped and cut into one slice per core AT RECORD BOUNDARIES: newlines are counted in
 // parallel first, so the line number (mod 4) of every slice start is known exactly -- no guessing where a
 // FASTQ record starts -- and the slices are parsed concurrently.  Counting commutes, so slice order is free.
-bool stream_plain_parallel(const char *data, size_t size, size_t batch_bytes, ReadSink &sink, std::mutex *sink_mu) {
-    static const size_t slice_min = [] { const char *e = getenv("KQ_CLI_SLICE"); const long v = e ? atol(e) : 0; return v > 0 ? (size_t)v : (size_t)64 << 20; }();
+bool stream_plain_parallel(const char *data, size_t size, size_t batch_bytes, ReadSink &sink, std::mutex *sink_mu, size_t slice_default = (size_t)64 << 20) {
+    static const size_t slice_env = [] { const char *e = getenv("KQ_CLI_SLICE"); const long v = e ? atol(e) : 0; return v > 0 ? (size_t)v : (size_t)0; }();
+    const size_t slice_min = slice_env ? slice_env : slice_default;
     const size_t nt = std::max<size_t>(1, std::min<size_t>({(size_t)std::thread::hardware_concurrency(), (size_t)16, size / slice_min}));
     std::vector<size_t> cut(nt + 1), lines(nt, 0);
     for (size_t t = 0; t <= nt; ++t) cut[t] = size / nt * t;
@@ -163,6 +215,51 @@ bool stream_reads(const std::string &path, size_t batch_bytes, ReadSink &sink, s
             }
         }
         close(fd);
+    }
+    {
+        Mapped m(path);
+        if (wants_parallel_gz(m)) {
+            // Pieces of the decompressed file arrive in order; each is cut at its last record boundary (newline
+            // count divisible by four -- the piece starts at a boundary by induction) and parsed in slices.
+            struct Pieces : pgz::Sink {
+                size_t batch_bytes; ReadSink &sink; int threads; bool first = true, fastq = true;
+                Pieces(size_t bb, ReadSink &s, int t) : batch_bytes(bb), sink(s), threads(t) {}
+                size_t split(const char *d, size_t n, bool) override {
+                    if (!fastq) return n;
+                    const size_t nt = std::max<size_t>(1, std::min<size_t>((size_t)threads, n >> 20));
+                    std::vector<size_t> lines(nt, 0);
+                    std::vector<std::thread> th;
+                    for (size_t t = 0; t < nt; ++t)
+                        th.emplace_back([&, t] {
+                            size_t c = 0;
+                            for (const char *p = d + n / nt * t, *e = t + 1 == nt ? d + n : d + n / nt * (t + 1); p < e;) {
+                                const char *nl = (const char *)memchr(p, '\n', (size_t)(e - p));
+                                if (!nl) break;
+                                ++c; p = nl + 1;
+                            }
+                            lines[t] = c;
+                        });
+                    for (auto &x : th) x.join();
+                    size_t total = 0;
+                    for (size_t c : lines) total += c;
+                    if (total < 4) return 0;
+                    size_t pos = n;                      // walk back over the partial line and total % 4 whole lines
+                    for (size_t back = total % 4 + 1; back; --back) {
+                        const void *nl = memrchr(d, '\n', pos);
+                        pos = (size_t)((const char *)nl - d);
+                    }
+                    return pos + 1;
+                }
+                bool consume(const char *d, size_t n, bool) override {
+                    if (first && n) { first = false; fastq = d[0] == '@'; }    // loadKmers only takes FASTQ (fastx.h:95-118)
+                    if (!fastq || !n) return true;
+                    return stream_plain_parallel(d, n, batch_bytes, sink, nullptr, (size_t)16 << 20);
+                }
+            } pieces(batch_bytes, sink, feed_threads());
+            std::string e;
+            if (!pgz::inflate_parallel(m.data, m.size, feed_threads(), pieces, e, nullptr, pgz_chunk())) { err = e + " in " + path; return false; }
+            return true;
+        }
     }
     GzReader r(path);
     if (!r.f) { err = "cannot open " + path; return false; }

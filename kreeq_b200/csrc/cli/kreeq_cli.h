@@ -5,6 +5,7 @@
 #ifndef KREEQ_CLI_H
 #define KREEQ_CLI_H
 
+#include <atomic>
 #include <cstdint>
 #include <string>
 #include <vector>
@@ -55,6 +56,11 @@ bool read_file(const std::string &path, std::string &out, std::string &err);
 // sink(batch) with batches of about `batch_bytes`; FASTA inputs ('>') yield nothing, as in loadKmers.
 struct ReadSink { virtual bool operator()(const char *data, size_t len) = 0; virtual ~ReadSink() {} };
 bool stream_reads(const std::string &path, size_t batch_bytes, ReadSink &sink, std::string &err);
+
+// Host threads one input file may use for decoding / slicing: all cores divided by the number of files being
+// read at the same time (g_feed_share, set by the caller).
+extern std::atomic<int> g_feed_share;
+int feed_threads();
 
 bool load_genome(const std::string &path, Genome &g, std::string &err);   // src/input.cpp:188-308
 

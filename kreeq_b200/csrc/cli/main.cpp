@@ -224,6 +224,7 @@ bool count_files(kq_ctx *ctx, const std::vector<std::string> &files, std::string
     std::mutex next_mu; size_t next = 0;
     const size_t nthreads = std::min<size_t>(files.size(), 4);
     bq.producers = nthreads;
+    g_feed_share = (int)std::max<size_t>(1, nthreads);
     std::vector<std::thread> threads;
     for (size_t t = 0; t < nthreads; ++t)
         threads.emplace_back([&] {
@@ -241,6 +242,7 @@ bool count_files(kq_ctx *ctx, const std::vector<std::string> &files, std::string
     while (bq.get(batch))
         if (rc == KQ_OK) rc = kq_count_push(ctx, batch.data(), batch.size());      // keep draining after an error
     for (auto &t : threads) t.join();
+    g_feed_share = 1;
     if (rc != KQ_OK) die(ctx, rc);
     err = bq.error;
     return err.empty();

@@ -1,0 +1,84 @@
+// Test helper for the host feed path (no GPU needed): runs the command line's own input layer on a file.
+//   kreeq-feedcheck inflate <file.gz> [threads] [chunk_bytes]   decompressed bytes to stdout, stats to stderr
+//   kreeq-feedcheck reads <file>                                 what stream_reads hands to kq_count_push:
+//        prints  batches bytes separators digest   (digest = order-independent sum of a hash of every
+//        maximal N-free stretch, so it does not depend on how reads were grouped into batches)
+//   kreeq-feedcheck genome <file>                                paths / segments / bases / digest of load_genome
+#include "../kreeq_cli.h"
+#include "../pgzip.h"
+
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+
+static uint64_t stretch_hash(const char *p, size_t n) {
+    uint64_t h = 0xcbf29ce484222325ull;
+    for (size_t i = 0; i < n; ++i) { h ^= (unsigned char)p[i]; h *= 0x100000001b3ull; }
+    return h * 0x9e3779b97f4a7c15ull + n;
+}
+
+int main(int argc, char **argv) {
+    if (argc < 3) { fprintf(stderr, "usage: kreeq-feedcheck inflate|reads|genome <file> ...\n"); return 2; }
+    const std::string mode = argv[1], path = argv[2];
+    const auto t0 = std::chrono::steady_clock::now();
+    auto secs = [&] { return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(); };
+    if (mode == "inflate") {
+        const int fd = open(path.c_str(), O_RDONLY);
+        struct stat st;
+        if (fd < 0 || fstat(fd, &st) != 0) { perror("open"); return 1; }
+        void *m = st.st_size ? mmap(nullptr, (size_t)st.st_size, PROT_READ, MAP_PRIVATE, fd, 0) : nullptr;
+        if (st.st_size && m == MAP_FAILED) { perror("mmap"); return 1; }
+        const bool quiet = getenv("KQ_FEEDCHECK_QUIET") != nullptr;
+        struct Out : pgz::Sink {
+            bool quiet; size_t n = 0, pieces = 0;
+            bool consume(const char *d, size_t len, bool) override { n += len; ++pieces; return quiet || fwrite(d, 1, len, stdout) == len; }
+        } out;
+        out.quiet = quiet;
+        std::string err; pgz::Stats s;
+        const int threads = argc > 3 ? atoi(argv[3]) : cli::feed_threads();
+        const size_t chunk = argc > 4 ? (size_t)atol(argv[4]) : 0;
+        const bool ok = pgz::inflate_parallel((const unsigned char *)m, (size_t)st.st_size, threads, out, err, &s, chunk);
+        fflush(stdout);
+        fprintf(stderr, "{\"ok\": %s, \"threads\": %d, \"in_bytes\": %zu, \"out_bytes\": %zu, \"pieces\": %zu, \"chunks\": %zu, \"chained\": %zu, \"fallbacks\": %zu, \"members\": %zu, \"seconds\": %.4f, \"stages\": [%.3f, %.3f, %.3f, %.3f, %.3f], \"error\": \"%s\"}\n",
+                ok ? "true" : "false", threads, (size_t)st.st_size, out.n, out.pieces, s.chunks, s.chained, s.fallbacks, s.members, secs(), s.t_find, s.t_decode, s.t_chain, s.t_resolve, s.t_hand, err.c_str());
+        return ok ? 0 : 1;
+    }
+    if (mode == "reads") {
+        struct Digest : cli::ReadSink {
+            std::mutex mu; uint64_t batches = 0, bytes = 0, seps = 0, digest = 0;
+            bool operator()(const char *d, size_t len) override {
+                uint64_t s = 0, h = 0; size_t a = 0;
+                for (size_t i = 0; i <= len; ++i)
+                    if (i == len || d[i] == 'N') { if (i > a) h += stretch_hash(d + a, i - a); if (i < len) ++s; a = i + 1; }
+                std::lock_guard<std::mutex> lk(mu);
+                ++batches; bytes += len; seps += s; digest += h;
+                return true;
+            }
+        } sink;
+        std::string err;
+        const size_t batch = argc > 3 ? (size_t)atol(argv[3]) : (size_t)128 << 20;
+        if (!cli::stream_reads(path, batch, sink, err)) { fprintf(stderr, "%s\n", err.c_str()); return 1; }
+        printf("%llu %llu %llu %016llx\n", (unsigned long long)sink.batches, (unsigned long long)sink.bytes, (unsigned long long)sink.seps, (unsigned long long)sink.digest);
+        fprintf(stderr, "seconds %.4f\n", secs());
+        return 0;
+    }
+    if (mode == "genome") {
+        cli::Genome g; std::string err;
+        if (!cli::load_genome(path, g, err)) { fprintf(stderr, "%s\n", err.c_str()); return 1; }
+        uint64_t bases = 0, h = 0;
+        for (const std::string &s : g.segments) { bases += s.size(); h = h * 31 + stretch_hash(s.data(), s.size()); }
+        for (const cli::Path &p : g.paths) h = h * 31 + stretch_hash(p.header.data(), p.header.size()) + p.components.size();
+        printf("%zu %zu %llu %016llx\n", g.paths.size(), g.segments.size(), (unsigned long long)bases, (unsigned long long)h);
+        fprintf(stderr, "seconds %.4f\n", secs());
+        return 0;
+    }
+    fprintf(stderr, "unknown mode %s\n", mode.c_str());
+    return 2;
+}
