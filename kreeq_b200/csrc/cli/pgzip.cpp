@@ -60,7 +60,7 @@ struct Bits {
 // ---------------------------------------------------------------------------------------------------------
 // Huffman decode tables.  Entry: bits 0-7 = code bits to drop, bits 8-15 = op, bits 16-31 = value.
 constexpr uint32_t OP_LIT = 0x80, OP_EOB = 0x40, OP_SUB = 0x20, OP_BAD = 0x10;   // else: base + (op & 15) extra bits
-constexpr int LIT_PB = 10, DIST_PB = 8, PRE_PB = 7;
+constexpr int LIT_PB = 11, DIST_PB = 8, PRE_PB = 7;
 constexpr int LIT_CAP = (1 << LIT_PB) + 2048, DIST_CAP = (1 << DIST_PB) + 1024, PRE_CAP = 1 << PRE_PB;
 
 const uint16_t kLenBase[29] = {3, 4, 5, 6, 7, 8, 9, 10, 11, 13, 15, 17, 19, 23, 27, 31, 35, 43, 51, 59, 67, 83, 99, 115, 131, 163, 195, 227, 258};
@@ -141,6 +141,21 @@ Kraft build_table(const uint8_t *lens, int n, int pb, uint32_t *tab, int cap, En
     return kraft == 32768u ? K_COMPLETE : K_INCOMPLETE;
 }
 
+// Second pass over the primary literal/length table: where a literal's code leaves room for another complete
+// literal code inside the LIT_PB index bits, the entry yields both (op LIT | 1, value = first | second << 8).
+// Sequence lines of a FASTQ file are 2-3 bit codes, so most lookups there return two bases.
+void pair_literals(uint32_t *tab) {
+    uint32_t copy[1 << LIT_PB];
+    memcpy(copy, tab, sizeof copy);
+    for (uint32_t i = 0; i < (1u << LIT_PB); ++i) {
+        const uint32_t e = copy[i];
+        if (!(e & (OP_LIT << 8))) continue;
+        const uint32_t l1 = e & 0xff, e2 = copy[i >> l1];
+        if (!(e2 & (OP_LIT << 8)) || l1 + (e2 & 0xff) > (uint32_t)LIT_PB) continue;
+        tab[i] = ((e2 >> 16) << 24) | (e & 0x00ff0000u) | ((OP_LIT | 1u) << 8) | (l1 + (e2 & 0xff));
+    }
+}
+
 struct Tables {
     uint32_t lit[LIT_CAP];
     uint32_t dist[DIST_CAP];
@@ -197,6 +212,7 @@ bool read_dynamic_header(Bits &in, Tables &t, bool strict) {
     if (!lens[256]) return false;                                   // no end-of-block code
     const Kraft lk = build_table(lens, hlit, LIT_PB, t.lit, LIT_CAP, lit_entry);
     if (lk == K_OVER || lk == K_EMPTY || (strict && lk != K_COMPLETE)) return false;
+    if (!strict) pair_literals(t.lit);
     const Kraft dk = build_table(lens + hlit, hdist, DIST_PB, t.dist, DIST_CAP, dist_entry);
     if (dk == K_OVER) return false;
     if (strict && dk == K_INCOMPLETE) {                             // zlib allows ONE distance code of length 1
@@ -266,16 +282,16 @@ int inflate_block(Bits &in, const Tables &t, OutBuf<T> &o) {
         if (PGZ_UNLIKELY(e & (OP_SUB << 8))) { in.drop(e & 0xff); e = t.lit[(e >> 16) + in.peek((e >> 8) & 15)]; }
         in.drop(e & 0xff);
         if (e & (OP_LIT << 8)) {
-            base[pos++] = (T)(e >> 16);
-            // a second and third literal fit the bits already buffered (3 x 15 <= 56)
+            // up to three lookups fit the bits already buffered (3 x 15 <= 56); each yields one or two literals
+            base[pos] = (T)((e >> 16) & 0xff); base[pos + 1] = (T)(e >> 24); pos += 1 + ((e >> 8) & 1);
             e = t.lit[in.peek(LIT_PB)];
-            if (!(e & ((OP_LIT) << 8))) continue;
+            if (!(e & (OP_LIT << 8))) continue;
             in.drop(e & 0xff);
-            base[pos++] = (T)(e >> 16);
+            base[pos] = (T)((e >> 16) & 0xff); base[pos + 1] = (T)(e >> 24); pos += 1 + ((e >> 8) & 1);
             e = t.lit[in.peek(LIT_PB)];
-            if (!(e & ((OP_LIT) << 8))) continue;
+            if (!(e & (OP_LIT << 8))) continue;
             in.drop(e & 0xff);
-            base[pos++] = (T)(e >> 16);
+            base[pos] = (T)((e >> 16) & 0xff); base[pos + 1] = (T)(e >> 24); pos += 1 + ((e >> 8) & 1);
             continue;
         }
         if (PGZ_UNLIKELY(e & ((OP_EOB | OP_BAD) << 8))) { o.pos = pos; return (e & (OP_EOB << 8)) ? 0 : -1; }

@@ -256,3 +256,44 @@ def test_parallel_fastq_slicing_is_exact(slice_bytes, fixture_dbs, tmp_path):
         if os.path.exists(REF_BIN):                       # and the reference agrees on the end-of-file rules
             ref = subprocess.run([REF_BIN, "validate", "-r", fq, "-k", "15", "-o", str(tmp_path / "r.kreeq")], cwd=str(tmp_path), capture_output=True, timeout=300)
             assert ref.stdout == par.stdout
+
+
+def test_parallel_gzip_inputs_are_exact(tmp_path):
+    """.fastq.gz / .fasta.gz inputs through the parallel gzip decoder (csrc/cli/pgzip.cpp): the reference's
+    goldens that read gz files, with the size threshold lowered and tiny chunks so that chunk borders fall
+    inside deflate blocks; then a multi-megabyte two-file data set, gz against plain, default chunking."""
+    env = dict(os.environ, KQ_CLI_PGZ_MIN="1", KQ_CLI_PGZ_CHUNK="300", KQ_CLI_PAR_MIN="1", KQ_CLI_SLICE="200")
+    names = [n for n in REF if ".gz" in REF[n]["cmd"]]
+    assert len(names) >= 8
+    for name in names:
+        args = [a.replace("testFiles/", os.path.join(GOLD, "inputs") + "/") for a in shlex.split(REF[name]["cmd"])[1:]]
+        p = subprocess.run([EXE] + args, cwd=str(tmp_path), env=env, capture_output=True, timeout=300)
+        assert p.returncode == 0 and p.stdout.decode() == REF[name]["stdout"], name
+    from helpers import random_genome
+    rng = np.random.default_rng(77)
+    genome = random_genome(rng, 300_000).tobytes()
+    files = []
+    for r in range(2):
+        recs = []
+        for i in range(40_000):
+            s = int(rng.integers(0, len(genome) - 150))
+            read = bytearray(genome[s:s + 150])
+            for e in np.nonzero(rng.random(150) < 0.01)[0]:
+                read[e] = b"ACGT"[int(rng.integers(0, 4))]
+            recs.append(b"@r%d/%d\n" % (i, r + 1) + bytes(read) + b"\n+\n" + bytes(rng.integers(35, 74, 150, dtype=np.uint8)) + b"\n")
+        fq = tmp_path / ("R%d.fastq" % (r + 1))
+        fq.write_bytes(b"".join(recs))
+        with open(str(fq) + ".gz", "wb") as f:
+            f.write(gzip.compress(fq.read_bytes(), 6))
+        files.append(str(fq))
+    fa = tmp_path / "asm.fasta"
+    fa.write_bytes(b">chr1\n" + genome + b"\n")
+    with open(str(fa) + ".gz", "wb") as f:
+        f.write(gzip.compress(fa.read_bytes(), 6))
+    plain = run(["validate", "-f", str(fa), "-r"] + files + ["-o", str(tmp_path / "a.kwig")], str(tmp_path))
+    env = dict(os.environ, KQ_CLI_PGZ_MIN="1")
+    p = subprocess.run([EXE, "validate", "-f", str(fa) + ".gz", "-r"] + [f + ".gz" for f in files] + ["-o", str(tmp_path / "b.kwig")],
+                       cwd=str(tmp_path), env=env, capture_output=True, timeout=300)
+    assert p.returncode == 0 and p.stdout.decode() == plain and "Total kmers" in plain
+    with open(tmp_path / "a.kwig", "rb") as a, open(tmp_path / "b.kwig", "rb") as b:
+        assert a.read() == b.read()

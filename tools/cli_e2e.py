@@ -62,6 +62,12 @@ def main():
             if p.returncode != 0:
                 raise RuntimeError(name + " failed: " + p.stderr.decode()[-500:])
             res[name] = (p.stdout, kw)
+            if name == "ours" and a.gz:                  # same run with the gz files decoded by zlib, one thread per file
+                t = time.perf_counter()
+                q = subprocess.run([exe, "validate", "-f", fa, "-r", r1, r2, "-k", str(K), "-o", os.path.join(cwd, "zlib.kwig")], cwd=cwd,
+                                   stdout=subprocess.PIPE, stderr=subprocess.PIPE, env=dict(os.environ, KQ_CLI_PGZ_MIN="999999999999"))
+                out["ours_zlib_gz_s"] = time.perf_counter() - t
+                out["zlib_gz_identical"] = q.returncode == 0 and q.stdout == p.stdout and filecmp.cmp(kw, os.path.join(cwd, "zlib.kwig"), shallow=False)
             if name == "ours" and a.verbose:
                 out["phases"] = p.stderr.decode().splitlines()
         if len(res) == 2:
