@@ -16,7 +16,8 @@ def pytest_configure(config):
 def _build_once():
     import __graft_entry__ as g
     lib = os.path.join(ROOT, "kreeq_b200", "libkreeq_b200.so")
-    if not os.path.exists(lib) or not os.path.exists(os.path.join(ROOT, "kreeq_b200", "kreeq")):
+    tools = [os.path.join(ROOT, "kreeq_b200", t) for t in ("kreeq", "kreeq-feedcheck", "kreeq-decompressor")]
+    if not os.path.exists(lib) or not all(os.path.exists(t) for t in tools):
         g.build()
 
 

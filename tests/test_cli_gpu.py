@@ -297,3 +297,23 @@ def test_parallel_gzip_inputs_are_exact(tmp_path):
     assert p.returncode == 0 and p.stdout.decode() == plain and "Total kmers" in plain
     with open(tmp_path / "a.kwig", "rb") as a, open(tmp_path / "b.kwig", "rb") as b:
         assert a.read() == b.read()
+
+
+def test_bkwig_written_on_the_gpu_path_inflates_to_the_kwig(tmp_path):
+    """`-o x.bkwig` and `-o x.kwig` of the same run carry the same triples: our .bkwig reader and, where it was
+    built, the reference's own kreeq-decompressor turn the binary file into the text file byte for byte."""
+    asm = os.path.join(tmp_path, "asm.fasta")
+    with open(asm, "wb") as f:
+        f.write(_gz("ref_runs/synthA_k21.fasta.gz"))
+    fq = os.path.join(tmp_path, "r.fastq")
+    with open(fq, "wb") as f:
+        f.write(_gz("ref_runs/synthA_k21.fastq.gz"))
+    run(["validate", "-f", asm, "-r", fq, "-o", "x.kwig"], str(tmp_path))
+    run(["validate", "-f", asm, "-r", fq, "-o", "x.bkwig"], str(tmp_path))
+    with open(tmp_path / "x.kwig", "rb") as f:
+        kwig = f.read()
+    assert kwig == _gz("ref_runs/synthA_k21.kwig.gz")
+    for exe in (os.path.join(ROOT, "kreeq_b200", "kreeq-decompressor"), os.path.join(ROOT, "oracle", "_ref", "kreeq-decompressor")):
+        if os.path.exists(exe):
+            p = subprocess.run([exe, "inflate", "-i", "x.bkwig"], cwd=str(tmp_path), capture_output=True, timeout=60)
+            assert p.returncode == 0 and p.stdout == kwig, exe
