@@ -128,7 +128,10 @@ int  kq_hist(kq_ctx *ctx, uint64_t *cov, uint64_t *n, size_t *len);
 /* replaces DBG::evaluateSegment src/kreeq.cpp:110-229 for one segment (no
  * N/n/X/x inside).  out has len entries; entries >= len-k+1 are zeroed.
  * acc ACCUMULATES.  With nranks>1 only positions whose key this shard owns are
- * filled/counted (same as the reference's mapRange test, kreeq.cpp:150). */
+ * filled/counted (same as the reference's mapRange test, kreeq.cpp:150).
+ * `out` may be pageable memory (rows are staged through pinned buffers and copied once on the host) or
+ * page-locked memory (cudaHostAlloc / cudaHostRegister: rows are copied into it directly, about twice as
+ * fast since 16 bytes per base make the host copy the bottleneck). */
 int  kq_validate_segment(kq_ctx *ctx, const char *seq, uint64_t len,
                          uint32_t cov_cutoff, kq_base *out, kq_qv *acc);
 /* errorRate src/kreeq.cpp:36-40 and QV = -10 log10(err) :87,96 */

@@ -45,7 +45,7 @@ struct Stage {                                   // one staging slot (count and 
     uint64_t *d_bases = nullptr, *d_inv = nullptr;    // validate only
     Base *h_out = nullptr, *d_out = nullptr;          // validate results (pinned / device)
     size_t words = 0, dwords = 0, out_n = 0;
-    cudaEvent_t done = nullptr; bool busy = false;
+    cudaEvent_t done = nullptr, kernel_done = nullptr; bool busy = false;
 };
 
 struct TimedRange { cudaEvent_t a, b; int which; };
@@ -458,7 +458,7 @@ extern "C" int kq_create(kq_ctx **out, int k, int device, uint64_t expected_dist
     CC(cudaMemsetAsync(ctx->d_acc, 0, 3 * sizeof(unsigned long long), ctx->stream));
     CC(cudaMemsetAsync(ctx->d_ovf_n, 0, sizeof(unsigned long long), ctx->stream));
     CC(cudaMemsetAsync(ctx->d_err, 0, sizeof(int), ctx->stream));
-    for (auto &s : ctx->st) CC(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
+    for (auto &s : ctx->st) { CC(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming)); CC(cudaEventCreateWithFlags(&s.kernel_done, cudaEventDisableTiming)); }
 #undef CC
     ctx->optimistic = expected_distinct != 0;
     const uint64_t want = expected_distinct ? (uint64_t)((double)expected_distinct / TARGET_LOAD) : (1ull << 20);
@@ -479,6 +479,7 @@ extern "C" void kq_destroy(kq_ctx *c) {
         if (s.d_bases) { cudaFree(s.d_bases); cudaFree(s.d_inv); }
         if (s.h_out) { cudaFreeHost(s.h_out); cudaFree(s.d_out); }
         if (s.done) cudaEventDestroy(s.done);
+        if (s.kernel_done) cudaEventDestroy(s.kernel_done);
     }
     for (auto &r : c->ranges) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
     for (auto e : c->ev_pool) cudaEventDestroy(e);
@@ -915,10 +916,20 @@ extern "C" int kq_validate_segment(kq_ctx *c, const char *seq, uint64_t len, uin
     const uint64_t kcount = len >= k ? len - k + 1 : 0;                // src/kreeq.cpp:123-126
     CU(cudaMemsetAsync(c->d_acc, 0, 3 * sizeof(unsigned long long), c->stream));
     const uint64_t VCH = 4ull << 20;                                   // output entries per staged chunk
+    // A caller that hands in page-locked memory (cudaHostAlloc / cudaHostRegister) gets the rows copied straight
+    // into it; pageable memory goes through the pinned staging slot and one host copy (which, at 16 bytes per
+    // base, costs more than the PCIe transfer).
+    bool direct = false;
+    {
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, out) == cudaSuccess) direct = at.type == cudaMemoryTypeHost;
+        else cudaGetLastError();
+    }
     struct Pending { Stage *s; uint64_t c0, n; };
     Pending pend[NBUF]; int npend = 0;
     auto drain_one = [&](Pending &p) -> int {                          // pinned -> caller memory, on the pool
         int rc = stage_acquire(c, *p.s); if (rc) return rc;
+        if (direct) return KQ_OK;
         const size_t grain = 1 << 18, tasks = (p.n + grain - 1) / grain;
         Base *src = p.s->h_out; kq_base *dst = out + p.c0; const uint64_t n = p.n;
         global_pool().parallel_for(tasks, [&](size_t t) {
@@ -945,9 +956,12 @@ extern "C" int kq_validate_segment(kq_ctx *c, const char *seq, uint64_t len, uin
         const int t = time_begin(c, 1);
         CU(launch_validate(c->stream, view(c), s.d_bases, s.d_inv, a0, c0, n, kcount, cutoff, s.d_out, c->d_acc, c->d_peers, c->nranks, &c->launches));
         time_end(c, t);
-        CU(cudaMemcpyAsync(s.h_out, s.d_out, n * sizeof(Base), cudaMemcpyDeviceToHost, c->stream));
+        // results leave on the copy stream, so the next chunk's kernel runs under this chunk's transfer
+        CU(cudaEventRecord(s.kernel_done, c->stream));
+        CU(cudaStreamWaitEvent(c->copy_stream, s.kernel_done, 0));
+        CU(cudaMemcpyAsync(direct ? (void *)(out + c0) : (void *)s.h_out, s.d_out, n * sizeof(Base), cudaMemcpyDeviceToHost, c->copy_stream));
         c->d2h += n * sizeof(Base);
-        CU(cudaEventRecord(s.done, c->stream)); s.busy = true;
+        CU(cudaEventRecord(s.done, c->copy_stream)); s.busy = true;
         pend[npend++] = Pending{&s, c0, n};
     }
     for (int i = 0; i < npend; ++i) { int rc = drain_one(pend[i]); if (rc) return rc; }

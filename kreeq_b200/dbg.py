@@ -132,19 +132,23 @@ class DBG:
         return keys, recs
 
     # -- validate ------------------------------------------------------------------------------
-    def evaluateSegment(self, seq, cov_cutoff=0):
-        """Returns the DBGbase array of one segment and accumulates the three QV counters."""
+    def evaluateSegment(self, seq, cov_cutoff=0, out=None):
+        """Returns the DBGbase array of one segment and accumulates the three QV counters.  `out` may be a
+        caller-owned BASE array (e.g. a view of page-locked memory, which the library fills directly)."""
         if isinstance(seq, np.ndarray):
             a = np.ascontiguousarray(seq, dtype=np.uint8)
         else:
             a = np.frombuffer(bytes(seq), dtype=np.uint8)
-        out = np.zeros(a.size, dtype=BASE)
+        if out is None:
+            out = np.zeros(a.size, dtype=BASE)
+        elif out.dtype != BASE or out.size < a.size or not out.flags["C_CONTIGUOUS"]:
+            raise ValueError("out must be a contiguous BASE array of at least len(seq) entries")
         q = KqQV()
         check(lib().kq_validate_segment(self._h, ptr(a), a.size, int(cov_cutoff), ptr(out), C.byref(q)), self._h)
         self.tot_missing += q.missing
         self.tot_kcount += q.kcount
         self.tot_edge_missing += q.edge_missing
-        return out
+        return out[:a.size]
 
     def qv_rows(self):
         """(missing, total, QV, error) for the Merqury and Kreeq rows, src/kreeq.cpp:87-104."""

@@ -441,3 +441,31 @@ def test_peer_tables_validate_shards_one_gpu(mods):
     assert own.tobytes() != rout.tobytes()
     for g in gs:
         g.close()
+
+
+def test_validate_into_page_locked_output(mods):
+    """kq_validate_segment copies rows straight into page-locked caller memory and stages them for pageable
+    memory; a segment of several staging chunks (4 Mi rows each) must come out identical both ways and equal
+    the oracle."""
+    import torch
+    kb, ko = mods
+    rng = np.random.default_rng(909)
+    genome = random_genome(rng, 300_000)
+    batch = sample_reads(rng, genome, 20_000, 150, err=0.01)
+    ref = ko.Table(21); ref.count_batch(batch)
+    asm = np.concatenate([genome] * 30 + [genome[:123_457]])           # 9.1 M positions: three chunks
+    asm = asm.copy(); asm[rng.integers(0, asm.size, 500)] = ord("C")
+    with kb.DBG(k=21) as g:
+        g.traverseInReads(batch); g.finalize()
+        pageable = g.evaluateSegment(asm)
+        a = (g.tot_missing, g.tot_kcount, g.tot_edge_missing)
+        g.tot_missing = g.tot_kcount = g.tot_edge_missing = 0
+        pinned_t = torch.empty(asm.size * kb.BASE.itemsize, dtype=torch.uint8, pin_memory=True)
+        pinned_t.fill_(0xAB)
+        pinned = g.evaluateSegment(asm, out=pinned_t.numpy().view(kb.BASE))
+        assert (g.tot_missing, g.tot_kcount, g.tot_edge_missing) == a
+        assert pinned.tobytes() == pageable.tobytes()
+        short = g.evaluateSegment(asm[:1000], out=pinned_t.numpy().view(kb.BASE))   # reuse, shorter segment
+        assert short.tobytes() == g.evaluateSegment(asm[:1000]).tobytes() and short[980:].tobytes() == bytes(16 * 20)
+    rc, rout, racc = ref.validate_segment(asm[:600_000].tobytes())
+    assert rout.tobytes()[:16 * 500_000] == pageable.tobytes()[:16 * 500_000]
