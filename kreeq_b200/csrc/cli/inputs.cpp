@@ -281,31 +281,51 @@ bool stream_reads(const std::string &path, size_t batch_bytes, ReadSink &sink, s
 
 namespace {
 
-bool is_gap(char c) { return c == 'N' || c == 'n' || c == 'X' || c == 'x'; }
-
 // traverseInSequence, gfalibs/src/gfa.cpp:90-304: newlines dropped, runs of N/n/X/x become gaps, anything
 // else stays inside a segment.
-void add_record(Genome &g, const std::string &header, const char *s, size_t n) {
-    Path path;
-    path.header = header;
+struct ParsedRecord { Path path; std::vector<std::string> segments; };   // component.segment is local to the record
+
+void parse_record(ParsedRecord &r, const std::string &header, const char *s, size_t n) {
+    static const std::vector<uint8_t> gap = [] { std::vector<uint8_t> t(256, 0); t['N'] = t['n'] = t['X'] = t['x'] = 1; return t; }();
+    r.path.header = header;
     std::string seq;
     seq.reserve(n);
-    for (size_t i = 0; i < n; ++i)
-        if (s[i] != '\n') seq.push_back(s[i]);
+    for (const char *p = s, *end = s + n; p < end;) {
+        const char *nl = (const char *)memchr(p, '\n', (size_t)(end - p));
+        const char *stop = nl ? nl : end;
+        seq.append(p, (size_t)(stop - p));
+        p = stop + 1;
+    }
+    const uint8_t *q = (const uint8_t *)seq.data();
+    const size_t len = seq.size();
     size_t i = 0;
-    while (i < seq.size()) {
-        size_t j = i;
-        if (is_gap(seq[i])) {
-            while (j < seq.size() && is_gap(seq[j])) ++j;
-            path.components.push_back({false, i, j - i, 0});
+    while (i < len) {
+        size_t j = i + 1;
+        if (gap[q[i]]) {
+            while (j < len && gap[q[j]]) ++j;
+            r.path.components.push_back({false, i, j - i, 0});
         } else {
-            while (j < seq.size() && !is_gap(seq[j])) ++j;
-            path.components.push_back({true, i, j - i, g.segments.size()});
-            g.segments.emplace_back(seq, i, j - i);
+            while (j < len && !gap[q[j]]) ++j;
+            r.path.components.push_back({true, i, j - i, r.segments.size()});
+            if (i == 0 && j == len) r.segments.push_back(std::move(seq));      // the usual case: one segment, no copy
+            else r.segments.emplace_back(seq, i, j - i);
         }
         i = j;
     }
-    g.paths.push_back(std::move(path));
+}
+
+void append_record(Genome &g, ParsedRecord &&r) {
+    const size_t base = g.segments.size();
+    for (Component &c : r.path.components)
+        if (c.is_segment) c.segment += base;
+    for (std::string &seg : r.segments) g.segments.push_back(std::move(seg));
+    g.paths.push_back(std::move(r.path));
+}
+
+void add_record(Genome &g, const std::string &header, const char *s, size_t n) {
+    ParsedRecord r;
+    parse_record(r, header, s, n);
+    append_record(g, std::move(r));
 }
 
 std::string first_word(const char *s, size_t n) {
@@ -379,18 +399,28 @@ bool load_genome(const std::string &path, Genome &g, std::string &err) {
     if (data.empty()) return true;
     if (data[0] == '>') {
         // header = first line up to the first blank ('>' may occur inside the rest of the header line);
-        // sequence = everything up to the next '>' (src/input.cpp:206-228)
+        // sequence = everything up to the next '>' (src/input.cpp:206-228).  Records are found with memchr and
+        // parsed on all cores (a chromosome-scale assembly is a handful of records of 10^8 bases each).
+        struct Rec { std::string header; size_t body, len; };
+        std::vector<Rec> recs;
         size_t pos = 1;
         while (pos < data.size()) {
-            size_t nl = data.find('\n', pos);
-            if (nl == std::string::npos) nl = data.size();
-            const std::string header = first_word(data.data() + pos, nl - pos);
-            size_t next = nl < data.size() ? data.find('>', nl) : std::string::npos;
-            if (next == std::string::npos) next = data.size();
+            const char *nlp = (const char *)memchr(data.data() + pos, '\n', data.size() - pos);
+            const size_t nl = nlp ? (size_t)(nlp - data.data()) : data.size();
+            const char *gt = nl < data.size() ? (const char *)memchr(data.data() + nl, '>', data.size() - nl) : nullptr;
+            const size_t next = gt ? (size_t)(gt - data.data()) : data.size();
             const size_t body = nl < data.size() ? nl + 1 : data.size();
-            add_record(g, header, data.data() + body, next - body);
+            recs.push_back({first_word(data.data() + pos, nl - pos), body, next - body});
             pos = next + 1;
         }
+        std::vector<ParsedRecord> parsed(recs.size());
+        std::atomic<size_t> next_rec{0};
+        auto work = [&] { for (size_t i; (i = next_rec++) < recs.size();) parse_record(parsed[i], recs[i].header, data.data() + recs[i].body, recs[i].len); };
+        std::vector<std::thread> th;
+        for (size_t t = 1; t < std::min<size_t>((size_t)feed_threads(), recs.size()); ++t) th.emplace_back(work);
+        work();
+        for (auto &x : th) x.join();
+        for (ParsedRecord &r : parsed) append_record(g, std::move(r));
         return true;
     }
     if (data[0] == '@') {                           // src/input.cpp:230-258: strict 4-line records

@@ -256,3 +256,54 @@ def test_reference_fixture_gz_and_genome_loader(tmp_path):
         return p.stdout
     a, b = genome(dict(PAR, KQ_CLI_PGZ_CHUNK="5000")), genome(SER)
     assert a == b and int(a.split()[0]) == 5
+
+
+def _fnv(s):
+    h = 0xcbf29ce484222325
+    for c in s:
+        h = ((h ^ c) * 0x100000001b3) & 0xFFFFFFFFFFFFFFFF
+    return (h * 0x9e3779b97f4a7c15 + len(s)) & 0xFFFFFFFFFFFFFFFF
+
+
+def test_fasta_loader_records_segments_gaps(tmp_path):
+    """load_genome on FASTA (src/input.cpp:206-228, gfalibs/src/gfa.cpp:90-304): header = first word, sequence =
+    everything up to the next '>', newlines dropped, runs of N/n/X/x are gaps between segments.  Records are
+    parsed in parallel; the result must equal a direct restatement, in file order."""
+    import re
+    rng = np.random.default_rng(31)
+    recs = []
+    for i in range(37):
+        n = int(rng.integers(0, 60_000)) if i % 9 else 0
+        s = bytearray(rng.choice(np.frombuffer(b"ACGTacgt", dtype=np.uint8), size=n).tobytes())
+        for _ in range(int(rng.integers(0, 6))):
+            if n > 100:
+                a = int(rng.integers(0, n - 50)); ln = int(rng.integers(1, 50))
+                s[a:a + ln] = bytes(rng.choice(np.frombuffer(b"NnXx", dtype=np.uint8), size=ln))
+        if i == 3 and n:
+            s[:5] = b"NNNNN"                                    # gap first
+        if i == 4 and n:
+            s[-3:] = b"xxx"                                     # gap last
+        recs.append((b"seq%d" % i, b" desc > with gt" if i == 5 else b"", bytes(s)))
+    fa = b""
+    for h, d, s in recs:
+        w = int(rng.integers(40, 90))
+        fa += b">" + h + d.replace(b">", b"") + b"\n" + b"".join(s[a:a + w] + b"\n" for a in range(0, len(s), w))
+    fa = fa[:-1]                                                # no final newline
+    h_total, nseg, bases = 0, 0, 0
+    seg_hashes, path_hashes = [], []
+    for h, d, s in recs:
+        comps = [m for m in re.finditer(rb"[NnXx]+|[^NnXx]+", s)]
+        for m in comps:
+            if m.group()[0:1] not in (b"N", b"n", b"X", b"x"):
+                seg_hashes.append(_fnv(m.group())); nseg += 1; bases += len(m.group())
+        path_hashes.append((_fnv(h) + len(comps)) & 0xFFFFFFFFFFFFFFFF)
+    for x in seg_hashes:
+        h_total = (h_total * 31 + x) & 0xFFFFFFFFFFFFFFFF
+    for x in path_hashes:
+        h_total = (h_total * 31 + x) & 0xFFFFFFFFFFFFFFFF
+    want = b"%d %d %d %016x\n" % (len(recs), nseg, bases, h_total)
+    f = tmp_path / "g.fa"
+    f.write_bytes(fa)
+    for threads in ("1", "3", "8"):
+        p = subprocess.run([TOOL, "genome", str(f)], capture_output=True, timeout=120, env=dict(os.environ, KQ_CLI_THREADS=threads))
+        assert p.returncode == 0 and p.stdout == want, threads
