@@ -700,7 +700,7 @@ extern "C" int kq_route_setup(kq_ctx *c, uint64_t slab_tuples, int nb_bits, void
     if (c->nranks > KQ_MAX_RANKS) return fail(c, KQ_EINVAL, "kq_route_setup: too many ranks");
     CU(cudaSetDevice(c->device));
     const int tw = tuple_words(c->k);
-    if (scatter_pick_cap((unsigned long long)c->nranks << nb_bits, tw) == 0)
+    if (scatter_pick_cap((unsigned long long)c->nranks << nb_bits, tw, KQ_ROUTE_MAX_CAP) == 0)
         return fail(c, KQ_EINVAL, "kq_route_setup: nranks << nb_bits bins do not fit shared memory");
     CU(cudaStreamSynchronize(c->stream));
     for (void *p : c->ipc_opened) cudaIpcCloseMemHandle(p);
@@ -773,7 +773,7 @@ extern "C" int kq_route_scatter(kq_ctx *c, const uint64_t *d_bases, const uint64
     CU(cudaSetDevice(c->device));
     const int t = time_begin(c, 3);
     const int tw = tuple_words(c->k);
-    const int cap = scatter_pick_cap((unsigned long long)c->nranks << c->route.nb_bits, tw);
+    const int cap = scatter_pick_cap((unsigned long long)c->nranks << c->route.nb_bits, tw, KQ_ROUTE_MAX_CAP);
     unsigned long long totals[2 * KQ_MAX_RANKS];
     // the padding sentinels go to the peers' slabs from this kernel: like the scatter, it runs after the
     // all-gather that ordered this round behind every rank's previous insert

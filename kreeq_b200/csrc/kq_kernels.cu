@@ -520,7 +520,7 @@ size_t scatter_smem_bytes(unsigned long long nslices, int cap, int tw) {
 }
 
 // bin capacity (tuples) of the scatter kernel's shared-memory bins; one CTA per SM owns them
-int scatter_pick_cap(unsigned long long nslices, int tw) {
+int scatter_pick_cap(unsigned long long nslices, int tw, int max_cap) {
     static int max_smem = 0, sm_smem = 0;
     if (!max_smem) {
         int dev = 0; cudaGetDevice(&dev);
@@ -531,12 +531,12 @@ int scatter_pick_cap(unsigned long long nslices, int tw) {
     }
     if (const char *e = std::getenv("KQ_SCATTER_CAP")) {              // tuning knob
         const int cap = std::atoi(e);
-        if (cap > 0 && scatter_smem_bytes(nslices, cap, tw) <= (size_t)max_smem - 1024) return cap;
+        if (cap > 0 && cap <= max_cap && scatter_smem_bytes(nslices, cap, tw) <= (size_t)max_smem - 1024) return cap;
     }
     // a tile brings NT * R = 8192 tuples: with few bins a small capacity would overflow several times per
     // tile (each time costs a round of barriers), so take the largest power of two that fits
     for (int cap : {512, 256, 128, 64, 32, 16, 8})
-        if (scatter_smem_bytes(nslices, cap, tw) <= (size_t)max_smem - 1024) return cap;
+        if (cap <= max_cap && scatter_smem_bytes(nslices, cap, tw) <= (size_t)max_smem - 1024) return cap;
     return 0;
 }
 

@@ -50,7 +50,10 @@ struct RouteMap {
 int sm_count();   // multiprocessors of the current device (cached)
 // shared memory the scatter kernel needs for `nslices` bins of `cap` tuples; 0 if it cannot fit
 size_t scatter_smem_bytes(unsigned long long nslices, int cap, int tw);
-int scatter_pick_cap(unsigned long long nslices, int tw);       // largest of 32/16/8 that fits, 0 = none
+int scatter_pick_cap(unsigned long long nslices, int tw, int max_cap = 512);   // largest power of two <= max_cap that fits, 0 = none
+// routed bins flush straight into a peer's slab: chunks of at most 32 tuples (256-byte peer stores), so a
+// (sender, bin) region is padded by fewer than 32 tuples
+constexpr int KQ_ROUTE_MAX_CAP = 32;
 
 // ---- count pipeline (rows A2 + A3) -------------------------------------------------------------------
 // single-slice tables / small inputs: fused extract + insert
