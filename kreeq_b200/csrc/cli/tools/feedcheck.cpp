@@ -17,6 +17,8 @@
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
+#include <string>
+#include <vector>
 
 static uint64_t stretch_hash(const char *p, size_t n) {
     uint64_t h = 0xcbf29ce484222325ull;
@@ -78,6 +80,67 @@ int main(int argc, char **argv) {
         printf("%zu %zu %llu %016llx\n", g.paths.size(), g.segments.size(), (unsigned long long)bases, (unsigned long long)h);
         fprintf(stderr, "seconds %.4f\n", secs());
         return 0;
+    }
+    if (mode == "rewrite") {
+        // kreeq-feedcheck rewrite <asm.fa> <in.bkwig> <out.kwig|.bed|.csvtable|.bkwig>: the (cov, F, B) rows of a
+        // .bkwig laid over the genome's segments and written again by the command line's writers
+        if (argc < 5) { fprintf(stderr, "rewrite needs <asm> <in.bkwig> <out>\n"); return 2; }
+        cli::Genome g; std::string err;
+        if (!cli::load_genome(path, g, err)) { fprintf(stderr, "%s\n", err.c_str()); return 1; }
+        FILE *f = fopen(argv[3], "rb");
+        if (!f) { perror("bkwig"); return 1; }
+        uint8_t k = 0; uint32_t npaths = 0;
+        bool ok = fread(&k, 1, 1, f) == 1 && fread(&npaths, 4, 1, f) == 1;
+        for (uint32_t i = 0; ok && i < npaths; ++i) {
+            uint16_t hl = 0; uint32_t ns = 0;
+            ok = fread(&hl, 2, 1, f) == 1 && fseek(f, hl, SEEK_CUR) == 0 && fread(&ns, 4, 1, f) == 1 && fseek(f, 17L * ns, SEEK_CUR) == 0;
+        }
+        g.bases.resize(g.segments.size());
+        for (const cli::Path &p : g.paths)
+            for (const cli::Component &c : p.components) {
+                if (!c.is_segment) continue;
+                std::vector<kq_base> &b = g.bases[c.segment];
+                b.resize(c.len);
+                for (kq_base &e : b) {
+                    uint32_t v[3];
+                    ok = ok && fread(v, 4, 3, f) == 3;
+                    e.cov = v[0]; e.fw = v[1]; e.bw = v[2]; e.isFw = 1;
+                }
+            }
+        ok = ok && fgetc(f) == EOF;
+        fclose(f);
+        if (!ok) { fprintf(stderr, "bkwig does not match the genome\n"); return 1; }
+        const std::string out = argv[4], ext = cli::file_ext(out);
+        ok = ext == "kwig" ? cli::write_kwig(out, k, g) : ext == "bkwig" ? cli::write_bkwig(out, k, g) : cli::write_table(out, ext, k, g);
+        return ok ? 0 : 1;
+    }
+    if (mode == "writebench") {                       // kreeq-feedcheck writebench <out.kwig|.bed|.bkwig> <bases> [k]: writer throughput
+        const uint64_t n = argc > 3 ? (uint64_t)atoll(argv[3]) : 10000000;
+        const int k = argc > 4 ? atoi(argv[4]) : 21;
+        cli::Genome g;
+        const uint64_t per = (n + 9) / 10;
+        uint64_t x = 88172645463325252ull;
+        for (int r = 0; r < 10; ++r) {
+            cli::Path p; p.header = "chr" + std::to_string(r + 1);
+            p.components.push_back({true, 0, per, g.segments.size()});
+            g.segments.emplace_back();               // the writers only read the DBGbase rows
+            std::vector<kq_base> b(per);
+            for (auto &e : b) {
+                x ^= x << 13; x ^= x >> 7; x ^= x << 17;
+                e.cov = 20 + (uint32_t)(x % 21); e.fw = (uint32_t)((x >> 8) % 30); e.bw = (uint32_t)((x >> 16) % 30); e.isFw = (uint8_t)((x >> 24) & 1);
+                if ((x >> 40) % 53 == 0) {            // now and then values of every width up to 2^32 - 1
+                    const int w = (int)((x >> 50) % 33);
+                    e.cov = w ? (uint32_t)(0xffffffffull >> (32 - w)) - (uint32_t)((x >> 30) & 1) : 0; e.fw = e.cov / 7; e.bw = e.cov / 1000;
+                }
+            }
+            g.bases.push_back(std::move(b));
+            g.paths.push_back(std::move(p));
+        }
+        const double t1 = secs();
+        const std::string ext = cli::file_ext(path);
+        const bool ok = ext == "kwig" ? cli::write_kwig(path, k, g) : ext == "bkwig" ? cli::write_bkwig(path, k, g) : cli::write_table(path, ext, k, g);
+        printf("{\"ok\": %s, \"bases\": %llu, \"seconds\": %.4f}\n", ok ? "true" : "false", (unsigned long long)(per * 10), secs() - t1);
+        return ok ? 0 : 1;
     }
     fprintf(stderr, "unknown mode %s\n", mode.c_str());
     return 2;

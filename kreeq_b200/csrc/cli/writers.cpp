@@ -54,6 +54,25 @@ bool emit_blocks(FILE *f, size_t n, const std::function<void(size_t, std::string
     return lseek(fd, pos, SEEK_SET) >= 0;
 }
 
+// decimal digits of v at p, returns the end; two digits at a time from a table
+inline char *put_num(char *p, uint64_t v) {
+    static const char *const pairs =
+        "0001020304050607080910111213141516171819202122232425262728293031323334353637383940414243444546474849"
+        "5051525354555657585960616263646566676869707172737475767778798081828384858687888990919293949596979899";
+    if (v < 10) { *p = (char)('0' + v); return p + 1; }
+    if (v < 100) { memcpy(p, pairs + 2 * v, 2); return p + 2; }
+    char tmp[20];
+    int len = 0;
+    while (v >= 100) { memcpy(tmp + len, pairs + 2 * (v % 100), 2); len += 2; v /= 100; }   // stored low pair first, digits swapped back below
+    if (v >= 10) { memcpy(tmp + len, pairs + 2 * v, 2); len += 2; }
+    else tmp[len++] = (char)('0' + v), tmp[len++] = 0;
+    // tmp holds pairs "ab" least significant first; emit most significant first
+    int i = len - 2;
+    if (tmp[i + 1] == 0) { *p++ = tmp[i]; i -= 2; }
+    for (; i >= 0; i -= 2) { p[0] = tmp[i]; p[1] = tmp[i + 1]; p += 2; }
+    return p;
+}
+
 inline void append_num(std::string &o, uint64_t v) {
     char tmp[20];
     int len = 0;
@@ -64,7 +83,7 @@ inline void append_num(std::string &o, uint64_t v) {
 constexpr uint64_t BLOCK = 1u << 20;               // bases per formatting task
 struct Span { const Path *path; const Component *comp; uint64_t abs_pos, from, to; };   // bases [from, to) of one segment
 
-std::vector<Span> spans_of(const Genome &g) {
+std::vector<Span> spans_of(const Genome &g, uint64_t block = BLOCK) {
     std::vector<Span> v;
     for (const Path &p : g.paths) {
         uint64_t abs_pos = 0;
@@ -72,7 +91,7 @@ std::vector<Span> spans_of(const Genome &g) {
             if (c.is_segment) {
                 const uint64_t len = g.bases[c.segment].size();
                 if (len == 0) v.push_back({&p, &c, abs_pos, 0, 0});
-                for (uint64_t a = 0; a < len; a += BLOCK) v.push_back({&p, &c, abs_pos, a, std::min(len, a + BLOCK)});
+                for (uint64_t a = 0; a < len; a += block) v.push_back({&p, &c, abs_pos, a, std::min(len, a + block)});
             }
             abs_pos += c.len;
         }
@@ -128,62 +147,65 @@ bool write_kwig(const std::string &file, int k, const Genome &g) {
             o += "fixedStep chrom="; o += sp.path->header; o += " start="; append_num(o, sp.abs_pos); o += " step=1\n";
         }
         const kq_base *b = g.bases[sp.comp->segment].data();
+        const size_t head = o.size();
+        o.resize(head + (sp.to - sp.from) * 33);   // 3 x (10 digits + separator) per row at most
+        char *p = &o[head];
         for (uint64_t x = sp.from; x < sp.to; ++x) {
             uint32_t cov, F, B;
             triple(b[x], cov, F, B);
-            append_num(o, cov); o.push_back(','); append_num(o, F); o.push_back(','); append_num(o, B); o.push_back('\n');
+            p = put_num(p, cov); *p++ = ','; p = put_num(p, F); *p++ = ','; p = put_num(p, B); *p++ = '\n';
         }
+        o.resize((size_t)(p - o.data()));
     });
     return (fclose(f) == 0) && ok;
 }
 
-// Each line repeats the last k values of the three tracks (zeros before the segment start), so a line is
-// three joins over a ring of pre-formatted numbers.
+// Each line repeats the last k values of the three tracks (zeros before the segment start).  Consecutive lines
+// share k - 1 of their k values, so a block first writes every track once as one joined text
+// "v0:v1:v2:..." with the offset of every value; a line's column is then ONE slice of that text.
 bool write_table(const std::string &file, const std::string &ext, int k, const Genome &g) {
     char col = ',', entry = ',';
     if (ext == "bed") { col = '\t'; entry = ':'; }
     else if (ext == "csv") { col = ','; entry = ' '; }
     FILE *f = fopen(file.c_str(), "wb");
     if (!f) return false;
-    struct Tok { char s[11]; uint8_t len; };
-    auto fmt = [](uint32_t v, Tok &t) {
-        char tmp[10];
-        int len = 0;
-        do { tmp[len++] = (char)('0' + v % 10); v /= 10; } while (v);
-        t.len = (uint8_t)len;
-        for (int i = 0; i < len; ++i) t.s[i] = tmp[len - 1 - i];
-    };
-    const std::vector<Span> spans = spans_of(g);
+    const std::vector<Span> spans = spans_of(g, 1u << 16);          // a line is ~200 bytes: 64 Ki lines per task
+    const uint64_t K = (uint64_t)k;
     const bool ok = emit_blocks(f, spans.size(), [&](size_t idx, std::string &o) {
         const Span &sp = spans[idx];
         const kq_base *b = g.bases[sp.comp->segment].data();
-        std::vector<Tok> ring[3];
-        for (auto &r : ring) { r.resize((size_t)k); for (Tok &t : r) { t.s[0] = '0'; t.len = 1; } }
-        size_t head = 0;                            // slot of the oldest value
-        const uint64_t warm = sp.from >= (uint64_t)(k - 1) ? sp.from - (uint64_t)(k - 1) : 0;
-        for (uint64_t x = warm; x < sp.from; ++x) {   // the window a block inherits from the bases before it
-            uint32_t v[3];
-            triple(b[x], v[0], v[1], v[2]);
-            for (int t = 0; t < 3; ++t) fmt(v[t], ring[t][head]);
-            head = (head + 1) % (size_t)k;
-        }
-        o.reserve((sp.to - sp.from) * (size_t)(3 * k * 3 + 32));
-        for (uint64_t x = sp.from; x < sp.to; ++x) {
-            uint32_t v[3];
-            triple(b[x], v[0], v[1], v[2]);
-            for (int t = 0; t < 3; ++t) fmt(v[t], ring[t][head]);
-            head = (head + 1) % (size_t)k;         // the newest value is now the last of the window
-            o += sp.path->header; o.push_back(col); append_num(o, sp.abs_pos + x);
+        const uint64_t rows = sp.to - sp.from, vals = rows + K - 1;   // values from - (k - 1) .. to - 1, zeros before 0
+        std::string joined[3];
+        std::vector<uint32_t> off[3];
+        for (int t = 0; t < 3; ++t) { joined[t].resize(vals * 11); off[t].resize(vals + 1); }
+        char *w[3] = {&joined[0][0], &joined[1][0], &joined[2][0]};
+        for (uint64_t i = 0; i < vals; ++i) {
+            uint32_t v[3] = {0, 0, 0};
+            if (sp.from + i >= K - 1) triple(b[sp.from + i - (K - 1)], v[0], v[1], v[2]);
             for (int t = 0; t < 3; ++t) {
-                o.push_back(col);
-                for (int i = 0; i < k; ++i) {
-                    const Tok &tk = ring[t][(head + (size_t)i) % (size_t)k];
-                    o.append(tk.s, tk.len);
-                    if (i + 1 < k) o.push_back(entry);
-                }
+                off[t][i] = (uint32_t)(w[t] - joined[t].data());
+                w[t] = put_num(w[t], v[t]); *w[t]++ = entry;
             }
-            o.push_back('\n');
         }
+        for (int t = 0; t < 3; ++t) off[t][vals] = (uint32_t)(w[t] - joined[t].data());
+        size_t total = 0;
+        for (uint64_t r = 0; r < rows; ++r)
+            for (int t = 0; t < 3; ++t) total += off[t][r + K] - off[t][r];      // k values, k - 1 separators + the column separator
+        total += rows * (sp.path->header.size() + 1 + 20 + 1);
+        o.resize(total);
+        char *p = &o[0];
+        const std::string &name = sp.path->header;
+        for (uint64_t r = 0; r < rows; ++r) {
+            memcpy(p, name.data(), name.size()); p += name.size();
+            *p++ = col; p = put_num(p, sp.abs_pos + sp.from + r);
+            for (int t = 0; t < 3; ++t) {
+                *p++ = col;
+                const size_t len = off[t][r + K] - off[t][r] - 1;               // without the trailing separator
+                memcpy(p, joined[t].data() + off[t][r], len); p += len;
+            }
+            *p++ = '\n';
+        }
+        o.resize((size_t)(p - o.data()));
     });
     return (fclose(f) == 0) && ok;
 }
@@ -211,16 +233,21 @@ bool write_bkwig(const std::string &file, int k, const Genome &g) {
             abs_pos += c.len;
         }
     }
-    for (const Path &p : g.paths)
-        for (const Component &c : p.components) {
-            if (!c.is_segment) continue;
-            for (const kq_base &b : g.bases[c.segment]) {
-                uint32_t v[3];
-                triple(b, v[0], v[1], v[2]);
-                o.put(reinterpret_cast<const char *>(v), 12);
-            }
+    FILE *f = o.f;
+    o.flush();
+    const std::vector<Span> spans = spans_of(g);
+    const bool ok = emit_blocks(f, spans.size(), [&](size_t i, std::string &out) {   // 12 bytes per base, blocks in parallel
+        const Span &sp = spans[i];
+        const kq_base *b = g.bases[sp.comp->segment].data();
+        out.resize((sp.to - sp.from) * 12);
+        char *p = &out[0];
+        for (uint64_t x = sp.from; x < sp.to; ++x, p += 12) {
+            uint32_t v[3];
+            triple(b[x], v[0], v[1], v[2]);
+            memcpy(p, v, 12);
         }
-    return o.close();
+    });
+    return o.close() && ok;
 }
 
 } // namespace cli
