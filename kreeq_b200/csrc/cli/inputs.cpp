@@ -122,8 +122,9 @@ struct FastqState {
             if (line == 3) {
                 batch.push_back('N');
                 if (batch.size() >= batch_bytes) {
-                    if (!sink(batch.data(), batch.size())) return false;
-                    batch.clear();
+                    if (!sink.take(std::move(batch))) return false;
+                    batch = std::string();
+                    batch.reserve(batch_bytes + (1u << 20));
                 }
             }
             line = (line + 1) & 3;
@@ -131,7 +132,7 @@ struct FastqState {
         }
         return true;
     }
-    bool finish() { return batch.empty() || sink(batch.data(), batch.size()); }
+    bool finish() { return batch.empty() || sink.take(std::move(batch)); }
 };
 
 // Uncompressed files are mapped and cut into one slice per core AT RECORD BOUNDARIES: newlines are counted in
@@ -179,6 +180,7 @@ bool stream_plain_parallel(const char *data, size_t size, size_t batch_bytes, Re
         ReadSink &inner; std::mutex &mu;
         Locked(ReadSink &i, std::mutex &m) : inner(i), mu(m) {}
         bool operator()(const char *d, size_t l) override { std::lock_guard<std::mutex> lk(mu); return inner(d, l); }
+        bool take(std::string &&b) override { std::lock_guard<std::mutex> lk(mu); return inner.take(std::move(b)); }
     };
     std::mutex local_mu;
     std::vector<std::thread> th;
@@ -186,7 +188,7 @@ bool stream_plain_parallel(const char *data, size_t size, size_t batch_bytes, Re
         th.emplace_back([&, t] {
             if (start[t] >= start[t + 1]) return;
             Locked locked(sink, sink_mu ? *sink_mu : local_mu);
-            FastqState st(batch_bytes, locked);
+            FastqState st(batch_bytes, sink.thread_safe() ? sink : static_cast<ReadSink &>(locked));
             if (!st.feed(data + start[t], data + start[t + 1]) || !st.finish()) ok = false;
         });
     for (auto &x : th) x.join();

@@ -54,7 +54,14 @@ bool read_file(const std::string &path, std::string &out, std::string &err);
 // FASTQ read batching with getKmers' exact end-of-file behaviour (gfalibs/include/functions.h:69-122):
 // sequence lines, each followed by 'N' iff the record's quality line ended with a newline.  Calls
 // sink(batch) with batches of about `batch_bytes`; FASTA inputs ('>') yield nothing, as in loadKmers.
-struct ReadSink { virtual bool operator()(const char *data, size_t len) = 0; virtual ~ReadSink() {} };
+struct ReadSink {
+    virtual bool operator()(const char *data, size_t len) = 0;
+    // a finished batch the producer no longer needs: sinks that keep batches override this to avoid a copy
+    virtual bool take(std::string &&batch) { return (*this)(batch.data(), batch.size()); }
+    // true if several parser threads may call the sink at the same time (else calls are serialised)
+    virtual bool thread_safe() const { return false; }
+    virtual ~ReadSink() {}
+};
 bool stream_reads(const std::string &path, size_t batch_bytes, ReadSink &sink, std::string &err);
 
 // Host threads one input file may use for decoding / slicing: all cores divided by the number of files being

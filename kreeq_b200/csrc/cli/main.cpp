@@ -217,6 +217,8 @@ struct QueueSink : ReadSink {
     BatchQueue &bq;
     explicit QueueSink(BatchQueue &b) : bq(b) {}
     bool operator()(const char *data, size_t len) override { bq.put(std::string(data, len)); return true; }
+    bool take(std::string &&batch) override { bq.put(std::move(batch)); return true; }
+    bool thread_safe() const override { return true; }     // the queue has its own lock
 };
 
 bool count_files(kq_ctx *ctx, const std::vector<std::string> &files, std::string &err) {

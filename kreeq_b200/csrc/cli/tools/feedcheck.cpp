@@ -63,6 +63,7 @@ int main(int argc, char **argv) {
                 ++batches; bytes += len; seps += s; digest += h;
                 return true;
             }
+            bool thread_safe() const override { return getenv("KQ_FEEDCHECK_SERIAL") == nullptr; }
         } sink;
         std::string err;
         const size_t batch = argc > 3 ? (size_t)atol(argv[3]) : (size_t)128 << 20;

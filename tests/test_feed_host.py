@@ -211,6 +211,8 @@ def test_fastq_batches_from_gz(chunk, slice_, tmp_path):
     assert reads_digest(plain, env) == want
     assert reads_digest(packed, env) == want
     assert reads_digest(packed, env, batch=50_000) == want
+    serial = dict(env, KQ_FEEDCHECK_SERIAL="1")               # a sink that is not thread safe: calls are serialised
+    assert reads_digest(plain, serial) == want and reads_digest(packed, serial, batch=50_000) == want
 
 
 def test_fastq_gz_truncated_records_and_fasta(tmp_path):
