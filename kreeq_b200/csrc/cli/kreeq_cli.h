@@ -7,7 +7,9 @@
 
 #include <atomic>
 #include <cstdint>
+#include <memory>
 #include <string>
+#include <utility>
 #include <vector>
 
 extern "C" {
@@ -42,10 +44,21 @@ struct Path {
     std::string header;
     std::vector<Component> components;
 };
+// std::vector whose resize() leaves new elements uninitialised: the DBGbase arrays (16 bytes per base) are
+// overwritten completely by kq_validate_segment, so zero-filling them first only costs a pass over memory.
+template <typename T> struct UninitAlloc : std::allocator<T> {
+    template <typename U> struct rebind { using other = UninitAlloc<U>; };
+    UninitAlloc() = default;
+    template <typename U> UninitAlloc(const UninitAlloc<U> &) {}
+    template <typename U> void construct(U *p) noexcept { ::new (static_cast<void *>(p)) U; }
+    template <typename U, typename... A> void construct(U *p, A &&...a) { ::new (static_cast<void *>(p)) U(std::forward<A>(a)...); }
+};
+using BaseRows = std::vector<kq_base, UninitAlloc<kq_base>>;
+
 struct Genome {
     std::vector<Path> paths;           // file order (sortPathsByOriginal)
     std::vector<std::string> segments;
-    std::vector<std::vector<kq_base>> bases;   // DBGbase arrays, one per segment
+    std::vector<BaseRows> bases;       // DBGbase arrays, one per segment
 };
 
 // Whole-file reader that understands gzip and plain files alike (gfalibs/src/stream-obj.cpp:98-158).

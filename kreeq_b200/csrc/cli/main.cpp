@@ -272,7 +272,7 @@ void report(kq_ctx *ctx, const Options &o, Genome *genome) {
         genome->bases.resize(genome->segments.size());
         for (size_t s = 0; s < genome->segments.size(); ++s) {
             const std::string &seg = genome->segments[s];
-            genome->bases[s].assign(seg.size(), kq_base{0, 0, 0, 0, {0, 0, 0}});
+            genome->bases[s].resize(seg.size());           // every row is written by the library
             CHECK(ctx, kq_validate_segment(ctx, seg.data(), seg.size(), o.cov_cutoff, genome->bases[s].data(), &qv));
         }
         if (dotted) print_qv(qv, k);

@@ -100,7 +100,7 @@ int main(int argc, char **argv) {
         for (const cli::Path &p : g.paths)
             for (const cli::Component &c : p.components) {
                 if (!c.is_segment) continue;
-                std::vector<kq_base> &b = g.bases[c.segment];
+                cli::BaseRows &b = g.bases[c.segment];
                 b.resize(c.len);
                 for (kq_base &e : b) {
                     uint32_t v[3];
@@ -125,7 +125,7 @@ int main(int argc, char **argv) {
             cli::Path p; p.header = "chr" + std::to_string(r + 1);
             p.components.push_back({true, 0, per, g.segments.size()});
             g.segments.emplace_back();               // the writers only read the DBGbase rows
-            std::vector<kq_base> b(per);
+            cli::BaseRows b(per);
             for (auto &e : b) {
                 x ^= x << 13; x ^= x >> 7; x ^= x << 17;
                 e.cov = 20 + (uint32_t)(x % 21); e.fw = (uint32_t)((x >> 8) % 30); e.bw = (uint32_t)((x >> 16) % 30); e.isFw = (uint8_t)((x >> 24) & 1);
