@@ -112,7 +112,14 @@ bool read_file(const std::string &path, std::string &out, std::string &err) {
 namespace {
 struct FastqState {
     std::string batch; int line = 0; size_t batch_bytes; ReadSink &sink;
-    FastqState(size_t bb, ReadSink &s) : batch_bytes(bb), sink(s) { batch.reserve(bb + (1u << 20)); }
+    FastqState(size_t bb, ReadSink &s) : batch_bytes(bb), sink(s) { fresh(); }
+    void fresh() {                                  // a buffer to fill: a recycled one if the sink has any
+        if (batch.capacity() < batch_bytes) {
+            if (!sink.recycle(batch)) batch = std::string();
+            batch.reserve(batch_bytes + (1u << 20));
+        }
+        batch.clear();
+    }
     bool feed(const char *p, const char *end) {
         while (p < end) {
             const char *nl = (const char *)memchr(p, '\n', (size_t)(end - p));
@@ -123,8 +130,7 @@ struct FastqState {
                 batch.push_back('N');
                 if (batch.size() >= batch_bytes) {
                     if (!sink.take(std::move(batch))) return false;
-                    batch = std::string();
-                    batch.reserve(batch_bytes + (1u << 20));
+                    fresh();
                 }
             }
             line = (line + 1) & 3;
@@ -181,6 +187,7 @@ bool stream_plain_parallel(const char *data, size_t size, size_t batch_bytes, Re
         Locked(ReadSink &i, std::mutex &m) : inner(i), mu(m) {}
         bool operator()(const char *d, size_t l) override { std::lock_guard<std::mutex> lk(mu); return inner(d, l); }
         bool take(std::string &&b) override { std::lock_guard<std::mutex> lk(mu); return inner.take(std::move(b)); }
+        bool recycle(std::string &o) override { std::lock_guard<std::mutex> lk(mu); return inner.recycle(o); }
     };
     std::mutex local_mu;
     std::vector<std::thread> th;

@@ -71,6 +71,8 @@ struct ReadSink {
     virtual bool operator()(const char *data, size_t len) = 0;
     // a finished batch the producer no longer needs: sinks that keep batches override this to avoid a copy
     virtual bool take(std::string &&batch) { return (*this)(batch.data(), batch.size()); }
+    // a used buffer the sink can spare (keeps its capacity and its already-faulted pages); false if none
+    virtual bool recycle(std::string &out) { (void)out; return false; }
     // true if several parser threads may call the sink at the same time (else calls are serialised)
     virtual bool thread_safe() const { return false; }
     virtual ~ReadSink() {}

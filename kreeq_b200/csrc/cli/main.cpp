@@ -205,6 +205,18 @@ struct BatchQueue {
         can_put.wait(lk, [&] { return q.size() < kDepth; });
         q.push_back(std::move(b)); can_get.notify_one();
     }
+    // consumed batches go back to the parsers: their pages are mapped already, a fresh 128 MB string is not
+    std::vector<std::string> spare;
+    void give_back(std::string &&b) {
+        std::lock_guard<std::mutex> lk(mu);
+        if (spare.size() < 24) spare.push_back(std::move(b));
+    }
+    bool take_spare(std::string &out) {
+        std::lock_guard<std::mutex> lk(mu);
+        if (spare.empty()) return false;
+        out = std::move(spare.back()); spare.pop_back();
+        return true;
+    }
     bool get(std::string &b) {
         std::unique_lock<std::mutex> lk(mu);
         can_get.wait(lk, [&] { return !q.empty() || producers == 0; });
@@ -218,6 +230,7 @@ struct QueueSink : ReadSink {
     explicit QueueSink(BatchQueue &b) : bq(b) {}
     bool operator()(const char *data, size_t len) override { bq.put(std::string(data, len)); return true; }
     bool take(std::string &&batch) override { bq.put(std::move(batch)); return true; }
+    bool recycle(std::string &out) override { return bq.take_spare(out); }
     bool thread_safe() const override { return true; }     // the queue has its own lock
 };
 
@@ -241,8 +254,11 @@ bool count_files(kq_ctx *ctx, const std::vector<std::string> &files, std::string
             bq.can_get.notify_all();
         });
     std::string batch; int rc = KQ_OK;
-    while (bq.get(batch))
+    while (bq.get(batch)) {
         if (rc == KQ_OK) rc = kq_count_push(ctx, batch.data(), batch.size());      // keep draining after an error
+        bq.give_back(std::move(batch));
+        batch = std::string();
+    }
     for (auto &t : threads) t.join();
     g_feed_share = 1;
     if (rc != KQ_OK) die(ctx, rc);

@@ -55,8 +55,10 @@ int main(int argc, char **argv) {
     if (mode == "reads") {
         struct Digest : cli::ReadSink {
             std::mutex mu; uint64_t batches = 0, bytes = 0, seps = 0, digest = 0;
+            bool cheap = getenv("KQ_FEEDCHECK_CHEAP") != nullptr;      // throughput runs: count bytes only
             bool operator()(const char *d, size_t len) override {
                 uint64_t s = 0, h = 0; size_t a = 0;
+                if (cheap) { std::lock_guard<std::mutex> lk(mu); ++batches; bytes += len; return true; }
                 for (size_t i = 0; i <= len; ++i)
                     if (i == len || d[i] == 'N') { if (i > a) h += stretch_hash(d + a, i - a); if (i < len) ++s; a = i + 1; }
                 std::lock_guard<std::mutex> lk(mu);
@@ -64,6 +66,21 @@ int main(int argc, char **argv) {
                 return true;
             }
             bool thread_safe() const override { return getenv("KQ_FEEDCHECK_SERIAL") == nullptr; }
+            // like the command line's queue: batches are taken over and handed back for reuse once consumed
+            bool pool = getenv("KQ_FEEDCHECK_NOPOOL") == nullptr;
+            std::vector<std::string> spare;
+            bool take(std::string &&b) override {
+                const bool r = (*this)(b.data(), b.size());
+                if (pool) { std::string mine = std::move(b); std::lock_guard<std::mutex> lk(mu); if (spare.size() < 24) spare.push_back(std::move(mine)); }
+                else { std::string gone = std::move(b); }
+                return r;
+            }
+            bool recycle(std::string &out) override {
+                std::lock_guard<std::mutex> lk(mu);
+                if (spare.empty()) return false;
+                out = std::move(spare.back()); spare.pop_back();
+                return true;
+            }
         } sink;
         std::string err;
         const size_t batch = argc > 3 ? (size_t)atol(argv[3]) : (size_t)128 << 20;
