@@ -332,10 +332,10 @@ struct RunResult {
 };
 
 // Decodes from (start_bit, start_kind) until a block boundary that is one of `targets` (sorted by bit, all
-// beyond the start), or lies at/after `stop_after`, or the end of the file.
+// beyond the start), or lies at/after `stop_after`, or comes after `soft_out` symbols of output, or the end of the file.
 template <typename T>
 void decode_run(const uint8_t *gz, size_t size, uint64_t start_bit, uint8_t start_kind, const Target *targets,
-                size_t nt, uint64_t stop_after, OutBuf<T> &o, RunResult &r) {
+                size_t nt, uint64_t stop_after, OutBuf<T> &o, RunResult &r, size_t soft_out = SIZE_MAX) {
     const uint64_t total_bits = (uint64_t)size * 8;
     uint64_t b = start_bit; uint8_t kind = start_kind;
     bool first = true; size_t ti = 0;
@@ -344,7 +344,7 @@ void decode_run(const uint8_t *gz, size_t size, uint64_t start_bit, uint8_t star
     if (!o.reserve(kWindow + (1u << 16))) { r.why = "out of memory"; return; }
     for (;;) {
         if (!first) {
-            bool stop = b >= stop_after;
+            bool stop = b >= stop_after || o.produced() >= soft_out;
             while (ti < nt && targets[ti].bit < b) ++ti;
             for (size_t tj = ti; !stop && tj < nt && targets[tj].bit == b; ++tj) stop = targets[tj].kind == kind;
             if (stop) break;
@@ -582,6 +582,11 @@ bool inflate_parallel(const unsigned char *gz, size_t size, int threads, Sink &s
     // A run that expands more than this is given up on (a false start decoding noise, or extremely repetitive
     // data); the chain walk then decodes that stretch sequentially without a limit.
     const size_t spec_limit = kWindow + std::max<size_t>(C * 64, (size_t)4 << 20);
+    // Runs with a known window are not limited, but they hand over at the next block boundary once they have
+    // produced soft_out bytes, and a wave ends early once it holds wave_out bytes: memory stays bounded on
+    // inputs that expand a thousandfold (a 2 MiB chunk of a run of one base is 2 GB of output).
+    static const size_t soft_env = [] { const char *e = getenv("KQ_PGZ_SOFT_OUT"); const long long v = e ? atoll(e) : 0; return v > 0 ? (size_t)v : (size_t)0; }();
+    const size_t soft_out = soft_env ? soft_env : (size_t)256 << 20, wave_out = soft_out * 4;
 
     std::vector<uint8_t> window(kWindow, 0);
     uint64_t pos_bit = 0; uint8_t pos_kind = 1;
@@ -624,7 +629,7 @@ bool inflate_parallel(const unsigned char *gz, size_t size, int threads, Sink &s
                 c.bytes.limit = SIZE_MAX / 2;
                 if (!c.bytes.reserve(kWindow + 4 * C)) return;
                 memcpy(c.bytes.base, window.data(), kWindow);
-                decode_run(gz, size, c.start.bit, c.start.kind, t, nt, stop_after, c.bytes, c.res);
+                decode_run(gz, size, c.start.bit, c.start.kind, t, nt, stop_after, c.bytes, c.res, soft_out);
             } else {
                 c.spec.limit = spec_limit;
                 if (!c.spec.reserve(std::min(spec_limit, kWindow + 4 * C))) return;
@@ -656,7 +661,7 @@ bool inflate_parallel(const unsigned char *gz, size_t size, int threads, Sink &s
                 else while (ft < targets.size() && targets[ft].bit <= at) ++ft;
                 if (!f->bytes.reserve(kWindow + (1u << 16))) { err = "gzip: out of memory"; good = false; break; }
                 memcpy(f->bytes.base, window.data(), kWindow);
-                decode_run(gz, size, at, at_kind, targets.data() + ft, targets.size() - ft, stop_after, f->bytes, f->res);
+                decode_run(gz, size, at, at_kind, targets.data() + ft, targets.size() - ft, stop_after, f->bytes, f->res, soft_out);
                 ++st.fallbacks;
                 if (!f->res.ok) { err = std::string("gzip: ") + f->res.why; good = false; break; }
                 c = f;
@@ -667,7 +672,7 @@ bool inflate_parallel(const unsigned char *gz, size_t size, int threads, Sink &s
             total += c->n_out();
             at = c->res.end_bit; at_kind = c->res.end_kind;
             if (c->res.eof) { eof = true; break; }
-            if (at >= stop_after) break;
+            if (at >= stop_after || total >= wave_out) break;
         }
         if (!good) break;
         pos_bit = at; pos_kind = at_kind;

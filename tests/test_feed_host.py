@@ -115,6 +115,11 @@ def test_inflate_extreme_ratio_falls_back(tmp_path):
     out, info = inflate(f, threads=4, chunk=4_000)
     assert out == data
     assert info["fallbacks"] >= 1
+    # runs with a known window hand over after KQ_PGZ_SOFT_OUT bytes and waves end after four times that, so
+    # memory stays bounded however far the data expands; with a tiny bound the result is still the same
+    p = subprocess.run([TOOL, "inflate", str(f), "4", "0"], capture_output=True, timeout=300, env=dict(os.environ, KQ_PGZ_SOFT_OUT="200000"))
+    small = json.loads(p.stderr.decode().strip().splitlines()[-1])
+    assert p.returncode == 0 and p.stdout == data and small["pieces"] >= 5
 
 
 def test_inflate_random_binary_and_long_distances(tmp_path):
@@ -309,3 +314,39 @@ def test_fasta_loader_records_segments_gaps(tmp_path):
     for threads in ("1", "3", "8"):
         p = subprocess.run([TOOL, "genome", str(f)], capture_output=True, timeout=120, env=dict(os.environ, KQ_CLI_THREADS=threads))
         assert p.returncode == 0 and p.stdout == want, threads
+
+
+def test_inflate_fuzz_small_inputs(tmp_path):
+    """Seeded sweep over content types, compression parameters, member layouts, chunk sizes and thread counts on
+    small inputs (0 bytes ... 300 KB, sizes around the 32 KiB window), every result compared with zlib."""
+    rng = np.random.default_rng(77)
+    alphabet = [np.frombuffer(b"ACGT", dtype=np.uint8), np.frombuffer(b"ACGTN\n@+IIIIFFFF:,#", dtype=np.uint8), np.arange(256, dtype=np.uint8)]
+    sizes = [0, 1, 2, 100, 32767, 32768, 32769, 65536, 70001, 150_000, 300_000]
+    for case in range(40):
+        n = sizes[case % len(sizes)] if case < 22 else int(rng.integers(0, 300_000))
+        kind = int(rng.integers(0, 4))
+        if kind == 3:                                            # long repeats with occasional changes
+            unit = bytes(rng.choice(alphabet[0], size=int(rng.integers(1, 400))))
+            data = bytearray((unit * (n // max(1, len(unit)) + 1))[:n])
+            for p in rng.integers(0, max(1, n), size=min(n, 20)):
+                if n:
+                    data[int(p)] = int(rng.integers(0, 256))
+            data = bytes(data)
+        else:
+            data = bytes(rng.choice(alphabet[kind], size=n))
+        level = int(rng.integers(1, 10))
+        strategy = [zlib.Z_DEFAULT_STRATEGY, zlib.Z_FILTERED, zlib.Z_RLE, zlib.Z_FIXED][int(rng.integers(0, 4))]
+        nmembers = int(rng.integers(1, 5))
+        cuts = sorted(int(x) for x in rng.integers(0, n + 1, size=nmembers - 1)) if n else [0] * (nmembers - 1)
+        blob, prev = b"", 0
+        for c in cuts + [n]:
+            flush = int(rng.integers(0, 3))
+            blob += gz(data[prev:c], level, strategy, flush_every=[0, 4000, 9973][flush], flush_mode=[zlib.Z_FULL_FLUSH, zlib.Z_SYNC_FLUSH][case % 2])
+            prev = c
+        assert gzip.decompress(blob) == data
+        f = tmp_path / ("f%d.gz" % case)
+        f.write_bytes(blob)
+        chunk = int(rng.integers(64, 6000)) if case % 3 else 0
+        out, info = inflate(f, threads=int(rng.integers(1, 6)), chunk=chunk)
+        assert out == data, (case, n, kind, level, strategy, nmembers, chunk)
+        assert info["members"] == nmembers
