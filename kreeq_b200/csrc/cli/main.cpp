@@ -45,8 +45,8 @@ bool is_int(const char *s) {                      // isInt: optional sign + digi
 void require_file(const char *path) {             // ifFileExists, gfalibs/include/functions.h
     struct stat st;
     if (stat(path, &st) != 0) {
-        fprintf(stderr, "Error - file '%s' does not exist. Terminating.\n", path);
-        exit(EXIT_FAILURE);
+        std::cout << "Error - file does not exist: " << path << std::endl;   // on stdout, like the reference
+        exit(1);
     }
 }
 
@@ -377,7 +377,7 @@ int run_union(Options &o) {                       // Input::read case 1, src/inp
 
 int main(int argc, char **argv) {
     if (argc == 1 || argc == 2) {
-        printf("kreeq [mode]\n-h for additional help.\n\nModes:\nvalidate\nunion\n");
+        printf("kreeq [mode] -h\nfor additional help.\n\nModes:\nvalidate\nunion\n");   // src/main.cpp:40-47, without subgraph
         return EXIT_SUCCESS;
     }
     Options o;

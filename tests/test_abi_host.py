@@ -207,3 +207,21 @@ def test_cli_binary_usage_and_no_cpu_fallback(tmp_path):
         reads = os.path.join(GOLD, "inputs", "random1.fastq")
         p = subprocess.run([exe, "validate", "-r", reads], capture_output=True, cwd=str(tmp_path))
         assert p.returncode != 0 and p.stdout == b"" and p.stderr.strip()
+
+
+def test_cli_argument_errors_match_the_reference(tmp_path):
+    """Failures before any k-mer work (missing files, bad numbers) print what the reference prints, where it
+    prints it (ifFileExists writes to stdout, gfalibs/include/functions.h:260-272), with the same exit status."""
+    import subprocess
+    exe = os.path.join(ROOT, "kreeq_b200", "kreeq")
+    ref = os.path.join(ROOT, "oracle", "_ref", "kreeq")
+    p = subprocess.run([exe, "validate", "-f", "/nonexistent.fa"], capture_output=True, cwd=str(tmp_path))
+    assert p.returncode == 1 and p.stdout == b"Error - file does not exist: /nonexistent.fa\n"
+    assert subprocess.run([exe], capture_output=True).stdout.startswith(b"kreeq [mode] -h\nfor additional help.\n\nModes:\nvalidate\nunion\n")
+    if not os.path.exists(ref):
+        pytest.skip("oracle/_ref/kreeq not built")
+    for args in (["validate", "-f", "/nonexistent.fa"], ["validate", "-r", "/nonexistent.fq"], ["union", "-d", "a"], ["validate", "-d", "no.kreeq"],
+                 ["validate", "-c", "x"], ["validate", "-k"], ["validate", "-v"]):
+        a = subprocess.run([exe] + args, capture_output=True, cwd=str(tmp_path))
+        b = subprocess.run([ref] + args, capture_output=True, cwd=str(tmp_path))
+        assert (a.returncode, a.stdout) == (b.returncode, b.stdout), args
