@@ -91,6 +91,10 @@ bool read_file(const std::string &path, std::string &out, std::string &err) {
             if (!pgz::inflate_parallel(m.data, m.size, feed_threads(), sink, e, nullptr, pgz_chunk())) { err = e + " in " + path; return false; }
             return true;
         }
+        if (m.data && !(m.size >= 2 && m.data[0] == 0x1f && m.data[1] == 0x8b)) {   // plain file: one copy out of the mapping
+            out.assign((const char *)m.data, m.size);
+            return true;
+        }
     }
     GzReader r(path);
     if (!r.f) { err = "cannot open " + path; return false; }
