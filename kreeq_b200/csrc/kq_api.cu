@@ -979,7 +979,11 @@ extern "C" int kq_lookup_batch(kq_ctx *c, const uint64_t *keys, size_t n, kq_rec
     if (!n) return KQ_OK;
     CU(cudaSetDevice(c->device));
     if (c->pend_len || c->ovf_pending) { int rc = kq_sync(c); if (rc) return rc; }
-    uint64_t *dk = nullptr; Rec32 *dr = nullptr; uint8_t *df = nullptr;
+    struct Scratch {                                                   // freed on every way out, error returns included
+        uint64_t *dk = nullptr; Rec32 *dr = nullptr; uint8_t *df = nullptr;
+        ~Scratch() { cudaFree(dk); cudaFree(dr); cudaFree(df); }
+    } scratch;
+    uint64_t *&dk = scratch.dk; Rec32 *&dr = scratch.dr; uint8_t *&df = scratch.df;
     CU(cudaMalloc(&dk, n * 8)); CU(cudaMalloc(&dr, n * sizeof(Rec32))); CU(cudaMalloc(&df, n));
     CU(cudaMemcpyAsync(dk, keys, n * 8, cudaMemcpyHostToDevice, c->stream));
     CU(launch_lookup(c->stream, view(c), dk, n, dr, df, &c->launches));
@@ -988,7 +992,6 @@ extern "C" int kq_lookup_batch(kq_ctx *c, const uint64_t *keys, size_t n, kq_rec
     CU(cudaMemcpyAsync(found, df, n, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
     c->h2d += n * 8; c->d2h += n * (sizeof(Rec32) + 1);
-    cudaFree(dk); cudaFree(dr); cudaFree(df);
     for (size_t i = 0; i < n; ++i) if (found[i]) std::memcpy(&rec[i], &hr[i], sizeof(Rec32));
     return check_device_error(c);
 }
