@@ -1,0 +1,436 @@
+// kq_count3.cu -- the table side of the count pipeline: second scatter level and shared-memory insert.
+//
+// A table larger than 32 MiB is cut into slices of 2^12 slots (64 KiB): a key is probed inside its slice
+// only, so ONE CTA can own a slice while it counts into it.  The level-1 scatter (kq_kernels.cu) brings the
+// (key, edgeBit) tuples of a batch into COARSE order (2^cshift consecutive slices per bin); here
+//   fine_plan_kernel     cuts the coarse bins into tasks of at most `part` tuples,
+//   fine_hist_kernel     counts the tuples of every slice (shared-memory histogram per task),
+//   fine_scatter_kernel  brings them into slice order through shared-memory ring bins, a full chunk leaves
+//                        as ONE coalesced 256-byte store,
+//   smem_insert_kernel   per slice: the 64 KiB table piece comes in with ONE bulk async copy
+//                        (cp.async.bulk + mbarrier, SASS UBLKCP), the slice's tuples are counted with
+//                        shared-memory CAS (exact 7-bit lanes, same closed form as insert_instance), and
+//                        the piece goes back with one bulk store.
+// The table is streamed through the SMs exactly once per batch and no k-mer instance costs an L2 atomic
+// (the L2 CAS kernel insert_tuples_kernel sustains 35 G tuples/s on B200, profiles/r01c_ncu_insert_full.md).
+//
+// Reference semantics: DBG::processBuffers src/graph-builder.cpp:160-206 in closed form (exact sums; the
+// 8-bit / 32-bit split is decided when the database is written).
+#include "kq_kernels.h"
+
+#include <algorithm>
+
+namespace kq {
+
+namespace {
+
+template <int TW> __device__ __forceinline__ void t_unpack(const uint64_t *t, uint64_t i, uint64_t &key, uint32_t &e) {
+    if (TW == 1) { const uint64_t w = __ldcs(t + i); key = w >> 8; e = (uint32_t)w & 255u; }
+    else { const ulonglong2 w = __ldcs(reinterpret_cast<const ulonglong2 *>(t) + i); key = w.x; e = (uint32_t)w.y & 255u; }
+}
+template <int TW> __device__ __forceinline__ void t_store(uint64_t *t, uint64_t i, uint64_t key, uint32_t e) {
+    if (TW == 1) t[i] = (key << 8) | e;
+    else reinterpret_cast<ulonglong2 *>(t)[i] = make_ulonglong2(key, e);
+}
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+}  // namespace
+
+// ---- plan -------------------------------------------------------------------------------------------------
+
+// Coarse bin b of the level-1 output holds the tuples [start[b], start[b] + n[b]) of slices
+// [b << cshift, (b + 1) << cshift).  One task = at most `part` consecutive tuples of one coarse bin.
+__global__ void __launch_bounds__(1024, 1)
+fine_plan_kernel(TableView tv, unsigned ncoarse, const unsigned long long *start, const unsigned long long *n,
+                 unsigned long long part, FineTask *tasks, unsigned task_cap, unsigned *ntasks) {
+    __shared__ unsigned first[KQ_MAX_COARSE + 1];
+    for (unsigned b = threadIdx.x; b < ncoarse; b += 1024) first[b] = (unsigned)((n[b] + part - 1) / part);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned run = 0;
+        for (unsigned b = 0; b < ncoarse; ++b) { const unsigned v = first[b]; first[b] = run; run += v; }
+        first[ncoarse] = run;
+        *ntasks = run < task_cap ? run : task_cap;                    // task_cap is an upper bound by construction
+    }
+    __syncthreads();
+    for (unsigned b = threadIdx.x; b < ncoarse; b += 1024) {
+        const unsigned long long lo = start[b], hi = lo + n[b];
+        const unsigned s_lo = b << tv.cshift;
+        const unsigned ns = (unsigned)min((unsigned long long)(1u << tv.cshift), tv.nslices - s_lo);
+        unsigned t = first[b];
+        for (unsigned long long a = lo; a < hi && t < task_cap; a += part, ++t)
+            tasks[t] = FineTask{a, min(hi, a + part), s_lo, ns};
+    }
+}
+
+// ---- tuples per slice ---------------------------------------------------------------------------------------
+
+constexpr int FH_NT = 512;
+
+template <int TW>
+__global__ void __launch_bounds__(FH_NT, 2)
+fine_hist_kernel(TableView tv, const uint64_t *__restrict__ in, const FineTask *__restrict__ tasks,
+                 const unsigned *__restrict__ ntasks, unsigned long long *fhist) {
+    extern __shared__ unsigned int fh[];
+    const unsigned nt = *ntasks;
+    for (unsigned t = blockIdx.x; t < nt; t += gridDim.x) {
+        const FineTask tk = tasks[t];
+        for (unsigned i = threadIdx.x; i < tk.ns; i += FH_NT) fh[i] = 0;
+        __syncthreads();
+        for (unsigned long long i0 = tk.lo; i0 < tk.hi; i0 += FH_NT * 4) {
+            uint64_t key[4]; uint32_t e[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const unsigned long long i = i0 + (unsigned)j * FH_NT + threadIdx.x;
+                e[j] = 255u;
+                if (i < tk.hi) t_unpack<TW>(in, i, key[j], e[j]);
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                if (e[j] != 255u) atomicAdd(&fh[(unsigned)slice_of_key(key[j], tv.nslices) - tk.s_lo], 1u);
+        }
+        __syncthreads();
+        for (unsigned i = threadIdx.x; i < tk.ns; i += FH_NT)
+            if (fh[i]) atomicAdd(&fhist[tk.s_lo + i], (unsigned long long)fh[i]);
+        __syncthreads();
+    }
+}
+
+// ---- scatter into slice order ----------------------------------------------------------------------------------
+
+// Shared memory: `ns` ring bins of RING = 3/2 CAP tuples, an append counter and a flushed counter per bin.
+// A tuple is appended with one shared-memory atomic and one store; a bin that holds CAP tuples leaves as one
+// coalesced CAP * 8 * TW byte store at a position reserved with one global atomic on the slice's cursor.
+// The ring takes what arrives while a chunk waits for its flush, so a round of the CTA needs two barriers and
+// (practically) never a second pass.
+template <int TW, int NT, int R>
+__global__ void __launch_bounds__(NT, 1)
+fine_scatter_kernel(TableView tv, const uint64_t *__restrict__ in, const FineTask *__restrict__ tasks,
+                    const unsigned *__restrict__ ntasks, uint64_t *__restrict__ out, unsigned long long *cursor,
+                    unsigned ns_max, unsigned cap) {
+    extern __shared__ uint64_t sm3[];
+    const unsigned ring = cap + cap / 2;
+    uint64_t *bins = sm3;
+    unsigned int *fill = reinterpret_cast<unsigned int *>(bins + (size_t)ns_max * ring * TW);
+    unsigned int *done = fill + ns_max;
+    const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = NT / 32;
+    const unsigned nt = *ntasks;
+    for (unsigned t = blockIdx.x; t < nt; t += gridDim.x) {
+        const FineTask tk = tasks[t];
+        for (unsigned i = threadIdx.x; i < tk.ns; i += NT) { fill[i] = 0; done[i] = 0; }
+        __syncthreads();
+        for (unsigned long long tile = tk.lo; tile < tk.hi; tile += (unsigned long long)NT * R) {
+            uint64_t key[R]; uint32_t e[R]; unsigned bin[R], pos[R];
+            uint32_t m = 0;
+#pragma unroll
+            for (int i = 0; i < R; ++i) {
+                const unsigned long long j = tile + (unsigned)i * NT + threadIdx.x;
+                e[i] = 255u;
+                if (j < tk.hi) t_unpack<TW>(in, j, key[i], e[i]);
+            }
+#pragma unroll
+            for (int i = 0; i < R; ++i) {
+                if (e[i] == 255u) continue;                              // padding of the routed layout
+                bin[i] = (unsigned)slice_of_key(key[i], tv.nslices) - tk.s_lo;
+                pos[i] = atomicAdd(&fill[bin[i]], 1u);
+                m |= 1u << i;
+            }
+            for (;;) {
+                bool full = false;
+#pragma unroll
+                for (int i = 0; i < R; ++i) {
+                    if (!(m >> i & 1u)) continue;
+                    const unsigned d = pos[i] - *reinterpret_cast<volatile unsigned int *>(&done[bin[i]]);
+                    if (d < ring) { t_store<TW>(bins, (size_t)bin[i] * ring + pos[i] % ring, key[i], e[i]); m &= ~(1u << i); }
+                    full |= d + 1 >= cap;
+                }
+                if (!__syncthreads_or(full)) break;
+                // lane l of a warp looks at bin b0 + l; the reservations of the warp's 32 bins are issued together
+                for (unsigned b0 = warp * 32; b0 < tk.ns; b0 += nwarps * 32) {
+                    const unsigned b = b0 + lane;
+                    unsigned d0 = 0, chunks = 0;
+                    if (b < tk.ns) { d0 = done[b]; chunks = min(fill[b] - d0, ring) / cap; }
+                    unsigned long long g = 0;
+                    if (chunks) { g = atomicAdd(&cursor[tk.s_lo + b], (unsigned long long)chunks * cap); done[b] = d0 + chunks * cap; }
+                    unsigned todo = __ballot_sync(0xffffffffu, chunks != 0);
+                    while (todo) {
+                        const int l = __ffs(todo) - 1; todo &= todo - 1;
+                        const unsigned long long gg = __shfl_sync(0xffffffffu, g, l);
+                        const unsigned dd = __shfl_sync(0xffffffffu, d0, l);
+                        const unsigned nn = __shfl_sync(0xffffffffu, chunks, l) * cap;
+                        const uint64_t *srcw = bins + (size_t)(b0 + l) * ring * TW;
+                        uint64_t *dst = out + gg * TW;
+                        for (unsigned w = lane; w < nn * TW; w += 32)
+                            __stcs(dst + w, srcw[((dd + w / TW) % ring) * TW + w % TW]);
+                    }
+                }
+                if (!__syncthreads_or(m != 0)) break;                    // nobody had to wait for a flush
+            }
+        }
+        __syncthreads();
+        for (unsigned b0 = warp * 32; b0 < tk.ns; b0 += nwarps * 32) {       // what is left in the bins
+            const unsigned b = b0 + lane;
+            unsigned d0 = 0, f = 0;
+            if (b < tk.ns) { d0 = done[b]; f = fill[b] - d0; }
+            unsigned long long g = 0;
+            if (f) g = atomicAdd(&cursor[tk.s_lo + b], (unsigned long long)f);
+            unsigned todo = __ballot_sync(0xffffffffu, f != 0);
+            while (todo) {
+                const int l = __ffs(todo) - 1; todo &= todo - 1;
+                const unsigned long long gg = __shfl_sync(0xffffffffu, g, l);
+                const unsigned dd = __shfl_sync(0xffffffffu, d0, l);
+                const unsigned nn = __shfl_sync(0xffffffffu, f, l);
+                const uint64_t *srcw = bins + (size_t)(b0 + l) * ring * TW;
+                uint64_t *dst = out + gg * TW;
+                for (unsigned w = lane; w < nn * TW; w += 32)
+                    __stcs(dst + w, srcw[((dd + w / TW) % ring) * TW + w % TW]);
+            }
+        }
+        __syncthreads();
+    }
+}
+
+// ---- shared-memory insert -----------------------------------------------------------------------------------------
+
+namespace {
+
+__device__ __forceinline__ void mbar_init(uint64_t *bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, unsigned parity) {
+    asm volatile(
+        "{\n .reg .pred p;\n"
+        "KQ_WAIT_%=:\n"
+        " mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        " @p bra KQ_DONE_%=;\n"
+        " bra KQ_WAIT_%=;\n"
+        "KQ_DONE_%=:\n}"
+        ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// global -> shared bulk async copy, completion reported to the mbarrier in bytes
+__device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src, unsigned bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst_smem)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+// shared -> global bulk async copy (bulk group)
+__device__ __forceinline__ void bulk_s2g(void *dst, const void *src_smem, unsigned bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(smem_u32(src_smem)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// Count n = cov lane of `inc` instances of key (inc = their summed increments, every lane <= 32) into the
+// slice held in shared memory.  1 = new key, 0 = existed, -1 = the slice is full (nothing counted).
+__device__ __forceinline__ int smem_insert(Slot *piece, unsigned mask, const TableView &tv, uint64_t key, unsigned long long inc) {
+    const unsigned long long tag = key + 1;
+    const unsigned n = (unsigned)(inc >> 56);
+    unsigned j = (unsigned)mix64(key) & mask;
+    const unsigned limit = min(mask + 1, 1024u);                       // a longer run means the slice is (locally) full
+    int fresh = 0;
+    for (unsigned probes = 0; probes < limit; ++probes) {
+        unsigned long long *ptag = &piece[j].tag, *pcnt = &piece[j].cnt;
+        unsigned long long t = *reinterpret_cast<volatile unsigned long long *>(ptag);
+        if (t == 0) {
+            t = atomicCAS(ptag, 0ULL, tag);
+            if (t == 0) { t = tag; fresh = 1; }
+        }
+        if (t == tag) {
+            unsigned long long cur = *reinterpret_cast<volatile unsigned long long *>(pcnt);
+            for (;;) {
+                if (cnt_cov(cur) + n > KQ_LANE_MAX) {
+                    // move 63 of the coverage and up to 63 of every lane to the remainder table in the same CAS that
+                    // counts these instances (the slot stays >= KQ_REM_FLOOR: readers then look into R)
+                    uint32_t fw[4], bw[4];
+                    unsigned long long take = 63ull << 56;
+#pragma unroll
+                    for (int w = 0; w < 4; ++w) {
+                        fw[w] = min(cnt_lane(cur, w), 63u); bw[w] = min(cnt_lane(cur, 4 + w), 63u);
+                        take |= (unsigned long long)fw[w] << (7 * w) | (unsigned long long)bw[w] << (7 * (4 + w));
+                    }
+                    const unsigned long long old = atomicCAS(pcnt, cur, cur - take + inc);
+                    if (old == cur) { remainder_add(tv, key, 63, fw, bw); return fresh; }
+                    cur = old;
+                    continue;
+                }
+                const unsigned long long old = atomicCAS(pcnt, cur, cur + inc);   // lanes <= cov: no carry between lanes
+                if (old == cur) return fresh;
+                cur = old;
+            }
+        }
+        j = (j + 1) & mask;
+    }
+    return -1;
+}
+
+}  // namespace
+
+// One CTA per slice at a time (ticket counter; slices without tuples are skipped): bulk-load the slice,
+// count its tuples in shared memory, bulk-store it.  Three CTAs per SM overlap each other's copies.
+// Tuples of one key that sit next to each other in the stream (poly-A runs, satellites) are combined inside
+// the warp first, so a hot key costs one CAS per warp and not a CAS storm.
+template <int TW, int NT>
+__global__ void __launch_bounds__(NT, 3)
+smem_insert_kernel(TableView tv, const uint64_t *__restrict__ tuples, const unsigned long long *__restrict__ fstart,
+                   const unsigned long long *__restrict__ fcount, uint64_t *ovf, unsigned long long ovf_cap,
+                   unsigned long long *ovf_n, unsigned long long *ticket) {
+    extern __shared__ __align__(128) unsigned char sm_piece[];
+    __shared__ __align__(8) uint64_t bar;
+    __shared__ unsigned long long sh_ticket, sh_fresh;
+    Slot *piece = reinterpret_cast<Slot *>(sm_piece);
+    const unsigned slots = 1u << tv.slice_bits, mask = slots - 1, bytes = slots * (unsigned)sizeof(Slot);
+    const unsigned lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) { mbar_init(&bar, 1); sh_fresh = 0; asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+    __syncthreads();
+    unsigned parity = 0;
+    unsigned long long fresh = 0;
+    for (;;) {
+        if (threadIdx.x == 0) {
+            // next slice that has tuples (the counts are read by one thread: most slices of a small batch are empty)
+            unsigned long long s;
+            for (;;) { s = atomicAdd(ticket, 1ULL); if (s >= tv.nslices || fcount[s]) break; }
+            sh_ticket = s;
+            if (s < tv.nslices) { mbar_expect_tx(&bar, bytes); bulk_g2s(piece, tv.T + (s << tv.slice_bits), bytes, &bar); }
+        }
+        __syncthreads();
+        const unsigned long long s = sh_ticket;
+        if (s >= tv.nslices) break;
+        const unsigned long long a = fstart[s], n = fcount[s];
+        mbar_wait(&bar, parity); parity ^= 1;
+        for (unsigned long long i0 = 0; i0 < n; i0 += (unsigned long long)NT * 4) {
+            uint64_t key[4]; uint32_t e[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const unsigned long long i = i0 + (unsigned)j * NT + threadIdx.x;
+                e[j] = 255u; key[j] = ~0ULL - lane;                    // distinct dummies: no false match below
+                if (i < n) t_unpack<TW>(tuples, a + i, key[j], e[j]);
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const bool live = e[j] != 255u;
+                unsigned long long inc = live ? inc_of_edge(e[j]) : 0ULL;
+                // combine the instances of one key inside the warp (all 32 lanes take part: i0 is warp-uniform)
+                const unsigned peers = __match_any_sync(0xffffffffu, key[j]);
+                if (__any_sync(0xffffffffu, live && (peers & (peers - 1)))) {
+                    unsigned long long sum = 0;
+#pragma unroll
+                    for (int b = 0; b < 8; ++b) {
+                        const unsigned has = __ballot_sync(0xffffffffu, live && ((e[j] >> (7 - b)) & 1u));
+                        sum |= (unsigned long long)__popc(has & peers) << (7 * b);
+                    }
+                    sum |= (unsigned long long)__popc(peers) << 56;
+                    inc = lane == (unsigned)__ffs(peers) - 1 ? sum : 0ULL;   // the lowest lane of a group counts for it
+                }
+                if (!live || inc == 0) continue;
+                const int r = smem_insert(piece, mask, tv, key[j], inc);
+                if (r < 0) {                                              // slice full: keep the instances for after a grow
+                    const unsigned cnt = (unsigned)(inc >> 56);
+                    const unsigned long long q = atomicAdd(ovf_n, (unsigned long long)cnt);
+                    for (unsigned c = 0; c < cnt; ++c) {
+                        // a combined group goes back as single tuples: instance c carries edge b iff c < count of b
+                        uint32_t eb = 0;
+#pragma unroll
+                        for (int b = 0; b < 8; ++b) if (c < cnt_lane(inc, b)) eb |= 0x80u >> b;
+                        if (q + c < ovf_cap) t_store<TW>(ovf, q + c, key[j], eb);
+                    }
+                } else fresh += r;
+            }
+        }
+        __syncthreads();                                                  // every update is in the piece
+        if (threadIdx.x == 0) {
+            fence_async_smem();
+            bulk_s2g(tv.T + (s << tv.slice_bits), piece, bytes);
+            bulk_commit();
+            bulk_wait_read();                                             // the piece may be overwritten again
+        }
+    }
+    if (threadIdx.x == 0) bulk_wait_all();
+    // new keys of this CTA -> occupancy counter
+    for (int o = 16; o; o >>= 1) fresh += __shfl_xor_sync(0xffffffffu, fresh, o);
+    if (lane == 0 && fresh) atomicAdd(&sh_fresh, fresh);
+    __syncthreads();
+    if (threadIdx.x == 0 && sh_fresh) atomicAdd(&tv.occ[0], sh_fresh);
+}
+
+// ---- launchers -------------------------------------------------------------------------------------------------------
+
+#define KQ_TW_DISPATCH3(tw, CALL) do { if ((tw) == 1) { constexpr int TW = 1; CALL; } else { constexpr int TW = 2; CALL; } } while (0)
+
+static size_t fine_scatter_smem(unsigned ns_max, unsigned cap, int tw) {
+    return (size_t)ns_max * (cap + cap / 2) * tw * 8 + (size_t)ns_max * 8;
+}
+
+// flush chunk (tuples) of the level-2 scatter for bins of `ns_max` slices: the largest that fits shared memory
+unsigned fine_pick_cap(unsigned ns_max, int tw) {
+    static int max_smem = 0;
+    if (!max_smem) {
+        int dev = 0; cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+        if (max_smem <= 0) max_smem = 227 * 1024;
+    }
+    for (unsigned cap : {64u, 32u, 16u, 8u, 4u, 2u})
+        if (fine_scatter_smem(ns_max, cap, tw) <= (size_t)max_smem - 1024) return cap;
+    return 0;
+}
+
+cudaError_t launch_fine_plan(cudaStream_t st, const TableView &tv, unsigned ncoarse, const unsigned long long *start,
+                             const unsigned long long *n, unsigned long long part, FineTask *tasks, unsigned task_cap,
+                             unsigned *ntasks, uint64_t *launches) {
+    fine_plan_kernel<<<1, 1024, 0, st>>>(tv, ncoarse, start, n, part, tasks, task_cap, ntasks);
+    ++*launches;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_fine_hist(cudaStream_t st, const TableView &tv, const uint64_t *in, const FineTask *tasks,
+                             const unsigned *ntasks, unsigned task_bound, unsigned ns_max, unsigned long long *fhist,
+                             uint64_t *launches) {
+    if (!task_bound) return cudaSuccess;
+    const unsigned grid = std::min<unsigned>(task_bound, (unsigned)sm_count() * 2);
+    KQ_TW_DISPATCH3(tuple_words(tv.k), (fine_hist_kernel<TW><<<grid, FH_NT, (size_t)ns_max * 4, st>>>(tv, in, tasks, ntasks, fhist)));
+    ++*launches;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_fine_scatter(cudaStream_t st, const TableView &tv, const uint64_t *in, const FineTask *tasks,
+                                const unsigned *ntasks, unsigned task_bound, unsigned ns_max, uint64_t *out,
+                                unsigned long long *cursor, uint64_t *launches) {
+    if (!task_bound) return cudaSuccess;
+    const int tw = tuple_words(tv.k);
+    const unsigned cap = fine_pick_cap(ns_max, tw);
+    if (!cap) return cudaErrorInvalidConfiguration;
+    const size_t smem = fine_scatter_smem(ns_max, cap, tw);
+    const unsigned grid = std::min<unsigned>(task_bound, (unsigned)sm_count());
+    cudaError_t e;
+#define KQ_FS_LAUNCH(TWV) do {                                                                                         \
+        e = cudaFuncSetAttribute(fine_scatter_kernel<TWV, 1024, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+        if (e != cudaSuccess) return e;                                                                                \
+        fine_scatter_kernel<TWV, 1024, 2><<<grid, 1024, smem, st>>>(tv, in, tasks, ntasks, out, cursor, ns_max, cap); } while (0)
+    if (tw == 1) KQ_FS_LAUNCH(1); else KQ_FS_LAUNCH(2);
+#undef KQ_FS_LAUNCH
+    ++*launches;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_smem_insert(cudaStream_t st, const TableView &tv, const uint64_t *tuples, const unsigned long long *fstart,
+                               const unsigned long long *fcount, uint64_t *ovf, unsigned long long ovf_cap,
+                               unsigned long long *ovf_n, unsigned long long *ticket, uint64_t *launches) {
+    cudaError_t e = cudaMemsetAsync(ticket, 0, sizeof(unsigned long long), st);
+    if (e != cudaSuccess) return e;
+    const size_t smem = sizeof(Slot) << tv.slice_bits;
+    const unsigned grid = (unsigned)std::min<unsigned long long>(tv.nslices, (unsigned long long)sm_count() * 3);
+#define KQ_SI_LAUNCH(TWV) do {                                                                                         \
+        e = cudaFuncSetAttribute(smem_insert_kernel<TWV, KQ_S3_NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+        if (e != cudaSuccess) return e;                                                                                \
+        smem_insert_kernel<TWV, KQ_S3_NT><<<grid, KQ_S3_NT, smem, st>>>(tv, tuples, fstart, fcount, ovf, ovf_cap, ovf_n, ticket); } while (0)
+    if (tuple_words(tv.k) == 1) KQ_SI_LAUNCH(1); else KQ_SI_LAUNCH(2);
+#undef KQ_SI_LAUNCH
+    ++*launches;
+    return cudaGetLastError();
+}
+
+}  // namespace kq

@@ -23,7 +23,9 @@ namespace kq {
 constexpr uint32_t KQ_LANE_MAX = 127u;         // a slot lane counts to 127, the rest lives in R
 constexpr uint32_t KQ_REM_FLOOR = 64u;         // counted slots that own a remainder never drop below this coverage
 constexpr uint32_t KQ_LARGEST = 4294967295u;   // LARGEST, include/kreeq.h:68
-constexpr int KQ_MAX_SLICE_BITS = 21;          // 2^21 slots x 16 B = 32 MiB per slice
+constexpr int KQ_MAX_SLICE_BITS = 21;          // a table of up to 2^21 slots (32 MiB, L2 resident) is ONE slice
+constexpr int KQ_PIECE_BITS = 12;              // larger tables: slices of 2^12 slots = 64 KiB, one CTA's shared memory
+constexpr int KQ_MAX_COARSE = 4096;            // bins of the level-1 scatter at most
 
 constexpr unsigned long long CNT_PLACEHOLDER = 1ull << 63;
 constexpr unsigned long long CNT_COV_ONE = 1ull << 56;
@@ -48,6 +50,7 @@ struct Base  { uint32_t fw, bw, cov; uint8_t isFw, pad[3]; }; // == kq_base
 // what every kernel needs to know about the resident database
 struct TableView {
     Slot *T; unsigned long long nslices; int slice_bits;
+    int cshift;                    // count pipeline: 2^cshift consecutive slices form one bin of the level-1 scatter
     SideSlot *R; unsigned long long rcap;      // remainders
     SideSlot *M; unsigned long long mcap;      // literal maps32 entries
     unsigned long long *occ;       // [0] slots claimed in T, [1] in R, [2] in M

@@ -23,6 +23,30 @@ constexpr int TPB = 256;          // threads per CTA of the grid-stride kernels
 constexpr int CTAS_PER_SM = 6;
 constexpr int RUN = 8;            // consecutive k-mer start positions one thread extracts per round
 
+// Tuning knobs: process-wide, read ONCE from the KQ_* environment variables (first use) and changeable through
+// kq_set_tuning; no kernel launcher and no per-batch function reads the environment.
+Tuning &tuning() {
+    static Tuning t = [] {
+        auto num = [](const char *name, long dflt) { const char *e = std::getenv(name); return e && *e ? std::atol(e) : dflt; };
+        Tuning v;
+        v.scatter_cap = (int)num("KQ_SCATTER_CAP", 0);
+        v.rt_variant = (int)num("KQ_RT_VARIANT", 0);
+        v.sc_variant = (int)num("KQ_SC_VARIANT", 0);
+        { const char *e = std::getenv("KQ_SCATTER"); v.scatter_direct = e && e[0] == 'd'; }
+        v.insert_ctas = (int)num("KQ_INSERT_CTAS", 8); if (v.insert_ctas < 1 || v.insert_ctas > 8) v.insert_ctas = 8;
+        v.validate_ctas = (int)num("KQ_VALIDATE_CTAS", 8); if (v.validate_ctas < 1 || v.validate_ctas > 8) v.validate_ctas = 8;
+        v.single_slice_bits = (int)num("KQ_SINGLE_SLICE_BITS", KQ_MAX_SLICE_BITS);
+        if (v.single_slice_bits < 8 || v.single_slice_bits > 26) v.single_slice_bits = KQ_MAX_SLICE_BITS;
+        v.piece_bits = (int)num("KQ_PIECE_BITS", KQ_PIECE_BITS); if (v.piece_bits < 6 || v.piece_bits > 13) v.piece_bits = KQ_PIECE_BITS;
+        v.part = (unsigned long long)num("KQ_FINE_PART", 1 << 18); if (v.part < 64) v.part = 64;
+        v.smem_insert = (int)num("KQ_SMEM_INSERT", 1);
+        v.direct_pct = (int)num("KQ_DIRECT_PCT", 25);
+        { const char *e = std::getenv("KQ_DB_HOST"); v.db_host = e && e[0] == '1'; }
+        return v;
+    }();
+    return t;
+}
+
 int sm_count() {
     static int n = 0;
     if (!n) {
@@ -167,14 +191,14 @@ count_direct_kernel(TableView tv, Source src, unsigned long long *instances,
 // tuples in bin order are in slice order on the table that receives them, whatever its geometry.
 template <bool RT>
 __device__ __forceinline__ unsigned bin_of_key(const TableView &tv, const RouteMap &rt, uint64_t key) {
-    if (!RT) return (unsigned)slice_of_key(key, tv.nslices);
+    if (!RT) return (unsigned)(slice_of_key(key, tv.nslices) >> tv.cshift);
     const unsigned owner = (unsigned)(key & 127u) >> rt.shift;
     const uint64_t h = (uint32_t)((key * 0x9E3779B97F4A7C15ULL) >> 32);
     return (owner << rt.nb_bits) | (unsigned)(h >> (32 - rt.nb_bits));
 }
 template <bool RT>
 __device__ __forceinline__ unsigned bin_count(const TableView &tv, const RouteMap &rt) {
-    return RT ? (unsigned)rt.nranks << rt.nb_bits : (unsigned)tv.nslices;
+    return RT ? (unsigned)rt.nranks << rt.nb_bits : (unsigned)(((tv.nslices - 1) >> tv.cshift) + 1);
 }
 
 template <int TW, bool RT>
@@ -201,7 +225,7 @@ slice_hist_kernel(TableView tv, Source src, unsigned long long *hist, RouteMap r
 
 __global__ void __launch_bounds__(1024, 1)
 slice_offsets_kernel(unsigned long long nslices, const unsigned long long *hist, unsigned long long *cursor,
-                     unsigned long long *total, unsigned long long *instances) {
+                     unsigned long long *start, unsigned long long *total, unsigned long long *instances) {
     __shared__ unsigned long long part[1024];
     const unsigned long long per = (nslices + 1023) / 1024;
     const unsigned long long b = threadIdx.x * per, e = min(nslices, b + per);
@@ -216,7 +240,7 @@ slice_offsets_kernel(unsigned long long nslices, const unsigned long long *hist,
     }
     __syncthreads();
     s = part[threadIdx.x];
-    for (unsigned long long i = b; i < e; ++i) { cursor[i] = s; s += hist[i]; }
+    for (unsigned long long i = b; i < e; ++i) { cursor[i] = s; if (start) start[i] = s; s += hist[i]; }
 }
 
 // Routed pipeline: H[s][b] = tuples rank s sends into global bin b = (owner d, j).  Destination d lays its
@@ -367,7 +391,7 @@ slice_scatter_direct_kernel(TableView tv, Source src, uint64_t *__restrict__ out
         const uint32_t m = produce<TW>(src, tv, tile, total, key, e);
 #pragma unroll
         for (int i = 0; i < RUN; ++i)
-            if (m >> i & 1u) at[i] = atomicAdd(&cursor[slice_of_key(key[i], tv.nslices)], 1ULL);
+            if (m >> i & 1u) at[i] = atomicAdd(&cursor[slice_of_key(key[i], tv.nslices) >> tv.cshift], 1ULL);
 #pragma unroll
         for (int i = 0; i < RUN; ++i)
             if (m >> i & 1u) tuple_store<TW>(out, at[i], key[i], e[i]);
@@ -529,10 +553,8 @@ int scatter_pick_cap(unsigned long long nslices, int tw, int max_cap) {
         if (max_smem <= 0) max_smem = 227 * 1024;
         if (sm_smem <= 0) sm_smem = 228 * 1024;
     }
-    if (const char *e = std::getenv("KQ_SCATTER_CAP")) {              // tuning knob
-        const int cap = std::atoi(e);
-        if (cap > 0 && cap <= max_cap && scatter_smem_bytes(nslices, cap, tw) <= (size_t)max_smem - 1024) return cap;
-    }
+    if (const int cap = tuning().scatter_cap)                          // tuning knob
+        if (cap <= max_cap && scatter_smem_bytes(nslices, cap, tw) <= (size_t)max_smem - 1024) return cap;
     // a tile brings NT * R = 8192 tuples: with few bins a small capacity would overflow several times per
     // tile (each time costs a round of barriers), so take the largest power of two that fits
     for (int cap : {512, 256, 128, 64, 32, 16, 8})
@@ -560,7 +582,7 @@ cudaError_t launch_slice_hist(cudaStream_t st, const TableView &tv, const Source
     const uint64_t n = source_bound(src);
     if (!n) return cudaSuccess;
     const unsigned grid = std::min<uint64_t>((n + TPB * RUN - 1) / (TPB * RUN), (uint64_t)sm_count() * 4);
-    const size_t smem = (size_t)tv.nslices * 4;
+    const size_t smem = (size_t)coarse_bins(tv) * 4;
     KQ_TW_DISPATCH(tuple_words(tv.k), (slice_hist_kernel<TW, false><<<grid, TPB, smem, st>>>(tv, src, hist, RouteMap{})));
     ++*launches;
     return cudaGetLastError();
@@ -603,7 +625,7 @@ cudaError_t launch_route_scatter(cudaStream_t st, const TableView &tv, const Sou
         if (e != cudaSuccess) return e;                                                                             \
         const unsigned grid = std::min<uint64_t>((n + NTV * RV - 1) / (NTV * RV), (uint64_t)sm_count());           \
         slice_scatter_kernel<TWV, RV, NTV, true><<<grid, NTV, smem, st>>>(v, src, nullptr, cursor, cap, rt, back); } while (0)
-    static const int variant = [] { const char *e = std::getenv("KQ_RT_VARIANT"); return e ? std::atoi(e) : 0; }();   // tuning knob
+    const int variant = tuning().rt_variant;
     if (tw == 1) {
         if (variant == 1) KQ_ROUTE_LAUNCH(1, 8, 1024);
         else if (variant == 2) KQ_ROUTE_LAUNCH(1, 8, 512);
@@ -616,9 +638,9 @@ cudaError_t launch_route_scatter(cudaStream_t st, const TableView &tv, const Sou
 }
 
 cudaError_t launch_slice_offsets(cudaStream_t st, unsigned long long nslices, const unsigned long long *hist,
-                                 unsigned long long *cursor, unsigned long long *total, unsigned long long *instances,
-                                 uint64_t *launches) {
-    slice_offsets_kernel<<<1, 1024, 0, st>>>(nslices, hist, cursor, total, instances);
+                                 unsigned long long *cursor, unsigned long long *start, unsigned long long *total,
+                                 unsigned long long *instances, uint64_t *launches) {
+    slice_offsets_kernel<<<1, 1024, 0, st>>>(nslices, hist, cursor, start, total, instances);
     ++*launches;
     return cudaGetLastError();
 }
@@ -628,15 +650,14 @@ cudaError_t launch_slice_scatter(cudaStream_t st, const TableView &tv, const Sou
     const uint64_t n = source_bound(src);
     if (!n) return cudaSuccess;
     const int tw = tuple_words(tv.k);
-    static const bool direct = [] { const char *e = std::getenv("KQ_SCATTER"); return e && e[0] == 'd'; }();
-    if (direct) {
+    if (tuning().scatter_direct) {
         const unsigned g = std::min<uint64_t>((n + TPB * RUN - 1) / (TPB * RUN), (uint64_t)sm_count() * 4);
         KQ_TW_DISPATCH(tw, (slice_scatter_direct_kernel<TW><<<g, TPB, 0, st>>>(tv, src, out, cursor)));
         ++*launches;
         return cudaGetLastError();
     }
-    const size_t smem = scatter_smem_bytes(tv.nslices, cap, tw);
-    static const int variant = [] { const char *e = std::getenv("KQ_SC_VARIANT"); return e ? std::atoi(e) : 0; }();
+    const size_t smem = scatter_smem_bytes(coarse_bins(tv), cap, tw);
+    const int variant = tuning().sc_variant;
     cudaError_t e = cudaSuccess;
 #define KQ_SCATTER_LAUNCH(TWV, RV, NTV) do {                                                                        \
         e = cudaFuncSetAttribute(slice_scatter_kernel<TWV, RV, NTV, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
@@ -664,7 +685,7 @@ cudaError_t launch_insert_tuples(cudaStream_t st, const TableView &tv, const uin
     if (e != cudaSuccess) return e;
     // 8 CTAs of 256 threads = every thread slot of the SM (32 registers, a few spilled words): the kernel waits on
     // L2 round trips and its rate follows the warps in flight (3/4/5/6/7/8 CTAs: 125/101/86/76/70/67 ms on C2)
-    static const int ctas = [] { const char *e = std::getenv("KQ_INSERT_CTAS"); const int v = e ? std::atoi(e) : 0; return v >= 1 && v <= 8 ? v : 8; }();   // tuning knob
+    const int ctas = tuning().insert_ctas;
     const unsigned grid = (unsigned)std::min<uint64_t>((n_max + INS_TILE - 1) / INS_TILE, (uint64_t)sm_count() * ctas);
     if (ctas > CTAS_PER_SM) KQ_TW_DISPATCH(tuple_words(tv.k), (insert_tuples_kernel<TW, 8><<<grid, TPB, 0, st>>>(tv, tuples, n, ovf, ovf_cap, ovf_n, ticket)));
     else KQ_TW_DISPATCH(tuple_words(tv.k), (insert_tuples_kernel<TW, CTAS_PER_SM><<<grid, TPB, 0, st>>>(tv, tuples, n, ovf, ovf_cap, ovf_n, ticket)));
@@ -685,7 +706,7 @@ cudaError_t launch_validate(cudaStream_t st, const TableView &tv, const uint64_t
                             uint64_t base0, uint64_t c0, uint64_t n, uint64_t kcount, uint32_t cutoff,
                             Base *out, unsigned long long *acc3, const TableView *peers, int npeers, uint64_t *launches) {
     if (!n) return cudaSuccess;
-    static const int ctas = [] { const char *e = std::getenv("KQ_VALIDATE_CTAS"); const int v = e ? std::atoi(e) : 0; return v >= 1 && v <= 8 ? v : 8; }();   // tuning knob (8: 0.42 ms, 6: 0.45 ms per 1e7 positions)
+    const int ctas = tuning().validate_ctas;                         // 8: 0.42 ms, 6: 0.45 ms per 1e7 positions
     const unsigned grid = (unsigned)std::min<uint64_t>((n + TPB - 1) / TPB, (uint64_t)sm_count() * ctas);
     if (ctas > CTAS_PER_SM) validate_kernel<8><<<grid, TPB, 0, st>>>(tv, B, M, base0, c0, n, kcount, cutoff, out, acc3, peers, npeers);
     else validate_kernel<CTAS_PER_SM><<<grid, TPB, 0, st>>>(tv, B, M, base0, c0, n, kcount, cutoff, out, acc3, peers, npeers);

@@ -48,6 +48,20 @@ struct RouteMap {
 };
 
 int sm_count();   // multiprocessors of the current device (cached)
+
+// tuning knobs (defaults are the measured best on B200); kq_set_tuning changes them
+struct Tuning {
+    int scatter_cap;           // bin capacity of the level-1 scatter (0 = largest that fits)
+    int rt_variant, sc_variant, scatter_direct;
+    int insert_ctas, validate_ctas;
+    int single_slice_bits;     // a table of up to 2^this slots is one slice (fused extract + insert)
+    int piece_bits;            // larger tables: log2 slots per slice
+    unsigned long long part;   // tuples per task of the level-2 kernels
+    int smem_insert;           // 0 = count with L2 CAS (insert_tuples_kernel) also on multi-slice tables
+    int direct_pct;            // batches below this share of the table's slots skip the sweep (fused kernel)
+    int db_host;               // .kreeq codec on the host (cross-check of the device codec)
+};
+Tuning &tuning();
 // shared memory the scatter kernel needs for `nslices` bins of `cap` tuples; 0 if it cannot fit
 size_t scatter_smem_bytes(unsigned long long nslices, int cap, int tw);
 int scatter_pick_cap(unsigned long long nslices, int tw, int max_cap = 512);   // largest power of two <= max_cap that fits, 0 = none
@@ -63,10 +77,11 @@ cudaError_t launch_count_direct(cudaStream_t st, const TableView &tv, const Sour
 // 1. tuples per slice -> hist[nslices]
 cudaError_t launch_slice_hist(cudaStream_t st, const TableView &tv, const Source &src, unsigned long long *hist,
                               uint64_t *launches);
-// 2. exclusive scan: cursor[p] = first tuple index of slice p; *total = number of tuples; *instances += total
-cudaError_t launch_slice_offsets(cudaStream_t st, unsigned long long nslices, const unsigned long long *hist,
-                                 unsigned long long *cursor, unsigned long long *total, unsigned long long *instances,
-                                 uint64_t *launches);
+// 2. exclusive scan: cursor[p] = start[p] = first tuple index of bin p (start may be NULL; cursor is advanced by
+//    the scatter, start is not); *total = number of tuples; *instances += total
+cudaError_t launch_slice_offsets(cudaStream_t st, unsigned long long nbins, const unsigned long long *hist,
+                                 unsigned long long *cursor, unsigned long long *start, unsigned long long *total,
+                                 unsigned long long *instances, uint64_t *launches);
 // 3. scatter tuples into slice order (out holds *total tuples afterwards)
 cudaError_t launch_slice_scatter(cudaStream_t st, const TableView &tv, const Source &src, uint64_t *out,
                                  unsigned long long *cursor, int cap, uint64_t *launches);
@@ -76,6 +91,29 @@ cudaError_t launch_insert_tuples(cudaStream_t st, const TableView &tv, const uin
                                  const unsigned long long *n, uint64_t n_max, uint64_t *ovf,
                                  unsigned long long ovf_cap, unsigned long long *ovf_n, unsigned long long *ticket,
                                  uint64_t *launches);
+// ---- level 2 + shared-memory insert (kq_count3.cu) --------------------------------------------------------
+// bins of the level-1 scatter: 2^cshift consecutive slices each
+inline unsigned coarse_bins(const TableView &tv) { return (unsigned)(((tv.nslices - 1) >> tv.cshift) + 1); }
+// at most `part` consecutive tuples [lo, hi) of the level-1 output whose keys live in slices [s_lo, s_lo + ns)
+struct FineTask { unsigned long long lo, hi; unsigned s_lo, ns; };
+constexpr int KQ_S3_NT = 512;                 // threads per CTA of the shared-memory insert
+unsigned fine_pick_cap(unsigned ns_max, int tw);   // flush chunk of the level-2 scatter, 0 = bins do not fit
+cudaError_t launch_fine_plan(cudaStream_t st, const TableView &tv, unsigned ncoarse, const unsigned long long *start,
+                             const unsigned long long *n, unsigned long long part, FineTask *tasks, unsigned task_cap,
+                             unsigned *ntasks, uint64_t *launches);
+// fhist[s] += tuples of slice s
+cudaError_t launch_fine_hist(cudaStream_t st, const TableView &tv, const uint64_t *in, const FineTask *tasks,
+                             const unsigned *ntasks, unsigned task_bound, unsigned ns_max, unsigned long long *fhist,
+                             uint64_t *launches);
+// out = tuples in slice order (cursor[s] = first tuple index of slice s, advanced)
+cudaError_t launch_fine_scatter(cudaStream_t st, const TableView &tv, const uint64_t *in, const FineTask *tasks,
+                                const unsigned *ntasks, unsigned task_bound, unsigned ns_max, uint64_t *out,
+                                unsigned long long *cursor, uint64_t *launches);
+// count the tuples [fstart[s], fstart[s] + fcount[s]) of every slice s in shared memory
+cudaError_t launch_smem_insert(cudaStream_t st, const TableView &tv, const uint64_t *tuples, const unsigned long long *fstart,
+                               const unsigned long long *fcount, uint64_t *ovf, unsigned long long ovf_cap,
+                               unsigned long long *ovf_n, unsigned long long *ticket, uint64_t *launches);
+
 // routed pipeline, steps 1-3: hist[nranks << nb_bits] of this rank's tuples; from the all-gathered
 // histograms H[nranks][P] the start of this rank's tuples inside every destination bin (cursor[P]) and what
 // every rank receives (recv[d] = extent of d's slab with the alignment padding, recv[nranks + d] = real
