@@ -410,7 +410,7 @@ def main_ours(args):
         barrier()
         c0 = g.counters()
         g.set_timing(True)
-        for w in range(4):
+        for w in range(7):
             g.kernel_time_ms(w)
         sampler = ClockSampler(local); sampler.start()
         evs = [step_fn() for _ in range(steps)]
@@ -420,6 +420,7 @@ def main_ours(args):
         kt_val, kn_val = g.kernel_time_ms(1)
         kt_pipe, kn_pipe = g.kernel_time_ms(0)
         kt_scat, kn_scat = g.kernel_time_ms(3)
+        kt_l2, _ = g.kernel_time_ms(4); kt_s1, _ = g.kernel_time_ms(5); kt_s2, _ = g.kernel_time_ms(6)
         g.set_timing(False)
         c1 = g.counters()
         tc = sum(a.elapsed_time(b) for a, b, _ in evs) / steps
@@ -431,7 +432,8 @@ def main_ours(args):
                 "launches": c1["kernel_launches"] - c0["kernel_launches"],
                 "h2d": (c1["h2d_bytes"] - c0["h2d_bytes"]) / steps, "d2h": (c1["d2h_bytes"] - c0["d2h_bytes"]) / steps,
                 "kt_count": kt_count, "kn_count": kn_count, "kt_val": kt_val, "kn_val": kn_val,
-                "kt_pipe": kt_pipe, "kn_pipe": kn_pipe, "kt_scat": kt_scat, "kn_scat": kn_scat}
+                "kt_pipe": kt_pipe, "kn_pipe": kn_pipe, "kt_scat": kt_scat, "kn_scat": kn_scat,
+                "kt_l2": kt_l2, "kt_s1": kt_s1, "kt_s2": kt_s2}
 
     res = run(step_resident, args.warmup, args.steps)
     inst_total = inst_per_rank * world
@@ -470,6 +472,9 @@ def main_ours(args):
                             "avg_launch_ms": per_launch_s * 1e3, "launches_timed": res["kn_count"],
                             "share_of_count_ms": res["kt_count"] / args.steps / res["count_ms"],
                             "hist_scatter_ms_per_step": res["kt_scat"] / args.steps,
+                            "kernels_ms_per_step": {"level1_hist": (res["kt_scat"] - res["kt_s1"]) / args.steps, "level1_scatter": res["kt_s1"] / args.steps,
+                                                    "level2_hist": (res["kt_l2"] - res["kt_s2"]) / args.steps, "level2_scatter": res["kt_s2"] / args.steps,
+                                                    "insert": res["kt_count"] / args.steps},
                             "pipeline_ms_per_step": res["kt_pipe"] / args.steps}
         if res["kn_val"]:
             vs = res["kt_val"] * 1e-3 / res["kn_val"]

@@ -12,6 +12,8 @@
  * returns 0 or a negative KQ_E* code and never exit()s; kq_last_error() gives
  * the message.  There is NO CPU fallback: without a usable CUDA device
  * kq_create fails with KQ_ENODEV.
+ * Threads: a handle may be driven by ONE thread at a time; different handles (one per GPU) may be driven by
+ * different threads concurrently (the host pool the library packs and writes files with serialises its callers).
  * One handle = one GPU = one shard of the key space.  Multi-GPU = one process
  * (or handle) per GPU, kq_set_shard(rank, nranks), with tuples routed by
  * kq_owner_of().
@@ -228,11 +230,19 @@ int  kq_reserve(kq_ctx *ctx, uint64_t extra_distinct);
  * kq_count_finish / kq_sync, and before anything that reads the table. */
 int  kq_set_flush_positions(kq_ctx *ctx, uint64_t positions);
 
+/* process-wide tuning knobs (defaults: measured best on B200; the KQ_* environment variables are read
+ * once, at first use): "single_slice_bits" (a table of up to 2^v slots is one slice), "piece_bits" (log2 slots per
+ * slice of larger tables), "fine_part", "smem_insert" (0: count with L2 CAS), "direct_pct", "scatter_cap",
+ * "insert_ctas", "validate_ctas", "db_host".  Geometry knobs apply to tables created or grown afterwards. */
+int  kq_set_tuning(const char *name, long long value);
+
 /* counters for bench.py: kernels launched by this handle, bytes copied */
 int  kq_counters(kq_ctx *ctx, uint64_t *kernel_launches, uint64_t *h2d_bytes, uint64_t *d2h_bytes);
 /* CUDA-event time (ms) on the launching stream since the last call with reset=1:
  * which = 0 whole count pipeline (per batch), 1 validate/probe kernel, 2 insert kernel,
- * 3 slice histogram + scatter (or extract_route / kq_route_hist + kq_route_scatter).  Only measured when kq_set_timing(ctx,1). */
+ * 3 level-1 histogram + scatter (or extract_route / kq_route_hist + kq_route_scatter), 4 level-2 histogram + scatter,
+ * 5 the level-1 scatter kernel alone, 6 the level-2 scatter kernel alone.
+ * Only measured when kq_set_timing(ctx,1). */
 int  kq_set_timing(kq_ctx *ctx, int on);
 int  kq_kernel_time_ms(kq_ctx *ctx, int which, double *ms, uint64_t *launches, int reset);
 

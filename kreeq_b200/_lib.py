@@ -72,6 +72,7 @@ PROTOTYPES = {
     "kq_dev_extract_route": (_i, [_vp, _vp, _vp, _u64, _u64, _u64, _vp, _u64, _vp]),
     "kq_dev_insert_tuples": (_i, [_vp, _vp, _u64]),
     "kq_set_flush_positions": (_i, [_vp, _u64]),
+    "kq_set_tuning": (_i, [_cp, C.c_longlong]),
     "kq_route_setup": (_i, [_vp, _u64, _i, C.POINTER(_vp), _vp]),
     "kq_route_open": (_i, [_vp, _vp, C.POINTER(_vp)]),
     "kq_route_connect": (_i, [_vp, C.POINTER(_vp)]),

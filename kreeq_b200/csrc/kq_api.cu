@@ -36,7 +36,8 @@ constexpr uint64_t MIN_SLOTS = 1ull << 12;
 constexpr uint64_t MIN_SCAP = 1ull << 12;
 constexpr uint64_t OVF_CAP = 4ull << 20;         // tuples kept when their slice is full
 constexpr uint64_t DEFAULT_FLUSH = 1ull << 29;   // pending k-mer start positions that trigger the pipeline
-constexpr int NTIMERS = 4;                       // 0 count pipeline, 1 validate, 2 insert kernel, 3 hist + scatter
+constexpr int NTIMERS = 7;                       // 0 count pipeline, 1 validate, 2 insert kernel, 3 level-1 hist + scatter, 4 level-2 hist + scatter,
+                                                 // 5 level-1 scatter kernel alone, 6 level-2 scatter kernel alone
 
 thread_local std::string g_create_error;
 
@@ -55,7 +56,7 @@ struct TimedRange { cudaEvent_t a, b; int which; };
 struct kq_ctx {
     int k = 0, device = 0;
     cudaStream_t own_stream = nullptr, stream = nullptr;
-    Slot *T = nullptr; uint64_t nslices = 0; int slice_bits = 0;
+    Slot *T = nullptr; uint64_t nslices = 0; int slice_bits = 0, cshift = 0;
     SideSlot *R = nullptr; uint64_t rcap = 0;
     SideSlot *M = nullptr; uint64_t mcap = 0;
     unsigned long long *d_occ = nullptr;         // [0] T, [1] R, [2] M
@@ -83,6 +84,11 @@ struct kq_ctx {
     unsigned long long *d_hist = nullptr, *d_cursor = nullptr; uint64_t hist_cap = 0;
     unsigned long long *d_total = nullptr, *d_nsrc = nullptr, *d_ticket = nullptr;
     uint64_t *d_ovf = nullptr; unsigned long long *d_ovf_n = nullptr; bool ovf_pending = false;
+    uint64_t *ovf_list = nullptr; uint64_t ovf_list_cap = 0;    // where the last batch put the tuples of full slices
+    // level 2 of the pipeline: tuples in slice order, per-slice counts / offsets, tasks
+    uint64_t *d_tuples2 = nullptr; uint64_t tup2_cap = 0;
+    unsigned long long *d_cstart = nullptr, *d_fhist = nullptr, *d_fcursor = nullptr, *d_fstart = nullptr; uint64_t fine_cap = 0;
+    FineTask *d_tasks = nullptr; uint64_t task_cap = 0; unsigned *d_ntasks = nullptr;
     // routed (multi-GPU) pipeline: receive slab the owners' tuples are written into by every rank
     uint64_t *d_slab = nullptr; uint64_t slab_cap = 0;          // tuples
     RouteMap route{}; bool route_ready = false;
@@ -93,7 +99,7 @@ struct kq_ctx {
     Stage st[NBUF]; int next_stage = 0;
     uint64_t launches = 0, h2d = 0, d2h = 0;
     bool timing = false; std::vector<TimedRange> ranges; std::vector<cudaEvent_t> ev_pool;
-    double time_ms[NTIMERS] = {0, 0, 0, 0}; uint64_t time_n[NTIMERS] = {0, 0, 0, 0};
+    double time_ms[NTIMERS] = {}; uint64_t time_n[NTIMERS] = {};
     std::string err;
 };
 
@@ -110,7 +116,7 @@ inline uint64_t table_slots(const kq_ctx *c) { return c->nslices << c->slice_bit
 
 TableView view(const kq_ctx *c) {
     TableView tv;
-    tv.T = c->T; tv.nslices = c->nslices; tv.slice_bits = c->slice_bits;
+    tv.T = c->T; tv.nslices = c->nslices; tv.slice_bits = c->slice_bits; tv.cshift = c->cshift;
     tv.R = c->R; tv.rcap = c->rcap; tv.M = c->M; tv.mcap = c->mcap;
     tv.occ = c->d_occ; tv.err = c->d_err; tv.k = c->k;
     tv.shard_rank = c->nranks > 1 ? c->rank : -1;
@@ -141,27 +147,30 @@ int read_occ(kq_ctx *c, uint64_t occ[3]) {
     return KQ_OK;
 }
 
-// geometry of a table with at least `need` slots: one slice while it fits 2^21 slots (32 MiB), else
-// 32 MiB slices (64 MiB once there would be more slices than the scatter kernel has bins for)
-void table_geometry(uint64_t need, uint64_t &nslices, int &slice_bits) {
+// geometry of a table with at least `need` slots: one slice while it fits 2^21 slots (32 MiB, L2 resident),
+// else slices of 2^12 slots (64 KiB: what one CTA of the shared-memory insert holds), grouped 2^cshift at a
+// time into the bins of the level-1 scatter (about sqrt(nslices) bins at either level)
+void table_geometry(uint64_t need, uint64_t &nslices, int &slice_bits, int &cshift) {
     need = std::max(need, MIN_SLOTS);
-    static const int max_bits = [] { const char *e = std::getenv("KQ_SLICE_BITS"); const int v = e ? std::atoi(e) : 0;
-                                     return v >= 12 && v <= 26 ? v : KQ_MAX_SLICE_BITS; }();   // tuning knob
-    int b = 12; while (b < max_bits && (1ull << b) < need) ++b;
+    const int max_bits = tuning().single_slice_bits;
+    int b = std::min(12, max_bits); while (b < max_bits && (1ull << b) < need) ++b;
+    cshift = 0;
     if ((1ull << b) >= need) { nslices = 1; slice_bits = b; return; }
-    slice_bits = max_bits;
-    if (((need + (1ull << slice_bits) - 1) >> slice_bits) > 1600) ++slice_bits;
+    slice_bits = tuning().piece_bits;
     nslices = (need + (1ull << slice_bits) - 1) >> slice_bits;
+    int lg = 0; while ((2ull << lg) <= nslices) ++lg;                // floor(log2 nslices)
+    cshift = lg / 2;
+    while ((((nslices - 1) >> cshift) + 1) > 3000) ++cshift;          // bins of the level-1 scatter must fit shared memory
 }
 
 int grow_table(kq_ctx *c, uint64_t need) {
     if (c->exported) return fail(c, KQ_ESTATE, "the table is mapped by peers (kq_peer_export): call kq_peer_disconnect first");
     Slot *old = c->T; const uint64_t old_slots = table_slots(c);
-    uint64_t ns; int sb; table_geometry(need, ns, sb);
+    uint64_t ns; int sb, cs; table_geometry(need, ns, sb, cs);
     Slot *nt = nullptr;
     CU(cudaMalloc(&nt, (ns << sb) * sizeof(Slot)));
     CU(cudaMemsetAsync(nt, 0, (ns << sb) * sizeof(Slot), c->stream));
-    c->T = nt; c->nslices = ns; c->slice_bits = sb;
+    c->T = nt; c->nslices = ns; c->slice_bits = sb; c->cshift = cs;
     if (old) {
         CU(launch_rehash(c->stream, view(c), old, old_slots, &c->launches));
         CU(cudaStreamSynchronize(c->stream));
@@ -244,11 +253,12 @@ void time_collect(kq_ctx *c) {
 
 namespace {
 
-int pipeline_scratch(kq_ctx *c, uint64_t tuples) {
-    if (c->hist_cap < c->nslices) {
-        cudaFree(c->d_hist); cudaFree(c->d_cursor); c->d_hist = c->d_cursor = nullptr; c->hist_cap = 0;
-        CU(cudaMalloc(&c->d_hist, c->nslices * 8)); CU(cudaMalloc(&c->d_cursor, c->nslices * 8));
-        c->hist_cap = c->nslices;
+int pipeline_scratch(kq_ctx *c, uint64_t tuples, bool level2 = false) {
+    const uint64_t nbins = coarse_bins(view(c));
+    if (c->hist_cap < nbins) {
+        cudaFree(c->d_hist); cudaFree(c->d_cursor); cudaFree(c->d_cstart); c->d_hist = c->d_cursor = c->d_cstart = nullptr; c->hist_cap = 0;
+        CU(cudaMalloc(&c->d_hist, nbins * 8)); CU(cudaMalloc(&c->d_cursor, nbins * 8)); CU(cudaMalloc(&c->d_cstart, nbins * 8));
+        c->hist_cap = nbins;
     }
     if (!c->d_ovf) CU(cudaMalloc(&c->d_ovf, OVF_CAP * 16));
     if (c->tup_cap < tuples) {
@@ -256,6 +266,24 @@ int pipeline_scratch(kq_ctx *c, uint64_t tuples) {
         CU(cudaMalloc(&c->d_tuples, tuples * 8 * tuple_words(c->k)));
         c->tup_cap = tuples;
     }
+    if (!level2) return KQ_OK;
+    if (c->tup2_cap < tuples) {
+        cudaFree(c->d_tuples2); c->d_tuples2 = nullptr; c->tup2_cap = 0;
+        CU(cudaMalloc(&c->d_tuples2, tuples * 8 * tuple_words(c->k)));
+        c->tup2_cap = tuples;
+    }
+    if (c->fine_cap < c->nslices) {
+        cudaFree(c->d_fhist); cudaFree(c->d_fcursor); cudaFree(c->d_fstart); c->d_fhist = c->d_fcursor = c->d_fstart = nullptr; c->fine_cap = 0;
+        CU(cudaMalloc(&c->d_fhist, c->nslices * 8)); CU(cudaMalloc(&c->d_fcursor, c->nslices * 8)); CU(cudaMalloc(&c->d_fstart, c->nslices * 8));
+        c->fine_cap = c->nslices;
+    }
+    const uint64_t tasks = tuples / tuning().part + nbins + 1;
+    if (c->task_cap < tasks) {
+        cudaFree(c->d_tasks); c->d_tasks = nullptr; c->task_cap = 0;
+        CU(cudaMalloc(&c->d_tasks, tasks * sizeof(FineTask)));
+        c->task_cap = tasks;
+    }
+    if (!c->d_ntasks) CU(cudaMalloc(&c->d_ntasks, sizeof(unsigned)));
     return KQ_OK;
 }
 
@@ -274,14 +302,19 @@ int settle(kq_ctx *c) {
     CU(cudaMemcpyAsync(&n, c->d_ovf_n, 8, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
     if (!n) return KQ_OK;
-    if (n > OVF_CAP)
+    // the shared-memory insert keeps the tuples of full slices in the (batch-sized) level-1 buffer, so a size
+    // hint that was too small costs a grow and a second insert, never the batch; the other kernels have the
+    // 4 Mi-tuple list
+    uint64_t *list = c->ovf_list ? c->ovf_list : c->d_ovf;
+    const uint64_t list_cap = c->ovf_list ? c->ovf_list_cap : OVF_CAP;
+    if (n > list_cap)
         return fail(c, KQ_ENOMEM, "k-mer table too small for the batch (" + std::to_string(n) +
                                   " instances found their slice full): pass a larger expected_distinct to kq_create / kq_reserve");
     rc = grow_table(c, std::max<uint64_t>(2 * table_slots(c), (uint64_t)((double)(occ[0] + n) / TARGET_LOAD))); if (rc) return rc;
     CU(cudaMemsetAsync(c->d_ovf_n, 0, 8, c->stream));
     CU(cudaMemcpyAsync(c->d_nsrc, &n, 8, cudaMemcpyHostToDevice, c->stream));
-    rc = pipeline_scratch(c, OVF_CAP); if (rc) return rc;
-    CU(launch_insert_tuples(c->stream, view(c), c->d_ovf, c->d_nsrc, n, c->d_tuples, c->tup_cap, c->d_ovf_n, c->d_ticket, &c->launches));
+    // second-chance failures go to the fixed list (a different buffer than the one being read)
+    CU(launch_insert_tuples(c->stream, view(c), list, c->d_nsrc, n, c->d_ovf, OVF_CAP, c->d_ovf_n, c->d_ticket, &c->launches));
     CU(cudaMemcpyAsync(&n, c->d_ovf_n, 8, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
     if (n) return fail(c, KQ_ENOMEM, "k-mer table full after growing");
@@ -296,11 +329,13 @@ int run_batch(kq_ctx *c, Source src) {
     if (!bound) return KQ_OK;
     const TableView tv = view(c);
     const int tw = tuple_words(c->k);
-    const int cap = c->nslices > 1 ? scatter_pick_cap(c->nslices, tw) : 0;
+    const unsigned ncoarse = coarse_bins(tv);
+    const int cap = c->nslices > 1 ? scatter_pick_cap(ncoarse, tw) : 0;
     { int rc = pipeline_scratch(c, 0); if (rc) return rc; }
+    c->ovf_list = nullptr; c->ovf_list_cap = 0;
     const int t0 = time_begin(c, 0);
     // a sweep over the table pays off once the batch touches a good part of it
-    if (src.ordered || c->nslices == 1 || cap == 0 || (double)bound < 0.25 * (double)table_slots(c)) {
+    if (src.ordered || c->nslices == 1 || cap == 0 || (double)bound * 100.0 < (double)tuning().direct_pct * (double)table_slots(c)) {
         if (src.tuples) {
             const int t2 = time_begin(c, src.ordered ? 2 : -1);
             CU(launch_insert_tuples(c->stream, tv, src.tuples, src.ntuples, bound, c->d_ovf, OVF_CAP, c->d_ovf_n, c->d_ticket, &c->launches));
@@ -313,32 +348,42 @@ int run_batch(kq_ctx *c, Source src) {
         time_end(c, t0);
         return KQ_OK;
     }
-    int rc = pipeline_scratch(c, bound); if (rc) return rc;
+    // level 2 + shared-memory insert when a slice fits one CTA's shared memory and its bins the scatter's
+    const unsigned ns_max = 1u << c->cshift;
+    const bool level2 = tuning().smem_insert && c->slice_bits <= 13 && fine_pick_cap(ns_max, tw) != 0;
+    int rc = pipeline_scratch(c, bound, level2); if (rc) return rc;
     const int t3 = time_begin(c, 3);
-    CU(cudaMemsetAsync(c->d_hist, 0, c->nslices * 8, c->stream));
+    CU(cudaMemsetAsync(c->d_hist, 0, (size_t)ncoarse * 8, c->stream));
     CU(launch_slice_hist(c->stream, tv, src, c->d_hist, &c->launches));
-    CU(launch_slice_offsets(c->stream, c->nslices, c->d_hist, c->d_cursor, c->d_total,
+    CU(launch_slice_offsets(c->stream, ncoarse, c->d_hist, c->d_cursor, c->d_cstart, c->d_total,
                             src.tuples ? nullptr : c->d_inst, &c->launches));
+    const int t5 = time_begin(c, 5);
     CU(launch_slice_scatter(c->stream, tv, src, c->d_tuples, c->d_cursor, cap, &c->launches));
+    time_end(c, t5);
     time_end(c, t3);
-    if (std::getenv("KQ_DEBUG_ORDER")) {                              // debugging aid: is the scatter output in slice order?
-        unsigned long long total = 0;
-        cudaMemcpyAsync(&total, c->d_total, 8, cudaMemcpyDeviceToHost, c->stream); cudaStreamSynchronize(c->stream);
-        std::vector<uint64_t> h(total * tw);
-        cudaMemcpy(h.data(), c->d_tuples, total * tw * 8, cudaMemcpyDeviceToHost);
-        uint64_t changes = 0, backwards = 0, prev = 0;
-        for (uint64_t i = 0; i < total; ++i) {
-            const uint64_t key = tw == 1 ? h[i] >> 8 : h[2 * i];
-            const uint64_t sl = slice_of_key(key, c->nslices);
-            if (i && sl != prev) { ++changes; if (sl < prev) ++backwards; }
-            prev = sl;
-        }
-        std::fprintf(stderr, "KQ_DEBUG_ORDER: %llu tuples, %llu slices, %llu slice changes, %llu backwards\n",
-                     total, (unsigned long long)c->nslices, (unsigned long long)changes, (unsigned long long)backwards);
+    if (!level2) {
+        const int t2 = time_begin(c, 2);
+        CU(launch_insert_tuples(c->stream, tv, c->d_tuples, c->d_total, bound, c->d_ovf, OVF_CAP, c->d_ovf_n, c->d_ticket, &c->launches));
+        time_end(c, t2);
+        c->ovf_pending = true;
+        time_end(c, t0);
+        return KQ_OK;
     }
+    const int t4 = time_begin(c, 4);
+    const unsigned task_bound = (unsigned)std::min<uint64_t>(c->task_cap, bound / tuning().part + ncoarse + 1);
+    CU(launch_fine_plan(c->stream, tv, ncoarse, c->d_cstart, c->d_hist, tuning().part, c->d_tasks, task_bound, c->d_ntasks, &c->launches));
+    CU(cudaMemsetAsync(c->d_fhist, 0, c->nslices * 8, c->stream));
+    CU(launch_fine_hist(c->stream, tv, c->d_tuples, c->d_tasks, c->d_ntasks, task_bound, ns_max, c->d_fhist, &c->launches));
+    CU(launch_slice_offsets(c->stream, c->nslices, c->d_fhist, c->d_fcursor, c->d_fstart, c->d_total, nullptr, &c->launches));
+    const int t6 = time_begin(c, 6);
+    CU(launch_fine_scatter(c->stream, tv, c->d_tuples, c->d_tasks, c->d_ntasks, task_bound, ns_max, c->d_tuples2, c->d_fcursor, &c->launches));
+    time_end(c, t6);
+    time_end(c, t4);
     const int t2 = time_begin(c, 2);
-    CU(launch_insert_tuples(c->stream, tv, c->d_tuples, c->d_total, bound, c->d_ovf, OVF_CAP, c->d_ovf_n, c->d_ticket, &c->launches));
+    // tuples of full slices go back into the level-1 buffer (free by now, as large as the batch)
+    CU(launch_smem_insert(c->stream, tv, c->d_tuples2, c->d_fstart, c->d_fhist, c->d_tuples, c->tup_cap, c->d_ovf_n, c->d_ticket, &c->launches));
     time_end(c, t2);
+    c->ovf_list = c->d_tuples; c->ovf_list_cap = c->tup_cap;
     c->ovf_pending = true;
     time_end(c, t0);
     return KQ_OK;
@@ -490,6 +535,8 @@ extern "C" void kq_destroy(kq_ctx *c) {
     if (c->ev_read_alt) cudaEventDestroy(c->ev_read_alt);
     cudaFree(c->d_pb_alt); cudaFree(c->d_pi_alt);
     cudaFree(c->d_pb); cudaFree(c->d_pi); cudaFree(c->d_tuples); cudaFree(c->d_hist); cudaFree(c->d_cursor);
+    cudaFree(c->d_tuples2); cudaFree(c->d_cstart); cudaFree(c->d_fhist); cudaFree(c->d_fcursor); cudaFree(c->d_fstart);
+    cudaFree(c->d_tasks); cudaFree(c->d_ntasks);
     cudaFree(c->d_total); cudaFree(c->d_nsrc); cudaFree(c->d_ticket); cudaFree(c->d_ovf); cudaFree(c->d_ovf_n);
     for (void *p : c->ipc_opened) cudaIpcCloseMemHandle(p);
     for (void *p : c->peer_opened) cudaIpcCloseMemHandle(p);
@@ -562,6 +609,24 @@ extern "C" int kq_reserve(kq_ctx *c, uint64_t extra) {
     if ((double)(c->occ_known + extra) > TARGET_LOAD * (double)table_slots(c)) {
         rc = grow_table(c, (uint64_t)((double)(c->occ_known + extra) / TARGET_LOAD)); if (rc) return rc;
     }
+    return KQ_OK;
+}
+
+// process-wide tuning knobs (kq_kernels.h Tuning); geometry knobs apply to tables created or grown afterwards
+extern "C" int kq_set_tuning(const char *name, long long value) {
+    if (!name) return KQ_EINVAL;
+    Tuning &t = tuning();
+    const std::string n(name);
+    if (n == "single_slice_bits" && value >= 8 && value <= 26) t.single_slice_bits = (int)value;
+    else if (n == "piece_bits" && value >= 6 && value <= 13) t.piece_bits = (int)value;
+    else if (n == "fine_part" && value >= 64) t.part = (unsigned long long)value;
+    else if (n == "smem_insert" && (value == 0 || value == 1)) t.smem_insert = (int)value;
+    else if (n == "direct_pct" && value >= 0 && value <= 100) t.direct_pct = (int)value;
+    else if (n == "scatter_cap" && value >= 0 && value <= 512) t.scatter_cap = (int)value;
+    else if (n == "insert_ctas" && value >= 1 && value <= 8) t.insert_ctas = (int)value;
+    else if (n == "validate_ctas" && value >= 1 && value <= 8) t.validate_ctas = (int)value;
+    else if (n == "db_host" && (value == 0 || value == 1)) t.db_host = (int)value;
+    else return KQ_EINVAL;
     return KQ_OK;
 }
 
@@ -1175,7 +1240,7 @@ int save_maps_gpu(kq_ctx *c, const std::string &dir, std::vector<Rec32Entry> &hc
 int load_maps_gpu(kq_ctx *c, const std::string &dir, XRec **d_xs, uint64_t *n_out);
 
 // KQ_DB_HOST=1 keeps the file codec on the host (the first implementation; useful to cross-check the device one)
-bool db_on_host() { static const bool v = [] { const char *e = std::getenv("KQ_DB_HOST"); return e && e[0] == '1'; }(); return v; }
+bool db_on_host() { return tuning().db_host != 0; }
 
 int save_impl(kq_ctx *c, const char *dir_c, bool maps_too) {
     if (!c || !dir_c) return KQ_EINVAL;
@@ -1466,7 +1531,9 @@ int feed_device(kq_ctx *c, const XRec *d, uint64_t total, Feed mode) {
         CU(cudaMemcpyAsync(&big, c->d_total, 8, cudaMemcpyDeviceToHost, c->stream));
         uint64_t occ[3]; int rc = read_occ(c, occ); if (rc) return rc;
         c->big_seen += big;
-        const uint64_t need_r = occ[1] + big, need_m = occ[2] + c->big_seen;
+        // Put: keys are new, only a field above a lane spills.  Merges: two records that each fit a lane can
+        // sum past it (cov 80 + 80), so every record of the launch may create a remainder entry
+        const uint64_t need_r = occ[1] + (mode == Feed::Put ? big : n), need_m = occ[2] + c->big_seen;
         if (need_r * 2 > c->rcap) { rc = grow_side(c, 1, std::max<uint64_t>(4 * c->rcap, 4 * need_r)); if (rc) return rc; }
         if (mode != Feed::Put && need_m * 2 > c->mcap) { rc = grow_side(c, 2, std::max<uint64_t>(4 * c->mcap, 4 * need_m)); if (rc) return rc; }
         if ((double)(occ[0] + n) > MAX_LOAD * (double)table_slots(c)) {

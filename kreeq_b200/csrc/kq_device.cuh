@@ -247,7 +247,10 @@ __device__ __forceinline__ int insert_instance(const TableView &tv, uint64_t key
     Slot *base = tv.T + (slice_of_key(key, tv.nslices) << tv.slice_bits);
     const unsigned long long mask = (1ull << tv.slice_bits) - 1;
     unsigned long long j = h & mask;
-    for (unsigned long long n = 0; n <= mask; ++n) {
+    // a run of 4096 occupied slots means the slice is (locally) full: give the tuple back instead of walking a
+    // full slice slot by slot; the caller grows the table and counts it again
+    const unsigned long long limit = mask < 4095 ? mask : 4095;
+    for (unsigned long long n = 0; n <= limit; ++n) {
         Slot *p = base + j;
         Slot s = ld_slot(p);
         if (s.tag == 0) {                                           // claim and count in one 128-bit CAS

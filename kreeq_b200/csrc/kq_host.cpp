@@ -41,6 +41,7 @@ void Pool::worker() {
 void Pool::parallel_for(size_t n, const std::function<void(size_t)> &fn) {
     if (n == 0) return;
     if (workers_.empty() || n == 1) { for (size_t i = 0; i < n; ++i) fn(i); return; }
+    std::lock_guard<std::mutex> one_call(call_mu_);                   // concurrent callers (one thread per GPU) take turns
     std::unique_lock<std::mutex> l(mu_);
     fn_ = &fn; n_ = n; next_ = 0; ++epoch_;
     cv_.notify_all();

@@ -18,12 +18,13 @@ public:
     explicit Pool(int nthreads);
     ~Pool();
     int size() const { return (int)workers_.size() + 1; }
-    // runs fn(i) for i in [0,n) on the workers and the calling thread; returns when all are done
+    // runs fn(i) for i in [0,n) on the workers and the calling thread; returns when all are done.  Calls from
+    // several threads are serialised (fn must not call parallel_for on the same pool)
     void parallel_for(size_t n, const std::function<void(size_t)> &fn);
 private:
     void worker();
     std::vector<std::thread> workers_;
-    std::mutex mu_;
+    std::mutex mu_, call_mu_;
     std::condition_variable cv_, done_cv_;
     const std::function<void(size_t)> *fn_ = nullptr;
     size_t next_ = 0, n_ = 0, running_ = 0;
