@@ -44,6 +44,7 @@ def parse_args():
     ap.add_argument("--k", type=int, default=21, help="k-mer length (default: C2's 21; 29..32 use 16-byte tuples)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the seeded parity problem that runs before the timed region")
     ap.add_argument("--pageable-out", action="store_true", help="e2e validate into pageable host memory (staged copy)")
     ap.add_argument("--no-union", action="store_true", help="skip the database rows (save / union / load timing)")
     ap.add_argument("--ref-sample-reads", type=int, default=1_500_000)
@@ -353,6 +354,51 @@ def main_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    def parity_check():
+        """A seeded 2 Mbp / 30x problem (5.2e7 instances) counted and validated through the SAME table, routing
+        and kernels the timed steps use, compared with constants the CPU checker produced
+        (tests/golden/bench_parity.json).  Every rank feeds every world-th read; contigs are dealt to ranks."""
+        from kreeq_b200 import paritycheck as pc
+        reads, asm, kk = pc.problem("bench")
+        want = pc.expected("bench")
+        if kk != K:
+            return {"ok": None, "skipped": "parity constants are for k=%d" % kk}
+        g.clear()
+        mine = np.ascontiguousarray(reads.reshape(-1, 151)[rank::world]).reshape(-1)
+        if world > 1:
+            b, m = pack_to_device(mine)
+            router.count(b, m, mine.size)
+            g.finalize()
+        else:
+            g.traverseInReads(mine)
+            g.finalize()
+        keys, recs = g.export()
+        got = pc.db_digest(keys, recs) + [g.instances()]
+        clen = asm.size // want["contigs"]
+        rows, acc = 0, kreeq_b200._lib.KqQV()
+        out = np.zeros(clen, dtype=kreeq_b200.BASE)
+
+        def vloop():
+            nonlocal rows
+            for i in range(rank, want["contigs"], world):
+                seg = np.ascontiguousarray(asm[i * clen:(i + 1) * clen])
+                check(L.kq_validate_segment(g.handle, C.c_void_p(seg.ctypes.data), clen, 0, C.c_void_p(out.ctypes.data), C.byref(acc)), g.handle)
+                rows = pc.add_mod64(rows, pc.rows_digest(out, i * clen))
+        if world > 1:
+            with peers:
+                vloop()
+        else:
+            vloop()
+        got += [rows, acc.missing, acc.kcount, acc.edge_missing]
+        if world > 1:
+            allv = [None] * world
+            dist.all_gather_object(allv, got)
+            got = [sum(v[i] for v in allv) & 0xFFFFFFFFFFFFFFFF for i in range(len(got))]
+        exp = want["db"] + [want["instances"], want["rows"]] + want["qv"]
+        g.clear()
+        return {"ok": got == exp, "digest": got, "expected": exp,
+                "what": "db [sum key*cov mod 2^64, sum edges, distinct, total], instances, validate rows digest, missing, kcount, edge_missing"}
+
     ev = lambda: torch.cuda.Event(enable_timing=True)
 
     def step_resident():
@@ -435,6 +481,11 @@ def main_ours(args):
                 "kt_pipe": kt_pipe, "kn_pipe": kn_pipe, "kt_scat": kt_scat, "kn_scat": kn_scat,
                 "kt_l2": kt_l2, "kt_s1": kt_s1, "kt_s2": kt_s2}
 
+    parity = parity_check() if not args.no_parity else {"ok": None, "skipped": "--no-parity"}
+    if parity["ok"] is False:
+        if rank == 0:
+            print(json.dumps({"metric": "kmers_counted_per_sec", "value": None, "parity_check": parity, "error": "parity check failed"}))
+        raise SystemExit(3)
     res = run(step_resident, args.warmup, args.steps)
     inst_total = inst_per_rank * world
     value = inst_total / (res["count_ms"] * 1e-3)
@@ -449,7 +500,7 @@ def main_ours(args):
                               % (est_distinct / 0.5 * 16 / 1e9, reads_np.size * 0.375 / 1e9)),
             "count_ms": res["count_ms"], "validate_ms": res["validate_ms"],
             "validate": {"metric": "assembly_kmers_validated_per_sec", "value": asm_k * world / (res["validate_ms"] * 1e-3), "unit": "k-mers/s"},
-            "clocks": res["clocks"], "gpu_launches": res["launches"]}
+            "clocks": res["clocks"], "gpu_launches": res["launches"], "parity_check": parity}
     # roofline of the dominant kernel (count/insert), per launch, from CUDA events around each launch
     if res["kn_count"]:
         per_launch_s = res["kt_count"] * 1e-3 / res["kn_count"]
