@@ -216,6 +216,53 @@ int  kq_peer_connect(kq_ctx *ctx, const void *blobs);
 int  kq_peer_connect_local(kq_ctx *ctx, kq_ctx *const *handles);   /* shards held by this process */
 int  kq_peer_disconnect(kq_ctx *ctx);
 
+/* ---- validate across GPUs with routed queries (SURVEY 8e "Collective": all-to-all of (key, origin) queries ->
+ * the owners probe their own HBM -> answers back into the origin's row slab) ----------------------------------
+ * kq_vroute_setup allocates this rank's inbox (nranks regions of `chunk_positions` 16-byte queries + the
+ * per-sender counts) and its row slab (chunk_positions kq_base rows) and returns their device pointers and
+ * CUDA IPC handles (64 bytes each, may be NULL); kq_vroute_connect takes every rank's inbox and row-slab
+ * pointers (own ones at index rank; peers' opened with kq_route_open or passed directly inside one process).
+ * Per chunk of at most chunk_positions assembly positions, on EVERY rank and in this order:
+ *   kq_vroute_send     positions [c0, c0+n) of a segment with kcount windows (packed arrays start at segment
+ *                      position base0): queries to the owners' inboxes; rows of windows without a key are final
+ *   (caller)           barrier on the streams of all ranks
+ *   kq_vroute_answer   probe what arrived, store the finished rows into the origins' slabs
+ *   (caller)           barrier; then rows [0, n) of kq_vroute_rows() are this rank's DBGbase rows of the chunk
+ * kq_vroute_counters adds this rank's share of the three QV counters (sum over ranks = the totals). */
+int  kq_vroute_setup(kq_ctx *ctx, uint64_t chunk_positions, void **d_inbox, void *ipc_inbox64, void **d_rows, void *ipc_rows64);
+int  kq_vroute_connect(kq_ctx *ctx, void *const *inboxes, void *const *rows);
+int  kq_vroute_send(kq_ctx *ctx, const uint64_t *d_bases, const uint64_t *d_invalid, uint64_t base0, uint64_t c0, uint64_t n, uint64_t kcount);
+int  kq_vroute_answer(kq_ctx *ctx, uint32_t cov_cutoff);
+int  kq_vroute_rows(kq_ctx *ctx, kq_base **d_rows);
+int  kq_vroute_counters(kq_ctx *ctx, kq_qv *acc, int reset);
+
+/* ---- all GPUs of one box behind one handle (SURVEY 5.6 `--gpus N`, 8b kq_create(..., ngpus, ...)) ---------------
+ * One process, one host thread per GPU while a collective step runs; shard g owns maps [g*128/G, (g+1)*128/G).
+ * Same meaning as the single-GPU calls above: count_push deals the batches to the GPUs (tuples are routed to
+ * their owners over peer memory inside the scatter kernel), save / load / union / stats are shard-local and the
+ * results are those of one GPU (same database files, same counters).  ngpus: a power of two, 0 = all visible;
+ * devices: CUDA ordinals (NULL = 0..ngpus-1; an ordinal may repeat, e.g. every shard on one GPU). */
+typedef struct kq_multi kq_multi;
+int  kq_multi_create(kq_multi **out, int k, int ngpus, const int *devices, uint64_t expected_distinct);
+void kq_multi_destroy(kq_multi *m);
+const char *kq_multi_last_error(kq_multi *m);
+int  kq_multi_ngpus(kq_multi *m);
+kq_ctx *kq_multi_shard(kq_multi *m, int g);
+/* positions a GPU routes per count round / assembly positions per validate chunk (0 = keep; before first use) */
+int  kq_multi_set_round(kq_multi *m, uint64_t round_positions, uint64_t validate_chunk);
+int  kq_multi_count_push(kq_multi *m, const char *ascii, size_t len);
+int  kq_multi_count_finish(kq_multi *m);
+int  kq_multi_count_instances(kq_multi *m, uint64_t *n);
+int  kq_multi_clear(kq_multi *m);
+int  kq_multi_stats_get(kq_multi *m, kq_stats *out);
+int  kq_multi_hist(kq_multi *m, uint64_t *cov, uint64_t *n, size_t *len);
+int  kq_multi_export(kq_multi *m, uint64_t *keys, kq_rec32 *recs, size_t *n);
+int  kq_multi_lookup_batch(kq_multi *m, const uint64_t *keys, size_t n, kq_rec32 *rec, uint8_t *found);
+int  kq_multi_db_save(kq_multi *m, const char *dir);
+int  kq_multi_db_load(kq_multi *m, const char *dir);
+int  kq_multi_union(kq_multi *m, const char *const *dirs, int n, int ref_compatible);
+int  kq_multi_validate_segment(kq_multi *m, const char *seq, uint64_t len, uint32_t cov_cutoff, kq_base *out, kq_qv *acc);
+
 /* probe positions [0, len-k+1) of one packed device-resident segment;
  * d_out (len entries) and d_acc (kq_qv, accumulates) are device memory. */
 int  kq_dev_validate_packed(kq_ctx *ctx, const uint64_t *d_bases, const uint64_t *d_invalid,

@@ -85,6 +85,30 @@ PROTOTYPES = {
     "kq_peer_connect_local": (_i, [_vp, C.POINTER(_vp)]),
     "kq_peer_disconnect": (_i, [_vp]),
     "kq_dev_validate_packed": (_i, [_vp, _vp, _vp, _u64, C.c_uint32, _vp, _vp]),
+    "kq_vroute_setup": (_i, [_vp, _u64, C.POINTER(_vp), _vp, C.POINTER(_vp), _vp]),
+    "kq_vroute_connect": (_i, [_vp, C.POINTER(_vp), C.POINTER(_vp)]),
+    "kq_vroute_send": (_i, [_vp, _vp, _vp, _u64, _u64, _u64, _u64]),
+    "kq_vroute_answer": (_i, [_vp, C.c_uint32]),
+    "kq_vroute_rows": (_i, [_vp, C.POINTER(_vp)]),
+    "kq_vroute_counters": (_i, [_vp, C.POINTER(KqQV), _i]),
+    "kq_multi_create": (_i, [C.POINTER(_vp), _i, _i, C.POINTER(_i), _u64]),
+    "kq_multi_destroy": (None, [_vp]),
+    "kq_multi_last_error": (_cp, [_vp]),
+    "kq_multi_ngpus": (_i, [_vp]),
+    "kq_multi_shard": (_vp, [_vp, _i]),
+    "kq_multi_set_round": (_i, [_vp, _u64, _u64]),
+    "kq_multi_count_push": (_i, [_vp, _vp, _sz]),
+    "kq_multi_count_finish": (_i, [_vp]),
+    "kq_multi_count_instances": (_i, [_vp, C.POINTER(_u64)]),
+    "kq_multi_clear": (_i, [_vp]),
+    "kq_multi_stats_get": (_i, [_vp, C.POINTER(KqStats)]),
+    "kq_multi_hist": (_i, [_vp, _vp, _vp, C.POINTER(_sz)]),
+    "kq_multi_export": (_i, [_vp, _vp, _vp, C.POINTER(_sz)]),
+    "kq_multi_lookup_batch": (_i, [_vp, _vp, _sz, _vp, _vp]),
+    "kq_multi_db_save": (_i, [_vp, _cp]),
+    "kq_multi_db_load": (_i, [_vp, _cp]),
+    "kq_multi_union": (_i, [_vp, C.POINTER(_cp), _i, _i]),
+    "kq_multi_validate_segment": (_i, [_vp, _vp, _u64, C.c_uint32, _vp, C.POINTER(KqQV)]),
     "kq_reserve": (_i, [_vp, _u64]),
     "kq_counters": (_i, [_vp, C.POINTER(_u64), C.POINTER(_u64), C.POINTER(_u64)]),
     "kq_set_timing": (_i, [_vp, _i]),

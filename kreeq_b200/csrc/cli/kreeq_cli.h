@@ -30,6 +30,8 @@ struct Options {                       // UserInputKreeq, include/input.h:11-33 
     uint32_t cov_cutoff = 0;           // -c
     int verbose = 0, cmd = 0;
     int device = 0;                    // --gpu (ours)
+    int gpus = 1;                      // --gpus (ours): shards of the key space, 0 = all visible GPUs
+    std::vector<int> devices;          // --devices a,b,.. (ours): explicit ordinal per shard (may repeat)
     uint64_t expected = 0;             // --expected-distinct (ours): table size hint
 };
 

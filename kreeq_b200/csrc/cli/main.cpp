@@ -50,8 +50,8 @@ void require_file(const char *path) {             // ifFileExists, gfalibs/inclu
     }
 }
 
-[[noreturn]] void die(kq_ctx *ctx, int rc) {
-    fprintf(stderr, "%s\n", kq_last_error(ctx));
+[[noreturn]] void die(kq_multi *ctx, int rc) {
+    fprintf(stderr, "%s\n", kq_multi_last_error(ctx));
     (void)rc;
     exit(EXIT_FAILURE);
 }
@@ -72,7 +72,8 @@ void print_help_validate() {
     printf("\t-t --tmp-prefix accepted for compatibility (no temporary files are written).\n");
     printf("\t-m --max-memory accepted for compatibility.\n");
     printf("\t-j --threads <n> accepted for compatibility.\n");
-    printf("\t--gpu <n> CUDA device to use (default: 0).\n");
+    printf("\t--gpu <n> first CUDA device to use (default: 0).\n");
+    printf("\t--gpus <n> number of GPUs the k-mer table is sharded over (1, 2, 4, 8; 0 = all visible; default: 1).\n");
     printf("\t--expected-distinct <n> size hint for the k-mer table.\n");
     printf("\t--cmd print $0 to stdout.\n");
 }
@@ -83,7 +84,8 @@ void print_help_union() {
     printf("\t-d --databases DBG databases to merge.\n");
     printf("\t-j --threads <n> accepted for compatibility.\n");
     printf("\t-o --out-format generates various kinds of outputs (currently supported: .kreeq).\n");
-    printf("\t--gpu <n> CUDA device to use (default: 0).\n");
+    printf("\t--gpu <n> first CUDA device to use (default: 0).\n");
+    printf("\t--gpus <n> number of GPUs the merge is sharded over (default: 1).\n");
     printf("\t--cmd print $0 to stdout.\n");
 }
 
@@ -115,6 +117,7 @@ int parse(int argc, char **argv, Options &o) {
         {"out-format", required_argument, 0, 'o'},      {"input-reads", required_argument, 0, 'r'},
         {"tmp-prefix", required_argument, 0, 't'},      {"max-memory", required_argument, 0, 'm'},
         {"threads", required_argument, 0, 'j'},         {"gpu", required_argument, 0, 0},
+        {"gpus", required_argument, 0, 0},              {"devices", required_argument, 0, 0},
         {"expected-distinct", required_argument, 0, 0}, {"verbose", no_argument, &verbose_flag, 1},
         {"cmd", no_argument, &cmd_flag, 1},             {"version", no_argument, 0, 'v'},
         {"help", no_argument, 0, 'h'},                  {0, 0, 0, 0}};
@@ -129,6 +132,14 @@ int parse(int argc, char **argv, Options &o) {
             return EXIT_FAILURE;
         case 0:
             if (!strcmp(long_options[idx].name, "gpu")) o.device = atoi(optarg);
+            if (!strcmp(long_options[idx].name, "gpus")) {
+                if (!is_number(optarg)) { fprintf(stderr, "input '%s' to option --gpus must be a number\n", optarg); return EXIT_FAILURE; }
+                o.gpus = atoi(optarg);
+            }
+            if (!strcmp(long_options[idx].name, "devices")) {
+                o.devices.clear();
+                for (const char *p = optarg; *p;) { o.devices.push_back(atoi(p)); while (*p && *p != ',') ++p; if (*p == ',') ++p; }
+            }
             if (!strcmp(long_options[idx].name, "expected-distinct")) o.expected = strtoull(optarg, nullptr, 10);
             break;
         case 'c':
@@ -170,9 +181,18 @@ int parse(int argc, char **argv, Options &o) {
 
 void make_dir(const std::string &dir) { mkdir(dir.c_str(), 0777); }
 
-void print_stats(kq_ctx *ctx) {                   // DBG::DBstats, src/graph-builder.cpp:284-295
+// the k-mer table: one handle over --gpus N devices (shard g on device --gpu + g, or the ordinals of --devices)
+int create(kq_multi **ctx, int k, const Options &o) {
+    std::vector<int> dev = o.devices;
+    int n = o.gpus;
+    if (!dev.empty()) n = (int)dev.size();
+    else if (n > 0) for (int g = 0; g < n; ++g) dev.push_back(o.device + g);
+    return kq_multi_create(ctx, k, n, dev.empty() ? nullptr : dev.data(), o.expected);
+}
+
+void print_stats(kq_multi *ctx) {                   // DBG::DBstats, src/graph-builder.cpp:284-295
     kq_stats s;
-    CHECK(ctx, kq_stats_get(ctx, &s));
+    CHECK(ctx, kq_multi_stats_get(ctx, &s));
     std::cout << "DBG Summary statistics:\n"
               << "Total kmers: " << s.total << "\n"
               << "Unique kmers: " << s.unique << "\n"
@@ -234,7 +254,7 @@ struct QueueSink : ReadSink {
     bool thread_safe() const override { return true; }     // the queue has its own lock
 };
 
-bool count_files(kq_ctx *ctx, const std::vector<std::string> &files, std::string &err) {
+bool count_files(kq_multi *ctx, const std::vector<std::string> &files, std::string &err) {
     BatchQueue bq;
     std::mutex next_mu; size_t next = 0;
     const size_t nthreads = std::min<size_t>(files.size(), 4);
@@ -255,7 +275,7 @@ bool count_files(kq_ctx *ctx, const std::vector<std::string> &files, std::string
         });
     std::string batch; int rc = KQ_OK;
     while (bq.get(batch)) {
-        if (rc == KQ_OK) rc = kq_count_push(ctx, batch.data(), batch.size());      // keep draining after an error
+        if (rc == KQ_OK) rc = kq_multi_count_push(ctx, batch.data(), batch.size());      // keep draining after an error
         bq.give_back(std::move(batch));
         batch = std::string();
     }
@@ -272,8 +292,7 @@ void write_index(const std::string &dir, int k) {  // kreeq-output.cpp:88-94
 }
 
 // DBG::report, src/kreeq-output.cpp:34-136, for the extensions the validate/union path produces.
-void report(kq_ctx *ctx, const Options &o, Genome *genome) {
-    const int k = kq_k(ctx);
+void report(kq_multi *ctx, int k, const Options &o, Genome *genome) {
     const std::string ext = o.out.empty() ? "stdout" : file_ext("." + o.out);
     const bool dotted = o.out.find('.') != std::string::npos || o.out.empty();
     if (dotted || ext == "kreeq") print_stats(ctx);
@@ -289,7 +308,7 @@ void report(kq_ctx *ctx, const Options &o, Genome *genome) {
         for (size_t s = 0; s < genome->segments.size(); ++s) {
             const std::string &seg = genome->segments[s];
             genome->bases[s].resize(seg.size());           // every row is written by the library
-            CHECK(ctx, kq_validate_segment(ctx, seg.data(), seg.size(), o.cov_cutoff, genome->bases[s].data(), &qv));
+            CHECK(ctx, kq_multi_validate_segment(ctx, seg.data(), seg.size(), o.cov_cutoff, genome->bases[s].data(), &qv));
         }
         if (dotted) print_qv(qv, k);
     }
@@ -299,9 +318,9 @@ void report(kq_ctx *ctx, const Options &o, Genome *genome) {
     else if (ext == "bkwig") good = !genome || write_bkwig(o.out, k, *genome);
     else if (ext == "hist") {                      // Kmap::printHist, gfalibs/include/kmer.h:906-914
         size_t len = 0;
-        CHECK(ctx, kq_hist(ctx, nullptr, nullptr, &len));
+        CHECK(ctx, kq_multi_hist(ctx, nullptr, nullptr, &len));
         std::vector<uint64_t> cov(len), cnt(len);
-        CHECK(ctx, kq_hist(ctx, cov.data(), cnt.data(), &len));
+        CHECK(ctx, kq_multi_hist(ctx, cov.data(), cnt.data(), &len));
         std::ofstream ofs(o.out);
         for (size_t i = 0; i < len; ++i) ofs << cov[i] << "\t" << cnt[i] << "\n";
         good = ofs.good();
@@ -316,26 +335,29 @@ void report(kq_ctx *ctx, const Options &o, Genome *genome) {
 
 int run_validate(Options &o) {                    // Input::read case 0, src/input.cpp:87-117
     const bool keep_db = o.out.find(".kreeq") != std::string::npos;
-    kq_ctx *ctx = nullptr;
+    kq_multi *ctx = nullptr;
+    int k_used = o.k;
     if (!o.reads.empty()) {
         if (o.k < 1 || o.k > 32) { fprintf(stderr, "Invalid kmer length.\n"); return EXIT_FAILURE; }
-        if (kq_create(&ctx, o.k, o.device, o.expected) != KQ_OK) die(nullptr, 0);
+        k_used = o.k;
+        if (create(&ctx, o.k, o) != KQ_OK) die(nullptr, 0);
         verbose("Loading input reads.");
         std::string err;
         if (!count_files(ctx, o.reads, err)) { fprintf(stderr, "%s\n", err.c_str()); return EXIT_FAILURE; }
-        CHECK(ctx, kq_count_finish(ctx));
+        CHECK(ctx, kq_multi_count_finish(ctx));
         verbose("Reads loaded.");
-        if (keep_db) { make_dir(o.out); CHECK(ctx, kq_db_save(ctx, o.out.c_str())); }
+        if (keep_db) { make_dir(o.out); CHECK(ctx, kq_multi_db_save(ctx, o.out.c_str())); }
     } else {
         if (o.dbs.empty()) { fprintf(stderr, "Cannot load DBG input. Exiting.\n"); return EXIT_FAILURE; }   // loadGraph, src/input.cpp:56-74
         const int kdb = kq_db_read_k(o.dbs[0].c_str());
         if (kdb < 1) { fprintf(stderr, "Cannot load DBG input. Exiting.\n"); return EXIT_FAILURE; }
         if (o.k_given && o.k != kdb)
             fprintf(stderr, "Warning: -k %d ignored, database was built with k=%d.\n", o.k, kdb);
-        if (kq_create(&ctx, kdb, o.device, o.expected) != KQ_OK) die(nullptr, 0);
-        CHECK(ctx, kq_db_load(ctx, o.dbs[0].c_str()));
+        k_used = kdb;
+        if (create(&ctx, kdb, o) != KQ_OK) die(nullptr, 0);
+        CHECK(ctx, kq_multi_db_load(ctx, o.dbs[0].c_str()));
         verbose("DBG loaded.");
-        if (keep_db && o.out != o.dbs[0]) { make_dir(o.out); CHECK(ctx, kq_db_save(ctx, o.out.c_str())); }
+        if (keep_db && o.out != o.dbs[0]) { make_dir(o.out); CHECK(ctx, kq_multi_db_save(ctx, o.out.c_str())); }
     }
     Genome genome;
     bool have_genome = false;
@@ -346,8 +368,8 @@ int run_validate(Options &o) {                    // Input::read case 0, src/inp
         verbose("Sequences loaded");
         have_genome = true;
     }
-    report(ctx, o, have_genome ? &genome : nullptr);
-    kq_destroy(ctx);
+    report(ctx, k_used, o, have_genome ? &genome : nullptr);
+    kq_multi_destroy(ctx);
     return EXIT_SUCCESS;
 }
 
@@ -361,15 +383,15 @@ int run_union(Options &o) {                       // Input::read case 1, src/inp
         if (k != kd) { fprintf(stderr, "Cannot merge databases with different kmer length.\n"); return EXIT_FAILURE; }
     }
     if (k == 0 || k > 32) { fprintf(stderr, "Invalid kmer length.\n"); return EXIT_FAILURE; }
-    kq_ctx *ctx = nullptr;
-    if (kq_create(&ctx, k, o.device, o.expected) != KQ_OK) die(nullptr, 0);
+    kq_multi *ctx = nullptr;
+    if (create(&ctx, k, o) != KQ_OK) die(nullptr, 0);
     verbose("DBG object generated. Merging.");
     std::vector<const char *> dirs;
     for (const std::string &db : o.dbs) dirs.push_back(db.c_str());
-    CHECK(ctx, kq_union(ctx, dirs.data(), (int)dirs.size(), 1));
-    if (o.out.find(".kreeq") != std::string::npos) { make_dir(o.out); CHECK(ctx, kq_db_save(ctx, o.out.c_str())); }
-    report(ctx, o, nullptr);
-    kq_destroy(ctx);
+    CHECK(ctx, kq_multi_union(ctx, dirs.data(), (int)dirs.size(), 1));
+    if (o.out.find(".kreeq") != std::string::npos) { make_dir(o.out); CHECK(ctx, kq_multi_db_save(ctx, o.out.c_str())); }
+    report(ctx, k, o, nullptr);
+    kq_multi_destroy(ctx);
     return EXIT_SUCCESS;
 }
 

@@ -96,6 +96,10 @@ struct kq_ctx {
     unsigned long long *d_rcursor = nullptr, *d_rback = nullptr, *d_rtotals = nullptr; uint64_t route_real = 0;
     // peer tables (multi-GPU validate): views of every rank's shard, mapped into this process
     TableView *d_peers = nullptr; std::vector<void *> peer_opened; bool exported = false;
+    // routed validate: inbox the peers' queries arrive in, row slab their answers arrive in, local cursors / counters
+    unsigned char *d_vinbox = nullptr; uint64_t vcap = 0; Base *d_vrows = nullptr;
+    unsigned long long *d_vcursor = nullptr, *d_vacc = nullptr; VRoute vroute{}; bool vroute_ready = false;
+    bool hold_pending = false;                   // kq_multi routes the pending reads itself: nothing else may flush them
     Stage st[NBUF]; int next_stage = 0;
     uint64_t launches = 0, h2d = 0, d2h = 0;
     bool timing = false; std::vector<TimedRange> ranges; std::vector<cudaEvent_t> ev_pool;
@@ -446,7 +450,7 @@ int pending_reserve(kq_ctx *c, uint64_t bases) {
 
 // run the pipeline over everything pending
 int pending_flush(kq_ctx *c) {
-    if (!c->pend_len) return KQ_OK;
+    if (!c->pend_len || c->hold_pending) return KQ_OK;
     const uint64_t len = c->pend_len;
     CU(cudaStreamWaitEvent(c->stream, c->ev_copied, 0));               // every batch of this buffer has arrived
     if (len >= (uint64_t)c->k) {
@@ -542,6 +546,7 @@ extern "C" void kq_destroy(kq_ctx *c) {
     for (void *p : c->peer_opened) cudaIpcCloseMemHandle(p);
     cudaFree(c->d_peers);
     cudaFree(c->d_slab); cudaFree(c->d_rcursor); cudaFree(c->d_rback); cudaFree(c->d_rtotals);
+    cudaFree(c->d_vinbox); cudaFree(c->d_vrows); cudaFree(c->d_vcursor); cudaFree(c->d_vacc);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     delete c;
 }
@@ -948,6 +953,87 @@ extern "C" int kq_peer_disconnect(kq_ctx *c) {
     cudaFree(c->d_peers); c->d_peers = nullptr;
     c->exported = false;
     return KQ_OK;
+}
+
+// ---- routed validate: queries to the owners, rows back (row E) ------------------------------------------------
+
+extern "C" int kq_vroute_setup(kq_ctx *c, uint64_t chunk, void **d_inbox, void *ipc_inbox, void **d_rows, void *ipc_rows) {
+    if (!c || !chunk || chunk > 0xFFFFFFFFull) return KQ_EINVAL;
+    if (c->nranks > KQ_MAX_RANKS) return fail(c, KQ_EINVAL, "kq_vroute_setup: too many ranks");
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    cudaFree(c->d_vinbox); cudaFree(c->d_vrows); c->d_vinbox = nullptr; c->d_vrows = nullptr; c->vroute_ready = false;
+    const size_t qbytes = (size_t)c->nranks * chunk * 16;
+    CU(cudaMalloc(&c->d_vinbox, qbytes + KQ_MAX_RANKS * 8));
+    CU(cudaMemsetAsync(c->d_vinbox + qbytes, 0, KQ_MAX_RANKS * 8, c->stream));
+    CU(cudaMalloc(&c->d_vrows, chunk * sizeof(Base)));
+    if (!c->d_vcursor) {
+        CU(cudaMalloc(&c->d_vcursor, KQ_MAX_RANKS * 8)); CU(cudaMalloc(&c->d_vacc, 3 * 8));
+        CU(cudaMemsetAsync(c->d_vcursor, 0, KQ_MAX_RANKS * 8, c->stream)); CU(cudaMemsetAsync(c->d_vacc, 0, 3 * 8, c->stream));
+    }
+    CU(cudaStreamSynchronize(c->stream));
+    c->vcap = chunk;
+    if (d_inbox) *d_inbox = c->d_vinbox;
+    if (d_rows) *d_rows = c->d_vrows;
+    cudaIpcMemHandle_t h;
+    if (ipc_inbox) { CU(cudaIpcGetMemHandle(&h, c->d_vinbox)); std::memcpy(ipc_inbox, &h, sizeof h); }
+    if (ipc_rows) { CU(cudaIpcGetMemHandle(&h, c->d_vrows)); std::memcpy(ipc_rows, &h, sizeof h); }
+    return KQ_OK;
+}
+
+extern "C" int kq_vroute_connect(kq_ctx *c, void *const *inboxes, void *const *rows) {
+    if (!c || !inboxes || !rows || !c->d_vinbox) return KQ_EINVAL;
+    VRoute &v = c->vroute;
+    v = VRoute{};
+    v.nranks = c->nranks; v.me = c->rank; v.shift = view(c).shard_shift; v.cap = c->vcap; v.cursor = c->d_vcursor;
+    for (int r = 0; r < c->nranks; ++r) {
+        if (!inboxes[r] || !rows[r]) return fail(c, KQ_EINVAL, "kq_vroute_connect: NULL pointer");
+        v.inbox[r] = inboxes[r];
+        v.counts[r] = reinterpret_cast<unsigned long long *>(static_cast<unsigned char *>(inboxes[r]) + (size_t)c->nranks * c->vcap * 16);
+        v.rows[r] = static_cast<Base *>(rows[r]);
+    }
+    if (v.inbox[c->rank] != c->d_vinbox || v.rows[c->rank] != c->d_vrows) return fail(c, KQ_EINVAL, "kq_vroute_connect: entry [rank] is not this handle's buffer");
+    c->vroute_ready = true;
+    return KQ_OK;
+}
+
+extern "C" int kq_vroute_send(kq_ctx *c, const uint64_t *d_bases, const uint64_t *d_invalid, uint64_t base0, uint64_t c0, uint64_t n, uint64_t kcount) {
+    if (!c || (n && (!d_bases || !d_invalid))) return KQ_EINVAL;
+    if (!c->vroute_ready) return fail(c, KQ_ESTATE, "kq_vroute_send: call kq_vroute_connect first");
+    if (n > c->vcap) return fail(c, KQ_EINVAL, "kq_vroute_send: chunk larger than the one given to kq_vroute_setup");
+    CU(cudaSetDevice(c->device));
+    const int t = time_begin(c, 1);
+    CU(launch_vroute_send(c->stream, view(c), d_bases, d_invalid, base0, c0, n, kcount, c->d_vrows, c->d_vacc, c->vroute, &c->launches));
+    time_end(c, t);
+    return KQ_OK;
+}
+
+extern "C" int kq_vroute_answer(kq_ctx *c, uint32_t cutoff) {
+    if (!c) return KQ_EINVAL;
+    if (!c->vroute_ready) return fail(c, KQ_ESTATE, "kq_vroute_answer: call kq_vroute_connect first");
+    CU(cudaSetDevice(c->device));
+    const int t = time_begin(c, 1);
+    CU(launch_vroute_answer(c->stream, view(c), c->d_vinbox, c->vroute.counts[c->rank], (uint64_t)c->nranks * c->vcap, cutoff, c->d_vacc, c->vroute, &c->launches));
+    time_end(c, t);
+    return KQ_OK;
+}
+
+extern "C" int kq_vroute_rows(kq_ctx *c, kq_base **d_rows) {
+    if (!c || !d_rows || !c->d_vrows) return KQ_EINVAL;
+    *d_rows = reinterpret_cast<kq_base *>(c->d_vrows);
+    return KQ_OK;
+}
+
+// this rank's share of the QV counters since the last reset (sum over all ranks = the three totals)
+extern "C" int kq_vroute_counters(kq_ctx *c, kq_qv *acc, int reset) {
+    if (!c || !acc || !c->d_vacc) return KQ_EINVAL;
+    CU(cudaSetDevice(c->device));
+    unsigned long long h[3];
+    CU(cudaMemcpyAsync(h, c->d_vacc, sizeof h, cudaMemcpyDeviceToHost, c->stream));
+    if (reset) CU(cudaMemsetAsync(c->d_vacc, 0, sizeof h, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    acc->missing += h[0]; acc->kcount += h[1]; acc->edge_missing += h[2];
+    return check_device_error(c);
 }
 
 // ---- validate -----------------------------------------------------------------------------------------------
@@ -1772,3 +1858,5 @@ extern "C" int kq_db_read_records(const char *dir_c, uint64_t *keys, kq_rec32 *r
     *n = m;
     return KQ_OK;
 }
+
+#include "kq_multi.inl"

@@ -526,6 +526,104 @@ validate_kernel(TableView tv, const uint64_t *__restrict__ B, const uint64_t *__
     block_add(edge_missing, &acc3[2], &sh[2]);
 }
 
+// ---- validate across GPUs: queries to the owners, rows back (SURVEY 8e "Collective") -------------------------------
+//
+// Phase 1 (origin GPU): every valid window of the chunk becomes a 16-byte query {key, position, neighbours} appended
+// to the region this rank owns in the OWNER's inbox (peer-mapped memory: the stores are the all-to-all; cursors are
+// local, appends warp-aggregated).  Windows without a key (non-ACGT) and positions past the last window get their
+// row here.  Phase 2 (owner GPU): one thread per received query probes the owner's own table in its own HBM and
+// stores the finished 16-byte DBGbase row straight into the origin's row slab (peer store).  Only rows and queries
+// cross NVLink, in bulk-friendly streams; no GPU ever dereferences another GPU's table.
+
+__device__ __forceinline__ uint4 evaluate_row(const Rec32 &kh, int found, uint32_t cutoff, bool isFw, uint32_t nxt, uint32_t prv,
+                                              bool has_next, bool has_prev, unsigned long long &missing, unsigned long long &edge_missing) {
+    uint4 o = make_uint4(0, 0, 0, 0);                                                // fw, bw, cov, isFw
+    if (found) { o.z = kh.cov; o.w = isFw ? 1u : 0u; }                               // src/kreeq.cpp:168-169
+    if (o.z == 0 || o.z < cutoff) { ++missing; return o; }                           // :172-175
+    bool no_left = false, no_right = false;
+    if (isFw) {                                                                      // :178-192
+        if (has_next) { const uint32_t v = nxt <= 3 ? kh.fw[nxt] : 0; if (v) o.x = v; else no_right = true; }
+        if (has_prev) { const uint32_t v = prv <= 3 ? kh.bw[prv] : 0; if (v) o.y = v; else no_left = true; }
+    } else {                                                                         // :194-210
+        if (has_prev) { const uint32_t v = prv <= 3 ? kh.fw[3 - prv] : 0; if (v) o.x = v; else no_left = true; }
+        if (has_next) { const uint32_t v = nxt <= 3 ? kh.bw[3 - nxt] : 0; if (v) o.y = v; else no_right = true; }
+    }
+    if (no_left && no_right) ++edge_missing;                                         // :211-214
+    return o;
+}
+
+__global__ void __launch_bounds__(TPB, CTAS_PER_SM)
+vroute_send_kernel(TableView tv, const uint64_t *__restrict__ B, const uint64_t *__restrict__ M, uint64_t base0, uint64_t c0,
+                   uint64_t n, uint64_t kcount, Base *__restrict__ rows, unsigned long long *acc3, VRoute vr) {
+    __shared__ unsigned long long sh[2];
+    if (threadIdx.x < 2) sh[threadIdx.x] = 0;
+    __syncthreads();
+    unsigned long long missing = 0, counted = 0;
+    const unsigned lane = threadIdx.x & 31;
+    const uint64_t stride = (uint64_t)gridDim.x * TPB, rounds = (n + stride - 1) / stride;
+    for (uint64_t r = 0; r < rounds; ++r) {                          // warp-uniform trip count (match_any below)
+        const uint64_t i = r * stride + (uint64_t)blockIdx.x * TPB + threadIdx.x;
+        int dest = -1; Kmer km; km.key = 0;
+        if (i < n) {
+            const uint64_t c = c0 + i;
+            if (c < kcount) {
+                km = kmer_at(B, M, c - base0, tv.k);
+                if (km.valid) dest = (int)((km.key & 127) >> vr.shift);
+                else { ++missing; ++counted; }                        // never found; still counts (kreeq.cpp:216)
+            }
+            if (dest < 0) __stcs(reinterpret_cast<uint4 *>(rows) + i, make_uint4(0, 0, 0, 0));
+        }
+        const unsigned peers = __match_any_sync(0xffffffffu, dest);
+        if (dest < 0) continue;
+        const unsigned leader = __ffs(peers) - 1;
+        unsigned long long slot = 0;
+        if (lane == leader) slot = atomicAdd(&vr.cursor[dest], (unsigned long long)__popc(peers));
+        slot = __shfl_sync(peers, slot, leader) + __popc(peers & ((1u << lane) - 1));
+        const uint64_t c = c0 + i;
+        const unsigned meta = km.nxt | km.prv << 3 | (km.isFw ? 64u : 0u) | (c < kcount - 1 ? 128u : 0u) | (c > 0 ? 256u : 0u);
+        uint4 q; q.x = (unsigned)km.key; q.y = (unsigned)(km.key >> 32); q.z = (unsigned)i; q.w = meta;
+        reinterpret_cast<uint4 *>(vr.inbox[dest])[(uint64_t)vr.me * vr.cap + slot] = q;
+    }
+    block_add(missing, &acc3[0], &sh[0]);
+    block_add(counted, &acc3[1], &sh[1]);
+}
+
+// after the send kernel: tell every owner how many queries this rank left in its inbox, reset the cursors
+__global__ void vroute_publish_kernel(VRoute vr) {
+    const int o = threadIdx.x;
+    if (o < vr.nranks) { vr.counts[o][vr.me] = vr.cursor[o]; vr.cursor[o] = 0; }
+}
+
+__global__ void __launch_bounds__(TPB, 8)
+vroute_answer_kernel(TableView tv, const uint4 *__restrict__ inbox, const unsigned long long *__restrict__ counts, uint32_t cutoff,
+                     unsigned long long *acc3, VRoute vr) {
+    __shared__ unsigned long long sh[3], first[KQ_MAX_RANKS + 1];
+    if (threadIdx.x < 3) sh[threadIdx.x] = 0;
+    if (threadIdx.x == 0) {
+        unsigned long long run = 0;
+        for (int s = 0; s < vr.nranks; ++s) { first[s] = run; run += counts[s]; }
+        first[vr.nranks] = run;
+    }
+    __syncthreads();
+    unsigned long long missing = 0, counted = 0, edge_missing = 0;
+    const uint64_t total = first[vr.nranks], stride = (uint64_t)gridDim.x * TPB;
+    for (uint64_t j = (uint64_t)blockIdx.x * TPB + threadIdx.x; j < total; j += stride) {
+        int s = 0;
+        while (j >= first[s + 1]) ++s;
+        const uint4 q = __ldcs(inbox + (uint64_t)s * vr.cap + (j - first[s]));
+        const uint64_t key = (uint64_t)q.y << 32 | q.x;
+        Rec32 kh; int found = lookup(tv, key, kh);
+        if (found < 0) { atomicOr(tv.err, 4); found = 0; }
+        const uint4 o = evaluate_row(kh, found, cutoff, (q.w & 64u) != 0, q.w & 7u, (q.w >> 3) & 7u, (q.w & 128u) != 0, (q.w & 256u) != 0,
+                                     missing, edge_missing);
+        ++counted;
+        reinterpret_cast<uint4 *>(vr.rows[s])[q.z] = o;              // the origin's row slab (peer store)
+    }
+    block_add(missing, &acc3[0], &sh[0]);
+    block_add(counted, &acc3[1], &sh[1]);
+    block_add(edge_missing, &acc3[2], &sh[2]);
+}
+
 __global__ void __launch_bounds__(TPB, CTAS_PER_SM)
 lookup_kernel(TableView tv, const uint64_t *__restrict__ keys, uint64_t n, Rec32 *rec, uint8_t *found) {
     const uint64_t stride = (uint64_t)gridDim.x * TPB;
@@ -710,6 +808,24 @@ cudaError_t launch_validate(cudaStream_t st, const TableView &tv, const uint64_t
     const unsigned grid = (unsigned)std::min<uint64_t>((n + TPB - 1) / TPB, (uint64_t)sm_count() * ctas);
     if (ctas > CTAS_PER_SM) validate_kernel<8><<<grid, TPB, 0, st>>>(tv, B, M, base0, c0, n, kcount, cutoff, out, acc3, peers, npeers);
     else validate_kernel<CTAS_PER_SM><<<grid, TPB, 0, st>>>(tv, B, M, base0, c0, n, kcount, cutoff, out, acc3, peers, npeers);
+    ++*launches;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_vroute_send(cudaStream_t st, const TableView &tv, const uint64_t *B, const uint64_t *M, uint64_t base0,
+                               uint64_t c0, uint64_t n, uint64_t kcount, Base *rows, unsigned long long *acc3, const VRoute &vr,
+                               uint64_t *launches) {
+    if (n) { vroute_send_kernel<<<grid_for(n), TPB, 0, st>>>(tv, B, M, base0, c0, n, kcount, rows, acc3, vr); ++*launches; }
+    vroute_publish_kernel<<<1, 32, 0, st>>>(vr);                      // also for an empty chunk: the owners read the counts
+    ++*launches;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_vroute_answer(cudaStream_t st, const TableView &tv, const void *inbox, const unsigned long long *counts,
+                                 uint64_t max_queries, uint32_t cutoff, unsigned long long *acc3, const VRoute &vr, uint64_t *launches) {
+    if (!max_queries) return cudaSuccess;
+    const unsigned grid = (unsigned)std::min<uint64_t>((max_queries + TPB - 1) / TPB, (uint64_t)sm_count() * 8);
+    vroute_answer_kernel<<<grid, TPB, 0, st>>>(tv, static_cast<const uint4 *>(inbox), counts, cutoff, acc3, vr);
     ++*launches;
     return cudaGetLastError();
 }

@@ -47,6 +47,17 @@ struct RouteMap {
     uint64_t *out[KQ_MAX_RANKS];
 };
 
+// routed validate: where a rank's queries go (the owners' inboxes) and where an owner's answers go (the origins'
+// row slabs); every pointer is mapped into this rank's address space (peer access or CUDA IPC)
+struct VRoute {
+    int nranks, me, shift;                         // owner = (key & 127) >> shift
+    unsigned long long cap;                        // queries per (owner, sender) region of an inbox
+    void *inbox[KQ_MAX_RANKS];                     // inbox[o] + (me * cap + slot) * 16
+    unsigned long long *counts[KQ_MAX_RANKS];      // counts[o][me] = queries this rank left at owner o
+    Base *rows[KQ_MAX_RANKS];                      // rows[s][position] = row slab of origin s
+    unsigned long long *cursor;                    // local append cursors, one per owner
+};
+
 int sm_count();   // multiprocessors of the current device (cached)
 
 // tuning knobs (defaults are the measured best on B200); kq_set_tuning changes them
@@ -136,6 +147,12 @@ cudaError_t launch_extract_route(cudaStream_t st, const TableView &tv, const Sou
 cudaError_t launch_validate(cudaStream_t st, const TableView &tv, const uint64_t *B, const uint64_t *M,
                             uint64_t base0, uint64_t c0, uint64_t n, uint64_t kcount, uint32_t cutoff,
                             Base *out, unsigned long long *acc3, const TableView *peers, int npeers, uint64_t *launches);
+// routed validate: phase 1 on the origin (queries -> owners' inboxes, counts published), phase 2 on the owner
+cudaError_t launch_vroute_send(cudaStream_t st, const TableView &tv, const uint64_t *B, const uint64_t *M, uint64_t base0,
+                               uint64_t c0, uint64_t n, uint64_t kcount, Base *rows, unsigned long long *acc3, const VRoute &vr,
+                               uint64_t *launches);
+cudaError_t launch_vroute_answer(cudaStream_t st, const TableView &tv, const void *inbox, const unsigned long long *counts,
+                                 uint64_t max_queries, uint32_t cutoff, unsigned long long *acc3, const VRoute &vr, uint64_t *launches);
 cudaError_t launch_lookup(cudaStream_t st, const TableView &tv, const uint64_t *keys, uint64_t n, Rec32 *rec,
                           uint8_t *found, uint64_t *launches);
 
