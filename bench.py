@@ -427,7 +427,15 @@ def main_ours(args):
     # multi-GPU validate probes the owners' shards over peer memory; the peers' tables are mapped once (first
     # warm-up step, reported as peer_connect_ms) and stay mapped: the steady-state steps refill tables that
     # do not move
-    peers = shard.PeerTables(g, world, dev, keep=True) if world > 1 else None
+    vmode = os.environ.get("KQ_VALIDATE", "routed") if world > 1 else None     # "peer": probe the owners' tables over NVLink loads
+    peers = shard.PeerTables(g, world, dev, keep=True) if vmode == "peer" else None
+    router_v = shard.RoutedValidator(g, rank, world, contig, dev) if vmode == "routed" else None
+    v_bufs = []
+    if router_v is not None and not args.no_e2e:
+        words = L.kq_packed_words(contig)
+        for _ in range(2):
+            v_bufs.append((torch.empty(words, dtype=torch.int64, pin_memory=True), torch.empty(words, dtype=torch.int64, pin_memory=True),
+                           torch.empty(words, dtype=torch.int64, device=dev), torch.empty(words, dtype=torch.int64, device=dev), torch.cuda.Event()))
     e2e_bufs = []
     if world > 1 and not args.no_e2e:
         words = L.kq_packed_words(5 * 64 * (READ_LEN + 1) * 10000)
@@ -455,8 +463,15 @@ def main_ours(args):
         if world == 1:
             validate_contigs()
             return
-        # every rank validates its own genome; each k-mer is probed in its owner's shard over peer memory
-        # (mapping the peers' tables is part of the step), only the three QV counters are reduced
+        if router_v is not None:
+            # every rank validates its own genome: queries are routed to the owners, rows come back (two stream
+            # barriers per contig); only the three QV counters are reduced
+            g.finalize()
+            for b, m in d_asm:
+                router_v.chunk_packed(b, m, contig)
+            router_v.counters()
+            return
+        # KQ_VALIDATE=peer: each k-mer is probed in its owner's shard over peer memory
         with peers:
             validate_contigs()
             dist.all_reduce(d_acc)
@@ -498,7 +513,22 @@ def main_ours(args):
                 seg = np.ascontiguousarray(asm[i * clen:(i + 1) * clen])
                 check(L.kq_validate_segment(g.handle, C.c_void_p(seg.ctypes.data), clen, 0, C.c_void_p(out.ctypes.data), C.byref(acc)), g.handle)
                 rows = pc.add_mod64(rows, pc.rows_digest(out, i * clen))
-        if world > 1:
+        if router_v is not None:
+            rounds = (want["contigs"] + world - 1) // world
+            for r_ in range(rounds):
+                i = r_ * world + rank
+                if i < want["contigs"]:
+                    b, m = pack_to_device(np.ascontiguousarray(asm[i * clen:(i + 1) * clen]))
+                    router_v.chunk_packed(b, m, clen)
+                    check(L.kq_vroute_copy_rows(g.handle, C.c_void_p(out.ctypes.data), clen), g.handle)
+                    torch.cuda.current_stream().synchronize()
+                    rows = pc.add_mod64(rows, pc.rows_digest(out, i * clen))
+                else:
+                    router_v.chunk_packed(None, None, 0)
+            qv_all = router_v.counters()
+            if rank == 0:                           # counters() is already the sum over ranks
+                acc.missing, acc.kcount, acc.edge_missing = qv_all
+        elif world > 1:
             with peers:
                 vloop()
         else:
@@ -556,7 +586,21 @@ def main_ours(args):
                 seg = asm_np[i * contig:(i + 1) * contig]
                 check(L.kq_validate_segment(g.handle, C.c_void_p(seg.ctypes.data), contig, 0,
                                             C.c_void_p(h_out.ctypes.data), C.byref(acc)), g.handle)
-        if world > 1:
+        def validate_host_routed():
+            # pack on the host, copy in, route the queries, copy the rows of this rank's slab out
+            for i in range(n_contigs):
+                seg = asm_np[i * contig:(i + 1) * contig]
+                hb, hm, db, dm, done = v_bufs[i % 2]
+                done.synchronize()
+                check(L.kq_pack_host(C.c_void_p(seg.ctypes.data), contig, C.c_void_p(hb.data_ptr()), C.c_void_p(hm.data_ptr()), 0))
+                db.copy_(hb, non_blocking=True); dm.copy_(hm, non_blocking=True)
+                done.record(stream)
+                router_v.chunk_packed(db, dm, contig)
+                check(L.kq_vroute_copy_rows(g.handle, C.c_void_p(h_out.ctypes.data), contig), g.handle)
+            router_v.counters()
+        if router_v is not None:
+            validate_host_routed()
+        elif world > 1:
             with peers:
                 validate_host()
         else:
@@ -643,9 +687,10 @@ def main_ours(args):
                             "pipeline_ms_per_step": res["kt_pipe"] / args.steps}
         if res["kn_val"]:
             vs = res["kt_val"] * 1e-3 / res["kn_val"]
-            va = ALG_BYTES_VALIDATE * (asm_k * args.steps / res["kn_val"]) / vs / 1e9
-            line["validate"]["roofline"] = {"bound": "hbm", "kernel": "validate_kernel", "achieved": va, "peak": peak,
-                                            "unit": "GB/s", "frac": va / peak, "avg_launch_ms": vs * 1e3}
+            va = ALG_BYTES_VALIDATE * asm_k * args.steps / (res["kt_val"] * 1e-3) / 1e9      # this rank's positions / its kernels' time
+            line["validate"]["roofline"] = {"bound": "hbm", "kernel": "validate_kernel" if world == 1 or vmode == "peer" else "vroute_send_kernel + vroute_answer_kernel",
+                                            "achieved": va, "peak": peak, "unit": "GB/s", "frac": va / peak, "avg_launch_ms": vs * 1e3,
+                                            "launches_timed": res["kn_val"]}
     try:
         line["config"]["distinct_kmers"] = g.distinct() if world == 1 else None
     except Exception:
@@ -669,6 +714,8 @@ def main_ours(args):
                              "files_on": u["files_on"], "mode": "reference-compatible (kq_union ..., 1)"}
         except Exception as ex:                       # never lose the main line to the side measurement
             line["union"] = {"error": str(ex)[:200]}
+    if world > 1:
+        line["validate"]["exchange"] = vmode
     if peers is not None:
         line["validate"]["peer_connect_ms"] = peers.connect_ms
         peers.disconnect()

@@ -234,6 +234,7 @@ int  kq_vroute_connect(kq_ctx *ctx, void *const *inboxes, void *const *rows);
 int  kq_vroute_send(kq_ctx *ctx, const uint64_t *d_bases, const uint64_t *d_invalid, uint64_t base0, uint64_t c0, uint64_t n, uint64_t kcount);
 int  kq_vroute_answer(kq_ctx *ctx, uint32_t cov_cutoff);
 int  kq_vroute_rows(kq_ctx *ctx, kq_base **d_rows);
+int  kq_vroute_copy_rows(kq_ctx *ctx, kq_base *host_dst, uint64_t n);      /* slab rows [0, n) -> host, async on the stream */
 int  kq_vroute_counters(kq_ctx *ctx, kq_qv *acc, int reset);
 
 /* ---- all GPUs of one box behind one handle (SURVEY 5.6 `--gpus N`, 8b kq_create(..., ngpus, ...)) ---------------

@@ -90,6 +90,7 @@ PROTOTYPES = {
     "kq_vroute_send": (_i, [_vp, _vp, _vp, _u64, _u64, _u64, _u64]),
     "kq_vroute_answer": (_i, [_vp, C.c_uint32]),
     "kq_vroute_rows": (_i, [_vp, C.POINTER(_vp)]),
+    "kq_vroute_copy_rows": (_i, [_vp, _vp, _u64]),
     "kq_vroute_counters": (_i, [_vp, C.POINTER(KqQV), _i]),
     "kq_multi_create": (_i, [C.POINTER(_vp), _i, _i, C.POINTER(_i), _u64]),
     "kq_multi_destroy": (None, [_vp]),

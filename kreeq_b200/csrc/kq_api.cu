@@ -1024,6 +1024,15 @@ extern "C" int kq_vroute_rows(kq_ctx *c, kq_base **d_rows) {
     return KQ_OK;
 }
 
+// rows [0, n) of this rank's slab -> host memory, asynchronously on the handle's stream
+extern "C" int kq_vroute_copy_rows(kq_ctx *c, kq_base *host_dst, uint64_t n) {
+    if (!c || !host_dst || !c->d_vrows || n > c->vcap) return KQ_EINVAL;
+    CU(cudaSetDevice(c->device));
+    CU(cudaMemcpyAsync(host_dst, c->d_vrows, n * sizeof(Base), cudaMemcpyDeviceToHost, c->stream));
+    c->d2h += n * sizeof(Base);
+    return KQ_OK;
+}
+
 // this rank's share of the QV counters since the last reset (sum over all ranks = the three totals)
 extern "C" int kq_vroute_counters(kq_ctx *c, kq_qv *acc, int reset) {
     if (!c || !acc || !c->d_vacc) return KQ_EINVAL;

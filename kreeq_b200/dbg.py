@@ -205,3 +205,120 @@ def db_read_records(db_dir):
     recs = np.zeros(n.value, dtype=REC32)
     check(lib().kq_db_read_records(str(db_dir).encode(), ptr(keys), ptr(recs), C.byref(n)))
     return keys, recs
+
+
+class MultiDBG:
+    """Same interface as DBG over kq_multi: one handle, `ngpus` shards of the key space, one per GPU of this
+    process (devices = CUDA ordinals, may repeat: every shard on one GPU runs the same code path).  Replaces the
+    reference's 128 host maps (gfalibs/include/kmer.h:126-153) by shard g = maps [g*128/G, (g+1)*128/G)."""
+
+    def __init__(self, k=21, ngpus=0, devices=None, expected_distinct=0, round_positions=0, validate_chunk=0):
+        self.k = int(k)
+        self._h = C.c_void_p()
+        dev = None
+        if devices is not None:
+            ngpus = len(devices)
+            dev = (C.c_int * ngpus)(*devices)
+        rc = lib().kq_multi_create(C.byref(self._h), self.k, int(ngpus), dev, int(expected_distinct))
+        if rc != 0:
+            self._h = C.c_void_p()
+            msg = lib().kq_multi_last_error(None)
+            raise _lib.KreeqError(rc, msg.decode() if msg else "")
+        self.ngpus = lib().kq_multi_ngpus(self._h)
+        if round_positions or validate_chunk:
+            self._check(lib().kq_multi_set_round(self._h, int(round_positions), int(validate_chunk)))
+        self.tot_missing = self.tot_kcount = self.tot_edge_missing = 0
+
+    def _check(self, rc):
+        if rc != 0:
+            msg = lib().kq_multi_last_error(self._h)
+            raise _lib.KreeqError(rc, msg.decode() if msg else "")
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            lib().kq_multi_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def shard(self, g):
+        return C.c_void_p(lib().kq_multi_shard(self._h, g))
+
+    def traverseInReads(self, batch):
+        if isinstance(batch, np.ndarray):
+            a = np.ascontiguousarray(batch, dtype=np.uint8)
+            self._check(lib().kq_multi_count_push(self._h, ptr(a), a.size))
+        else:
+            b = bytes(batch)
+            self._check(lib().kq_multi_count_push(self._h, C.cast(C.c_char_p(b), C.c_void_p), len(b)))
+
+    def finalize(self):
+        self._check(lib().kq_multi_count_finish(self._h))
+
+    def clear(self):
+        self._check(lib().kq_multi_clear(self._h))
+        self.tot_missing = self.tot_kcount = self.tot_edge_missing = 0
+
+    def instances(self):
+        n = C.c_uint64()
+        self._check(lib().kq_multi_count_instances(self._h, C.byref(n)))
+        return n.value
+
+    def stats(self):
+        s = KqStats()
+        self._check(lib().kq_multi_stats_get(self._h, C.byref(s)))
+        return {n: getattr(s, n) for n, _ in KqStats._fields_}
+
+    def hist(self):
+        n = C.c_size_t(0)
+        self._check(lib().kq_multi_hist(self._h, None, None, C.byref(n)))
+        cov = np.zeros(n.value, dtype=np.uint64)
+        cnt = np.zeros(n.value, dtype=np.uint64)
+        self._check(lib().kq_multi_hist(self._h, ptr(cov), ptr(cnt), C.byref(n)))
+        return cov, cnt
+
+    def export(self):
+        n = C.c_size_t(0)
+        self._check(lib().kq_multi_export(self._h, None, None, C.byref(n)))
+        keys = np.zeros(n.value, dtype=np.uint64)
+        recs = np.zeros(n.value, dtype=REC32)
+        self._check(lib().kq_multi_export(self._h, ptr(keys), ptr(recs), C.byref(n)))
+        return keys, recs
+
+    def save(self, db_dir):
+        self._check(lib().kq_multi_db_save(self._h, str(db_dir).encode()))
+
+    def load(self, db_dir):
+        self._check(lib().kq_multi_db_load(self._h, str(db_dir).encode()))
+
+    def kunion(self, db_dirs, ref_compatible=True):
+        arr = (C.c_char_p * len(db_dirs))(*[str(d).encode() for d in db_dirs])
+        self._check(lib().kq_multi_union(self._h, arr, len(db_dirs), 1 if ref_compatible else 0))
+
+    def evaluateSegment(self, seq, cov_cutoff=0, out=None):
+        a = np.ascontiguousarray(seq, dtype=np.uint8) if isinstance(seq, np.ndarray) else np.frombuffer(bytes(seq), dtype=np.uint8)
+        if out is None:
+            out = np.zeros(a.size, dtype=BASE)
+        q = KqQV()
+        self._check(lib().kq_multi_validate_segment(self._h, ptr(a), a.size, int(cov_cutoff), ptr(out), C.byref(q)))
+        self.tot_missing += q.missing
+        self.tot_kcount += q.kcount
+        self.tot_edge_missing += q.edge_missing
+        return out[:a.size]
+
+    def find(self, keys):
+        keys = np.ascontiguousarray(keys, dtype=np.uint64)
+        rec = np.zeros(keys.size, dtype=REC32)
+        found = np.zeros(keys.size, dtype=np.uint8)
+        self._check(lib().kq_multi_lookup_batch(self._h, ptr(keys), keys.size, ptr(rec), ptr(found)))
+        return rec, found.astype(bool)

@@ -237,3 +237,62 @@ class PeerTables:
         else:
             self.disconnect()
         return False
+
+
+class RoutedValidator:
+    """Validate against a key-sharded table with routed queries (kq_vroute_*, SURVEY 8e "Collective"): per chunk of
+    assembly positions every rank sends 16-byte (key, position, neighbours) queries into the OWNERS' inboxes (peer
+    stores from the send kernel), the owners probe their own HBM and store the finished DBGbase rows into the
+    origins' row slabs; two stream barriers per chunk, no rank ever reads another rank's table.
+
+    One process per GPU: inboxes and row slabs are exchanged once as CUDA IPC handles.  Every call is collective
+    (ranks without a chunk pass length 0).  The library's stream must be the stream the collectives run on."""
+
+    def __init__(self, dbg, rank, nranks, chunk, device, group=None):
+        L = lib()
+        self.g, self.rank, self.n, self.chunk, self.device, self.group = dbg, rank, nranks, int(chunk), device, group
+        inbox, rows = C.c_void_p(), C.c_void_p()
+        h_in, h_rows = (C.c_ubyte * 64)(), (C.c_ubyte * 64)()
+        check(L.kq_vroute_setup(dbg.handle, self.chunk, C.byref(inbox), h_in, C.byref(rows), h_rows), dbg.handle)
+        mine = torch.tensor(list(h_in) + list(h_rows), dtype=torch.uint8, device=device)
+        allh = torch.empty(nranks * 128, dtype=torch.uint8, device=device)
+        dist.all_gather_into_tensor(allh, mine, group=group)
+        allh = allh.cpu().numpy().reshape(nranks, 2, 64)
+        pin, prow = (C.c_void_p * nranks)(), (C.c_void_p * nranks)()
+        for r in range(nranks):
+            if r == rank:
+                pin[r], prow[r] = inbox.value, rows.value
+                continue
+            for k_, dst in ((0, pin), (1, prow)):
+                p = C.c_void_p()
+                check(L.kq_route_open(dbg.handle, C.c_void_p(allh[r, k_].ctypes.data), C.byref(p)), dbg.handle)
+                dst[r] = p.value
+        check(L.kq_vroute_connect(dbg.handle, pin, prow), dbg.handle)
+        self.rows_ptr = rows.value
+        self.flag = torch.zeros(1, dtype=torch.int32, device=device)
+        self.acc = torch.zeros(3, dtype=torch.int64, device=device)
+        dist.barrier(group=group)                    # every rank is connected before the first query is stored
+
+    def _barrier(self):
+        dist.all_reduce(self.flag, group=self.group)
+
+    def chunk_packed(self, d_bases, d_invalid, length, cutoff=0):
+        """One chunk: a whole packed device-resident segment of `length` <= chunk bases (0: take part empty-handed).
+        Afterwards rows [0, length) of this rank's slab (rows_ptr, kq_base) hold the segment's DBGbase rows."""
+        g, L = self.g, lib()
+        kcount = max(0, length - g.k + 1)
+        pb = C.c_void_p(d_bases.data_ptr()) if length else None
+        pi = C.c_void_p(d_invalid.data_ptr()) if length else None
+        check(L.kq_vroute_send(g.handle, pb, pi, 0, 0, length, kcount), g.handle)
+        self._barrier()                               # every inbox is complete
+        check(L.kq_vroute_answer(g.handle, cutoff), g.handle)
+        self._barrier()                               # every row slab is complete, the inboxes are free again
+
+    def counters(self, reset=True):
+        """the three QV counters summed over all ranks (collective)"""
+        from ._lib import KqQV
+        q = KqQV()
+        check(lib().kq_vroute_counters(self.g.handle, C.byref(q), 1 if reset else 0), self.g.handle)
+        t = torch.tensor([q.missing, q.kcount, q.edge_missing], dtype=torch.int64, device=self.device)
+        dist.all_reduce(t, group=self.group)
+        return [int(x) for x in t.tolist()]
