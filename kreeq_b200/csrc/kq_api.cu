@@ -92,6 +92,7 @@ struct kq_ctx {
     // routed (multi-GPU) pipeline: receive slab the owners' tuples are written into by every rank
     uint64_t *d_slab = nullptr; uint64_t slab_cap = 0;          // tuples
     RouteMap route{}; bool route_ready = false;
+    uint64_t route_extent = 0; unsigned route_task_bound = 0, route_ns_max = 0;   // tasks over the slab of the last kq_route_scatter (0 = none)
     std::vector<void *> ipc_opened;
     unsigned long long *d_rcursor = nullptr, *d_rback = nullptr, *d_rtotals = nullptr; uint64_t route_real = 0;
     // peer tables (multi-GPU validate): views of every rank's shard, mapped into this process
@@ -257,7 +258,7 @@ void time_collect(kq_ctx *c) {
 
 namespace {
 
-int pipeline_scratch(kq_ctx *c, uint64_t tuples, bool level2 = false) {
+int pipeline_scratch(kq_ctx *c, uint64_t tuples, bool level2 = false, uint64_t tuples2 = 0) {
     const uint64_t nbins = coarse_bins(view(c));
     if (c->hist_cap < nbins) {
         cudaFree(c->d_hist); cudaFree(c->d_cursor); cudaFree(c->d_cstart); c->d_hist = c->d_cursor = c->d_cstart = nullptr; c->hist_cap = 0;
@@ -271,17 +272,18 @@ int pipeline_scratch(kq_ctx *c, uint64_t tuples, bool level2 = false) {
         c->tup_cap = tuples;
     }
     if (!level2) return KQ_OK;
-    if (c->tup2_cap < tuples) {
+    if (!tuples2) tuples2 = tuples;
+    if (c->tup2_cap < tuples2) {
         cudaFree(c->d_tuples2); c->d_tuples2 = nullptr; c->tup2_cap = 0;
-        CU(cudaMalloc(&c->d_tuples2, tuples * 8 * tuple_words(c->k)));
-        c->tup2_cap = tuples;
+        CU(cudaMalloc(&c->d_tuples2, tuples2 * 8 * tuple_words(c->k)));
+        c->tup2_cap = tuples2;
     }
     if (c->fine_cap < c->nslices) {
         cudaFree(c->d_fhist); cudaFree(c->d_fcursor); cudaFree(c->d_fstart); c->d_fhist = c->d_fcursor = c->d_fstart = nullptr; c->fine_cap = 0;
         CU(cudaMalloc(&c->d_fhist, c->nslices * 8)); CU(cudaMalloc(&c->d_fcursor, c->nslices * 8)); CU(cudaMalloc(&c->d_fstart, c->nslices * 8));
         c->fine_cap = c->nslices;
     }
-    const uint64_t tasks = tuples / tuning().part + nbins + 1;
+    const uint64_t tasks = std::max(tuples, tuples2) / tuning().part + std::max<uint64_t>(nbins, KQ_MAX_COARSE) + 1;
     if (c->task_cap < tasks) {
         cudaFree(c->d_tasks); c->d_tasks = nullptr; c->task_cap = 0;
         CU(cudaMalloc(&c->d_tasks, tasks * sizeof(FineTask)));
@@ -338,6 +340,28 @@ int run_batch(kq_ctx *c, Source src) {
     { int rc = pipeline_scratch(c, 0); if (rc) return rc; }
     c->ovf_list = nullptr; c->ovf_list_cap = 0;
     const int t0 = time_begin(c, 0);
+    // routed pipeline: the slab is in bin order already, its tasks were planned by kq_route_scatter
+    if (src.ordered && c->route_task_bound && bound == c->route_extent && c->nslices > 1 && tuning().smem_insert && c->slice_bits <= 13 &&
+        fine_pick_cap(c->route_ns_max, tw) != 0) {
+        int rc = pipeline_scratch(c, 0, true, bound); if (rc) return rc;
+        const int t4 = time_begin(c, 4);
+        CU(cudaMemsetAsync(c->d_fhist, 0, c->nslices * 8, c->stream));
+        CU(launch_fine_hist(c->stream, tv, src.tuples, c->d_tasks, c->d_ntasks, c->route_task_bound, c->route_ns_max, c->d_fhist, &c->launches));
+        CU(launch_slice_offsets(c->stream, c->nslices, c->d_fhist, c->d_fcursor, c->d_fstart, c->d_total, nullptr, &c->launches));
+        const int t6 = time_begin(c, 6);
+        CU(launch_fine_scatter(c->stream, tv, src.tuples, c->d_tasks, c->d_ntasks, c->route_task_bound, c->route_ns_max, c->d_tuples2, c->d_fcursor, &c->launches));
+        time_end(c, t6);
+        time_end(c, t4);
+        const int t2 = time_begin(c, 2);
+        // tuples of full slices go back into the slab (read completely by now, as large as the batch)
+        CU(launch_smem_insert(c->stream, tv, c->d_tuples2, c->d_fstart, c->d_fhist, c->d_slab, c->slab_cap, c->d_ovf_n, c->d_ticket, &c->launches));
+        time_end(c, t2);
+        c->ovf_list = c->d_slab; c->ovf_list_cap = c->slab_cap;
+        c->ovf_pending = true;
+        c->route_task_bound = 0;
+        time_end(c, t0);
+        return KQ_OK;
+    }
     // a sweep over the table pays off once the batch touches a good part of it
     if (src.ordered || c->nslices == 1 || cap == 0 || (double)bound * 100.0 < (double)tuning().direct_pct * (double)table_slots(c)) {
         if (src.tuples) {
@@ -631,6 +655,8 @@ extern "C" int kq_set_tuning(const char *name, long long value) {
     else if (n == "insert_ctas" && value >= 1 && value <= 8) t.insert_ctas = (int)value;
     else if (n == "validate_ctas" && value >= 1 && value <= 8) t.validate_ctas = (int)value;
     else if (n == "db_host" && (value == 0 || value == 1)) t.db_host = (int)value;
+    else if (n == "s3_threads" && (value == 256 || value == 384 || value == 512)) t.s3_threads = (int)value;
+    else if (n == "s3_ctas" && value >= 1 && value <= 8) t.s3_ctas = (int)value;
     else return KQ_EINVAL;
     return KQ_OK;
 }
@@ -858,6 +884,17 @@ extern "C" int kq_route_scatter(kq_ctx *c, const uint64_t *d_bases, const uint64
         }
     CU(launch_route_scatter(c->stream, view(c), Source{d_bases, d_invalid, pos0, npos, nullptr, nullptr, 0, 0}, c->route, c->d_rcursor, c->d_rback, cap, &c->launches));
     time_end(c, t);
+    // what this rank receives goes through the level-2 scatter and the shared-memory insert: plan its tasks from the
+    // same histograms (bin extents inside the slab, slices a bin's hash range maps to on the local table)
+    c->route_task_bound = 0;
+    if (c->nslices > 1 && totals[c->rank] && (1 << c->route.nb_bits) <= KQ_ROUTE_PLAN_BINS) {
+        const unsigned nb = 1u << c->route.nb_bits;
+        c->route_ns_max = (unsigned)(c->nslices / nb + 2);
+        int rc = pipeline_scratch(c, 0, true, totals[c->rank]); if (rc) return rc;
+        const unsigned bound = (unsigned)std::min<uint64_t>(c->task_cap, totals[c->rank] / tuning().part + nb + 1);
+        CU(launch_route_plan(c->stream, view(c), c->route, c->rank, cap, d_all_hist, tuning().part, c->d_tasks, bound, c->d_ntasks, &c->launches));
+        c->route_task_bound = bound; c->route_extent = totals[c->rank];
+    }
     c->route_real = totals[c->nranks + c->rank];
     *nrecv = totals[c->rank];
     return KQ_OK;

@@ -33,6 +33,17 @@ template <int TW> __device__ __forceinline__ void t_store(uint64_t *t, uint64_t 
     else reinterpret_cast<ulonglong2 *>(t)[i] = make_ulonglong2(key, e);
 }
 
+// raw tuple words (prefetched one round ahead of their use)
+template <int TW> __device__ __forceinline__ ulonglong2 t_raw(const uint64_t *t, uint64_t i) {
+    if (TW == 1) return make_ulonglong2(__ldcs(t + i), 0ULL);
+    return __ldcs(reinterpret_cast<const ulonglong2 *>(t) + i);
+}
+template <int TW> __device__ __forceinline__ void t_split(const ulonglong2 &w, uint64_t &key, uint32_t &e) {
+    if (TW == 1) { key = w.x >> 8; e = (uint32_t)w.x & 255u; }
+    else { key = w.x; e = (uint32_t)w.y & 255u; }
+}
+constexpr unsigned long long T_PAD1 = ~0ULL;       // a tuple word that unpacks to edge byte 0xFF (= "no tuple")
+
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 }  // namespace
@@ -61,6 +72,40 @@ fine_plan_kernel(TableView tv, unsigned ncoarse, const unsigned long long *start
         unsigned t = first[b];
         for (unsigned long long a = lo; a < hi && t < task_cap; a += part, ++t)
             tasks[t] = FineTask{a, min(hi, a + part), s_lo, ns};
+    }
+}
+
+// Routed (multi-GPU) pipeline: the receive slab of rank `me` is laid out bin by bin ((owner, hash range) bins,
+// route_offsets_kernel), every (sender, bin) region padded to whole flush chunks with sentinel tuples.  Bin j of
+// this owner holds the keys whose slice hash lies in [j, j + 1) << (32 - nb_bits), i.e. slices [s_lo, s_hi] of the
+// local table whatever its geometry: one task = at most `part` consecutive tuples of one bin's extent.
+__global__ void __launch_bounds__(1024, 1)
+route_plan_kernel(TableView tv, int nranks, int nb_bits, int me, int cap, const unsigned long long *H,
+                  unsigned long long part, FineTask *tasks, unsigned task_cap, unsigned *ntasks) {
+    __shared__ unsigned long long ext[KQ_ROUTE_PLAN_BINS + 1];
+    __shared__ unsigned first[KQ_ROUTE_PLAN_BINS + 1];
+    const unsigned nb = 1u << nb_bits, P = (unsigned)nranks * nb;
+    const unsigned long long c1 = (unsigned long long)cap - 1;
+    for (unsigned j = threadIdx.x; j < nb; j += 1024) {
+        unsigned long long L = 0;
+        for (int r = 0; r < nranks; ++r) L += (H[(size_t)r * P + (unsigned)me * nb + j] + c1) / cap * cap;
+        ext[j] = L; first[j] = (unsigned)((L + part - 1) / part);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long run = 0; unsigned t = 0;
+        for (unsigned j = 0; j < nb; ++j) { const unsigned long long L = ext[j]; ext[j] = run; run += L; const unsigned v = first[j]; first[j] = t; t += v; }
+        ext[nb] = run; first[nb] = t;
+        *ntasks = t < task_cap ? t : task_cap;
+    }
+    __syncthreads();
+    for (unsigned j = threadIdx.x; j < nb; j += 1024) {
+        const unsigned long long lo = ext[j], hi = ext[j + 1];
+        const unsigned long long h_lo = (unsigned long long)j << (32 - nb_bits), h_hi = (((unsigned long long)j + 1) << (32 - nb_bits)) - 1;
+        const unsigned s_lo = (unsigned)((h_lo * tv.nslices) >> 32), s_hi = (unsigned)((h_hi * tv.nslices) >> 32);
+        unsigned t = first[j];
+        for (unsigned long long a = lo; a < hi && t < task_cap; a += part, ++t)
+            tasks[t] = FineTask{a, min(hi, a + part), s_lo, s_hi - s_lo + 1};
     }
 }
 
@@ -120,14 +165,20 @@ fine_scatter_kernel(TableView tv, const uint64_t *__restrict__ in, const FineTas
         const FineTask tk = tasks[t];
         for (unsigned i = threadIdx.x; i < tk.ns; i += NT) { fill[i] = 0; done[i] = 0; }
         __syncthreads();
+        ulonglong2 nxt[R];                                               // the next round's tuples, loaded a round ahead
+#pragma unroll
+        for (int i = 0; i < R; ++i) {
+            const unsigned long long j = tk.lo + (unsigned)i * NT + threadIdx.x;
+            nxt[i] = j < tk.hi ? t_raw<TW>(in, j) : make_ulonglong2(T_PAD1, T_PAD1);
+        }
         for (unsigned long long tile = tk.lo; tile < tk.hi; tile += (unsigned long long)NT * R) {
             uint64_t key[R]; uint32_t e[R]; unsigned bin[R], pos[R];
             uint32_t m = 0;
 #pragma unroll
             for (int i = 0; i < R; ++i) {
-                const unsigned long long j = tile + (unsigned)i * NT + threadIdx.x;
-                e[i] = 255u;
-                if (j < tk.hi) t_unpack<TW>(in, j, key[i], e[i]);
+                t_split<TW>(nxt[i], key[i], e[i]);
+                const unsigned long long j = tile + (unsigned long long)NT * R + (unsigned)i * NT + threadIdx.x;
+                nxt[i] = j < tk.hi ? t_raw<TW>(in, j) : make_ulonglong2(T_PAD1, T_PAD1);
             }
 #pragma unroll
             for (int i = 0; i < R; ++i) {
@@ -275,7 +326,7 @@ __device__ __forceinline__ int smem_insert(Slot *piece, unsigned mask, const Tab
 // Tuples of one key that sit next to each other in the stream (poly-A runs, satellites) are combined inside
 // the warp first, so a hot key costs one CAS per warp and not a CAS storm.
 template <int TW, int NT>
-__global__ void __launch_bounds__(NT, 3)
+__global__ void __launch_bounds__(NT, NT >= 512 ? 3 : NT >= 384 ? 4 : 6)
 smem_insert_kernel(TableView tv, const uint64_t *__restrict__ tuples, const unsigned long long *__restrict__ fstart,
                    const unsigned long long *__restrict__ fcount, uint64_t *ovf, unsigned long long ovf_cap,
                    unsigned long long *ovf_n, unsigned long long *ticket) {
@@ -301,14 +352,21 @@ smem_insert_kernel(TableView tv, const uint64_t *__restrict__ tuples, const unsi
         const unsigned long long s = sh_ticket;
         if (s >= tv.nslices) break;
         const unsigned long long a = fstart[s], n = fcount[s];
+        ulonglong2 nxt[4];                                               // tuples are loaded one batch ahead (and under the bulk copy)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const unsigned long long i = (unsigned)j * NT + threadIdx.x;
+            nxt[j] = i < n ? t_raw<TW>(tuples, a + i) : make_ulonglong2(T_PAD1, T_PAD1);
+        }
         mbar_wait(&bar, parity); parity ^= 1;
         for (unsigned long long i0 = 0; i0 < n; i0 += (unsigned long long)NT * 4) {
             uint64_t key[4]; uint32_t e[4];
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-                const unsigned long long i = i0 + (unsigned)j * NT + threadIdx.x;
-                e[j] = 255u; key[j] = ~0ULL - lane;                    // distinct dummies: no false match below
-                if (i < n) t_unpack<TW>(tuples, a + i, key[j], e[j]);
+                t_split<TW>(nxt[j], key[j], e[j]);
+                if (e[j] == 255u) key[j] = ~0ULL - lane;               // distinct dummies: no false match below
+                const unsigned long long i = i0 + (unsigned long long)NT * 4 + (unsigned)j * NT + threadIdx.x;
+                nxt[j] = i < n ? t_raw<TW>(tuples, a + i) : make_ulonglong2(T_PAD1, T_PAD1);
             }
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
@@ -386,6 +444,13 @@ cudaError_t launch_fine_plan(cudaStream_t st, const TableView &tv, unsigned ncoa
     return cudaGetLastError();
 }
 
+cudaError_t launch_route_plan(cudaStream_t st, const TableView &tv, const RouteMap &rt, int me, int cap, const unsigned long long *H,
+                              unsigned long long part, FineTask *tasks, unsigned task_cap, unsigned *ntasks, uint64_t *launches) {
+    route_plan_kernel<<<1, 1024, 0, st>>>(tv, rt.nranks, rt.nb_bits, me, cap, H, part, tasks, task_cap, ntasks);
+    ++*launches;
+    return cudaGetLastError();
+}
+
 cudaError_t launch_fine_hist(cudaStream_t st, const TableView &tv, const uint64_t *in, const FineTask *tasks,
                              const unsigned *ntasks, unsigned task_bound, unsigned ns_max, unsigned long long *fhist,
                              uint64_t *launches) {
@@ -409,6 +474,7 @@ cudaError_t launch_fine_scatter(cudaStream_t st, const TableView &tv, const uint
 #define KQ_FS_LAUNCH(TWV) do {                                                                                         \
         e = cudaFuncSetAttribute(fine_scatter_kernel<TWV, 1024, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
         if (e != cudaSuccess) return e;                                                                                \
+        cudaFuncSetAttribute(fine_scatter_kernel<TWV, 1024, 2>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared); \
         fine_scatter_kernel<TWV, 1024, 2><<<grid, 1024, smem, st>>>(tv, in, tasks, ntasks, out, cursor, ns_max, cap); } while (0)
     if (tw == 1) KQ_FS_LAUNCH(1); else KQ_FS_LAUNCH(2);
 #undef KQ_FS_LAUNCH
@@ -422,12 +488,15 @@ cudaError_t launch_smem_insert(cudaStream_t st, const TableView &tv, const uint6
     cudaError_t e = cudaMemsetAsync(ticket, 0, sizeof(unsigned long long), st);
     if (e != cudaSuccess) return e;
     const size_t smem = sizeof(Slot) << tv.slice_bits;
-    const unsigned grid = (unsigned)std::min<unsigned long long>(tv.nslices, (unsigned long long)sm_count() * 3);
-#define KQ_SI_LAUNCH(TWV) do {                                                                                         \
-        e = cudaFuncSetAttribute(smem_insert_kernel<TWV, KQ_S3_NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+    const unsigned grid = (unsigned)std::min<unsigned long long>(tv.nslices, (unsigned long long)sm_count() * (unsigned)tuning().s3_ctas);
+#define KQ_SI_LAUNCH(TWV, NTV) do {                                                                                    \
+        e = cudaFuncSetAttribute(smem_insert_kernel<TWV, NTV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
         if (e != cudaSuccess) return e;                                                                                \
-        smem_insert_kernel<TWV, KQ_S3_NT><<<grid, KQ_S3_NT, smem, st>>>(tv, tuples, fstart, fcount, ovf, ovf_cap, ovf_n, ticket); } while (0)
-    if (tuple_words(tv.k) == 1) KQ_SI_LAUNCH(1); else KQ_SI_LAUNCH(2);
+        cudaFuncSetAttribute(smem_insert_kernel<TWV, NTV>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared); \
+        smem_insert_kernel<TWV, NTV><<<grid, NTV, smem, st>>>(tv, tuples, fstart, fcount, ovf, ovf_cap, ovf_n, ticket); } while (0)
+    const int nt = tuning().s3_threads;
+    if (tuple_words(tv.k) == 1) { if (nt == 256) KQ_SI_LAUNCH(1, 256); else if (nt == 384) KQ_SI_LAUNCH(1, 384); else KQ_SI_LAUNCH(1, 512); }
+    else { if (nt == 256) KQ_SI_LAUNCH(2, 256); else if (nt == 384) KQ_SI_LAUNCH(2, 384); else KQ_SI_LAUNCH(2, 512); }
 #undef KQ_SI_LAUNCH
     ++*launches;
     return cudaGetLastError();

@@ -42,6 +42,7 @@ Tuning &tuning() {
         v.smem_insert = (int)num("KQ_SMEM_INSERT", 1);
         v.direct_pct = (int)num("KQ_DIRECT_PCT", 25);
         { const char *e = std::getenv("KQ_DB_HOST"); v.db_host = e && e[0] == '1'; }
+        v.s3_threads = (int)num("KQ_S3_THREADS", 512); v.s3_ctas = (int)num("KQ_S3_CTAS", 3); if (v.s3_ctas < 1 || v.s3_ctas > 8) v.s3_ctas = 3;
         return v;
     }();
     return t;

@@ -71,6 +71,7 @@ struct Tuning {
     int smem_insert;           // 0 = count with L2 CAS (insert_tuples_kernel) also on multi-slice tables
     int direct_pct;            // batches below this share of the table's slots skip the sweep (fused kernel)
     int db_host;               // .kreeq codec on the host (cross-check of the device codec)
+    int s3_threads, s3_ctas;   // shared-memory insert: threads per CTA (256 / 384 / 512), CTAs per SM in the grid
 };
 Tuning &tuning();
 // shared memory the scatter kernel needs for `nslices` bins of `cap` tuples; 0 if it cannot fit
@@ -107,11 +108,15 @@ cudaError_t launch_insert_tuples(cudaStream_t st, const TableView &tv, const uin
 inline unsigned coarse_bins(const TableView &tv) { return (unsigned)(((tv.nslices - 1) >> tv.cshift) + 1); }
 // at most `part` consecutive tuples [lo, hi) of the level-1 output whose keys live in slices [s_lo, s_lo + ns)
 struct FineTask { unsigned long long lo, hi; unsigned s_lo, ns; };
+constexpr int KQ_ROUTE_PLAN_BINS = 2048;      // hash ranges per owner the routed plan kernel handles
 constexpr int KQ_S3_NT = 512;                 // threads per CTA of the shared-memory insert
 unsigned fine_pick_cap(unsigned ns_max, int tw);   // flush chunk of the level-2 scatter, 0 = bins do not fit
 cudaError_t launch_fine_plan(cudaStream_t st, const TableView &tv, unsigned ncoarse, const unsigned long long *start,
                              const unsigned long long *n, unsigned long long part, FineTask *tasks, unsigned task_cap,
                              unsigned *ntasks, uint64_t *launches);
+// tasks over the receive slab of rank `me` (routed pipeline; H = all-gathered histograms, cap = flush chunk)
+cudaError_t launch_route_plan(cudaStream_t st, const TableView &tv, const RouteMap &rt, int me, int cap, const unsigned long long *H,
+                              unsigned long long part, FineTask *tasks, unsigned task_cap, unsigned *ntasks, uint64_t *launches);
 // fhist[s] += tuples of slice s
 cudaError_t launch_fine_hist(cudaStream_t st, const TableView &tv, const uint64_t *in, const FineTask *tasks,
                              const unsigned *ntasks, unsigned task_bound, unsigned ns_max, unsigned long long *fhist,
