@@ -89,6 +89,9 @@ struct kq_ctx {
     uint64_t *d_tuples2 = nullptr; uint64_t tup2_cap = 0;
     unsigned long long *d_cstart = nullptr, *d_fhist = nullptr, *d_fcursor = nullptr, *d_fstart = nullptr; uint64_t fine_cap = 0;
     FineTask *d_tasks = nullptr; uint64_t task_cap = 0; unsigned *d_ntasks = nullptr;
+    // one-pass scatter: cursor per slice, big list for the tuples of slices that are full
+    unsigned long long *d_scur = nullptr; uint64_t scur_cap = 0;
+    uint64_t *d_ovf2 = nullptr; uint64_t ovf2_cap = 0;
     // routed (multi-GPU) pipeline: receive slab the owners' tuples are written into by every rank
     uint64_t *d_slab = nullptr; uint64_t slab_cap = 0;          // tuples
     RouteMap route{}; bool route_ready = false;
@@ -340,8 +343,44 @@ int run_batch(kq_ctx *c, Source src) {
     { int rc = pipeline_scratch(c, 0); if (rc) return rc; }
     c->ovf_list = nullptr; c->ovf_list_cap = 0;
     const int t0 = time_begin(c, 0);
+    // big table, batch worth a sweep: one-pass scatter into per-slice regions, then the shared-memory insert
+    if (tuning().pipeline == 4 && c->nslices > 1 && c->slice_bits <= 13 &&
+        (double)bound * 100.0 >= (double)tuning().direct_pct * (double)table_slots(c)) {
+        const int stride = tuning().cursor_stride;
+        const uint64_t cap_t = ((bound / c->nslices) * 5 / 4 + 64 + 31) & ~31ull;      // tuples per slice region
+        const uint64_t region = c->nslices * cap_t;
+        if (c->tup2_cap < region) {
+            cudaFree(c->d_tuples2); c->d_tuples2 = nullptr; c->tup2_cap = 0;
+            CU(cudaMalloc(&c->d_tuples2, region * 8 * tw));
+            c->tup2_cap = region;
+        }
+        if (c->scur_cap < c->nslices * (uint64_t)stride) {
+            cudaFree(c->d_scur); c->d_scur = nullptr; c->scur_cap = 0;
+            CU(cudaMalloc(&c->d_scur, c->nslices * (uint64_t)stride * 8));
+            c->scur_cap = c->nslices * (uint64_t)stride;
+        }
+        const uint64_t want_ovf = std::max<uint64_t>(OVF_CAP, bound / 8);
+        if (c->ovf2_cap < want_ovf) {
+            cudaFree(c->d_ovf2); c->d_ovf2 = nullptr; c->ovf2_cap = 0;
+            CU(cudaMalloc(&c->d_ovf2, want_ovf * 8 * tw));
+            c->ovf2_cap = want_ovf;
+        }
+        CU(cudaMemsetAsync(c->d_scur, 0, c->nslices * (uint64_t)stride * 8, c->stream));
+        const int t5 = time_begin(c, 5);
+        CU(launch_scatter_fine(c->stream, tv, src, c->d_tuples2, cap_t, c->d_scur, stride, src.tuples ? nullptr : c->d_inst,
+                               c->d_ovf2, c->ovf2_cap, c->d_ovf_n, &c->launches));
+        time_end(c, t5);
+        const int t2 = time_begin(c, 2);
+        CU(launch_smem_insert(c->stream, tv, c->d_tuples2, nullptr, c->d_scur, cap_t, stride, c->d_ovf2, c->ovf2_cap, c->d_ovf_n, c->d_ticket, &c->launches));
+        time_end(c, t2);
+        c->ovf_list = c->d_ovf2; c->ovf_list_cap = c->ovf2_cap;
+        c->ovf_pending = true;
+        c->route_task_bound = 0;
+        time_end(c, t0);
+        return KQ_OK;
+    }
     // routed pipeline: the slab is in bin order already, its tasks were planned by kq_route_scatter
-    if (src.ordered && c->route_task_bound && bound == c->route_extent && c->nslices > 1 && tuning().smem_insert && c->slice_bits <= 13 &&
+    if (tuning().pipeline == 3 && src.ordered && c->route_task_bound && bound == c->route_extent && c->nslices > 1 && tuning().smem_insert && c->slice_bits <= 13 &&
         fine_pick_cap(c->route_ns_max, tw) != 0) {
         int rc = pipeline_scratch(c, 0, true, bound); if (rc) return rc;
         const int t4 = time_begin(c, 4);
@@ -354,7 +393,7 @@ int run_batch(kq_ctx *c, Source src) {
         time_end(c, t4);
         const int t2 = time_begin(c, 2);
         // tuples of full slices go back into the slab (read completely by now, as large as the batch)
-        CU(launch_smem_insert(c->stream, tv, c->d_tuples2, c->d_fstart, c->d_fhist, c->d_slab, c->slab_cap, c->d_ovf_n, c->d_ticket, &c->launches));
+        CU(launch_smem_insert(c->stream, tv, c->d_tuples2, c->d_fstart, c->d_fhist, 0, 1, c->d_slab, c->slab_cap, c->d_ovf_n, c->d_ticket, &c->launches));
         time_end(c, t2);
         c->ovf_list = c->d_slab; c->ovf_list_cap = c->slab_cap;
         c->ovf_pending = true;
@@ -378,7 +417,7 @@ int run_batch(kq_ctx *c, Source src) {
     }
     // level 2 + shared-memory insert when a slice fits one CTA's shared memory and its bins the scatter's
     const unsigned ns_max = 1u << c->cshift;
-    const bool level2 = tuning().smem_insert && c->slice_bits <= 13 && fine_pick_cap(ns_max, tw) != 0;
+    const bool level2 = tuning().pipeline == 3 && tuning().smem_insert && c->slice_bits <= 13 && fine_pick_cap(ns_max, tw) != 0;
     int rc = pipeline_scratch(c, bound, level2); if (rc) return rc;
     const int t3 = time_begin(c, 3);
     CU(cudaMemsetAsync(c->d_hist, 0, (size_t)ncoarse * 8, c->stream));
@@ -409,7 +448,7 @@ int run_batch(kq_ctx *c, Source src) {
     time_end(c, t4);
     const int t2 = time_begin(c, 2);
     // tuples of full slices go back into the level-1 buffer (free by now, as large as the batch)
-    CU(launch_smem_insert(c->stream, tv, c->d_tuples2, c->d_fstart, c->d_fhist, c->d_tuples, c->tup_cap, c->d_ovf_n, c->d_ticket, &c->launches));
+    CU(launch_smem_insert(c->stream, tv, c->d_tuples2, c->d_fstart, c->d_fhist, 0, 1, c->d_tuples, c->tup_cap, c->d_ovf_n, c->d_ticket, &c->launches));
     time_end(c, t2);
     c->ovf_list = c->d_tuples; c->ovf_list_cap = c->tup_cap;
     c->ovf_pending = true;
@@ -564,7 +603,7 @@ extern "C" void kq_destroy(kq_ctx *c) {
     cudaFree(c->d_pb_alt); cudaFree(c->d_pi_alt);
     cudaFree(c->d_pb); cudaFree(c->d_pi); cudaFree(c->d_tuples); cudaFree(c->d_hist); cudaFree(c->d_cursor);
     cudaFree(c->d_tuples2); cudaFree(c->d_cstart); cudaFree(c->d_fhist); cudaFree(c->d_fcursor); cudaFree(c->d_fstart);
-    cudaFree(c->d_tasks); cudaFree(c->d_ntasks);
+    cudaFree(c->d_tasks); cudaFree(c->d_ntasks); cudaFree(c->d_scur); cudaFree(c->d_ovf2);
     cudaFree(c->d_total); cudaFree(c->d_nsrc); cudaFree(c->d_ticket); cudaFree(c->d_ovf); cudaFree(c->d_ovf_n);
     for (void *p : c->ipc_opened) cudaIpcCloseMemHandle(p);
     for (void *p : c->peer_opened) cudaIpcCloseMemHandle(p);
@@ -657,6 +696,8 @@ extern "C" int kq_set_tuning(const char *name, long long value) {
     else if (n == "db_host" && (value == 0 || value == 1)) t.db_host = (int)value;
     else if (n == "s3_threads" && (value == 256 || value == 384 || value == 512)) t.s3_threads = (int)value;
     else if (n == "s3_ctas" && value >= 1 && value <= 8) t.s3_ctas = (int)value;
+    else if (n == "pipeline" && value >= 2 && value <= 4) t.pipeline = (int)value;
+    else if (n == "cursor_stride" && value >= 1 && value <= 16) t.cursor_stride = (int)value;
     else return KQ_EINVAL;
     return KQ_OK;
 }
@@ -887,7 +928,7 @@ extern "C" int kq_route_scatter(kq_ctx *c, const uint64_t *d_bases, const uint64
     // what this rank receives goes through the level-2 scatter and the shared-memory insert: plan its tasks from the
     // same histograms (bin extents inside the slab, slices a bin's hash range maps to on the local table)
     c->route_task_bound = 0;
-    if (c->nslices > 1 && totals[c->rank] && (1 << c->route.nb_bits) <= KQ_ROUTE_PLAN_BINS) {
+    if (tuning().pipeline == 3 && c->nslices > 1 && totals[c->rank] && (1 << c->route.nb_bits) <= KQ_ROUTE_PLAN_BINS) {
         const unsigned nb = 1u << c->route.nb_bits;
         c->route_ns_max = (unsigned)(c->nslices / nb + 2);
         int rc = pipeline_scratch(c, 0, true, totals[c->rank]); if (rc) return rc;

@@ -276,82 +276,126 @@ __device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.w
 __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
-// Count n = cov lane of `inc` instances of key (inc = their summed increments, every lane <= 32) into the
-// slice held in shared memory.  1 = new key, 0 = existed, -1 = the slice is full (nothing counted).
-__device__ __forceinline__ int smem_insert(Slot *piece, unsigned mask, const TableView &tv, uint64_t key, unsigned long long inc) {
+// Slow paths of the shared-memory insert, kept out of line so that the hot loop stays small.
+
+// cov + n would pass a slot lane: move 63 of the coverage and up to 63 of every lane to the remainder table in the
+// same CAS that counts these instances (the slot stays >= KQ_REM_FLOOR: readers then look into R)
+__device__ __noinline__ void smem_spill(unsigned long long *pcnt, const TableView &tv, uint64_t key, unsigned long long inc) {
+    const unsigned n = (unsigned)(inc >> 56);
+    unsigned long long cur = *reinterpret_cast<volatile unsigned long long *>(pcnt);
+    for (;;) {
+        if (cnt_cov(cur) + n <= KQ_LANE_MAX) {                             // somebody else made room meanwhile
+            const unsigned long long old = atomicCAS(pcnt, cur, cur + inc);
+            if (old == cur) return;
+            cur = old; continue;
+        }
+        uint32_t fw[4], bw[4];
+        unsigned long long take = 63ull << 56;
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+            fw[w] = min(cnt_lane(cur, w), 63u); bw[w] = min(cnt_lane(cur, 4 + w), 63u);
+            take |= (unsigned long long)fw[w] << (7 * w) | (unsigned long long)bw[w] << (7 * (4 + w));
+        }
+        const unsigned long long old = atomicCAS(pcnt, cur, cur - take + inc);
+        if (old == cur) { remainder_add(tv, key, 63, fw, bw); return; }
+        cur = old;
+    }
+}
+
+// the slice is full: the instances go back to the overflow list as single tuples (instance c of a combined group
+// carries edge b iff c < count of b, which preserves every sum)
+template <int TW>
+__device__ __noinline__ void smem_give_back(uint64_t *ovf, unsigned long long ovf_cap, unsigned long long *ovf_n, uint64_t key, unsigned long long inc) {
+    const unsigned cnt = (unsigned)(inc >> 56);
+    const unsigned long long q = atomicAdd(ovf_n, (unsigned long long)cnt);
+    for (unsigned c = 0; c < cnt; ++c) {
+        uint32_t eb = 0;
+#pragma unroll
+        for (int b = 0; b < 8; ++b) if (c < cnt_lane(inc, b)) eb |= 0x80u >> b;
+        if (q + c < ovf_cap) t_store<TW>(ovf, q + c, key, eb);
+    }
+}
+
+// complete insert of one (combined) tuple: probe, claim, count; 1 = new key, 0 = existed / given back
+template <int TW>
+__device__ __noinline__ unsigned smem_insert_slow(Slot *piece, unsigned mask, unsigned limit, const TableView &tv, uint64_t key,
+                                                  unsigned long long inc, uint64_t *ovf, unsigned long long ovf_cap, unsigned long long *ovf_n) {
     const unsigned long long tag = key + 1;
     const unsigned n = (unsigned)(inc >> 56);
-    unsigned j = (unsigned)mix64(key) & mask;
-    const unsigned limit = min(mask + 1, 1024u);                       // a longer run means the slice is (locally) full
-    int fresh = 0;
+    unsigned j = (unsigned)mix64(key) & mask, fresh = 0;
     for (unsigned probes = 0; probes < limit; ++probes) {
-        unsigned long long *ptag = &piece[j].tag, *pcnt = &piece[j].cnt;
-        unsigned long long t = *reinterpret_cast<volatile unsigned long long *>(ptag);
+        unsigned long long t = *reinterpret_cast<volatile unsigned long long *>(&piece[j].tag);
         if (t == 0) {
-            t = atomicCAS(ptag, 0ULL, tag);
+            t = atomicCAS(&piece[j].tag, 0ULL, tag);
             if (t == 0) { t = tag; fresh = 1; }
         }
         if (t == tag) {
-            unsigned long long cur = *reinterpret_cast<volatile unsigned long long *>(pcnt);
+            unsigned long long cur = *reinterpret_cast<volatile unsigned long long *>(&piece[j].cnt);
             for (;;) {
-                if (cnt_cov(cur) + n > KQ_LANE_MAX) {
-                    // move 63 of the coverage and up to 63 of every lane to the remainder table in the same CAS that
-                    // counts these instances (the slot stays >= KQ_REM_FLOOR: readers then look into R)
-                    uint32_t fw[4], bw[4];
-                    unsigned long long take = 63ull << 56;
-#pragma unroll
-                    for (int w = 0; w < 4; ++w) {
-                        fw[w] = min(cnt_lane(cur, w), 63u); bw[w] = min(cnt_lane(cur, 4 + w), 63u);
-                        take |= (unsigned long long)fw[w] << (7 * w) | (unsigned long long)bw[w] << (7 * (4 + w));
-                    }
-                    const unsigned long long old = atomicCAS(pcnt, cur, cur - take + inc);
-                    if (old == cur) { remainder_add(tv, key, 63, fw, bw); return fresh; }
-                    cur = old;
-                    continue;
-                }
-                const unsigned long long old = atomicCAS(pcnt, cur, cur + inc);   // lanes <= cov: no carry between lanes
+                if (cnt_cov(cur) + n > KQ_LANE_MAX) { smem_spill(&piece[j].cnt, tv, key, inc); return fresh; }
+                const unsigned long long old = atomicCAS(&piece[j].cnt, cur, cur + inc);   // lanes <= cov: no carry between lanes
                 if (old == cur) return fresh;
                 cur = old;
             }
         }
         j = (j + 1) & mask;
     }
-    return -1;
+    smem_give_back<TW>(ovf, ovf_cap, ovf_n, key, inc);
+    return 0;
+}
+
+// runs of one key in the stream (poly-A, satellites): the lanes of a warp that hold the same key add their
+// increments up and the lowest lane counts for the group, so a hot key costs one CAS per warp, not a CAS storm
+__device__ __noinline__ unsigned long long warp_combine(uint64_t key, uint32_t e, bool live) {
+    const unsigned lane = threadIdx.x & 31;
+    const unsigned peers = __match_any_sync(0xffffffffu, key);
+    unsigned long long sum = 0;
+#pragma unroll
+    for (int b = 0; b < 8; ++b) {
+        const unsigned has = __ballot_sync(0xffffffffu, live && ((e >> (7 - b)) & 1u));
+        sum |= (unsigned long long)__popc(has & peers) << (7 * b);
+    }
+    sum |= (unsigned long long)__popc(peers) << 56;
+    return live && lane == (unsigned)__ffs(peers) - 1 ? sum : 0ULL;
 }
 
 }  // namespace
 
-// One CTA per slice at a time (ticket counter; slices without tuples are skipped): bulk-load the slice,
+// One CTA per slice at a time (ticket counter; slices without tuples are skipped): bulk-load the slice (UBLKCP),
 // count its tuples in shared memory, bulk-store it.  Three CTAs per SM overlap each other's copies.
-// Tuples of one key that sit next to each other in the stream (poly-A runs, satellites) are combined inside
-// the warp first, so a hot key costs one CAS per warp and not a CAS storm.
+// A thread takes four tuples at a time (loaded a batch ahead) and then runs a loop in which every lane does ONE
+// probe step per iteration on its current tuple -- slot load, claim or compare, one CAS -- and moves to its next
+// tuple as soon as one is counted: lanes never wait for the longest probe sequence of the warp.
 template <int TW, int NT>
-__global__ void __launch_bounds__(NT, NT >= 512 ? 3 : NT >= 384 ? 4 : 6)
+__global__ void __launch_bounds__(NT, 3)
 smem_insert_kernel(TableView tv, const uint64_t *__restrict__ tuples, const unsigned long long *__restrict__ fstart,
-                   const unsigned long long *__restrict__ fcount, uint64_t *ovf, unsigned long long ovf_cap,
-                   unsigned long long *ovf_n, unsigned long long *ticket) {
+                   const unsigned long long *__restrict__ fcount, unsigned long long cap, int stride, uint64_t *ovf,
+                   unsigned long long ovf_cap, unsigned long long *ovf_n, unsigned long long *ticket) {
     extern __shared__ __align__(128) unsigned char sm_piece[];
     __shared__ __align__(8) uint64_t bar;
-    __shared__ unsigned long long sh_ticket, sh_fresh;
+    __shared__ unsigned long long sh_ticket, sh_fresh, sh_n;
+    __shared__ unsigned long long inc_lut[256];
     Slot *piece = reinterpret_cast<Slot *>(sm_piece);
     const unsigned slots = 1u << tv.slice_bits, mask = slots - 1, bytes = slots * (unsigned)sizeof(Slot);
+    const unsigned limit = min(slots, 1024u);                          // a longer run means the slice is (locally) full
     const unsigned lane = threadIdx.x & 31;
+    for (unsigned i = threadIdx.x; i < 256; i += NT) inc_lut[i] = inc_of_edge(i);
     if (threadIdx.x == 0) { mbar_init(&bar, 1); sh_fresh = 0; asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
     __syncthreads();
     unsigned parity = 0;
-    unsigned long long fresh = 0;
+    unsigned fresh = 0;
     for (;;) {
         if (threadIdx.x == 0) {
             // next slice that has tuples (the counts are read by one thread: most slices of a small batch are empty)
-            unsigned long long s;
-            for (;;) { s = atomicAdd(ticket, 1ULL); if (s >= tv.nslices || fcount[s]) break; }
-            sh_ticket = s;
+            unsigned long long s, cnt = 0;
+            for (;;) { s = atomicAdd(ticket, 1ULL); if (s >= tv.nslices) break; cnt = fcount[s * stride]; if (cnt) break; }
+            sh_ticket = s; sh_n = fstart ? cnt : min(cnt, cap);
             if (s < tv.nslices) { mbar_expect_tx(&bar, bytes); bulk_g2s(piece, tv.T + (s << tv.slice_bits), bytes, &bar); }
         }
         __syncthreads();
         const unsigned long long s = sh_ticket;
         if (s >= tv.nslices) break;
-        const unsigned long long a = fstart[s], n = fcount[s];
+        const unsigned long long a = fstart ? fstart[s] : s * cap, n = sh_n;
         ulonglong2 nxt[4];                                               // tuples are loaded one batch ahead (and under the bulk copy)
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -360,43 +404,60 @@ smem_insert_kernel(TableView tv, const uint64_t *__restrict__ tuples, const unsi
         }
         mbar_wait(&bar, parity); parity ^= 1;
         for (unsigned long long i0 = 0; i0 < n; i0 += (unsigned long long)NT * 4) {
-            uint64_t key[4]; uint32_t e[4];
+            ulonglong2 cur[4];
+            bool run = false;
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-                t_split<TW>(nxt[j], key[j], e[j]);
-                if (e[j] == 255u) key[j] = ~0ULL - lane;               // distinct dummies: no false match below
+                cur[j] = nxt[j];
+                uint64_t kj; uint32_t ej; t_split<TW>(cur[j], kj, ej);
+                const uint64_t kn = __shfl_down_sync(0xffffffffu, kj, 1);
+                run |= ej != 255u && lane < 31 && kn == kj;
                 const unsigned long long i = i0 + (unsigned long long)NT * 4 + (unsigned)j * NT + threadIdx.x;
                 nxt[j] = i < n ? t_raw<TW>(tuples, a + i) : make_ulonglong2(T_PAD1, T_PAD1);
             }
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const bool live = e[j] != 255u;
-                unsigned long long inc = live ? inc_of_edge(e[j]) : 0ULL;
-                // combine the instances of one key inside the warp (all 32 lanes take part: i0 is warp-uniform)
-                const unsigned peers = __match_any_sync(0xffffffffu, key[j]);
-                if (__any_sync(0xffffffffu, live && (peers & (peers - 1)))) {
-                    unsigned long long sum = 0;
-#pragma unroll
-                    for (int b = 0; b < 8; ++b) {
-                        const unsigned has = __ballot_sync(0xffffffffu, live && ((e[j] >> (7 - b)) & 1u));
-                        sum |= (unsigned long long)__popc(has & peers) << (7 * b);
-                    }
-                    sum |= (unsigned long long)__popc(peers) << 56;
-                    inc = lane == (unsigned)__ffs(peers) - 1 ? sum : 0ULL;   // the lowest lane of a group counts for it
+            if (__any_sync(0xffffffffu, run)) {
+                // neighbours in the stream with the same key: combine inside the warp, count with the plain loop
+#pragma unroll 1
+                for (int j = 0; j < 4; ++j) {
+                    const ulonglong2 w = j == 0 ? cur[0] : j == 1 ? cur[1] : j == 2 ? cur[2] : cur[3];
+                    uint64_t kj; uint32_t ej; t_split<TW>(w, kj, ej);
+                    const bool live = ej != 255u;
+                    if (!live) kj = ~0ULL - lane;                        // distinct dummies: no false match
+                    const unsigned long long inc = warp_combine(kj, ej, live);
+                    if (inc) fresh += smem_insert_slow<TW>(piece, mask, limit, tv, kj, inc, ovf, ovf_cap, ovf_n);
                 }
-                if (!live || inc == 0) continue;
-                const int r = smem_insert(piece, mask, tv, key[j], inc);
-                if (r < 0) {                                              // slice full: keep the instances for after a grow
-                    const unsigned cnt = (unsigned)(inc >> 56);
-                    const unsigned long long q = atomicAdd(ovf_n, (unsigned long long)cnt);
-                    for (unsigned c = 0; c < cnt; ++c) {
-                        // a combined group goes back as single tuples: instance c carries edge b iff c < count of b
-                        uint32_t eb = 0;
-#pragma unroll
-                        for (int b = 0; b < 8; ++b) if (c < cnt_lane(inc, b)) eb |= 0x80u >> b;
-                        if (q + c < ovf_cap) t_store<TW>(ovf, q + c, key[j], eb);
+                continue;
+            }
+            // one probe step per lane and iteration
+            int idx = 0; bool have = false;
+            uint64_t ck = 0; unsigned long long ci = 0; unsigned cj = 0, probes = 0;
+            for (;;) {
+                if (!have) {
+                    while (idx < 4 && !have) {
+                        const ulonglong2 w = idx == 0 ? cur[0] : idx == 1 ? cur[1] : idx == 2 ? cur[2] : cur[3];
+                        uint32_t ej; t_split<TW>(w, ck, ej);
+                        ++idx;
+                        if (ej != 255u) { ci = inc_lut[ej]; have = true; }
                     }
-                } else fresh += r;
+                    if (have) { cj = (unsigned)mix64(ck) & mask; probes = 0; }
+                }
+                if (!__any_sync(0xffffffffu, have)) break;
+                if (have) {
+                    const unsigned long long tag = ck + 1;
+                    unsigned long long t, c;                                               // one 16-byte shared load: {tag, cnt}
+                    asm volatile("ld.volatile.shared.v2.u64 {%0, %1}, [%2];" : "=l"(t), "=l"(c) : "r"(smem_u32(&piece[cj])) : "memory");
+                    if (t == 0) {
+                        t = atomicCAS(&piece[cj].tag, 0ULL, tag);
+                        if (t == 0) { t = tag; ++fresh; c = 0; }
+                    }
+                    if (t == tag) {
+                        if (cnt_cov(c) + 1u > KQ_LANE_MAX) { smem_spill(&piece[cj].cnt, tv, ck, ci); have = false; }
+                        else if (atomicCAS(&piece[cj].cnt, c, c + ci) == c) have = false;       // else: look again next round
+                    } else {
+                        cj = (cj + 1) & mask;
+                        if (++probes >= limit) { smem_give_back<TW>(ovf, ovf_cap, ovf_n, ck, ci); have = false; }
+                    }
+                }
             }
         }
         __syncthreads();                                                  // every update is in the piece
@@ -409,8 +470,9 @@ smem_insert_kernel(TableView tv, const uint64_t *__restrict__ tuples, const unsi
     }
     if (threadIdx.x == 0) bulk_wait_all();
     // new keys of this CTA -> occupancy counter
-    for (int o = 16; o; o >>= 1) fresh += __shfl_xor_sync(0xffffffffu, fresh, o);
-    if (lane == 0 && fresh) atomicAdd(&sh_fresh, fresh);
+    unsigned long long f = fresh;
+    for (int o = 16; o; o >>= 1) f += __shfl_xor_sync(0xffffffffu, f, o);
+    if (lane == 0 && f) atomicAdd(&sh_fresh, f);
     __syncthreads();
     if (threadIdx.x == 0 && sh_fresh) atomicAdd(&tv.occ[0], sh_fresh);
 }
@@ -483,8 +545,8 @@ cudaError_t launch_fine_scatter(cudaStream_t st, const TableView &tv, const uint
 }
 
 cudaError_t launch_smem_insert(cudaStream_t st, const TableView &tv, const uint64_t *tuples, const unsigned long long *fstart,
-                               const unsigned long long *fcount, uint64_t *ovf, unsigned long long ovf_cap,
-                               unsigned long long *ovf_n, unsigned long long *ticket, uint64_t *launches) {
+                               const unsigned long long *fcount, unsigned long long cap, int stride, uint64_t *ovf,
+                               unsigned long long ovf_cap, unsigned long long *ovf_n, unsigned long long *ticket, uint64_t *launches) {
     cudaError_t e = cudaMemsetAsync(ticket, 0, sizeof(unsigned long long), st);
     if (e != cudaSuccess) return e;
     const size_t smem = sizeof(Slot) << tv.slice_bits;
@@ -493,7 +555,7 @@ cudaError_t launch_smem_insert(cudaStream_t st, const TableView &tv, const uint6
         e = cudaFuncSetAttribute(smem_insert_kernel<TWV, NTV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
         if (e != cudaSuccess) return e;                                                                                \
         cudaFuncSetAttribute(smem_insert_kernel<TWV, NTV>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared); \
-        smem_insert_kernel<TWV, NTV><<<grid, NTV, smem, st>>>(tv, tuples, fstart, fcount, ovf, ovf_cap, ovf_n, ticket); } while (0)
+        smem_insert_kernel<TWV, NTV><<<grid, NTV, smem, st>>>(tv, tuples, fstart, fcount, cap, stride, ovf, ovf_cap, ovf_n, ticket); } while (0)
     const int nt = tuning().s3_threads;
     if (tuple_words(tv.k) == 1) { if (nt == 256) KQ_SI_LAUNCH(1, 256); else if (nt == 384) KQ_SI_LAUNCH(1, 384); else KQ_SI_LAUNCH(1, 512); }
     else { if (nt == 256) KQ_SI_LAUNCH(2, 256); else if (nt == 384) KQ_SI_LAUNCH(2, 384); else KQ_SI_LAUNCH(2, 512); }

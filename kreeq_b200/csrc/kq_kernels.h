@@ -72,6 +72,9 @@ struct Tuning {
     int direct_pct;            // batches below this share of the table's slots skip the sweep (fused kernel)
     int db_host;               // .kreeq codec on the host (cross-check of the device codec)
     int s3_threads, s3_ctas;   // shared-memory insert: threads per CTA (256 / 384 / 512), CTAs per SM in the grid
+    int pipeline;              // big tables: 4 one-pass scatter + shared-memory insert, 3 two-level scatter + shared-memory
+                               // insert, 2 level-1 scatter + L2 CAS insert
+    int cursor_stride;         // one-pass scatter: 8-byte words between the cursors of two slices
 };
 Tuning &tuning();
 // shared memory the scatter kernel needs for `nslices` bins of `cap` tuples; 0 if it cannot fit
@@ -86,6 +89,11 @@ constexpr int KQ_ROUTE_MAX_CAP = 32;
 cudaError_t launch_count_direct(cudaStream_t st, const TableView &tv, const Source &src,
                                 unsigned long long *instances, uint64_t *ovf, unsigned long long ovf_cap,
                                 unsigned long long *ovf_n, uint64_t *launches);
+// one-pass scatter (big tables): tuple -> out[s * cap + atomicAdd(cursor[s * stride], 1)], s = slice of the key;
+// instances of over-subscribed slices are counted at once (L2 CAS); *instances += valid windows (may be NULL)
+cudaError_t launch_scatter_fine(cudaStream_t st, const TableView &tv, const Source &src, uint64_t *out, unsigned long long cap,
+                                unsigned long long *cursor, int stride, unsigned long long *instances, uint64_t *ovf,
+                                unsigned long long ovf_cap, unsigned long long *ovf_n, uint64_t *launches);
 // 1. tuples per slice -> hist[nslices]
 cudaError_t launch_slice_hist(cudaStream_t st, const TableView &tv, const Source &src, unsigned long long *hist,
                               uint64_t *launches);
@@ -126,9 +134,10 @@ cudaError_t launch_fine_scatter(cudaStream_t st, const TableView &tv, const uint
                                 const unsigned *ntasks, unsigned task_bound, unsigned ns_max, uint64_t *out,
                                 unsigned long long *cursor, uint64_t *launches);
 // count the tuples [fstart[s], fstart[s] + fcount[s]) of every slice s in shared memory
+// (fstart == NULL: slice s owns [s * cap, s * cap + min(fcount[s * stride], cap)), the one-pass scatter's layout)
 cudaError_t launch_smem_insert(cudaStream_t st, const TableView &tv, const uint64_t *tuples, const unsigned long long *fstart,
-                               const unsigned long long *fcount, uint64_t *ovf, unsigned long long ovf_cap,
-                               unsigned long long *ovf_n, unsigned long long *ticket, uint64_t *launches);
+                               const unsigned long long *fcount, unsigned long long cap, int stride, uint64_t *ovf,
+                               unsigned long long ovf_cap, unsigned long long *ovf_n, unsigned long long *ticket, uint64_t *launches);
 
 // routed pipeline, steps 1-3: hist[nranks << nb_bits] of this rank's tuples; from the all-gathered
 // histograms H[nranks][P] the start of this rank's tuples inside every destination bin (cursor[P]) and what

@@ -94,6 +94,8 @@ int multi_route_setup(kq_multi *m) {
     if (m->routed) return KQ_OK;
     const uint64_t slab = (uint64_t)((double)m->round_pos * 1.3) + 8192;
     int nb_bits = 0; { const int per = (m->n <= 2 ? 1024 : 2048) / m->n; while ((2 << nb_bits) <= per) ++nb_bits; }
+    // (owner, hash range) bins of the routed scatter must fit its shared memory (16-byte tuples: half as many)
+    while (nb_bits > 0 && scatter_pick_cap((unsigned long long)m->n << nb_bits, tuple_words(m->k), KQ_ROUTE_MAX_CAP) == 0) --nb_bits;
     std::vector<void *> slabs((size_t)m->n, nullptr);
     for (int g = 0; g < m->n; ++g) {
         int rc = kq_route_setup(m->sh[g], slab, nb_bits, &slabs[g], nullptr);
