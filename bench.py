@@ -712,6 +712,11 @@ def main_ours(args):
                              "save_records_per_sec": u["save_records_per_s"], "load_records_per_sec": u["load_records_per_s"],
                              "records_in": u["records_in"], "records_out": u["records_out"], "db_bytes": u["db_bytes"],
                              "files_on": u["files_on"], "mode": "reference-compatible (kq_union ..., 1)"}
+            if u.get("union_device_s"):
+                line["union"]["device"] = {"value": u["union_device_records_per_s"], "unit": "records/s", "seconds": u["union_device_s"],
+                                           "kernels": "db_decode_kernel + put_kernel + merge_ref_kernel (CUDA events)",
+                                           "roofline": {"bound": "hbm", "achieved": u["union_device_gbs"], "peak": peak, "unit": "GB/s",
+                                                        "frac": u["union_device_gbs"] / peak, "algorithmic_bytes_per_record": u["union_alg_bytes_per_record"]}}
         except Exception as ex:                       # never lose the main line to the side measurement
             line["union"] = {"error": str(ex)[:200]}
     if world > 1:

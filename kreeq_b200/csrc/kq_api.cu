@@ -36,8 +36,8 @@ constexpr uint64_t MIN_SLOTS = 1ull << 12;
 constexpr uint64_t MIN_SCAP = 1ull << 12;
 constexpr uint64_t OVF_CAP = 4ull << 20;         // tuples kept when their slice is full
 constexpr uint64_t DEFAULT_FLUSH = 1ull << 29;   // pending k-mer start positions that trigger the pipeline
-constexpr int NTIMERS = 7;                       // 0 count pipeline, 1 validate, 2 insert kernel, 3 level-1 hist + scatter, 4 level-2 hist + scatter,
-                                                 // 5 level-1 scatter kernel alone, 6 level-2 scatter kernel alone
+constexpr int NTIMERS = 8;                       // 0 count pipeline, 1 validate, 2 insert kernel, 3 level-1 hist + scatter, 4 level-2 hist + scatter,
+                                                 // 5 scatter kernel alone (level 1 / one-pass), 6 level-2 scatter kernel alone, 7 load / union kernels
 
 thread_local std::string g_create_error;
 
@@ -1678,7 +1678,9 @@ int load_maps_gpu(kq_ctx *c, const std::string &dir, XRec **d_xs, uint64_t *n_ou
     CUX(cudaMalloc(d_xs, (n + 1) * sizeof(XRec)));
     CUX(cudaMemcpyAsync(d_buckets, buckets.data(), buckets.size() * sizeof(DbBucket), cudaMemcpyHostToDevice, c->stream));
     CUX(cudaMemsetAsync(d_n, 0, 8, c->stream));
+    const int t7 = time_begin(c, 7);
     CUX(launch_db_decode(c->stream, d_img, d_buckets, (unsigned)buckets.size(), *d_xs, n, d_n, &c->launches));
+    time_end(c, t7);
     unsigned long long got = 0;
     CUX(cudaMemcpyAsync(&got, d_n, 8, cudaMemcpyDeviceToHost, c->stream));
     CUX(cudaStreamSynchronize(c->stream));
@@ -1714,9 +1716,11 @@ int feed_device(kq_ctx *c, const XRec *d, uint64_t total, Feed mode) {
             if (rc) return rc;
         }
         const TableView tv = view(c);
+        const int t7 = time_begin(c, 7);
         cudaError_t e = mode == Feed::Put ? launch_put(c->stream, tv, d + off, n, &c->launches)
                       : mode == Feed::MergeRef ? launch_merge_ref(c->stream, tv, d + off, n, &c->launches)
                                                : launch_add_records(c->stream, tv, d + off, n, &c->launches);
+        time_end(c, t7);
         if (e != cudaSuccess) return fail(c, KQ_ECUDA, cudaGetErrorString(e));
         off += n;
     }

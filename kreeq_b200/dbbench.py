@@ -31,7 +31,10 @@ def union_rows(genome_mbp=10.0, coverage=30.0, workdir=None, device=0):
             del reads
         out["records_in"] = recs
         with DBG(k=k, device=device, expected_distinct=int(1.8 * recs[0])) as g:
+            g.set_timing(True); g.kernel_time_ms(7)
             t = time.perf_counter(); g.kunion(dbs); g.sync(); out["union_s"] = time.perf_counter() - t
+            ms, nk = g.kernel_time_ms(7); g.set_timing(False)
+            out["union_device_s"] = ms * 1e-3; out["union_device_launches"] = nk
             out["records_out"] = g.distinct()
             d = os.path.join(work, "u.kreeq")
             t = time.perf_counter(); g.save(d); out["save_union_s"] = time.perf_counter() - t
@@ -41,6 +44,12 @@ def union_rows(genome_mbp=10.0, coverage=30.0, workdir=None, device=0):
             if g.distinct() != out["records_out"]:
                 raise RuntimeError("load after save lost records")
         out["union_input_records_per_s"] = sum(recs) / out["union_s"]
+        if out.get("union_device_s"):
+            # 17 B read per input record + 17 B written per output record, against the device time of the
+            # decode + put / merge kernels (CUDA events); the rest of union_s is file I/O and the host directory pass
+            out["union_device_records_per_s"] = sum(recs) / out["union_device_s"]
+            out["union_alg_bytes_per_record"] = 17.0 * (1.0 + out["records_out"] / sum(recs))
+            out["union_device_gbs"] = out["union_alg_bytes_per_record"] * sum(recs) / out["union_device_s"] / 1e9
         out["save_records_per_s"] = out["records_out"] / out["save_union_s"]
         out["load_records_per_s"] = out["records_out"] / out["load_s"]
     finally:
