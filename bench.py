@@ -42,6 +42,8 @@ def parse_args():
     ap.add_argument("--genome-mbp", type=float, default=100.0, help="C2 genome size (default 100 Mbp)")
     ap.add_argument("--coverage", type=float, default=30.0)
     ap.add_argument("--k", type=int, default=21, help="k-mer length (default: C2's 21; 29..32 use 16-byte tuples)")
+    ap.add_argument("--config", default="C2", choices=["C2", "C4", "C5"], help="BASELINE.json config (C3, the 8-way union, is tools/config3_union.py)")
+    ap.add_argument("--scale", type=float, default=0, help="divide C4 / C5 by this (default: 16 = the /16 twins; 1 = full size)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cli-e2e", action="store_true", help="skip the command-line run on full-size files")
@@ -51,16 +53,102 @@ def parse_args():
     ap.add_argument("--ref-sample-reads", type=int, default=1_500_000)
     a = ap.parse_args()
     global K
+    if a.config == "C5" and a.k == 21:
+        a.k = 31
+    if not a.scale:
+        a.scale = 16.0 if a.config in ("C4", "C5") else 1.0
+    if a.config != "C2":                               # the side measurements below are C2's
+        a.no_cpu_baseline = a.no_cli_e2e = a.no_union = a.no_parity = True
     K = a.k
     return a
 
 
 def workload(args):
+    """BASELINE.json configs (SURVEY 8d definitions): C2 (default, the configuration the metric is quoted on), C4 =
+    3.1 Gbp assembly in 24 records with 100 N-runs vs a 30x 150 bp read set, C5 = 1 Gbp, 30x 15 kb reads, k = 31;
+    --scale S divides the genome and the read set by S (C4 and C5 default to their /16 twins on one GPU)."""
+    if args.config == "C5":
+        genome = int(1e9 / args.scale)
+        n = int(genome * 30 / 15000)
+        return {"workload": "C5/%g: synthetic %.4g Mbp genome, 30x HiFi-like reads (15 kb +- 2 kb, 0.1%% error), k=%d: count then validate"
+                            % (args.scale, genome / 1e6, K), "genome_bp": genome, "reads_per_gpu": n, "k": K, "scale": args.scale}
+    if args.config == "C4":
+        genome = int(3.1e9 / args.scale)
+        pairs = int(genome * 30 / (2 * READ_LEN))
+        return {"workload": "C4/%g: synthetic %.4g Mbp assembly in 24 records with 100 N-runs, 30x %d bp paired reads, 1%% error, k=%d: count then validate"
+                            % (args.scale, genome / 1e6, READ_LEN, K), "genome_bp": genome, "read_pairs_per_gpu": pairs, "k": K, "scale": args.scale}
     genome = int(args.genome_mbp * 1e6)
     pairs = int(genome * args.coverage / (2 * READ_LEN))
     return {"workload": "C2: synthetic %g Mbp genome, %gx %d bp paired reads, %g%% error, k=%d: count then validate"
                         % (args.genome_mbp, args.coverage, READ_LEN, ERR * 100, K),
             "genome_bp": genome, "read_pairs_per_gpu": pairs, "k": K}
+
+
+HUMAN_MBP = [248, 242, 198, 190, 182, 171, 159, 145, 138, 134, 135, 133, 114, 107, 102, 90, 83, 80, 59, 64, 47, 51, 156, 57]
+
+
+def make_inputs(args, cfg, rank, dev):
+    """-> (reads: pinned uint8 'N'-joined batch, segs: list of pinned uint8 ASCII segments (no N inside), k-mer instances,
+    estimated distinct k-mers, push offsets (read boundaries ~97 MB apart))"""
+    import numpy as np
+    import torch
+    from kreeq_b200 import synth
+    gsize = cfg["genome_bp"]
+    genome = synth.random_genome_codes(gsize, 2 + rank, dev)
+
+    def pinned(t):
+        h = torch.empty(t.numel(), dtype=torch.uint8, pin_memory=True)
+        h.copy_(t)
+        return h
+
+    if args.config == "C5":
+        n, per = cfg["reads_per_gpu"], 2000
+        parts, lens = [], []
+        for o in range(0, n, per):
+            r = synth.long_reads_ascii(genome, min(per, n - o), 15000, 2000, 5000, 25000, 0.001, 5 + 1000 * rank + o)
+            parts.append(r.cpu())
+        reads_host = torch.empty(sum(p.numel() for p in parts), dtype=torch.uint8, pin_memory=True)
+        torch.cat(parts, out=reads_host)
+        del parts
+        reads_np = reads_host.numpy()
+        sep = np.flatnonzero(reads_np == 78)
+        lens = np.diff(np.concatenate(([-1], sep))) - 1
+        inst = int(np.maximum(lens - K + 1, 0).sum())
+        est = int((gsize + reads_np.size * 0.001 * K * 0.85) * 1.05)
+        step = 97 << 20
+        cuts = [0] + [int(sep[min(sep.size - 1, np.searchsorted(sep, o))]) + 1 for o in range(step, reads_np.size, step)] + [reads_np.size]
+        cuts = sorted(set(cuts))
+    else:
+        pairs = cfg["read_pairs_per_gpu"]
+        reads_host = pinned(synth.paired_reads_ascii(genome, pairs, READ_LEN, ERR, 2 + 1000 * rank))
+        reads_np = reads_host.numpy()
+        inst = 2 * pairs * (READ_LEN - K + 1)
+        est = int((gsize + 2 * pairs * READ_LEN * ERR * K * 0.85) * 1.05)
+        B = 64 * (READ_LEN + 1) * 10000                       # ~97 MB pushes, cut at read boundaries
+        cuts = list(range(0, reads_np.size, B)) + [reads_np.size]
+    asm_host = pinned(synth.codes_to_ascii(genome))
+    del genome
+    torch.cuda.empty_cache()
+    asm_np = asm_host.numpy()
+    if args.config == "C4":
+        # 24 records with sizes proportional to the human chromosomes; 100 runs of N (50 000 / scale bases) cut the
+        # records into segments (gfalibs/src/gfa.cpp:170-203); the runs themselves never reach the device
+        rng = np.random.default_rng(4 + rank)
+        w = np.array(HUMAN_MBP, dtype=np.float64)
+        ends = np.round(np.cumsum(w / w.sum()) * gsize).astype(np.int64)
+        gaps = np.sort(rng.choice(gsize - 2000, 100, replace=False) + 1000)
+        bounds = np.unique(np.concatenate(([0], ends, gaps)))
+        glen = max(1, int(50000 / args.scale))
+        segs = []
+        for a, b in zip(bounds[:-1], bounds[1:]):
+            a2 = a + (glen if a in gaps else 0)               # the run of N replaces the first bases after the cut
+            if b - a2 > 0:
+                segs.append(asm_np[a2:b])
+    else:
+        n_contigs = 10
+        contig = gsize // n_contigs
+        segs = [asm_np[i * contig:(i + 1) * contig] for i in range(n_contigs)]
+    return reads_host, segs, asm_host, inst, est, cuts
 
 
 # ---- clocks ------------------------------------------------------------------------------------------
@@ -368,24 +456,13 @@ def main_ours(args):
         dist.init_process_group("nccl", device_id=dev)
     L = lib()
     cfg = workload(args)
-    gsize, pairs = cfg["genome_bp"], cfg["read_pairs_per_gpu"]
-    n_reads = 2 * pairs
-    inst_per_rank = n_reads * (READ_LEN - K + 1)
-    n_contigs = 10
-    contig = gsize // n_contigs
+    gsize = cfg["genome_bp"]
 
-    # -- synthetic input: weak scaling = N copies of the C2 problem: rank r brings its own genome (seed
+    # -- synthetic input: weak scaling = N copies of the problem: rank r brings its own genome (seed
     #    2 + r) and the 30x read set sampled from it, and validates that genome against the shared table --
-    genome = synth.random_genome_codes(gsize, 2 + rank, dev)
-    reads_dev = synth.paired_reads_ascii(genome, pairs, READ_LEN, ERR, 2 + 1000 * rank)
-    reads_host = torch.empty(reads_dev.numel(), dtype=torch.uint8, pin_memory=True)
-    reads_host.copy_(reads_dev)
-    del reads_dev
-    asm_host = torch.empty(gsize, dtype=torch.uint8, pin_memory=True)
-    asm_host.copy_(synth.codes_to_ascii(genome))
-    del genome
-    torch.cuda.empty_cache()
-    reads_np, asm_np = reads_host.numpy(), asm_host.numpy()
+    reads_host, segs, asm_host, inst_per_rank, est_distinct, push_cuts = make_inputs(args, cfg, rank, dev)
+    reads_np = reads_host.numpy()
+    contig = max(s.size for s in segs)                 # largest segment: sizes the row buffers
 
     def pack_to_device(a):
         words = L.kq_packed_words(a.size)
@@ -395,8 +472,8 @@ def main_ours(args):
         return b.to(dev), m.to(dev)
 
     d_rb, d_rm = pack_to_device(reads_np)
-    d_asm = [pack_to_device(asm_np[i * contig:(i + 1) * contig]) for i in range(n_contigs)]
-    asm_k = n_contigs * (contig - K + 1)
+    d_asm = [pack_to_device(s) + (s.size,) for s in segs]
+    asm_k = sum(max(0, s.size - K + 1) for s in segs)
     d_out = torch.empty(contig * 4, dtype=torch.int32, device=dev)          # kq_base[contig]
     d_acc = torch.zeros(3, dtype=torch.int64, device=dev)
     # e2e validate results land in page-locked host memory (the library copies rows into it directly);
@@ -407,8 +484,7 @@ def main_ours(args):
         h_out_t = torch.empty(contig * kreeq_b200.BASE.itemsize, dtype=torch.uint8, pin_memory=True)
         h_out = h_out_t.numpy().view(kreeq_b200.BASE)
 
-    # distinct k-mers per shard: genome k-mers + ~k novel k-mers per error, an even 1/N share of N such sets
-    est_distinct = int((gsize + n_reads * READ_LEN * ERR * K * 0.85) * 1.05)
+    # (est_distinct: genome k-mers + ~k novel k-mers per error; every shard gets an even 1/N share of N such sets)
     g = kreeq_b200.DBG(k=K, device=local, expected_distinct=est_distinct, rank=rank, nranks=world)
     # a real (non-default) stream: kq_set_stream(NULL) would mean "the library's own stream", and the
     # CUDA events below must be recorded on the stream the kernels are launched on
@@ -455,8 +531,8 @@ def main_ours(args):
 
     def validate_contigs():
         d_acc.zero_()
-        for b, m in d_asm:
-            check(L.kq_dev_validate_packed(g.handle, C.c_void_p(b.data_ptr()), C.c_void_p(m.data_ptr()), contig, 0,
+        for b, m, n_ in d_asm:
+            check(L.kq_dev_validate_packed(g.handle, C.c_void_p(b.data_ptr()), C.c_void_p(m.data_ptr()), n_, 0,
                                            C.c_void_p(d_out.data_ptr()), C.c_void_p(d_acc.data_ptr())), g.handle)
 
     def validate_resident():
@@ -467,8 +543,8 @@ def main_ours(args):
             # every rank validates its own genome: queries are routed to the owners, rows come back (two stream
             # barriers per contig); only the three QV counters are reduced
             g.finalize()
-            for b, m in d_asm:
-                router_v.chunk_packed(b, m, contig)
+            for b, m, n_ in d_asm:
+                router_v.chunk_packed(b, m, n_)
             router_v.counters()
             return
         # KQ_VALIDATE=peer: each k-mer is probed in its owner's shard over peer memory
@@ -561,8 +637,8 @@ def main_ours(args):
         g.clear()
         if os.environ.get("KQ_E2E_FLUSH"):                     # tuning knob: pending positions that start the pipeline
             g.set_flush_positions(int(os.environ["KQ_E2E_FLUSH"]))
-        B = 64 * (READ_LEN + 1) * 10000                       # ~97 MB pushes, cut at read boundaries
         if world > 1:
+            B = 64 * (READ_LEN + 1) * 10000
             # chunks of five pushes: packed on this rank's share of the host cores into pinned memory, copied in,
             # routed as one round; the next chunk is packed while the GPUs insert this one
             CH = 5 * B
@@ -575,28 +651,26 @@ def main_ours(args):
                 done.record(stream)
                 router.count(db, dm, n)
         else:
-            for o in range(0, reads_np.size, B):
-                g.traverseInReads(reads_np[o:o + B])
+            for o, o2 in zip(push_cuts[:-1], push_cuts[1:]):          # ~97 MB pushes, cut at read boundaries
+                g.traverseInReads(reads_np[o:o2])
         g.finalize()
         e1.record(stream)
         acc = kreeq_b200._lib.KqQV()
 
         def validate_host():
-            for i in range(n_contigs):
-                seg = asm_np[i * contig:(i + 1) * contig]
-                check(L.kq_validate_segment(g.handle, C.c_void_p(seg.ctypes.data), contig, 0,
+            for seg in segs:
+                check(L.kq_validate_segment(g.handle, C.c_void_p(seg.ctypes.data), seg.size, 0,
                                             C.c_void_p(h_out.ctypes.data), C.byref(acc)), g.handle)
         def validate_host_routed():
             # pack on the host, copy in, route the queries, copy the rows of this rank's slab out
-            for i in range(n_contigs):
-                seg = asm_np[i * contig:(i + 1) * contig]
+            for i, seg in enumerate(segs):
                 hb, hm, db, dm, done = v_bufs[i % 2]
                 done.synchronize()
-                check(L.kq_pack_host(C.c_void_p(seg.ctypes.data), contig, C.c_void_p(hb.data_ptr()), C.c_void_p(hm.data_ptr()), 0))
+                check(L.kq_pack_host(C.c_void_p(seg.ctypes.data), seg.size, C.c_void_p(hb.data_ptr()), C.c_void_p(hm.data_ptr()), 0))
                 db.copy_(hb, non_blocking=True); dm.copy_(hm, non_blocking=True)
                 done.record(stream)
-                router_v.chunk_packed(db, dm, contig)
-                check(L.kq_vroute_copy_rows(g.handle, C.c_void_p(h_out.ctypes.data), contig), g.handle)
+                router_v.chunk_packed(db, dm, seg.size)
+                check(L.kq_vroute_copy_rows(g.handle, C.c_void_p(h_out.ctypes.data), seg.size), g.handle)
             router_v.counters()
         if router_v is not None:
             validate_host_routed()
@@ -701,7 +775,7 @@ def main_ours(args):
                        "h2d_bytes_per_step": e["h2d"] if world == 1 else reads_np.size * 0.375,
                        "d2h_bytes_per_step": e["d2h"], "count_ms": e["count_ms"], "validate_ms": e["validate_ms"],
                        "validate_value": asm_k * world / (e["validate_ms"] * 1e-3),
-                       "host_input_bytes_per_step": int(reads_np.size + asm_np.size), "steps": min(args.steps, 2),
+                       "host_input_bytes_per_step": int(reads_np.size + sum(s.size for s in segs)), "steps": min(args.steps, 2),
                        "validate_out": "pageable host memory (staged)" if args.pageable_out else "page-locked host memory (direct)"}
     if world == 1 and not args.no_union:
         # database rows (A4 / A8): 2 x 5.8e7-record databases of a 10 Mbp genome saved, merged, saved, loaded
