@@ -90,7 +90,7 @@ struct kq_ctx {
     unsigned long long *d_cstart = nullptr, *d_fhist = nullptr, *d_fcursor = nullptr, *d_fstart = nullptr; uint64_t fine_cap = 0;
     FineTask *d_tasks = nullptr; uint64_t task_cap = 0; unsigned *d_ntasks = nullptr;
     // one-pass scatter: cursor per slice, big list for the tuples of slices that are full
-    unsigned long long *d_scur = nullptr; uint64_t scur_cap = 0;
+    unsigned *d_scur = nullptr; uint64_t scur_cap = 0;
     uint64_t *d_ovf2 = nullptr; uint64_t ovf2_cap = 0;
     // routed (multi-GPU) pipeline: receive slab the owners' tuples are written into by every rank
     uint64_t *d_slab = nullptr; uint64_t slab_cap = 0;          // tuples
@@ -356,7 +356,7 @@ int run_batch(kq_ctx *c, Source src) {
         }
         if (c->scur_cap < c->nslices * (uint64_t)stride) {
             cudaFree(c->d_scur); c->d_scur = nullptr; c->scur_cap = 0;
-            CU(cudaMalloc(&c->d_scur, c->nslices * (uint64_t)stride * 8));
+            CU(cudaMalloc(&c->d_scur, c->nslices * (uint64_t)stride * 4));
             c->scur_cap = c->nslices * (uint64_t)stride;
         }
         const uint64_t want_ovf = std::max<uint64_t>(OVF_CAP, bound / 8);
@@ -365,9 +365,9 @@ int run_batch(kq_ctx *c, Source src) {
             CU(cudaMalloc(&c->d_ovf2, want_ovf * 8 * tw));
             c->ovf2_cap = want_ovf;
         }
-        CU(cudaMemsetAsync(c->d_scur, 0, c->nslices * (uint64_t)stride * 8, c->stream));
+        CU(cudaMemsetAsync(c->d_scur, 0, c->nslices * (uint64_t)stride * 4, c->stream));
         const int t5 = time_begin(c, 5);
-        CU(launch_scatter_fine(c->stream, tv, src, c->d_tuples2, cap_t, c->d_scur, stride, src.tuples ? nullptr : c->d_inst,
+        CU(launch_scatter_fine(c->stream, tv, src, c->d_tuples2, (unsigned)cap_t, c->d_scur, stride, src.tuples ? nullptr : c->d_inst,
                                c->d_ovf2, c->ovf2_cap, c->d_ovf_n, &c->launches));
         time_end(c, t5);
         const int t2 = time_begin(c, 2);
@@ -473,6 +473,7 @@ int count_source(kq_ctx *c, Source src) {
         }
         uint64_t nb = c->optimistic ? (uint64_t)room * 4 : (uint64_t)room;
         nb = std::min(nb, left);
+        nb = std::min<uint64_t>(nb, 1ull << 32);                       // 32-bit cursors and positions inside a batch
         Source b = src;
         if (!src.tuples) { b.pos0 = src.pos0 + (src.npos - left); b.npos = nb; }
         else {
@@ -697,7 +698,7 @@ extern "C" int kq_set_tuning(const char *name, long long value) {
     else if (n == "s3_threads" && (value == 256 || value == 384 || value == 512)) t.s3_threads = (int)value;
     else if (n == "s3_ctas" && value >= 1 && value <= 8) t.s3_ctas = (int)value;
     else if (n == "pipeline" && value >= 2 && value <= 4) t.pipeline = (int)value;
-    else if (n == "cursor_stride" && value >= 1 && value <= 16) t.cursor_stride = (int)value;
+    else if (n == "cursor_stride" && value >= 1 && value <= 32) t.cursor_stride = (int)value;
     else return KQ_EINVAL;
     return KQ_OK;
 }

@@ -369,8 +369,10 @@ __device__ __noinline__ unsigned long long warp_combine(uint64_t key, uint32_t e
 template <int TW, int NT>
 __global__ void __launch_bounds__(NT, 3)
 smem_insert_kernel(TableView tv, const uint64_t *__restrict__ tuples, const unsigned long long *__restrict__ fstart,
-                   const unsigned long long *__restrict__ fcount, unsigned long long cap, int stride, uint64_t *ovf,
+                   const void *__restrict__ fcount_, unsigned long long cap, int stride, uint64_t *ovf,
                    unsigned long long ovf_cap, unsigned long long *ovf_n, unsigned long long *ticket) {
+    const unsigned long long *fcount = static_cast<const unsigned long long *>(fcount_);     // level-2 layout: exact counts
+    const unsigned *fcur = static_cast<const unsigned *>(fcount_);                             // one-pass layout: 32-bit cursors
     extern __shared__ __align__(128) unsigned char sm_piece[];
     __shared__ __align__(8) uint64_t bar;
     __shared__ unsigned long long sh_ticket, sh_fresh, sh_n;
@@ -388,7 +390,7 @@ smem_insert_kernel(TableView tv, const uint64_t *__restrict__ tuples, const unsi
         if (threadIdx.x == 0) {
             // next slice that has tuples (the counts are read by one thread: most slices of a small batch are empty)
             unsigned long long s, cnt = 0;
-            for (;;) { s = atomicAdd(ticket, 1ULL); if (s >= tv.nslices) break; cnt = fcount[s * stride]; if (cnt) break; }
+            for (;;) { s = atomicAdd(ticket, 1ULL); if (s >= tv.nslices) break; cnt = fstart ? fcount[s] : fcur[s * stride]; if (cnt) break; }
             sh_ticket = s; sh_n = fstart ? cnt : min(cnt, cap);
             if (s < tv.nslices) { mbar_expect_tx(&bar, bytes); bulk_g2s(piece, tv.T + (s << tv.slice_bits), bytes, &bar); }
         }
@@ -545,7 +547,7 @@ cudaError_t launch_fine_scatter(cudaStream_t st, const TableView &tv, const uint
 }
 
 cudaError_t launch_smem_insert(cudaStream_t st, const TableView &tv, const uint64_t *tuples, const unsigned long long *fstart,
-                               const unsigned long long *fcount, unsigned long long cap, int stride, uint64_t *ovf,
+                               const void *fcount, unsigned long long cap, int stride, uint64_t *ovf,
                                unsigned long long ovf_cap, unsigned long long *ovf_n, unsigned long long *ticket, uint64_t *launches) {
     cudaError_t e = cudaMemsetAsync(ticket, 0, sizeof(unsigned long long), st);
     if (e != cudaSuccess) return e;

@@ -43,8 +43,8 @@ Tuning &tuning() {
         v.direct_pct = (int)num("KQ_DIRECT_PCT", 25);
         { const char *e = std::getenv("KQ_DB_HOST"); v.db_host = e && e[0] == '1'; }
         v.pipeline = (int)num("KQ_PIPELINE", 4); if (v.pipeline < 2 || v.pipeline > 4) v.pipeline = 4;
-        v.cursor_stride = (int)num("KQ_CURSOR_STRIDE", 4); if (v.cursor_stride < 1 || v.cursor_stride > 16) v.cursor_stride = 4;
-        v.s3_threads = (int)num("KQ_S3_THREADS", 512); v.s3_ctas = (int)num("KQ_S3_CTAS", 3); if (v.s3_ctas < 1 || v.s3_ctas > 8) v.s3_ctas = 3;
+        v.cursor_stride = (int)num("KQ_CURSOR_STRIDE", 8); if (v.cursor_stride < 1 || v.cursor_stride > 32) v.cursor_stride = 8;
+        v.s3_threads = (int)num("KQ_S3_THREADS", 384); v.s3_ctas = (int)num("KQ_S3_CTAS", 3); if (v.s3_ctas < 1 || v.s3_ctas > 8) v.s3_ctas = 3;
         return v;
     }();
     return t;
@@ -191,13 +191,13 @@ count_direct_kernel(TableView tv, Source src, unsigned long long *instances,
 
 // Slice s of the table owns the tuples [s * cap, s * cap + min(cursor[s], cap)) of `out`: a k-mer instance takes its
 // place with ONE returning L2 atomic on its slice's cursor and one 8 / 16-byte store.  No histogram pass and no
-// shared-memory bins: the cursors (8 bytes x stride per slice, a few MB) and the frontier line of every region
+// shared-memory bins: the cursors (4 bytes x stride per slice, a few MB) and the frontier line of every region
 // (nslices x 128 B, tens of MB) stay in L2, which merges the stores of a line before it goes to HBM.
 // cap is 5/4 of the mean plus slack; the instances of a slice that is over-subscribed (high-copy k-mers) are counted
 // at once with the L2 CAS path, so nothing is ever dropped and no capacity has to be guessed right.
 template <int TW>
 __global__ void __launch_bounds__(TPB, 4)
-scatter_fine_kernel(TableView tv, Source src, uint64_t *__restrict__ out, unsigned long long cap, unsigned long long *cursor,
+scatter_fine_kernel(TableView tv, Source src, uint64_t *__restrict__ out, unsigned cap, unsigned *cursor,
                     int stride, unsigned long long *instances, uint64_t *ovf, unsigned long long ovf_cap, unsigned long long *ovf_n) {
     __shared__ unsigned long long sh[2];
     if (threadIdx.x < 2) sh[threadIdx.x] = 0;
@@ -205,21 +205,24 @@ scatter_fine_kernel(TableView tv, Source src, uint64_t *__restrict__ out, unsign
     unsigned long long inst = 0, fresh = 0;
     const uint64_t total = source_total(src), per = (uint64_t)TPB * RUN;
     for (uint64_t tile = (uint64_t)blockIdx.x * per; tile < total; tile += (uint64_t)gridDim.x * per) {
-        uint64_t key[RUN]; uint32_t e[RUN]; unsigned long long at[RUN];
+        uint64_t key[RUN]; uint32_t e[RUN]; unsigned at[RUN], sl[RUN];
         uint32_t m = produce<TW>(src, tv, tile, total, key, e);
+        // all RUN atomics of the thread are issued back to back (predicated, one result register each): the L2 round
+        // trips overlap instead of adding up
 #pragma unroll
         for (int i = 0; i < RUN; ++i) {
             if ((m >> i & 1u) && e[i] == 255u) m &= ~(1u << i);             // padding of the routed layout
-            if (!(m >> i & 1u)) continue;
-            const unsigned long long s = slice_of_key(key[i], tv.nslices);
-            const unsigned long long pos = atomicAdd(&cursor[s * stride], 1ULL);
-            at[i] = pos < cap ? s * cap + pos : ~0ULL;
+            const unsigned live = m >> i & 1u;
+            sl[i] = live ? (unsigned)slice_of_key(key[i], tv.nslices) : 0u;
+            asm volatile("{\n .reg .pred q;\n setp.ne.u32 q, %2, 0;\n mov.u32 %0, 0;\n"
+                         " @q atom.relaxed.gpu.global.add.u32 %0, [%1], 1;\n}"
+                         : "=r"(at[i]) : "l"(cursor + (size_t)sl[i] * stride), "r"(live) : "memory");
         }
 #pragma unroll
         for (int i = 0; i < RUN; ++i) {
             if (!(m >> i & 1u)) continue;
             ++inst;
-            if (at[i] != ~0ULL) { tuple_store<TW>(out, at[i], key[i], e[i]); continue; }
+            if (at[i] < cap) { tuple_store<TW>(out, (uint64_t)sl[i] * cap + at[i], key[i], e[i]); continue; }
             const int r = insert_instance(tv, key[i], e[i]);                // over-subscribed slice: count it now
             if (r < 0) {
                 const unsigned long long j = atomicAdd(ovf_n, 1ULL);
@@ -722,8 +725,8 @@ cudaError_t launch_count_direct(cudaStream_t st, const TableView &tv, const Sour
     return cudaGetLastError();
 }
 
-cudaError_t launch_scatter_fine(cudaStream_t st, const TableView &tv, const Source &src, uint64_t *out, unsigned long long cap,
-                                unsigned long long *cursor, int stride, unsigned long long *instances, uint64_t *ovf,
+cudaError_t launch_scatter_fine(cudaStream_t st, const TableView &tv, const Source &src, uint64_t *out, unsigned cap,
+                                unsigned *cursor, int stride, unsigned long long *instances, uint64_t *ovf,
                                 unsigned long long ovf_cap, unsigned long long *ovf_n, uint64_t *launches) {
     const uint64_t n = source_bound(src);
     if (!n) return cudaSuccess;

@@ -74,7 +74,7 @@ struct Tuning {
     int s3_threads, s3_ctas;   // shared-memory insert: threads per CTA (256 / 384 / 512), CTAs per SM in the grid
     int pipeline;              // big tables: 4 one-pass scatter + shared-memory insert, 3 two-level scatter + shared-memory
                                // insert, 2 level-1 scatter + L2 CAS insert
-    int cursor_stride;         // one-pass scatter: 8-byte words between the cursors of two slices
+    int cursor_stride;         // one-pass scatter: 4-byte words between the cursors of two slices
 };
 Tuning &tuning();
 // shared memory the scatter kernel needs for `nslices` bins of `cap` tuples; 0 if it cannot fit
@@ -91,8 +91,8 @@ cudaError_t launch_count_direct(cudaStream_t st, const TableView &tv, const Sour
                                 unsigned long long *ovf_n, uint64_t *launches);
 // one-pass scatter (big tables): tuple -> out[s * cap + atomicAdd(cursor[s * stride], 1)], s = slice of the key;
 // instances of over-subscribed slices are counted at once (L2 CAS); *instances += valid windows (may be NULL)
-cudaError_t launch_scatter_fine(cudaStream_t st, const TableView &tv, const Source &src, uint64_t *out, unsigned long long cap,
-                                unsigned long long *cursor, int stride, unsigned long long *instances, uint64_t *ovf,
+cudaError_t launch_scatter_fine(cudaStream_t st, const TableView &tv, const Source &src, uint64_t *out, unsigned cap,
+                                unsigned *cursor, int stride, unsigned long long *instances, uint64_t *ovf,
                                 unsigned long long ovf_cap, unsigned long long *ovf_n, uint64_t *launches);
 // 1. tuples per slice -> hist[nslices]
 cudaError_t launch_slice_hist(cudaStream_t st, const TableView &tv, const Source &src, unsigned long long *hist,
@@ -134,9 +134,9 @@ cudaError_t launch_fine_scatter(cudaStream_t st, const TableView &tv, const uint
                                 const unsigned *ntasks, unsigned task_bound, unsigned ns_max, uint64_t *out,
                                 unsigned long long *cursor, uint64_t *launches);
 // count the tuples [fstart[s], fstart[s] + fcount[s]) of every slice s in shared memory
-// (fstart == NULL: slice s owns [s * cap, s * cap + min(fcount[s * stride], cap)), the one-pass scatter's layout)
+// (fstart == NULL: fcount is the one-pass scatter's array of 32-bit cursors, slice s owns [s * cap, s * cap + min(cursor[s * stride], cap)))
 cudaError_t launch_smem_insert(cudaStream_t st, const TableView &tv, const uint64_t *tuples, const unsigned long long *fstart,
-                               const unsigned long long *fcount, unsigned long long cap, int stride, uint64_t *ovf,
+                               const void *fcount, unsigned long long cap, int stride, uint64_t *ovf,
                                unsigned long long ovf_cap, unsigned long long *ovf_n, unsigned long long *ticket, uint64_t *launches);
 
 // routed pipeline, steps 1-3: hist[nranks << nb_bits] of this rank's tuples; from the all-gathered
