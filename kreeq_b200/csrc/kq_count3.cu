@@ -150,7 +150,7 @@ fine_hist_kernel(TableView tv, const uint64_t *__restrict__ in, const FineTask *
 // The ring takes what arrives while a chunk waits for its flush, so a round of the CTA needs two barriers and
 // (practically) never a second pass.
 template <int TW, int NT, int R>
-__global__ void __launch_bounds__(NT, 1)
+__global__ void __launch_bounds__(NT, NT >= 1024 ? 1 : 2)
 fine_scatter_kernel(TableView tv, const uint64_t *__restrict__ in, const FineTask *__restrict__ tasks,
                     const unsigned *__restrict__ ntasks, uint64_t *__restrict__ out, unsigned long long *cursor,
                     unsigned ns_max, unsigned cap) {
@@ -322,7 +322,7 @@ __device__ __noinline__ unsigned smem_insert_slow(Slot *piece, unsigned mask, un
                                                   unsigned long long inc, uint64_t *ovf, unsigned long long ovf_cap, unsigned long long *ovf_n) {
     const unsigned long long tag = key + 1;
     const unsigned n = (unsigned)(inc >> 56);
-    unsigned j = (unsigned)mix64(key) & mask, fresh = 0;
+    unsigned j = (unsigned)home_hash(key) & mask, fresh = 0;
     for (unsigned probes = 0; probes < limit; ++probes) {
         unsigned long long t = *reinterpret_cast<volatile unsigned long long *>(&piece[j].tag);
         if (t == 0) {
@@ -397,25 +397,28 @@ smem_insert_kernel(TableView tv, const uint64_t *__restrict__ tuples, const unsi
         __syncthreads();
         const unsigned long long s = sh_ticket;
         if (s >= tv.nslices) break;
-        const unsigned long long a = fstart ? fstart[s] : s * cap, n = sh_n;
+        const uint64_t *tp = tuples + (fstart ? fstart[s] : s * cap) * TW;   // this slice's tuples
+        const unsigned n = (unsigned)sh_n;                                 // (a batch brings fewer than 2^32 tuples)
         ulonglong2 nxt[4];                                               // tuples are loaded one batch ahead (and under the bulk copy)
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            const unsigned long long i = (unsigned)j * NT + threadIdx.x;
-            nxt[j] = i < n ? t_raw<TW>(tuples, a + i) : make_ulonglong2(T_PAD1, T_PAD1);
+            const unsigned i = (unsigned)j * NT + threadIdx.x;
+            nxt[j] = i < n ? t_raw<TW>(tp, i) : make_ulonglong2(T_PAD1, T_PAD1);
         }
         mbar_wait(&bar, parity); parity ^= 1;
-        for (unsigned long long i0 = 0; i0 < n; i0 += (unsigned long long)NT * 4) {
-            ulonglong2 cur[4];
+        for (unsigned i0 = 0; i0 < n; i0 += NT * 4) {
+            ulonglong2 cur[4]; unsigned hm[4];
             bool run = false;
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
                 cur[j] = nxt[j];
                 uint64_t kj; uint32_t ej; t_split<TW>(cur[j], kj, ej);
-                const uint64_t kn = __shfl_down_sync(0xffffffffu, kj, 1);
-                run |= ej != 255u && lane < 31 && kn == kj;
-                const unsigned long long i = i0 + (unsigned long long)NT * 4 + (unsigned)j * NT + threadIdx.x;
-                nxt[j] = i < n ? t_raw<TW>(tuples, a + i) : make_ulonglong2(T_PAD1, T_PAD1);
+                hm[j] = (unsigned)home_hash(kj) & mask;
+                // a run = three neighbours in the stream with one key (two happen by chance in every tenth batch)
+                const uint64_t kn = __shfl_down_sync(0xffffffffu, kj, 1), kn2 = __shfl_down_sync(0xffffffffu, kj, 2);
+                run |= ej != 255u && lane < 30 && kn == kj && kn2 == kj;
+                const unsigned i = i0 + NT * 4 + (unsigned)j * NT + threadIdx.x;
+                nxt[j] = i < n ? t_raw<TW>(tp, i) : make_ulonglong2(T_PAD1, T_PAD1);
             }
             if (__any_sync(0xffffffffu, run)) {
                 // neighbours in the stream with the same key: combine inside the warp, count with the plain loop
@@ -438,10 +441,9 @@ smem_insert_kernel(TableView tv, const uint64_t *__restrict__ tuples, const unsi
                     while (idx < 4 && !have) {
                         const ulonglong2 w = idx == 0 ? cur[0] : idx == 1 ? cur[1] : idx == 2 ? cur[2] : cur[3];
                         uint32_t ej; t_split<TW>(w, ck, ej);
+                        if (ej != 255u) { ci = inc_lut[ej]; have = true; cj = idx == 0 ? hm[0] : idx == 1 ? hm[1] : idx == 2 ? hm[2] : hm[3]; probes = 0; }
                         ++idx;
-                        if (ej != 255u) { ci = inc_lut[ej]; have = true; }
                     }
-                    if (have) { cj = (unsigned)mix64(ck) & mask; probes = 0; }
                 }
                 if (!__any_sync(0xffffffffu, have)) break;
                 if (have) {
@@ -488,15 +490,16 @@ static size_t fine_scatter_smem(unsigned ns_max, unsigned cap, int tw) {
 }
 
 // flush chunk (tuples) of the level-2 scatter for bins of `ns_max` slices: the largest that fits shared memory
-unsigned fine_pick_cap(unsigned ns_max, int tw) {
+unsigned fine_pick_cap(unsigned ns_max, int tw, int ctas_per_sm) {
     static int max_smem = 0;
     if (!max_smem) {
         int dev = 0; cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
         if (max_smem <= 0) max_smem = 227 * 1024;
     }
+    const size_t budget = ((size_t)max_smem + 1024) / (ctas_per_sm > 1 ? ctas_per_sm : 1) - 2048;   // 1 KiB per CTA is the system's
     for (unsigned cap : {64u, 32u, 16u, 8u, 4u, 2u})
-        if (fine_scatter_smem(ns_max, cap, tw) <= (size_t)max_smem - 1024) return cap;
+        if (fine_scatter_smem(ns_max, cap, tw) <= budget) return cap;
     return 0;
 }
 
@@ -530,17 +533,23 @@ cudaError_t launch_fine_scatter(cudaStream_t st, const TableView &tv, const uint
                                 unsigned long long *cursor, uint64_t *launches) {
     if (!task_bound) return cudaSuccess;
     const int tw = tuple_words(tv.k);
-    const unsigned cap = fine_pick_cap(ns_max, tw);
+    // two CTAs of 512 threads per SM (each other's barriers and flushes overlap) when bins of at least 16 tuples fit
+    // half the shared memory, else one CTA of 1024 threads with all of it
+    const int variant = tuning().fs_variant;
+    int ctas = variant == 1 ? 1 : 2;
+    unsigned cap = fine_pick_cap(ns_max, tw, ctas);
+    if (ctas == 2 && cap < 16 && variant != 2) { ctas = 1; cap = fine_pick_cap(ns_max, tw, 1); }
     if (!cap) return cudaErrorInvalidConfiguration;
     const size_t smem = fine_scatter_smem(ns_max, cap, tw);
-    const unsigned grid = std::min<unsigned>(task_bound, (unsigned)sm_count());
+    const unsigned grid = std::min<unsigned>(task_bound, (unsigned)sm_count() * ctas);
     cudaError_t e;
-#define KQ_FS_LAUNCH(TWV) do {                                                                                         \
-        e = cudaFuncSetAttribute(fine_scatter_kernel<TWV, 1024, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+#define KQ_FS_LAUNCH(TWV, NTV, RV) do {                                                                               \
+        e = cudaFuncSetAttribute(fine_scatter_kernel<TWV, NTV, RV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
         if (e != cudaSuccess) return e;                                                                                \
-        cudaFuncSetAttribute(fine_scatter_kernel<TWV, 1024, 2>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared); \
-        fine_scatter_kernel<TWV, 1024, 2><<<grid, 1024, smem, st>>>(tv, in, tasks, ntasks, out, cursor, ns_max, cap); } while (0)
-    if (tw == 1) KQ_FS_LAUNCH(1); else KQ_FS_LAUNCH(2);
+        cudaFuncSetAttribute(fine_scatter_kernel<TWV, NTV, RV>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared); \
+        fine_scatter_kernel<TWV, NTV, RV><<<grid, NTV, smem, st>>>(tv, in, tasks, ntasks, out, cursor, ns_max, cap); } while (0)
+    if (ctas == 2) { if (tw == 1) KQ_FS_LAUNCH(1, 512, 4); else KQ_FS_LAUNCH(2, 512, 4); }
+    else { if (tw == 1) KQ_FS_LAUNCH(1, 1024, 2); else KQ_FS_LAUNCH(2, 1024, 2); }
 #undef KQ_FS_LAUNCH
     ++*launches;
     return cudaGetLastError();

@@ -66,6 +66,10 @@ __host__ __device__ __forceinline__ uint64_t mix64(uint64_t x) {
     x ^= x >> 33; return x;
 }
 
+// home slot of a key inside its slice: one multiplication, bits 38.. of the product (they depend on every bit of a
+// key of up to 60 bits and are independent of the slice hash, which uses another multiplier)
+__host__ __device__ __forceinline__ uint64_t home_hash(uint64_t key) { return (key * 0xD6E8FEB86659FD93ULL) >> 38; }
+
 __host__ __device__ __forceinline__ uint32_t cnt_cov(unsigned long long c) { return (uint32_t)(c >> 56) & 127u; }
 __host__ __device__ __forceinline__ uint32_t cnt_lane(unsigned long long c, int i) { return (uint32_t)(c >> (7 * i)) & 127u; }
 // true if a remainder record may exist: the count path moves 63 of a full slot's 127 to R at a time and so
@@ -104,7 +108,7 @@ __device__ __forceinline__ bool owns(const TableView &tv, uint64_t key) {
 
 // Slice of a key: multiplicative hash, top 32 bits scaled to nslices (a handful of instructions: the
 // histogram and scatter kernels evaluate it for every k-mer instance).  The home slot inside the slice
-// comes from the low bits of mix64(key), which only the kernels that touch the table compute.
+// comes from home_hash(key), which only the kernels that touch the table compute.
 __host__ __device__ __forceinline__ unsigned long long slice_of_key(uint64_t key, unsigned long long nslices) {
     return ((unsigned long long)(uint32_t)((key * 0x9E3779B97F4A7C15ULL) >> 32) * nslices) >> 32;
 }
@@ -224,7 +228,7 @@ __device__ __forceinline__ void remainder_add(const TableView &tv, uint64_t key,
 // slot of key, or nullptr; *out receives a consistent snapshot of it
 __device__ __forceinline__ Slot *find_slot(const TableView &tv, uint64_t key, Slot *out) {
     const unsigned long long tag = key + 1;
-    const uint64_t h = mix64(key);
+    const uint64_t h = home_hash(key);
     Slot *base = tv.T + (slice_of_key(key, tv.nslices) << tv.slice_bits);
     const unsigned long long mask = (1ull << tv.slice_bits) - 1;
     unsigned long long j = h & mask;
@@ -243,7 +247,7 @@ __device__ __forceinline__ Slot *find_slot(const TableView &tv, uint64_t key, Sl
 // the 8-bit / 32-bit split of the reference is decided when the database is written).
 __device__ __forceinline__ int insert_instance(const TableView &tv, uint64_t key, uint32_t e) {
     const unsigned long long tag = key + 1, inc = inc_of_edge(e);
-    const uint64_t h = mix64(key);
+    const uint64_t h = home_hash(key);
     Slot *base = tv.T + (slice_of_key(key, tv.nslices) << tv.slice_bits);
     const unsigned long long mask = (1ull << tv.slice_bits) - 1;
     unsigned long long j = h & mask;
@@ -291,7 +295,7 @@ __device__ __forceinline__ int insert_instance(const TableView &tv, uint64_t key
 // find the slot of key, claiming an empty one (cnt 0) if needed; *is_new reports a claim
 __device__ __forceinline__ Slot *find_or_claim(const TableView &tv, uint64_t key, bool *is_new) {
     const unsigned long long tag = key + 1;
-    const uint64_t h = mix64(key);
+    const uint64_t h = home_hash(key);
     Slot *base = tv.T + (slice_of_key(key, tv.nslices) << tv.slice_bits);
     const unsigned long long mask = (1ull << tv.slice_bits) - 1;
     unsigned long long j = h & mask;

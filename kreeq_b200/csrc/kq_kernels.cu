@@ -42,9 +42,10 @@ Tuning &tuning() {
         v.smem_insert = (int)num("KQ_SMEM_INSERT", 1);
         v.direct_pct = (int)num("KQ_DIRECT_PCT", 25);
         { const char *e = std::getenv("KQ_DB_HOST"); v.db_host = e && e[0] == '1'; }
+        v.fs_variant = (int)num("KQ_FS_VARIANT", 0);
         v.pipeline = (int)num("KQ_PIPELINE", 4); if (v.pipeline < 2 || v.pipeline > 4) v.pipeline = 4;
         v.cursor_stride = (int)num("KQ_CURSOR_STRIDE", 8); if (v.cursor_stride < 1 || v.cursor_stride > 32) v.cursor_stride = 8;
-        v.s3_threads = (int)num("KQ_S3_THREADS", 384); v.s3_ctas = (int)num("KQ_S3_CTAS", 3); if (v.s3_ctas < 1 || v.s3_ctas > 8) v.s3_ctas = 3;
+        v.s3_threads = (int)num("KQ_S3_THREADS", 256); v.s3_ctas = (int)num("KQ_S3_CTAS", 3); if (v.s3_ctas < 1 || v.s3_ctas > 8) v.s3_ctas = 3;
         return v;
     }();
     return t;
@@ -198,7 +199,7 @@ count_direct_kernel(TableView tv, Source src, unsigned long long *instances,
 template <int TW>
 __global__ void __launch_bounds__(TPB, 4)
 scatter_fine_kernel(TableView tv, Source src, uint64_t *__restrict__ out, unsigned cap, unsigned *cursor,
-                    int stride, unsigned long long *instances, uint64_t *ovf, unsigned long long ovf_cap, unsigned long long *ovf_n) {
+                    int stride, unsigned long long *instances, uint64_t *ovf, unsigned long long ovf_cap, unsigned long long *ovf_n, int experiment) {
     __shared__ unsigned long long sh[2];
     if (threadIdx.x < 2) sh[threadIdx.x] = 0;
     __syncthreads();
@@ -214,6 +215,7 @@ scatter_fine_kernel(TableView tv, Source src, uint64_t *__restrict__ out, unsign
             if ((m >> i & 1u) && e[i] == 255u) m &= ~(1u << i);             // padding of the routed layout
             const unsigned live = m >> i & 1u;
             sl[i] = live ? (unsigned)slice_of_key(key[i], tv.nslices) : 0u;
+            if (experiment == 2) { at[i] = (unsigned)(key[i] * 2654435761u) % (cap ? cap : 1u); continue; }   // timing experiment: no atomics
             asm volatile("{\n .reg .pred q;\n setp.ne.u32 q, %2, 0;\n mov.u32 %0, 0;\n"
                          " @q atom.relaxed.gpu.global.add.u32 %0, [%1], 1;\n}"
                          : "=r"(at[i]) : "l"(cursor + (size_t)sl[i] * stride), "r"(live) : "memory");
@@ -222,6 +224,7 @@ scatter_fine_kernel(TableView tv, Source src, uint64_t *__restrict__ out, unsign
         for (int i = 0; i < RUN; ++i) {
             if (!(m >> i & 1u)) continue;
             ++inst;
+            if (experiment == 1) continue;                                     // timing experiment: no stores
             if (at[i] < cap) { tuple_store<TW>(out, (uint64_t)sl[i] * cap + at[i], key[i], e[i]); continue; }
             const int r = insert_instance(tv, key[i], e[i]);                // over-subscribed slice: count it now
             if (r < 0) {
@@ -731,7 +734,8 @@ cudaError_t launch_scatter_fine(cudaStream_t st, const TableView &tv, const Sour
     const uint64_t n = source_bound(src);
     if (!n) return cudaSuccess;
     const unsigned grid = std::min<uint64_t>((n + TPB * RUN - 1) / (TPB * RUN), (uint64_t)sm_count() * 4);
-    KQ_TW_DISPATCH(tuple_words(tv.k), (scatter_fine_kernel<TW><<<grid, TPB, 0, st>>>(tv, src, out, cap, cursor, stride, instances, ovf, ovf_cap, ovf_n)));
+    static const int experiment = [] { const char *e = std::getenv("KQ_K1_EXPERIMENT"); return e ? std::atoi(e) : 0; }();   // timing experiments only (results are wrong)
+    KQ_TW_DISPATCH(tuple_words(tv.k), (scatter_fine_kernel<TW><<<grid, TPB, 0, st>>>(tv, src, out, cap, cursor, stride, instances, ovf, ovf_cap, ovf_n, experiment)));
     ++*launches;
     return cudaGetLastError();
 }

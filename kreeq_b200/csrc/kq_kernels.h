@@ -72,6 +72,7 @@ struct Tuning {
     int direct_pct;            // batches below this share of the table's slots skip the sweep (fused kernel)
     int db_host;               // .kreeq codec on the host (cross-check of the device codec)
     int s3_threads, s3_ctas;   // shared-memory insert: threads per CTA (256 / 384 / 512), CTAs per SM in the grid
+    int fs_variant;            // level-2 scatter: 0 auto (two CTAs per SM when the bins allow), 1 one CTA, 2 two CTAs
     int pipeline;              // big tables: 4 one-pass scatter + shared-memory insert, 3 two-level scatter + shared-memory
                                // insert, 2 level-1 scatter + L2 CAS insert
     int cursor_stride;         // one-pass scatter: 4-byte words between the cursors of two slices
@@ -118,7 +119,7 @@ inline unsigned coarse_bins(const TableView &tv) { return (unsigned)(((tv.nslice
 struct FineTask { unsigned long long lo, hi; unsigned s_lo, ns; };
 constexpr int KQ_ROUTE_PLAN_BINS = 2048;      // hash ranges per owner the routed plan kernel handles
 constexpr int KQ_S3_NT = 512;                 // threads per CTA of the shared-memory insert
-unsigned fine_pick_cap(unsigned ns_max, int tw);   // flush chunk of the level-2 scatter, 0 = bins do not fit
+unsigned fine_pick_cap(unsigned ns_max, int tw, int ctas_per_sm = 1);   // flush chunk of the level-2 scatter, 0 = bins do not fit
 cudaError_t launch_fine_plan(cudaStream_t st, const TableView &tv, unsigned ncoarse, const unsigned long long *start,
                              const unsigned long long *n, unsigned long long part, FineTask *tasks, unsigned task_cap,
                              unsigned *ntasks, uint64_t *launches);
