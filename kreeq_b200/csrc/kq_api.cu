@@ -88,7 +88,8 @@ struct kq_ctx {
     // level 2 of the pipeline: tuples in slice order, per-slice counts / offsets, tasks
     uint64_t *d_tuples2 = nullptr; uint64_t tup2_cap = 0;
     unsigned long long *d_cstart = nullptr, *d_fhist = nullptr, *d_fcursor = nullptr, *d_fstart = nullptr; uint64_t fine_cap = 0;
-    FineTask *d_tasks = nullptr; uint64_t task_cap = 0; unsigned *d_ntasks = nullptr;
+    FineTask *d_tasks = nullptr; uint64_t task_cap = 0; unsigned *d_ntasks = nullptr, *d_task_first = nullptr;
+    unsigned *d_hist2 = nullptr; uint64_t hist2_cap = 0;
     // one-pass scatter: cursor per slice, big list for the tuples of slices that are full
     unsigned *d_scur = nullptr; uint64_t scur_cap = 0;
     uint64_t *d_ovf2 = nullptr; uint64_t ovf2_cap = 0;
@@ -292,7 +293,13 @@ int pipeline_scratch(kq_ctx *c, uint64_t tuples, bool level2 = false, uint64_t t
         CU(cudaMalloc(&c->d_tasks, tasks * sizeof(FineTask)));
         c->task_cap = tasks;
     }
-    if (!c->d_ntasks) CU(cudaMalloc(&c->d_ntasks, sizeof(unsigned)));
+    if (!c->d_ntasks) { CU(cudaMalloc(&c->d_ntasks, sizeof(unsigned))); CU(cudaMalloc(&c->d_task_first, (KQ_MAX_COARSE + 2) * sizeof(unsigned))); }
+    const uint64_t h2 = c->task_cap << c->cshift;                     // per-task histograms of the level-2 pass
+    if (c->hist2_cap < h2) {
+        cudaFree(c->d_hist2); c->d_hist2 = nullptr; c->hist2_cap = 0;
+        CU(cudaMalloc(&c->d_hist2, h2 * sizeof(unsigned)));
+        c->hist2_cap = h2;
+    }
     return KQ_OK;
 }
 
@@ -385,10 +392,10 @@ int run_batch(kq_ctx *c, Source src) {
         int rc = pipeline_scratch(c, 0, true, bound); if (rc) return rc;
         const int t4 = time_begin(c, 4);
         CU(cudaMemsetAsync(c->d_fhist, 0, c->nslices * 8, c->stream));
-        CU(launch_fine_hist(c->stream, tv, src.tuples, c->d_tasks, c->d_ntasks, c->route_task_bound, c->route_ns_max, c->d_fhist, &c->launches));
+        CU(launch_fine_hist(c->stream, tv, src.tuples, c->d_tasks, c->d_ntasks, c->route_task_bound, c->route_ns_max, c->d_fhist, nullptr, &c->launches));
         CU(launch_slice_offsets(c->stream, c->nslices, c->d_fhist, c->d_fcursor, c->d_fstart, c->d_total, nullptr, &c->launches));
         const int t6 = time_begin(c, 6);
-        CU(launch_fine_scatter(c->stream, tv, src.tuples, c->d_tasks, c->d_ntasks, c->route_task_bound, c->route_ns_max, c->d_tuples2, c->d_fcursor, &c->launches));
+        CU(launch_fine_scatter(c->stream, tv, src.tuples, c->d_tasks, c->d_ntasks, c->route_task_bound, c->route_ns_max, c->d_tuples2, c->d_fcursor, nullptr, nullptr, &c->launches));
         time_end(c, t6);
         time_end(c, t4);
         const int t2 = time_begin(c, 2);
@@ -438,12 +445,11 @@ int run_batch(kq_ctx *c, Source src) {
     }
     const int t4 = time_begin(c, 4);
     const unsigned task_bound = (unsigned)std::min<uint64_t>(c->task_cap, bound / tuning().part + ncoarse + 1);
-    CU(launch_fine_plan(c->stream, tv, ncoarse, c->d_cstart, c->d_hist, tuning().part, c->d_tasks, task_bound, c->d_ntasks, &c->launches));
-    CU(cudaMemsetAsync(c->d_fhist, 0, c->nslices * 8, c->stream));
-    CU(launch_fine_hist(c->stream, tv, c->d_tuples, c->d_tasks, c->d_ntasks, task_bound, ns_max, c->d_fhist, &c->launches));
-    CU(launch_slice_offsets(c->stream, c->nslices, c->d_fhist, c->d_fcursor, c->d_fstart, c->d_total, nullptr, &c->launches));
+    CU(launch_fine_plan(c->stream, tv, ncoarse, c->d_cstart, c->d_hist, tuning().part, c->d_tasks, task_bound, c->d_ntasks, c->d_task_first, &c->launches));
+    CU(launch_fine_hist(c->stream, tv, c->d_tuples, c->d_tasks, c->d_ntasks, task_bound, ns_max, nullptr, c->d_hist2, &c->launches));
+    CU(launch_fine_offsets(c->stream, tv, ncoarse, c->d_cstart, c->d_task_first, c->d_hist2, ns_max, c->d_fstart, c->d_fhist, &c->launches));
     const int t6 = time_begin(c, 6);
-    CU(launch_fine_scatter(c->stream, tv, c->d_tuples, c->d_tasks, c->d_ntasks, task_bound, ns_max, c->d_tuples2, c->d_fcursor, &c->launches));
+    CU(launch_fine_scatter(c->stream, tv, c->d_tuples, c->d_tasks, c->d_ntasks, task_bound, ns_max, c->d_tuples2, nullptr, c->d_hist2, c->d_fstart, &c->launches));
     time_end(c, t6);
     time_end(c, t4);
     const int t2 = time_begin(c, 2);
@@ -604,7 +610,7 @@ extern "C" void kq_destroy(kq_ctx *c) {
     cudaFree(c->d_pb_alt); cudaFree(c->d_pi_alt);
     cudaFree(c->d_pb); cudaFree(c->d_pi); cudaFree(c->d_tuples); cudaFree(c->d_hist); cudaFree(c->d_cursor);
     cudaFree(c->d_tuples2); cudaFree(c->d_cstart); cudaFree(c->d_fhist); cudaFree(c->d_fcursor); cudaFree(c->d_fstart);
-    cudaFree(c->d_tasks); cudaFree(c->d_ntasks); cudaFree(c->d_scur); cudaFree(c->d_ovf2);
+    cudaFree(c->d_tasks); cudaFree(c->d_ntasks); cudaFree(c->d_task_first); cudaFree(c->d_hist2); cudaFree(c->d_scur); cudaFree(c->d_ovf2);
     cudaFree(c->d_total); cudaFree(c->d_nsrc); cudaFree(c->d_ticket); cudaFree(c->d_ovf); cudaFree(c->d_ovf_n);
     for (void *p : c->ipc_opened) cudaIpcCloseMemHandle(p);
     for (void *p : c->peer_opened) cudaIpcCloseMemHandle(p);

@@ -54,7 +54,7 @@ __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)_
 // [b << cshift, (b + 1) << cshift).  One task = at most `part` consecutive tuples of one coarse bin.
 __global__ void __launch_bounds__(1024, 1)
 fine_plan_kernel(TableView tv, unsigned ncoarse, const unsigned long long *start, const unsigned long long *n,
-                 unsigned long long part, FineTask *tasks, unsigned task_cap, unsigned *ntasks) {
+                 unsigned long long part, FineTask *tasks, unsigned task_cap, unsigned *ntasks, unsigned *task_first) {
     __shared__ unsigned first[KQ_MAX_COARSE + 1];
     for (unsigned b = threadIdx.x; b < ncoarse; b += 1024) first[b] = (unsigned)((n[b] + part - 1) / part);
     __syncthreads();
@@ -65,6 +65,7 @@ fine_plan_kernel(TableView tv, unsigned ncoarse, const unsigned long long *start
         *ntasks = run < task_cap ? run : task_cap;                    // task_cap is an upper bound by construction
     }
     __syncthreads();
+    for (unsigned b = threadIdx.x; b <= ncoarse; b += 1024) task_first[b] = first[b] < task_cap ? first[b] : task_cap;
     for (unsigned b = threadIdx.x; b < ncoarse; b += 1024) {
         const unsigned long long lo = start[b], hi = lo + n[b];
         const unsigned s_lo = b << tv.cshift;
@@ -116,7 +117,7 @@ constexpr int FH_NT = 512;
 template <int TW>
 __global__ void __launch_bounds__(FH_NT, 2)
 fine_hist_kernel(TableView tv, const uint64_t *__restrict__ in, const FineTask *__restrict__ tasks,
-                 const unsigned *__restrict__ ntasks, unsigned long long *fhist) {
+                 const unsigned *__restrict__ ntasks, unsigned long long *fhist, unsigned *hist2, unsigned ns_max) {
     extern __shared__ unsigned int fh[];
     const unsigned nt = *ntasks;
     for (unsigned t = blockIdx.x; t < nt; t += gridDim.x) {
@@ -136,34 +137,68 @@ fine_hist_kernel(TableView tv, const uint64_t *__restrict__ in, const FineTask *
                 if (e[j] != 255u) atomicAdd(&fh[(unsigned)slice_of_key(key[j], tv.nslices) - tk.s_lo], 1u);
         }
         __syncthreads();
-        for (unsigned i = threadIdx.x; i < tk.ns; i += FH_NT)
-            if (fh[i]) atomicAdd(&fhist[tk.s_lo + i], (unsigned long long)fh[i]);
+        if (hist2) {                                                     // per task: fine_offsets_kernel turns them into positions
+            for (unsigned i = threadIdx.x; i < tk.ns; i += FH_NT) hist2[(size_t)t * ns_max + i] = fh[i];
+        } else {
+            for (unsigned i = threadIdx.x; i < tk.ns; i += FH_NT)
+                if (fh[i]) atomicAdd(&fhist[tk.s_lo + i], (unsigned long long)fh[i]);
+        }
         __syncthreads();
     }
+}
+
+// One CTA per coarse bin b: hist2[t][f] (tuples of slice s_lo + f in task t) becomes the offset of task t inside the
+// slice's region, fcount[s] the slice's total and fstart[s] its first tuple (regions follow each other inside the
+// coarse bin's range of the output, which starts where the bin starts in the level-1 output).
+__global__ void __launch_bounds__(1024, 1)
+fine_offsets_kernel(TableView tv, const unsigned long long *__restrict__ start, const unsigned *__restrict__ task_first,
+                    unsigned *hist2, unsigned ns_max, unsigned long long *fstart, unsigned long long *fcount) {
+    extern __shared__ unsigned long long tot[];
+    const unsigned b = blockIdx.x, s_lo = b << tv.cshift;
+    const unsigned ns = (unsigned)min((unsigned long long)(1u << tv.cshift), tv.nslices - s_lo);
+    const unsigned t0 = task_first[b], t1 = task_first[b + 1];
+    for (unsigned f = threadIdx.x; f < ns; f += 1024) {
+        unsigned run = 0;
+        for (unsigned t = t0; t < t1; ++t) { unsigned *p = hist2 + (size_t)t * ns_max + f; const unsigned v = *p; *p = run; run += v; }
+        tot[f] = run; fcount[s_lo + f] = run;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long run = start[b];
+        for (unsigned f = 0; f < ns; ++f) { const unsigned long long v = tot[f]; tot[f] = run; run += v; }
+    }
+    __syncthreads();
+    for (unsigned f = threadIdx.x; f < ns; f += 1024) fstart[s_lo + f] = tot[f];
 }
 
 // ---- scatter into slice order ----------------------------------------------------------------------------------
 
 // Shared memory: `ns` ring bins of RING = 3/2 CAP tuples, an append counter and a flushed counter per bin.
 // A tuple is appended with one shared-memory atomic and one store; a bin that holds CAP tuples leaves as one
-// coalesced CAP * 8 * TW byte store at a position reserved with one global atomic on the slice's cursor.
-// The ring takes what arrives while a chunk waits for its flush, so a round of the CTA needs two barriers and
-// (practically) never a second pass.
-template <int TW, int NT, int R>
+// coalesced CAP * 8 * TW byte store.  The ring takes what arrives while a chunk waits for its flush, so a round of
+// the CTA needs two barriers and (practically) never a second pass.
+// Where a chunk goes: PRIV (local pipeline) -- every task owns its part of every slice's region (fine_offsets_kernel
+// turned the per-task histograms into start positions), the cursors live in shared memory and a flush costs no global
+// round trip; !PRIV (routed slab, whose bins overlap at their edges) -- one global atomic on the slice's cursor.
+template <int TW, int NT, int R, int CAP, bool PRIV>
 __global__ void __launch_bounds__(NT, NT >= 1024 ? 1 : 2)
 fine_scatter_kernel(TableView tv, const uint64_t *__restrict__ in, const FineTask *__restrict__ tasks,
                     const unsigned *__restrict__ ntasks, uint64_t *__restrict__ out, unsigned long long *cursor,
-                    unsigned ns_max, unsigned cap) {
+                    const unsigned *__restrict__ hist2, const unsigned long long *__restrict__ fstart, unsigned ns_max) {
+    constexpr unsigned RING = CAP + CAP / 2;
     extern __shared__ uint64_t sm3[];
-    const unsigned ring = cap + cap / 2;
     uint64_t *bins = sm3;
-    unsigned int *fill = reinterpret_cast<unsigned int *>(bins + (size_t)ns_max * ring * TW);
+    unsigned long long *cur = reinterpret_cast<unsigned long long *>(bins + (size_t)ns_max * RING * TW);   // PRIV only
+    unsigned int *fill = reinterpret_cast<unsigned int *>(cur + (PRIV ? ns_max : 0));
     unsigned int *done = fill + ns_max;
     const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = NT / 32;
     const unsigned nt = *ntasks;
     for (unsigned t = blockIdx.x; t < nt; t += gridDim.x) {
         const FineTask tk = tasks[t];
-        for (unsigned i = threadIdx.x; i < tk.ns; i += NT) { fill[i] = 0; done[i] = 0; }
+        for (unsigned i = threadIdx.x; i < tk.ns; i += NT) {
+            fill[i] = 0; done[i] = 0;
+            if (PRIV) cur[i] = fstart[tk.s_lo + i] + hist2[(size_t)t * ns_max + i];
+        }
         __syncthreads();
         ulonglong2 nxt[R];                                               // the next round's tuples, loaded a round ahead
 #pragma unroll
@@ -193,27 +228,31 @@ fine_scatter_kernel(TableView tv, const uint64_t *__restrict__ in, const FineTas
                 for (int i = 0; i < R; ++i) {
                     if (!(m >> i & 1u)) continue;
                     const unsigned d = pos[i] - *reinterpret_cast<volatile unsigned int *>(&done[bin[i]]);
-                    if (d < ring) { t_store<TW>(bins, (size_t)bin[i] * ring + pos[i] % ring, key[i], e[i]); m &= ~(1u << i); }
-                    full |= d + 1 >= cap;
+                    if (d < RING) { t_store<TW>(bins, bin[i] * RING + pos[i] % RING, key[i], e[i]); m &= ~(1u << i); }
+                    full |= d + 1 >= (unsigned)CAP;
                 }
                 if (!__syncthreads_or(full)) break;
-                // lane l of a warp looks at bin b0 + l; the reservations of the warp's 32 bins are issued together
+                // lane l of a warp looks at bin b0 + l, then the warp copies the full chunks of its 32 bins one by one
                 for (unsigned b0 = warp * 32; b0 < tk.ns; b0 += nwarps * 32) {
                     const unsigned b = b0 + lane;
                     unsigned d0 = 0, chunks = 0;
-                    if (b < tk.ns) { d0 = done[b]; chunks = min(fill[b] - d0, ring) / cap; }
+                    if (b < tk.ns) { d0 = done[b]; chunks = min(fill[b] - d0, RING) / CAP; }
                     unsigned long long g = 0;
-                    if (chunks) { g = atomicAdd(&cursor[tk.s_lo + b], (unsigned long long)chunks * cap); done[b] = d0 + chunks * cap; }
+                    if (chunks) {
+                        if (PRIV) { g = cur[b]; cur[b] = g + chunks * CAP; }
+                        else g = atomicAdd(&cursor[tk.s_lo + b], (unsigned long long)chunks * CAP);
+                        done[b] = d0 + chunks * CAP;
+                    }
                     unsigned todo = __ballot_sync(0xffffffffu, chunks != 0);
                     while (todo) {
                         const int l = __ffs(todo) - 1; todo &= todo - 1;
                         const unsigned long long gg = __shfl_sync(0xffffffffu, g, l);
                         const unsigned dd = __shfl_sync(0xffffffffu, d0, l);
-                        const unsigned nn = __shfl_sync(0xffffffffu, chunks, l) * cap;
-                        const uint64_t *srcw = bins + (size_t)(b0 + l) * ring * TW;
+                        const unsigned nn = __shfl_sync(0xffffffffu, chunks, l) * CAP;
+                        const uint64_t *srcw = bins + (size_t)(b0 + l) * RING * TW;
                         uint64_t *dst = out + gg * TW;
                         for (unsigned w = lane; w < nn * TW; w += 32)
-                            __stcs(dst + w, srcw[((dd + w / TW) % ring) * TW + w % TW]);
+                            __stcs(dst + w, srcw[((dd + w / TW) % RING) * TW + w % TW]);
                     }
                 }
                 if (!__syncthreads_or(m != 0)) break;                    // nobody had to wait for a flush
@@ -225,17 +264,17 @@ fine_scatter_kernel(TableView tv, const uint64_t *__restrict__ in, const FineTas
             unsigned d0 = 0, f = 0;
             if (b < tk.ns) { d0 = done[b]; f = fill[b] - d0; }
             unsigned long long g = 0;
-            if (f) g = atomicAdd(&cursor[tk.s_lo + b], (unsigned long long)f);
+            if (f) g = PRIV ? cur[b] : atomicAdd(&cursor[tk.s_lo + b], (unsigned long long)f);
             unsigned todo = __ballot_sync(0xffffffffu, f != 0);
             while (todo) {
                 const int l = __ffs(todo) - 1; todo &= todo - 1;
                 const unsigned long long gg = __shfl_sync(0xffffffffu, g, l);
                 const unsigned dd = __shfl_sync(0xffffffffu, d0, l);
                 const unsigned nn = __shfl_sync(0xffffffffu, f, l);
-                const uint64_t *srcw = bins + (size_t)(b0 + l) * ring * TW;
+                const uint64_t *srcw = bins + (size_t)(b0 + l) * RING * TW;
                 uint64_t *dst = out + gg * TW;
                 for (unsigned w = lane; w < nn * TW; w += 32)
-                    __stcs(dst + w, srcw[((dd + w / TW) % ring) * TW + w % TW]);
+                    __stcs(dst + w, srcw[((dd + w / TW) % RING) * TW + w % TW]);
             }
         }
         __syncthreads();
@@ -485,11 +524,12 @@ smem_insert_kernel(TableView tv, const uint64_t *__restrict__ tuples, const unsi
 
 #define KQ_TW_DISPATCH3(tw, CALL) do { if ((tw) == 1) { constexpr int TW = 1; CALL; } else { constexpr int TW = 2; CALL; } } while (0)
 
-static size_t fine_scatter_smem(unsigned ns_max, unsigned cap, int tw) {
-    return (size_t)ns_max * (cap + cap / 2) * tw * 8 + (size_t)ns_max * 8;
+static size_t fine_scatter_smem(unsigned ns_max, unsigned cap, int tw, bool priv = true) {
+    return (size_t)ns_max * (cap + cap / 2) * tw * 8 + (size_t)ns_max * (priv ? 16 : 8);
 }
 
-// flush chunk (tuples) of the level-2 scatter for bins of `ns_max` slices: the largest that fits shared memory
+// flush chunk (tuples) of the level-2 scatter for bins of `ns_max` slices: the largest of 64 / 32 / 16 / 8 that fits
+// the shared memory of `ctas_per_sm` CTAs per SM (0: none does)
 unsigned fine_pick_cap(unsigned ns_max, int tw, int ctas_per_sm) {
     static int max_smem = 0;
     if (!max_smem) {
@@ -498,15 +538,15 @@ unsigned fine_pick_cap(unsigned ns_max, int tw, int ctas_per_sm) {
         if (max_smem <= 0) max_smem = 227 * 1024;
     }
     const size_t budget = ((size_t)max_smem + 1024) / (ctas_per_sm > 1 ? ctas_per_sm : 1) - 2048;   // 1 KiB per CTA is the system's
-    for (unsigned cap : {64u, 32u, 16u, 8u, 4u, 2u})
+    for (unsigned cap : {64u, 32u, 16u, 8u})
         if (fine_scatter_smem(ns_max, cap, tw) <= budget) return cap;
     return 0;
 }
 
 cudaError_t launch_fine_plan(cudaStream_t st, const TableView &tv, unsigned ncoarse, const unsigned long long *start,
                              const unsigned long long *n, unsigned long long part, FineTask *tasks, unsigned task_cap,
-                             unsigned *ntasks, uint64_t *launches) {
-    fine_plan_kernel<<<1, 1024, 0, st>>>(tv, ncoarse, start, n, part, tasks, task_cap, ntasks);
+                             unsigned *ntasks, unsigned *task_first, uint64_t *launches) {
+    fine_plan_kernel<<<1, 1024, 0, st>>>(tv, ncoarse, start, n, part, tasks, task_cap, ntasks, task_first);
     ++*launches;
     return cudaGetLastError();
 }
@@ -520,19 +560,29 @@ cudaError_t launch_route_plan(cudaStream_t st, const TableView &tv, const RouteM
 
 cudaError_t launch_fine_hist(cudaStream_t st, const TableView &tv, const uint64_t *in, const FineTask *tasks,
                              const unsigned *ntasks, unsigned task_bound, unsigned ns_max, unsigned long long *fhist,
-                             uint64_t *launches) {
+                             unsigned *hist2, uint64_t *launches) {
     if (!task_bound) return cudaSuccess;
     const unsigned grid = std::min<unsigned>(task_bound, (unsigned)sm_count() * 2);
-    KQ_TW_DISPATCH3(tuple_words(tv.k), (fine_hist_kernel<TW><<<grid, FH_NT, (size_t)ns_max * 4, st>>>(tv, in, tasks, ntasks, fhist)));
+    KQ_TW_DISPATCH3(tuple_words(tv.k), (fine_hist_kernel<TW><<<grid, FH_NT, (size_t)ns_max * 4, st>>>(tv, in, tasks, ntasks, fhist, hist2, ns_max)));
     ++*launches;
     return cudaGetLastError();
 }
 
+cudaError_t launch_fine_offsets(cudaStream_t st, const TableView &tv, unsigned ncoarse, const unsigned long long *start,
+                                const unsigned *task_first, unsigned *hist2, unsigned ns_max, unsigned long long *fstart,
+                                unsigned long long *fcount, uint64_t *launches) {
+    fine_offsets_kernel<<<ncoarse, 1024, (size_t)ns_max * 8, st>>>(tv, start, task_first, hist2, ns_max, fstart, fcount);
+    ++*launches;
+    return cudaGetLastError();
+}
+
+// hist2 / fstart != NULL: private cursors (local pipeline); else one global atomic per flush on `cursor`
 cudaError_t launch_fine_scatter(cudaStream_t st, const TableView &tv, const uint64_t *in, const FineTask *tasks,
                                 const unsigned *ntasks, unsigned task_bound, unsigned ns_max, uint64_t *out,
-                                unsigned long long *cursor, uint64_t *launches) {
+                                unsigned long long *cursor, const unsigned *hist2, const unsigned long long *fstart, uint64_t *launches) {
     if (!task_bound) return cudaSuccess;
     const int tw = tuple_words(tv.k);
+    const bool priv = hist2 != nullptr;
     // two CTAs of 512 threads per SM (each other's barriers and flushes overlap) when bins of at least 16 tuples fit
     // half the shared memory, else one CTA of 1024 threads with all of it
     const int variant = tuning().fs_variant;
@@ -540,17 +590,23 @@ cudaError_t launch_fine_scatter(cudaStream_t st, const TableView &tv, const uint
     unsigned cap = fine_pick_cap(ns_max, tw, ctas);
     if (ctas == 2 && cap < 16 && variant != 2) { ctas = 1; cap = fine_pick_cap(ns_max, tw, 1); }
     if (!cap) return cudaErrorInvalidConfiguration;
-    const size_t smem = fine_scatter_smem(ns_max, cap, tw);
+    const size_t smem = fine_scatter_smem(ns_max, cap, tw, priv);
     const unsigned grid = std::min<unsigned>(task_bound, (unsigned)sm_count() * ctas);
-    cudaError_t e;
-#define KQ_FS_LAUNCH(TWV, NTV, RV) do {                                                                               \
-        e = cudaFuncSetAttribute(fine_scatter_kernel<TWV, NTV, RV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+    cudaError_t e = cudaSuccess;
+#define KQ_FS_GO(TWV, NTV, RV, CAPV, PV) do {                                                                          \
+        e = cudaFuncSetAttribute(fine_scatter_kernel<TWV, NTV, RV, CAPV, PV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
         if (e != cudaSuccess) return e;                                                                                \
-        cudaFuncSetAttribute(fine_scatter_kernel<TWV, NTV, RV>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared); \
-        fine_scatter_kernel<TWV, NTV, RV><<<grid, NTV, smem, st>>>(tv, in, tasks, ntasks, out, cursor, ns_max, cap); } while (0)
-    if (ctas == 2) { if (tw == 1) KQ_FS_LAUNCH(1, 512, 4); else KQ_FS_LAUNCH(2, 512, 4); }
-    else { if (tw == 1) KQ_FS_LAUNCH(1, 1024, 2); else KQ_FS_LAUNCH(2, 1024, 2); }
-#undef KQ_FS_LAUNCH
+        cudaFuncSetAttribute(fine_scatter_kernel<TWV, NTV, RV, CAPV, PV>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared); \
+        fine_scatter_kernel<TWV, NTV, RV, CAPV, PV><<<grid, NTV, smem, st>>>(tv, in, tasks, ntasks, out, cursor, hist2, fstart, ns_max); } while (0)
+#define KQ_FS_CAP(TWV, NTV, RV, PV) do {                                                                               \
+        if (cap == 64) KQ_FS_GO(TWV, NTV, RV, 64, PV); else if (cap == 32) KQ_FS_GO(TWV, NTV, RV, 32, PV);             \
+        else if (cap == 16) KQ_FS_GO(TWV, NTV, RV, 16, PV); else KQ_FS_GO(TWV, NTV, RV, 8, PV); } while (0)
+#define KQ_FS_SHAPE(TWV, PV) do { if (ctas == 2) KQ_FS_CAP(TWV, 512, 4, PV); else KQ_FS_CAP(TWV, 1024, 2, PV); } while (0)
+    if (tw == 1) { if (priv) KQ_FS_SHAPE(1, true); else KQ_FS_SHAPE(1, false); }
+    else { if (priv) KQ_FS_SHAPE(2, true); else KQ_FS_SHAPE(2, false); }
+#undef KQ_FS_SHAPE
+#undef KQ_FS_CAP
+#undef KQ_FS_GO
     ++*launches;
     return cudaGetLastError();
 }

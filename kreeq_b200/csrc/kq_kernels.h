@@ -122,18 +122,22 @@ constexpr int KQ_S3_NT = 512;                 // threads per CTA of the shared-m
 unsigned fine_pick_cap(unsigned ns_max, int tw, int ctas_per_sm = 1);   // flush chunk of the level-2 scatter, 0 = bins do not fit
 cudaError_t launch_fine_plan(cudaStream_t st, const TableView &tv, unsigned ncoarse, const unsigned long long *start,
                              const unsigned long long *n, unsigned long long part, FineTask *tasks, unsigned task_cap,
-                             unsigned *ntasks, uint64_t *launches);
+                             unsigned *ntasks, unsigned *task_first, uint64_t *launches);
+// per coarse bin: hist2[t][f] -> offset of task t inside slice f's region; fstart / fcount of every slice
+cudaError_t launch_fine_offsets(cudaStream_t st, const TableView &tv, unsigned ncoarse, const unsigned long long *start,
+                                const unsigned *task_first, unsigned *hist2, unsigned ns_max, unsigned long long *fstart,
+                                unsigned long long *fcount, uint64_t *launches);
 // tasks over the receive slab of rank `me` (routed pipeline; H = all-gathered histograms, cap = flush chunk)
 cudaError_t launch_route_plan(cudaStream_t st, const TableView &tv, const RouteMap &rt, int me, int cap, const unsigned long long *H,
                               unsigned long long part, FineTask *tasks, unsigned task_cap, unsigned *ntasks, uint64_t *launches);
-// fhist[s] += tuples of slice s
+// hist2 == NULL: fhist[s] += tuples of slice s; else hist2[t * ns_max + f] = tuples of slice s_lo + f in task t
 cudaError_t launch_fine_hist(cudaStream_t st, const TableView &tv, const uint64_t *in, const FineTask *tasks,
                              const unsigned *ntasks, unsigned task_bound, unsigned ns_max, unsigned long long *fhist,
-                             uint64_t *launches);
+                             unsigned *hist2, uint64_t *launches);
 // out = tuples in slice order (cursor[s] = first tuple index of slice s, advanced)
 cudaError_t launch_fine_scatter(cudaStream_t st, const TableView &tv, const uint64_t *in, const FineTask *tasks,
                                 const unsigned *ntasks, unsigned task_bound, unsigned ns_max, uint64_t *out,
-                                unsigned long long *cursor, uint64_t *launches);
+                                unsigned long long *cursor, const unsigned *hist2, const unsigned long long *fstart, uint64_t *launches);
 // count the tuples [fstart[s], fstart[s] + fcount[s]) of every slice s in shared memory
 // (fstart == NULL: fcount is the one-pass scatter's array of 32-bit cursors, slice s owns [s * cap, s * cap + min(cursor[s * stride], cap)))
 cudaError_t launch_smem_insert(cudaStream_t st, const TableView &tv, const uint64_t *tuples, const unsigned long long *fstart,
