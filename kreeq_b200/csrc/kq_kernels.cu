@@ -432,6 +432,87 @@ slice_scatter_kernel(TableView tv, Source src, uint64_t *__restrict__ out, unsig
     }
 }
 
+// ---- count, step 3 (ring form): scatter into coarse order, single pass ------------------------------------------
+
+// Same job as slice_scatter_kernel<.., false> with the ring bins of the level-2 scatter (kq_count3.cu): a tuple is
+// appended with one shared-memory atomic and one store, a bin that holds CAP tuples leaves as one coalesced store at
+// a position reserved with one global atomic per chunk; the ring (3/2 CAP) takes what arrives while a chunk waits,
+// so a tile needs two barriers and (practically) never a second pass over its tuples.
+template <int TW, int R, int NT, int CAP>
+__global__ void __launch_bounds__(NT, 1)
+coarse_scatter_kernel(TableView tv, Source src, uint64_t *__restrict__ out, unsigned long long *cursor) {
+    constexpr unsigned RING = CAP + CAP / 2;
+    extern __shared__ uint64_t sm[];
+    const unsigned P = bin_count<false>(tv, RouteMap{});
+    uint64_t *bins = sm;
+    unsigned int *fill = reinterpret_cast<unsigned int *>(bins + (size_t)P * RING * TW);
+    unsigned int *done = fill + P;
+    for (unsigned i = threadIdx.x; i < P; i += NT) { fill[i] = 0; done[i] = 0; }
+    __syncthreads();
+    const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = NT / 32;
+    const uint64_t total = source_total(src), per = (uint64_t)NT * R;
+    for (uint64_t tile = (uint64_t)blockIdx.x * per; tile < total; tile += (uint64_t)gridDim.x * per) {
+        uint64_t key[R]; uint32_t e[R]; unsigned bin[R], pos[R];
+        uint32_t m = produce<TW, R>(src, tv, tile, total, key, e);
+#pragma unroll
+        for (int i = 0; i < R; ++i) {
+            if (!(m >> i & 1u)) continue;
+            if (e[i] == 255u) { m &= ~(1u << i); continue; }               // padding tuples of a routed source
+            bin[i] = (unsigned)(slice_of_key(key[i], tv.nslices) >> tv.cshift);
+            pos[i] = atomicAdd(&fill[bin[i]], 1u);
+        }
+        for (;;) {
+            bool full = false;
+#pragma unroll
+            for (int i = 0; i < R; ++i) {
+                if (!(m >> i & 1u)) continue;
+                const unsigned d = pos[i] - *reinterpret_cast<volatile unsigned int *>(&done[bin[i]]);
+                if (d < RING) { tuple_store<TW>(bins, bin[i] * RING + pos[i] % RING, key[i], e[i]); m &= ~(1u << i); }
+                full |= d + 1 >= (unsigned)CAP;
+            }
+            if (!__syncthreads_or(full)) break;
+            for (unsigned b0 = warp * 32; b0 < P; b0 += nwarps * 32) {
+                const unsigned b = b0 + lane;
+                unsigned d0 = 0, chunks = 0;
+                if (b < P) { d0 = done[b]; chunks = min(fill[b] - d0, RING) / CAP; }
+                unsigned long long g = 0;
+                if (chunks) { g = atomicAdd(&cursor[b], (unsigned long long)chunks * CAP); done[b] = d0 + chunks * CAP; }
+                unsigned todo = __ballot_sync(0xffffffffu, chunks != 0);
+                while (todo) {
+                    const int l = __ffs(todo) - 1; todo &= todo - 1;
+                    const unsigned long long gg = __shfl_sync(0xffffffffu, g, l);
+                    const unsigned dd = __shfl_sync(0xffffffffu, d0, l);
+                    const unsigned nn = __shfl_sync(0xffffffffu, chunks, l) * CAP;
+                    const uint64_t *srcw = bins + (size_t)(b0 + l) * RING * TW;
+                    uint64_t *dst = out + gg * TW;
+                    for (unsigned w = lane; w < nn * TW; w += 32)
+                        __stcs(dst + w, srcw[((dd + w / TW) % RING) * TW + w % TW]);
+                }
+            }
+            if (!__syncthreads_or(m != 0)) break;                        // nobody had to wait for a flush
+        }
+    }
+    __syncthreads();
+    for (unsigned b0 = warp * 32; b0 < P; b0 += nwarps * 32) {             // what is left in the bins
+        const unsigned b = b0 + lane;
+        unsigned d0 = 0, f = 0;
+        if (b < P) { d0 = done[b]; f = fill[b] - d0; }
+        unsigned long long g = 0;
+        if (f) g = atomicAdd(&cursor[b], (unsigned long long)f);
+        unsigned todo = __ballot_sync(0xffffffffu, f != 0);
+        while (todo) {
+            const int l = __ffs(todo) - 1; todo &= todo - 1;
+            const unsigned long long gg = __shfl_sync(0xffffffffu, g, l);
+            const unsigned dd = __shfl_sync(0xffffffffu, d0, l);
+            const unsigned nn = __shfl_sync(0xffffffffu, f, l);
+            const uint64_t *srcw = bins + (size_t)(b0 + l) * RING * TW;
+            uint64_t *dst = out + gg * TW;
+            for (unsigned w = lane; w < nn * TW; w += 32)
+                __stcs(dst + w, srcw[((dd + w / TW) % RING) * TW + w % TW]);
+        }
+    }
+}
+
 // Variant without shared-memory bins: one global atomic on the slice cursor per tuple and one 8/16-byte
 // store; L2 is the write combiner (the ~600 cursor lines and the ~600 frontier lines of the output stay
 // resident, every output line is complete before it is evicted).
@@ -819,15 +900,39 @@ cudaError_t launch_slice_scatter(cudaStream_t st, const TableView &tv, const Sou
         ++*launches;
         return cudaGetLastError();
     }
-    const size_t smem = scatter_smem_bytes(coarse_bins(tv), cap, tw);
     const int variant = tuning().sc_variant;
+    if (variant == 0) {
+        // ring form: bins of 3/2 cap tuples + two counters; the largest chunk of 64 / 32 / 16 / 8 tuples that fits
+        static int max_smem = 0;
+        if (!max_smem) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev); if (max_smem <= 0) max_smem = 227 * 1024; }
+        const unsigned P = coarse_bins(tv);
+        auto need = [&](unsigned c) { return (size_t)P * (c + c / 2) * tw * 8 + (size_t)P * 8; };
+        unsigned rc = 0;
+        for (unsigned c : {64u, 32u, 16u, 8u}) if (need(c) <= (size_t)max_smem - 1024) { rc = c; break; }
+        if (rc) {
+            const size_t smem_r = need(rc);
+            cudaError_t er = cudaSuccess;
+            const unsigned grid_r = (unsigned)std::min<uint64_t>((n + 512 * 8 - 1) / (512 * 8), (uint64_t)sm_count());
+#define KQ_CS_GO(TWV, CAPV) do {                                                                                       \
+            er = cudaFuncSetAttribute(coarse_scatter_kernel<TWV, 8, 512, CAPV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_r); \
+            if (er != cudaSuccess) return er;                                                                          \
+            coarse_scatter_kernel<TWV, 8, 512, CAPV><<<grid_r, 512, smem_r, st>>>(tv, src, out, cursor); } while (0)
+#define KQ_CS_CAP(TWV) do { if (rc == 64) KQ_CS_GO(TWV, 64); else if (rc == 32) KQ_CS_GO(TWV, 32); else if (rc == 16) KQ_CS_GO(TWV, 16); else KQ_CS_GO(TWV, 8); } while (0)
+            if (tw == 1) KQ_CS_CAP(1); else KQ_CS_CAP(2);
+#undef KQ_CS_CAP
+#undef KQ_CS_GO
+            ++*launches;
+            return cudaGetLastError();
+        }
+    }
+    const size_t smem = scatter_smem_bytes(coarse_bins(tv), cap, tw);
     cudaError_t e = cudaSuccess;
 #define KQ_SCATTER_LAUNCH(TWV, RV, NTV) do {                                                                        \
         e = cudaFuncSetAttribute(slice_scatter_kernel<TWV, RV, NTV, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
         if (e != cudaSuccess) return e;                                                                             \
         const unsigned grid = std::min<uint64_t>((n + NTV * RV - 1) / (NTV * RV), (uint64_t)sm_count());           \
         slice_scatter_kernel<TWV, RV, NTV, false><<<grid, NTV, smem, st>>>(tv, src, out, cursor, cap, RouteMap{}, nullptr); } while (0)
-    if (tw == 1) {                                                   // measured on C2 (profiles/): 16 x 512 is the fastest
+    if (tw == 1) {                                                   // the two-pass form (sc_variant 1..4)
         if (variant == 1) KQ_SCATTER_LAUNCH(1, 8, 512);
         else if (variant == 2) KQ_SCATTER_LAUNCH(1, 8, 1024);
         else if (variant == 3) KQ_SCATTER_LAUNCH(1, 4, 1024);
