@@ -495,7 +495,8 @@ def main_ours(args):
     # KQ_TRANSPORT=nccl selects the staged all-to-all (extract -> ncclSend/Recv -> second scatter) instead
     transport = os.environ.get("KQ_TRANSPORT", "peer") if world > 1 else None
     if transport == "peer":
-        router = shard.PeerRoutedCounter(g, rank, world, 512 << 20, dev, stream=stream)
+        # one round per step when the slab fits (every round sweeps the whole shard through the insert kernel)
+        router = shard.PeerRoutedCounter(g, rank, world, int(os.environ.get("KQ_ROUND_POS", min(reads_np.size + 1024, (1 << 32) - (1 << 24)))), dev, stream=stream)
     elif transport == "nccl":
         router = shard.RoutedCounter(g, rank, world, 512 << 20, dev)
     else:
@@ -517,8 +518,9 @@ def main_ours(args):
         words = L.kq_packed_words(5 * 64 * (READ_LEN + 1) * 10000)
         for _ in range(2):
             e2e_bufs.append((torch.empty(words, dtype=torch.int64, pin_memory=True), torch.empty(words, dtype=torch.int64, pin_memory=True),
-                             torch.empty(words, dtype=torch.int64, device=dev), torch.empty(words, dtype=torch.int64, device=dev),
-                             torch.cuda.Event()))
+                             None, None, torch.cuda.Event()))
+        wall = L.kq_packed_words(reads_np.size)
+        e2e_all = (torch.zeros(wall, dtype=torch.int64, device=dev), torch.full((wall,), -1, dtype=torch.int64, device=dev))
 
     def count_resident():
         total = reads_np.size - K + 1
@@ -639,17 +641,20 @@ def main_ours(args):
             g.set_flush_positions(int(os.environ["KQ_E2E_FLUSH"]))
         if world > 1:
             B = 64 * (READ_LEN + 1) * 10000
-            # chunks of five pushes: packed on this rank's share of the host cores into pinned memory, copied in,
-            # routed as one round; the next chunk is packed while the GPUs insert this one
+            # chunks of five pushes (a multiple of 64 bases, so the packed words of the chunks join up): packed on this
+            # rank's share of the host cores into pinned memory and copied to their place in the device-resident packed
+            # read set while the next chunk is packed; ONE routed round at the end (every round sweeps the whole shard)
             CH = 5 * B
             for i, o in enumerate(range(0, reads_np.size, CH)):
                 n = min(CH, reads_np.size - o)
-                hb, hm, db, dm, done = e2e_bufs[i % 2]
+                hb, hm, _, _, done = e2e_bufs[i % 2]
                 done.synchronize()
                 check(L.kq_pack_host(C.c_void_p(reads_np[o:o + n].ctypes.data), n, C.c_void_p(hb.data_ptr()), C.c_void_p(hm.data_ptr()), 0))
-                db.copy_(hb, non_blocking=True); dm.copy_(hm, non_blocking=True)
+                wb, wm = (n + 31) // 32, (n + 63) // 64
+                e2e_all[0][o // 32:o // 32 + wb].copy_(hb[:wb], non_blocking=True)
+                e2e_all[1][o // 64:o // 64 + wm].copy_(hm[:wm], non_blocking=True)
                 done.record(stream)
-                router.count(db, dm, n)
+            router.count(e2e_all[0], e2e_all[1], reads_np.size)
         else:
             for o, o2 in zip(push_cuts[:-1], push_cuts[1:]):          # ~97 MB pushes, cut at read boundaries
                 g.traverseInReads(reads_np[o:o2])
@@ -688,7 +693,7 @@ def main_ours(args):
         barrier()
         c0 = g.counters()
         g.set_timing(True)
-        for w in range(7):
+        for w in range(10):
             g.kernel_time_ms(w)
         sampler = ClockSampler(local); sampler.start()
         evs = [step_fn() for _ in range(steps)]
@@ -699,6 +704,7 @@ def main_ours(args):
         kt_pipe, kn_pipe = g.kernel_time_ms(0)
         kt_scat, kn_scat = g.kernel_time_ms(3)
         kt_l2, _ = g.kernel_time_ms(4); kt_s1, _ = g.kernel_time_ms(5); kt_s2, _ = g.kernel_time_ms(6)
+        kt_vs, _ = g.kernel_time_ms(8); kt_va, _ = g.kernel_time_ms(9)
         g.set_timing(False)
         c1 = g.counters()
         tc = sum(a.elapsed_time(b) for a, b, _ in evs) / steps
@@ -711,7 +717,7 @@ def main_ours(args):
                 "h2d": (c1["h2d_bytes"] - c0["h2d_bytes"]) / steps, "d2h": (c1["d2h_bytes"] - c0["d2h_bytes"]) / steps,
                 "kt_count": kt_count, "kn_count": kn_count, "kt_val": kt_val, "kn_val": kn_val,
                 "kt_pipe": kt_pipe, "kn_pipe": kn_pipe, "kt_scat": kt_scat, "kn_scat": kn_scat,
-                "kt_l2": kt_l2, "kt_s1": kt_s1, "kt_s2": kt_s2}
+                "kt_l2": kt_l2, "kt_s1": kt_s1, "kt_s2": kt_s2, "kt_vs": kt_vs, "kt_va": kt_va}
 
     parity = parity_check() if not args.no_parity else {"ok": None, "skipped": "--no-parity"}
     if parity["ok"] is False:
@@ -765,6 +771,8 @@ def main_ours(args):
             line["validate"]["roofline"] = {"bound": "hbm", "kernel": "validate_kernel" if world == 1 or vmode == "peer" else "vroute_send_kernel + vroute_answer_kernel",
                                             "achieved": va, "peak": peak, "unit": "GB/s", "frac": va / peak, "avg_launch_ms": vs * 1e3,
                                             "launches_timed": res["kn_val"]}
+            if res["kt_vs"]:
+                line["validate"]["roofline"]["kernels_ms_per_step"] = {"vroute_send": res["kt_vs"] / args.steps, "vroute_answer": res["kt_va"] / args.steps}
     try:
         line["config"]["distinct_kmers"] = g.distinct() if world == 1 else None
     except Exception:

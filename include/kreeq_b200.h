@@ -290,7 +290,7 @@ int  kq_counters(kq_ctx *ctx, uint64_t *kernel_launches, uint64_t *h2d_bytes, ui
  * which = 0 whole count pipeline (per batch), 1 validate/probe kernel, 2 insert kernel,
  * 3 level-1 histogram + scatter (or extract_route / kq_route_hist + kq_route_scatter), 4 level-2 histogram + scatter,
  * 5 the scatter kernel alone (level 1 / one-pass), 6 the level-2 scatter kernel alone, 7 the load / union kernels
- * (image decode + put / merge).
+ * (image decode + put / merge), 8 / 9 the query and the answer kernel of the routed validate.
  * Only measured when kq_set_timing(ctx,1). */
 int  kq_set_timing(kq_ctx *ctx, int on);
 int  kq_kernel_time_ms(kq_ctx *ctx, int which, double *ms, uint64_t *launches, int reset);

@@ -36,7 +36,7 @@ constexpr uint64_t MIN_SLOTS = 1ull << 12;
 constexpr uint64_t MIN_SCAP = 1ull << 12;
 constexpr uint64_t OVF_CAP = 4ull << 20;         // tuples kept when their slice is full
 constexpr uint64_t DEFAULT_FLUSH = 1ull << 29;   // pending k-mer start positions that trigger the pipeline
-constexpr int NTIMERS = 8;                       // 0 count pipeline, 1 validate, 2 insert kernel, 3 level-1 hist + scatter, 4 level-2 hist + scatter,
+constexpr int NTIMERS = 10;                       // 0 count pipeline, 1 validate, 2 insert kernel, 3 level-1 hist + scatter, 4 level-2 hist + scatter,
                                                  // 5 scatter kernel alone (level 1 / one-pass), 6 level-2 scatter kernel alone, 7 load / union kernels
 
 thread_local std::string g_create_error;
@@ -1087,8 +1087,9 @@ extern "C" int kq_vroute_send(kq_ctx *c, const uint64_t *d_bases, const uint64_t
     if (!c->vroute_ready) return fail(c, KQ_ESTATE, "kq_vroute_send: call kq_vroute_connect first");
     if (n > c->vcap) return fail(c, KQ_EINVAL, "kq_vroute_send: chunk larger than the one given to kq_vroute_setup");
     CU(cudaSetDevice(c->device));
-    const int t = time_begin(c, 1);
+    const int t = time_begin(c, 1), t8 = time_begin(c, 8);
     CU(launch_vroute_send(c->stream, view(c), d_bases, d_invalid, base0, c0, n, kcount, c->d_vrows, c->d_vacc, c->vroute, &c->launches));
+    time_end(c, t8);
     time_end(c, t);
     return KQ_OK;
 }
@@ -1097,8 +1098,9 @@ extern "C" int kq_vroute_answer(kq_ctx *c, uint32_t cutoff) {
     if (!c) return KQ_EINVAL;
     if (!c->vroute_ready) return fail(c, KQ_ESTATE, "kq_vroute_answer: call kq_vroute_connect first");
     CU(cudaSetDevice(c->device));
-    const int t = time_begin(c, 1);
+    const int t = time_begin(c, 1), t9 = time_begin(c, 9);
     CU(launch_vroute_answer(c->stream, view(c), c->d_vinbox, c->vroute.counts[c->rank], (uint64_t)c->nranks * c->vcap, cutoff, c->d_vacc, c->vroute, &c->launches));
+    time_end(c, t9);
     time_end(c, t);
     return KQ_OK;
 }
