@@ -159,23 +159,27 @@ int read_occ(kq_ctx *c, uint64_t occ[3]) {
 // geometry of a table with at least `need` slots: one slice while it fits 2^21 slots (32 MiB, L2 resident),
 // else slices of 2^12 slots (64 KiB: what one CTA of the shared-memory insert holds), grouped 2^cshift at a
 // time into the bins of the level-1 scatter (about sqrt(nslices) bins at either level)
-void table_geometry(uint64_t need, uint64_t &nslices, int &slice_bits, int &cshift) {
+void table_geometry(uint64_t need, int tw, uint64_t &nslices, int &slice_bits, int &cshift) {
     need = std::max(need, MIN_SLOTS);
     const int max_bits = tuning().single_slice_bits;
     int b = std::min(12, max_bits); while (b < max_bits && (1ull << b) < need) ++b;
     cshift = 0;
     if ((1ull << b) >= need) { nslices = 1; slice_bits = b; return; }
-    slice_bits = tuning().piece_bits;
-    nslices = (need + (1ull << slice_bits) - 1) >> slice_bits;
-    int lg = 0; while ((2ull << lg) <= nslices) ++lg;                // floor(log2 nslices)
-    cshift = lg / 2;
-    while ((((nslices - 1) >> cshift) + 1) > 3000) ++cshift;          // bins of the level-1 scatter must fit shared memory
+    // smallest slices (from the piece_bits knob up to 2^12 slots) whose coarse bins fit the level-1 scatter and whose
+    // slices per coarse bin fit the level-2 scatter
+    for (slice_bits = tuning().piece_bits;; ++slice_bits) {
+        nslices = (need + (1ull << slice_bits) - 1) >> slice_bits;
+        int lg = 0; while ((2ull << lg) <= nslices) ++lg;            // floor(log2 nslices)
+        cshift = lg / 2;
+        while ((((nslices - 1) >> cshift) + 1) > 3000) ++cshift;      // bins of the level-1 scatter must fit shared memory
+        if (slice_bits >= 12 || fine_pick_cap(1u << cshift, tw) != 0) break;
+    }
 }
 
 int grow_table(kq_ctx *c, uint64_t need) {
     if (c->exported) return fail(c, KQ_ESTATE, "the table is mapped by peers (kq_peer_export): call kq_peer_disconnect first");
     Slot *old = c->T; const uint64_t old_slots = table_slots(c);
-    uint64_t ns; int sb, cs; table_geometry(need, ns, sb, cs);
+    uint64_t ns; int sb, cs; table_geometry(need, tuple_words(c->k), ns, sb, cs);
     Slot *nt = nullptr;
     CU(cudaMalloc(&nt, (ns << sb) * sizeof(Slot)));
     CU(cudaMemsetAsync(nt, 0, (ns << sb) * sizeof(Slot), c->stream));
@@ -701,6 +705,7 @@ extern "C" int kq_set_tuning(const char *name, long long value) {
     else if (n == "insert_ctas" && value >= 1 && value <= 8) t.insert_ctas = (int)value;
     else if (n == "validate_ctas" && value >= 1 && value <= 8) t.validate_ctas = (int)value;
     else if (n == "db_host" && (value == 0 || value == 1)) t.db_host = (int)value;
+    else if (n == "warp_insert" && (value == 0 || value == 1)) t.warp_insert = (int)value;
     else if (n == "s3_threads" && (value == 256 || value == 384 || value == 512)) t.s3_threads = (int)value;
     else if (n == "s3_ctas" && value >= 1 && value <= 8) t.s3_ctas = (int)value;
     else if (n == "pipeline" && value >= 2 && value <= 4) t.pipeline = (int)value;

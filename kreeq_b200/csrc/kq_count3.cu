@@ -314,6 +314,16 @@ __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.comm
 __device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+// a whole range starts its way into L2 (address and size multiples of 16)
+__device__ __forceinline__ void bulk_prefetch_l2(const void *src, unsigned bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
+}
+// 64-bit CAS on a shared-memory address (shared window offset)
+__device__ __forceinline__ unsigned long long atom_cas_shared(uint32_t addr, unsigned long long cmp, unsigned long long val) {
+    unsigned long long old;
+    asm volatile("atom.shared.cas.b64 %0, [%1], %2, %3;" : "=l"(old) : "r"(addr), "l"(cmp), "l"(val) : "memory");
+    return old;
+}
 
 // Slow paths of the shared-memory insert, kept out of line so that the hot loop stays small.
 
@@ -402,9 +412,11 @@ __device__ __noinline__ unsigned long long warp_combine(uint64_t key, uint32_t e
 
 // One CTA per slice at a time (ticket counter; slices without tuples are skipped): bulk-load the slice (UBLKCP),
 // count its tuples in shared memory, bulk-store it.  Three CTAs per SM overlap each other's copies.
-// A thread takes four tuples at a time (loaded a batch ahead) and then runs a loop in which every lane does ONE
-// probe step per iteration on its current tuple -- slot load, claim or compare, one CAS -- and moves to its next
-// tuple as soon as one is counted: lanes never wait for the longest probe sequence of the warp.
+// A warp owns a contiguous share of the slice's tuples and its lanes POP tuples from it: every lane holds the tuple
+// it is counting and the next one (already loaded); an iteration is ONE probe step per lane -- slot load, claim or
+// compare, one CAS -- and the lanes that finished take the next unread tuples of the share (ballot + prefix count,
+// no atomics).  Lanes never wait for the longest probe sequence of the warp and stay busy until the share ends.
+// Four or more lanes losing their CAS in one iteration means a run of one key in the stream: the warp combines.
 template <int TW, int NT>
 __global__ void __launch_bounds__(NT, 3)
 smem_insert_kernel(TableView tv, const uint64_t *__restrict__ tuples, const unsigned long long *__restrict__ fstart,
@@ -419,7 +431,8 @@ smem_insert_kernel(TableView tv, const uint64_t *__restrict__ tuples, const unsi
     Slot *piece = reinterpret_cast<Slot *>(sm_piece);
     const unsigned slots = 1u << tv.slice_bits, mask = slots - 1, bytes = slots * (unsigned)sizeof(Slot);
     const unsigned limit = min(slots, 1024u);                          // a longer run means the slice is (locally) full
-    const unsigned lane = threadIdx.x & 31;
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5, lt_mask = (1u << lane) - 1;
+    const uint32_t piece_a = smem_u32(piece);
     for (unsigned i = threadIdx.x; i < 256; i += NT) inc_lut[i] = inc_of_edge(i);
     if (threadIdx.x == 0) { mbar_init(&bar, 1); sh_fresh = 0; asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
     __syncthreads();
@@ -431,77 +444,73 @@ smem_insert_kernel(TableView tv, const uint64_t *__restrict__ tuples, const unsi
             unsigned long long s, cnt = 0;
             for (;;) { s = atomicAdd(ticket, 1ULL); if (s >= tv.nslices) break; cnt = fstart ? fcount[s] : fcur[s * stride]; if (cnt) break; }
             sh_ticket = s; sh_n = fstart ? cnt : min(cnt, cap);
-            if (s < tv.nslices) { mbar_expect_tx(&bar, bytes); bulk_g2s(piece, tv.T + (s << tv.slice_bits), bytes, &bar); }
+            if (s < tv.nslices) {
+                mbar_expect_tx(&bar, bytes); bulk_g2s(piece, tv.T + (s << tv.slice_bits), bytes, &bar);
+                // the slice's tuples start their way into L2 now (one instruction for the whole range)
+                const unsigned long long a0 = (unsigned long long)(tuples + (fstart ? fstart[s] : s * cap) * TW);
+                const unsigned long long a = a0 & ~15ULL, e = (a0 + sh_n * TW * 8) & ~15ULL;
+                if (e > a) bulk_prefetch_l2(reinterpret_cast<const void *>(a), (unsigned)(e - a));
+            }
         }
         __syncthreads();
         const unsigned long long s = sh_ticket;
         if (s >= tv.nslices) break;
         const uint64_t *tp = tuples + (fstart ? fstart[s] : s * cap) * TW;   // this slice's tuples
         const unsigned n = (unsigned)sh_n;                                 // (a batch brings fewer than 2^32 tuples)
-        ulonglong2 nxt[4];                                               // tuples are loaded one batch ahead (and under the bulk copy)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const unsigned i = (unsigned)j * NT + threadIdx.x;
-            nxt[j] = i < n ? t_raw<TW>(tp, i) : make_ulonglong2(T_PAD1, T_PAD1);
-        }
+        // this warp's share [lo, hi): whole groups of 32 tuples
+        const unsigned per = ((n + NT / 32 - 1) / (NT / 32) + 31u) & ~31u;
+        const unsigned lo = min(n, warp * per), hi = min(n, lo + per);
+        unsigned head = lo + 64;                                           // first tuple of the share nobody holds yet
+        ulonglong2 cur = lo + lane < hi ? t_raw<TW>(tp, lo + lane) : make_ulonglong2(T_PAD1, T_PAD1);
+        bool more = lo + 32 + lane < hi;                                   // nxt holds an element of the stream
+        ulonglong2 nxt = t_raw<TW>(tp, min(lo + 32 + lane, n - 1));
         mbar_wait(&bar, parity); parity ^= 1;
-        for (unsigned i0 = 0; i0 < n; i0 += NT * 4) {
-            ulonglong2 cur[4]; unsigned hm[4];
-            bool run = false;
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                cur[j] = nxt[j];
-                uint64_t kj; uint32_t ej; t_split<TW>(cur[j], kj, ej);
-                hm[j] = (unsigned)home_hash(kj) & mask;
-                // a run = three neighbours in the stream with one key (two happen by chance in every tenth batch)
-                const uint64_t kn = __shfl_down_sync(0xffffffffu, kj, 1), kn2 = __shfl_down_sync(0xffffffffu, kj, 2);
-                run |= ej != 255u && lane < 30 && kn == kj && kn2 == kj;
-                const unsigned i = i0 + NT * 4 + (unsigned)j * NT + threadIdx.x;
-                nxt[j] = i < n ? t_raw<TW>(tp, i) : make_ulonglong2(T_PAD1, T_PAD1);
-            }
-            if (__any_sync(0xffffffffu, run)) {
-                // neighbours in the stream with the same key: combine inside the warp, count with the plain loop
-#pragma unroll 1
-                for (int j = 0; j < 4; ++j) {
-                    const ulonglong2 w = j == 0 ? cur[0] : j == 1 ? cur[1] : j == 2 ? cur[2] : cur[3];
-                    uint64_t kj; uint32_t ej; t_split<TW>(w, kj, ej);
-                    const bool live = ej != 255u;
-                    if (!live) kj = ~0ULL - lane;                        // distinct dummies: no false match
-                    const unsigned long long inc = warp_combine(kj, ej, live);
-                    if (inc) fresh += smem_insert_slow<TW>(piece, mask, limit, tv, kj, inc, ovf, ovf_cap, ovf_n);
+        // state of the tuple in hand
+        uint64_t ck; uint32_t ce; t_split<TW>(cur, ck, ce);
+        unsigned long long ci = inc_lut[ce];
+        uint32_t ca = piece_a + (((unsigned)home_hash(ck) & mask) << 4);   // shared address of the slot to look at
+        unsigned probes = 0;
+        for (;;) {
+            const bool live = ce != 255u;
+            if (!__any_sync(0xffffffffu, live || more)) break;
+            bool done = !live && more;                                     // padding inside the stream: move on
+            bool clash = false;
+            if (live) {
+                const unsigned long long tag = ck + 1;
+                unsigned long long t, c;                                   // one 16-byte shared load: {tag, cnt}
+                asm volatile("ld.volatile.shared.v2.u64 {%0, %1}, [%2];" : "=l"(t), "=l"(c) : "r"(ca) : "memory");
+                if (t == 0) {
+                    t = atom_cas_shared(ca, 0ULL, tag);
+                    if (t == 0) { t = tag; ++fresh; c = 0; }
                 }
-                continue;
-            }
-            // one probe step per lane and iteration
-            int idx = 0; bool have = false;
-            uint64_t ck = 0; unsigned long long ci = 0; unsigned cj = 0, probes = 0;
-            for (;;) {
-                if (!have) {
-                    while (idx < 4 && !have) {
-                        const ulonglong2 w = idx == 0 ? cur[0] : idx == 1 ? cur[1] : idx == 2 ? cur[2] : cur[3];
-                        uint32_t ej; t_split<TW>(w, ck, ej);
-                        if (ej != 255u) { ci = inc_lut[ej]; have = true; cj = idx == 0 ? hm[0] : idx == 1 ? hm[1] : idx == 2 ? hm[2] : hm[3]; probes = 0; }
-                        ++idx;
-                    }
-                }
-                if (!__any_sync(0xffffffffu, have)) break;
-                if (have) {
-                    const unsigned long long tag = ck + 1;
-                    unsigned long long t, c;                                               // one 16-byte shared load: {tag, cnt}
-                    asm volatile("ld.volatile.shared.v2.u64 {%0, %1}, [%2];" : "=l"(t), "=l"(c) : "r"(smem_u32(&piece[cj])) : "memory");
-                    if (t == 0) {
-                        t = atomicCAS(&piece[cj].tag, 0ULL, tag);
-                        if (t == 0) { t = tag; ++fresh; c = 0; }
-                    }
-                    if (t == tag) {
-                        if (cnt_cov(c) + 1u > KQ_LANE_MAX) { smem_spill(&piece[cj].cnt, tv, ck, ci); have = false; }
-                        else if (atomicCAS(&piece[cj].cnt, c, c + ci) == c) have = false;       // else: look again next round
-                    } else {
-                        cj = (cj + 1) & mask;
-                        if (++probes >= limit) { smem_give_back<TW>(ovf, ovf_cap, ovf_n, ck, ci); have = false; }
-                    }
+                if (t == tag) {
+                    if (cnt_cov(c) + 1u > KQ_LANE_MAX) { smem_spill(&piece[(ca - piece_a) >> 4].cnt, tv, ck, ci); done = true; }
+                    else if (atom_cas_shared(ca + 8, c, c + ci) == c) done = true;
+                    else clash = true;                                     // somebody else counted into the slot: look again
+                } else {
+                    ca = piece_a + ((ca - piece_a + 16u) & (bytes - 1));
+                    if (++probes >= limit) { smem_give_back<TW>(ovf, ovf_cap, ovf_n, ck, ci); done = true; }
                 }
             }
+            if (__popc(__ballot_sync(0xffffffffu, clash)) >= 4) {
+                // neighbours in the stream with one key (poly-A, satellites): combine inside the warp
+                const bool todo = live && !done;
+                const unsigned long long inc = warp_combine(todo ? ck : ~0ULL - lane, ce, todo);   // distinct dummies: no false match
+                if (inc) fresh += smem_insert_slow<TW>(piece, mask, limit, tv, ck, inc, ovf, ovf_cap, ovf_n);
+                done |= todo;
+            }
+            const unsigned dm = __ballot_sync(0xffffffffu, done);
+            if (done) {
+                cur = more ? nxt : make_ulonglong2(T_PAD1, T_PAD1);
+                const unsigned i = head + __popc(dm & lt_mask);
+                more = i < hi;
+                nxt = t_raw<TW>(tp, min(i, n - 1));                        // (always a valid address; used only if `more`)
+                t_split<TW>(cur, ck, ce);
+                ci = inc_lut[ce];
+                ca = piece_a + (((unsigned)home_hash(ck) & mask) << 4);
+                probes = 0;
+            }
+            head += __popc(dm);
         }
         __syncthreads();                                                  // every update is in the piece
         if (threadIdx.x == 0) {
@@ -513,6 +522,153 @@ smem_insert_kernel(TableView tv, const uint64_t *__restrict__ tuples, const unsi
     }
     if (threadIdx.x == 0) bulk_wait_all();
     // new keys of this CTA -> occupancy counter
+    unsigned long long f = fresh;
+    for (int o = 16; o; o >>= 1) f += __shfl_xor_sync(0xffffffffu, f, o);
+    if (lane == 0 && f) atomicAdd(&sh_fresh, f);
+    __syncthreads();
+    if (threadIdx.x == 0 && sh_fresh) atomicAdd(&tv.occ[0], sh_fresh);
+}
+
+// ---- warp-owned slices -------------------------------------------------------------------------------------------
+//
+// Shared-memory CAS costs about 4 cycles per LANE on B200 (profiles/r02_ncu_pipeline_full.md: the CTA-owned kernel
+// above sits at that bound whatever its instruction count).  With slices of 2^9 slots (8 KiB) ONE WARP owns a slice
+// while it counts into it, so no other warp can touch the slots and plain 16-byte shared loads / stores do the work:
+//   every iteration each lane reads the slot it looks at (LDS.128); the lanes that want to write it -- empty slot to
+//   claim, or their key -- put their lane number into the slot's LOCK BYTE, the warp synchronises, and the lane that
+//   reads its own number back owns the slot for this iteration: it stores {tag, cnt + inc} (STS.128).  The others
+//   look again in the next iteration.  All reads of an iteration come before all of its writes.
+// A warp takes a ticket for 32 consecutive slices, skips the empty ones, and for each: bulk-loads the 8 KiB piece
+// (cp.async.bulk + its own mbarrier), pops the slice's tuples as above, bulk-stores the piece.  Warps never meet.
+__device__ __noinline__ unsigned long long excl_spill(const TableView &tv, uint64_t key, unsigned long long c) {
+    uint32_t fw[4], bw[4];
+    unsigned long long take = 63ull << 56;
+#pragma unroll
+    for (int w = 0; w < 4; ++w) {
+        fw[w] = min(cnt_lane(c, w), 63u); bw[w] = min(cnt_lane(c, 4 + w), 63u);
+        take |= (unsigned long long)fw[w] << (7 * w) | (unsigned long long)bw[w] << (7 * (4 + w));
+    }
+    remainder_add(tv, key, 63, fw, bw);
+    return c - take;
+}
+
+// the lanes that hold ONE instance of the same key add up (warp_combine); lanes with a combined increment stay alone
+__device__ __noinline__ unsigned long long warp_combine_singles(uint64_t key, uint32_t e, bool todo, unsigned long long ci) {
+    const unsigned lane = threadIdx.x & 31;
+    const bool single = todo && (ci >> 56) == 1;
+    const unsigned long long inc = warp_combine(single ? key : ~0ULL - lane, e, single);
+    return single ? inc : ci;                                              // 0 = another lane counts for this one
+}
+
+template <int TW>
+__global__ void __launch_bounds__(256, 3)
+warp_insert_kernel(TableView tv, const uint64_t *__restrict__ tuples, const unsigned long long *__restrict__ fstart,
+                   const void *__restrict__ fcount_, unsigned long long cap, int stride, uint64_t *ovf,
+                   unsigned long long ovf_cap, unsigned long long *ovf_n, unsigned long long *ticket) {
+    const unsigned long long *fcount = static_cast<const unsigned long long *>(fcount_);     // level-2 layout: exact counts
+    const unsigned *fcur = static_cast<const unsigned *>(fcount_);                             // one-pass layout: 32-bit cursors
+    extern __shared__ __align__(128) unsigned char sm_w[];
+    __shared__ unsigned long long sh_fresh;
+    const unsigned nw = blockDim.x >> 5, lane = threadIdx.x & 31, warp = threadIdx.x >> 5, lt_mask = (1u << lane) - 1;
+    const unsigned slots = 1u << tv.slice_bits, mask = slots - 1, bytes = slots * (unsigned)sizeof(Slot);
+    const unsigned limit = slots;                                       // once around: the slice is full
+    // [nw pieces][nw x slots lock bytes][increment table][nw mbarriers]
+    unsigned char *piece = sm_w + (size_t)warp * bytes;
+    const uint32_t piece_a = smem_u32(piece), lock_a = smem_u32(sm_w + (size_t)nw * bytes + (size_t)warp * slots);
+    unsigned long long *inc_lut = reinterpret_cast<unsigned long long *>(sm_w + (size_t)nw * (bytes + slots));
+    uint64_t *bar = reinterpret_cast<uint64_t *>(sm_w + (size_t)nw * (bytes + slots) + 2048) + warp;
+    for (unsigned i = threadIdx.x; i < 256; i += blockDim.x) inc_lut[i] = inc_of_edge(i);
+    if (lane == 0) mbar_init(bar, 1);
+    if (threadIdx.x == 0) sh_fresh = 0;
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    __syncthreads();
+    const uint32_t lut_a = smem_u32(inc_lut);
+    unsigned parity = 0, fresh = 0;
+    for (;;) {
+        unsigned long long g = 0;
+        if (lane == 0) g = atomicAdd(ticket, 1ULL);
+        g = __shfl_sync(0xffffffffu, g, 0);
+        const unsigned long long s0 = g * 32;
+        if (s0 >= tv.nslices) break;
+        unsigned long long my_n = 0, my_start = 0;
+        if (s0 + lane < tv.nslices) {
+            const unsigned long long sl = s0 + lane;
+            my_n = fstart ? fcount[sl] : min((unsigned long long)fcur[sl * stride], cap);
+            my_start = fstart ? fstart[sl] : sl * cap;
+        }
+        unsigned todo_slices = __ballot_sync(0xffffffffu, my_n != 0);
+        while (todo_slices) {
+            const int src = __ffs(todo_slices) - 1; todo_slices &= todo_slices - 1;
+            const unsigned n = (unsigned)__shfl_sync(0xffffffffu, my_n, src);      // (a batch brings fewer than 2^32 tuples)
+            const uint64_t *tp = tuples + __shfl_sync(0xffffffffu, my_start, src) * TW;
+            Slot *gpiece = tv.T + ((s0 + src) << tv.slice_bits);
+            if (lane == 0) { mbar_expect_tx(bar, bytes); bulk_g2s(piece, gpiece, bytes, bar); }
+            unsigned head = 64;                                            // first tuple of the slice nobody holds yet
+            ulonglong2 cur = lane < n ? t_raw<TW>(tp, lane) : make_ulonglong2(T_PAD1, T_PAD1);
+            bool more = 32 + lane < n;                                     // nxt holds an element of the stream
+            ulonglong2 nxt = t_raw<TW>(tp, min(32 + lane, n - 1));
+            uint64_t ck; uint32_t ce; t_split<TW>(cur, ck, ce);
+            mbar_wait(bar, parity); parity ^= 1;
+            unsigned long long ci;
+            asm volatile("ld.shared.u64 %0, [%1];" : "=l"(ci) : "r"(lut_a + ce * 8));
+            unsigned slot = (unsigned)home_hash(ck) & mask, probes = 0;
+            for (;;) {
+                const bool live = ce != 255u;
+                if (!__any_sync(0xffffffffu, live || more)) break;
+                bool done = !live && more;                                 // padding inside the stream: move on
+                bool want = false;
+                const unsigned long long tag = ck + 1;
+                unsigned long long t = 0, c = 0;
+                if (live) {
+                    asm volatile("ld.shared.v2.u64 {%0, %1}, [%2];" : "=l"(t), "=l"(c) : "r"(piece_a + (slot << 4)) : "memory");
+                    if (t == 0 || t == tag) {
+                        want = true;
+                        asm volatile("st.shared.u8 [%0], %1;" ::"r"(lock_a + slot), "r"(lane) : "memory");
+                    } else {
+                        slot = (slot + 1) & mask;
+                        if (++probes >= limit) { smem_give_back<TW>(ovf, ovf_cap, ovf_n, ck, ci); done = true; }
+                    }
+                }
+                __syncwarp();
+                bool lost = false;
+                if (want) {
+                    unsigned who;
+                    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(who) : "r"(lock_a + slot) : "memory");
+                    if (who == lane) {
+                        if (t == 0) { c = 0; ++fresh; }
+                        if (cnt_cov(c) + (unsigned)(ci >> 56) > KQ_LANE_MAX) c = excl_spill(tv, ck, c);
+                        c += ci;                                           // lanes <= cov: no carry between lanes
+                        asm volatile("st.shared.v2.u64 [%0], {%1, %2};" ::"r"(piece_a + (slot << 4)), "l"(tag), "l"(c) : "memory");
+                        done = true;
+                    } else lost = true;
+                }
+                __syncwarp();
+                if (__popc(__ballot_sync(0xffffffffu, lost)) >= 12) {
+                    // neighbours in the stream with one key (poly-A, satellites): they add up, one lane counts for all
+                    const bool todo = live && !done;
+                    const unsigned long long inc = warp_combine_singles(ck, ce, todo, ci);
+                    if (todo) { if (inc) ci = inc; else done = true; }
+                }
+                const unsigned dm = __ballot_sync(0xffffffffu, done);
+                if (done) {
+                    cur = more ? nxt : make_ulonglong2(T_PAD1, T_PAD1);
+                    const unsigned i = head + __popc(dm & lt_mask);
+                    more = i < n;
+                    nxt = t_raw<TW>(tp, min(i, n - 1));                    // (always a valid address; used only if `more`)
+                    t_split<TW>(cur, ck, ce);
+                    asm volatile("ld.shared.u64 %0, [%1];" : "=l"(ci) : "r"(lut_a + ce * 8));
+                    slot = (unsigned)home_hash(ck) & mask;
+                    probes = 0;
+                }
+                head += __popc(dm);
+            }
+            fence_async_smem();                                            // every lane's stores, then one bulk store
+            __syncwarp();
+            if (lane == 0) { bulk_s2g(gpiece, piece, bytes); bulk_commit(); bulk_wait_read(); }
+            __syncwarp();                                                  // the piece may be overwritten again
+        }
+    }
+    if (lane == 0) bulk_wait_all();
     unsigned long long f = fresh;
     for (int o = 16; o; o >>= 1) f += __shfl_xor_sync(0xffffffffu, f, o);
     if (lane == 0 && f) atomicAdd(&sh_fresh, f);
@@ -616,6 +772,23 @@ cudaError_t launch_smem_insert(cudaStream_t st, const TableView &tv, const uint6
                                unsigned long long ovf_cap, unsigned long long *ovf_n, unsigned long long *ticket, uint64_t *launches) {
     cudaError_t e = cudaMemsetAsync(ticket, 0, sizeof(unsigned long long), st);
     if (e != cudaSuccess) return e;
+    if (tuning().warp_insert && tv.slice_bits <= 10) {
+        // warp-owned slices: 8 warps per CTA, as many CTAs per SM as fit (3 with 8 KiB slices)
+        const unsigned slots = 1u << tv.slice_bits, nw = 8;
+        const size_t smem_w = (size_t)nw * (slots * sizeof(Slot) + slots) + 2048 + nw * 8;
+        const unsigned per_sm = (unsigned)std::max<size_t>(1, std::min<size_t>(3, (size_t)(227 * 1024) / (smem_w + 1024)));
+        const unsigned long long groups = (tv.nslices + 31) / 32;
+        const unsigned grid_w = (unsigned)std::min<unsigned long long>((groups + nw - 1) / nw, (unsigned long long)sm_count() * per_sm);
+#define KQ_WI_LAUNCH(TWV) do {                                                                                         \
+        e = cudaFuncSetAttribute(warp_insert_kernel<TWV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_w);   \
+        if (e != cudaSuccess) return e;                                                                                \
+        cudaFuncSetAttribute(warp_insert_kernel<TWV>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared); \
+        warp_insert_kernel<TWV><<<grid_w, nw * 32, smem_w, st>>>(tv, tuples, fstart, fcount, cap, stride, ovf, ovf_cap, ovf_n, ticket); } while (0)
+        if (tuple_words(tv.k) == 1) KQ_WI_LAUNCH(1); else KQ_WI_LAUNCH(2);
+#undef KQ_WI_LAUNCH
+        ++*launches;
+        return cudaGetLastError();
+    }
     const size_t smem = sizeof(Slot) << tv.slice_bits;
     const unsigned grid = (unsigned)std::min<unsigned long long>(tv.nslices, (unsigned long long)sm_count() * (unsigned)tuning().s3_ctas);
 #define KQ_SI_LAUNCH(TWV, NTV) do {                                                                                    \

@@ -45,6 +45,7 @@ Tuning &tuning() {
         v.fs_variant = (int)num("KQ_FS_VARIANT", 0);
         v.pipeline = (int)num("KQ_PIPELINE", 3); if (v.pipeline < 2 || v.pipeline > 4) v.pipeline = 3;
         v.cursor_stride = (int)num("KQ_CURSOR_STRIDE", 8); if (v.cursor_stride < 1 || v.cursor_stride > 32) v.cursor_stride = 8;
+        v.warp_insert = (int)num("KQ_WARP_INSERT", 1);
         v.s3_threads = (int)num("KQ_S3_THREADS", 256); v.s3_ctas = (int)num("KQ_S3_CTAS", 3); if (v.s3_ctas < 1 || v.s3_ctas > 8) v.s3_ctas = 3;
         return v;
     }();

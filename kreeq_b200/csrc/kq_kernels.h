@@ -71,6 +71,7 @@ struct Tuning {
     int smem_insert;           // 0 = count with L2 CAS (insert_tuples_kernel) also on multi-slice tables
     int direct_pct;            // batches below this share of the table's slots skip the sweep (fused kernel)
     int db_host;               // .kreeq codec on the host (cross-check of the device codec)
+    int warp_insert;           // 1 = slices of at most 2^10 slots are counted by one warp each (no shared-memory atomics)
     int s3_threads, s3_ctas;   // shared-memory insert: threads per CTA (256 / 384 / 512), CTAs per SM in the grid
     int fs_variant;            // level-2 scatter: 0 auto (two CTAs per SM when the bins allow), 1 one CTA, 2 two CTAs
     int pipeline;              // big tables: 4 one-pass scatter + shared-memory insert, 3 two-level scatter + shared-memory

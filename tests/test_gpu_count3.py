@@ -22,7 +22,7 @@ def tuned():
     """set knobs for one test, restore the defaults afterwards"""
     from kreeq_b200._lib import lib
     L = lib()
-    defaults = {"single_slice_bits": 21, "piece_bits": 12, "fine_part": 1 << 18, "smem_insert": 1, "direct_pct": 25}
+    defaults = {"single_slice_bits": 21, "piece_bits": 9, "fine_part": 1 << 18, "smem_insert": 1, "direct_pct": 25, "warp_insert": 1}
 
     def set_(**kw):
         for n, v in kw.items():
@@ -48,7 +48,7 @@ def _run(kb, ko, k, batches, hint, genome=None):
             assert (g.tot_missing, g.tot_kcount, g.tot_edge_missing) == racc
 
 
-@pytest.mark.parametrize("k,piece,part", [(21, 8, 4096), (31, 10, 64), (15, 6, 1024), (32, 12, 1 << 18), (21, 12, 1 << 18)])
+@pytest.mark.parametrize("k,piece,part", [(21, 8, 4096), (31, 10, 64), (15, 6, 1024), (32, 12, 1 << 18), (21, 12, 1 << 18), (21, 9, 1 << 18), (32, 9, 4096)])
 def test_small_slices_match_oracle(mods, tuned, k, piece, part):
     kb, ko = mods
     tuned(single_slice_bits=8, piece_bits=piece, fine_part=part, direct_pct=0)
@@ -79,6 +79,16 @@ def test_small_slices_wrong_hint(mods, tuned):
     genome = random_genome(rng, 400_000)
     batch = sample_reads(rng, genome, 12_000, 150, err=0.01)
     _run(kb, ko, 21, [batch], 60_000)           # ~0.75 M distinct arrive
+
+
+def test_cta_owned_slices_still_available(mods, tuned):
+    """warp_insert = 0: small slices counted by the CTA-owned kernel (shared-memory CAS)"""
+    kb, ko = mods
+    tuned(single_slice_bits=8, piece_bits=8, fine_part=2048, direct_pct=0, warp_insert=0)
+    rng = np.random.default_rng(78)
+    genome = random_genome(rng, 100_000)
+    batch = (b"A" * 400 + b"N") * 3 + sample_reads(rng, genome, 5000, 150, err=0.01)
+    _run(kb, ko, 21, [batch], 600_000, genome.tobytes())
 
 
 def test_l2_insert_still_available(mods, tuned):
