@@ -147,6 +147,17 @@ double kq_qv_value(uint64_t missing, uint64_t total, int k);
  * found[i]=0 leaves rec[i] untouched. */
 int  kq_lookup_batch(kq_ctx *ctx, const uint64_t *keys, size_t n, kq_rec32 *rec, uint8_t *found);
 
+/* kq_lookup_batch without any allocation (no cudaMalloc / cudaFree, no host heap): keys and answers are staged in
+ * ONE file-scope device array of KQ_STATIC_LOOKUP_MAX keys (2.9 MiB per GPU that loads the library, held until
+ * exit).  For callers that cannot allocate: code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it.  No counterpart in the reference.
+ * Same answers as kq_lookup_batch (found[i]=0 leaves rec[i] untouched).  n > KQ_STATIC_LOOKUP_MAX -> KQ_EINVAL;
+ * pending reads (kq_count_push without kq_sync / kq_count_finish) -> KQ_ESTATE, because counting them may grow
+ * the table.  Every call shares the array: calls that overlap on one GPU (two handles, two threads) race. */
+#define KQ_STATIC_LOOKUP_MAX 65536
+size_t kq_lookup_static_max(void);
+int  kq_lookup_batch_static(kq_ctx *ctx, const uint64_t *keys, size_t n, kq_rec32 *rec, uint8_t *found);
+
 /* logical {key -> record} set of this shard sorted by key (parity checks,
  * writers).  *n in: capacity of keys/recs, out: records present. */
 int  kq_export(kq_ctx *ctx, uint64_t *keys, kq_rec32 *recs, size_t *n);

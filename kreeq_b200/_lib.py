@@ -63,6 +63,8 @@ PROTOTYPES = {
     "kq_error_rate": (C.c_double, [_u64, _u64, _i]),
     "kq_qv_value": (C.c_double, [_u64, _u64, _i]),
     "kq_lookup_batch": (_i, [_vp, _vp, _sz, _vp, _vp]),
+    "kq_lookup_batch_static": (_i, [_vp, _vp, _sz, _vp, _vp]),
+    "kq_lookup_static_max": (_sz, []),
     "kq_export": (_i, [_vp, _vp, _vp, C.POINTER(_sz)]),
     "kq_distinct": (_i, [_vp, C.POINTER(_u64)]),
     "kq_packed_words": (_sz, [_sz]),

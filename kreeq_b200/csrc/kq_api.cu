@@ -1965,3 +1965,4 @@ extern "C" int kq_db_read_records(const char *dir_c, uint64_t *keys, kq_rec32 *r
 }
 
 #include "kq_multi.inl"
+#include "kq_static.inl"
