@@ -172,6 +172,8 @@ void table_geometry(uint64_t need, int tw, uint64_t &nslices, int &slice_bits, i
         int lg = 0; while ((2ull << lg) <= nslices) ++lg;            // floor(log2 nslices)
         cshift = lg / 2;
         while ((((nslices - 1) >> cshift) + 1) > 3000) ++cshift;      // bins of the level-1 scatter must fit shared memory
+        // fewer, larger coarse bins while the level-2 scatter still has room for them (knob; measured in DESIGN.md)
+        for (int b2 = 0; b2 < tuning().coarse_bias && fine_pick_cap(2u << cshift, tw) != 0 && (1ull << (cshift + 1)) < nslices; ++b2) ++cshift;
         if (slice_bits >= 12 || fine_pick_cap(1u << cshift, tw) != 0) break;
     }
 }
@@ -705,6 +707,8 @@ extern "C" int kq_set_tuning(const char *name, long long value) {
     else if (n == "insert_ctas" && value >= 1 && value <= 8) t.insert_ctas = (int)value;
     else if (n == "validate_ctas" && value >= 1 && value <= 8) t.validate_ctas = (int)value;
     else if (n == "db_host" && (value == 0 || value == 1)) t.db_host = (int)value;
+    else if (n == "coarse_bias" && value >= 0 && value <= 4) t.coarse_bias = (int)value;
+    else if (n == "db_ordered" && (value == 0 || value == 1)) t.db_ordered = (int)value;
     else if (n == "warp_insert" && (value == 0 || value == 1)) t.warp_insert = (int)value;
     else if (n == "s3_threads" && (value == 256 || value == 384 || value == 512)) t.s3_threads = (int)value;
     else if (n == "s3_ctas" && value >= 1 && value <= 8) t.s3_ctas = (int)value;
@@ -1644,7 +1648,7 @@ int load_maps_gpu(kq_ctx *c, const std::string &dir, XRec **d_xs, uint64_t *n_ou
         file_off[m] = total; file_size[m] = (uint64_t)st.st_size;
         total = (total + file_size[m] + 255) & ~255ull;
     }
-    unsigned char *d_img = nullptr; DbBucket *d_buckets = nullptr; unsigned long long *d_n = nullptr;
+    unsigned char *d_img = nullptr; DbBucket *d_buckets = nullptr; unsigned long long *d_n = nullptr, *d_band = nullptr;
     CU(cudaMalloc(&d_img, std::max<uint64_t>(total, 256)));
     std::vector<DbBucket> buckets((size_t)(hi - lo) * 256, DbBucket{0, 0, 0, 0, 0});
     std::vector<std::string> errs((size_t)(hi - lo));
@@ -1686,14 +1690,24 @@ int load_maps_gpu(kq_ctx *c, const std::string &dir, XRec **d_xs, uint64_t *n_ou
     for (const auto &e : errs) if (!e.empty()) { cudaFree(d_img); return fail(c, KQ_EIO, e); }
     c->h2d += total;
     uint64_t n = 0; for (const auto &b : buckets) n += b.n;
-    auto cleanup = [&] { cudaFree(d_img); cudaFree(d_buckets); cudaFree(d_n); };
+    auto cleanup = [&] { cudaFree(d_img); cudaFree(d_buckets); cudaFree(d_n); cudaFree(d_band); };
 #define CUX(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { cleanup(); cudaFree(*d_xs); *d_xs = nullptr; return fail(c, e_ == cudaErrorMemoryAllocation ? KQ_ENOMEM : KQ_ECUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); } } while (0)
     CUX(cudaMalloc(&d_buckets, buckets.size() * sizeof(DbBucket))); CUX(cudaMalloc(&d_n, 8));
     CUX(cudaMalloc(d_xs, (n + 1) * sizeof(XRec)));
     CUX(cudaMemcpyAsync(d_buckets, buckets.data(), buckets.size() * sizeof(DbBucket), cudaMemcpyHostToDevice, c->stream));
     CUX(cudaMemsetAsync(d_n, 0, 8, c->stream));
     const int t7 = time_begin(c, 7);
-    CUX(launch_db_decode(c->stream, d_img, d_buckets, (unsigned)buckets.size(), *d_xs, n, d_n, &c->launches));
+    if (tuning().db_ordered && n >= (1u << 16)) {
+        // records per band of the slice hash, exclusive scan, decode into band order (= table order)
+        constexpr unsigned NB = 1u << KQ_DB_ORDER_BITS;
+        CUX(cudaMalloc(&d_band, 2 * NB * 8));
+        CUX(cudaMemsetAsync(d_band, 0, NB * 8, c->stream));
+        CUX(launch_db_band_hist(c->stream, d_img, d_buckets, (unsigned)buckets.size(), d_band, &c->launches));
+        CUX(launch_slice_offsets(c->stream, NB, d_band, d_band + NB, nullptr, d_n, nullptr, &c->launches));
+        CUX(launch_db_decode_ordered(c->stream, d_img, d_buckets, (unsigned)buckets.size(), *d_xs, n, d_band + NB, &c->launches));
+    } else {
+        CUX(launch_db_decode(c->stream, d_img, d_buckets, (unsigned)buckets.size(), *d_xs, n, d_n, &c->launches));
+    }
     time_end(c, t7);
     unsigned long long got = 0;
     CUX(cudaMemcpyAsync(&got, d_n, 8, cudaMemcpyDeviceToHost, c->stream));

@@ -175,6 +175,56 @@ db_decode_kernel(const unsigned char *__restrict__ img, const DbBucket *__restri
     }
 }
 
+// ---- load in table order ---------------------------------------------------------------------------------------
+//
+// slice_of_key is monotone in the slice hash, so records sorted by the top KQ_DB_ORDER_BITS bits of that hash are in
+// slice order on the table that receives them whatever its geometry: put / merge kernels that walk such an array
+// touch one narrow band of the table at a time (DRAM pages and TLB entries are reused, the band sits in L2), and
+// a union applies database after database over the table in the same sweep order.  Two passes over the uploaded
+// image: records per band, then decode straight to the record's place in band order (one L2 atomic per record).
+__device__ __forceinline__ unsigned order_band(uint64_t key) {
+    return (unsigned)((uint32_t)((key * 0x9E3779B97F4A7C15ULL) >> 32) >> (32 - KQ_DB_ORDER_BITS));
+}
+
+__global__ void __launch_bounds__(TPB)
+db_band_hist_kernel(const unsigned char *__restrict__ img, const DbBucket *__restrict__ buckets, unsigned nbuckets,
+                    unsigned long long *hist) {
+    __shared__ unsigned h[1u << KQ_DB_ORDER_BITS];
+    for (unsigned i = threadIdx.x; i < (1u << KQ_DB_ORDER_BITS); i += TPB) h[i] = 0;
+    __syncthreads();
+    for (unsigned b = blockIdx.x; b < nbuckets; b += gridDim.x) {
+        const DbBucket d = buckets[b];
+        if (!d.n) continue;
+        const unsigned char *ctrl = img + d.ctrl_off;
+        for (unsigned long long i = threadIdx.x; i < d.cap; i += TPB)
+            if (!(ctrl[i] & 0x80)) atomicAdd(&h[order_band(get64(img + d.slot_off + i * 24))], 1u);
+    }
+    __syncthreads();
+    for (unsigned i = threadIdx.x; i < (1u << KQ_DB_ORDER_BITS); i += TPB)
+        if (h[i]) atomicAdd(&hist[i], (unsigned long long)h[i]);
+}
+
+__global__ void __launch_bounds__(TPB)
+db_decode_ordered_kernel(const unsigned char *__restrict__ img, const DbBucket *__restrict__ buckets, unsigned nbuckets,
+                         XRec *out, unsigned long long cap_out, unsigned long long *cursor) {
+    for (unsigned b = blockIdx.x; b < nbuckets; b += gridDim.x) {
+        const DbBucket d = buckets[b];
+        if (!d.n) continue;
+        const unsigned char *ctrl = img + d.ctrl_off;
+        for (unsigned long long i = threadIdx.x; i < d.cap; i += TPB) {
+            if (ctrl[i] & 0x80) continue;
+            const unsigned char *s = img + d.slot_off + i * 24;
+            XRec x; x.key = get64(s);
+#pragma unroll
+            for (int w = 0; w < 4; ++w) { x.r.fw[w] = s[8 + w]; x.r.bw[w] = s[12 + w]; }
+            x.r.cov = s[16];
+            x.flags = x.r.cov == 255 ? F_PLACEHOLDER : 0u;
+            const unsigned long long j = atomicAdd(&cursor[order_band(x.key)], 1ULL);
+            if (j < cap_out) out[j] = x;
+        }
+    }
+}
+
 // records with a field above what a slot lane holds: only these can create remainder / maps32 entries
 __global__ void __launch_bounds__(TPB)
 db_count_big_kernel(const XRec *__restrict__ xs, unsigned long long n, unsigned long long *out) {
@@ -236,6 +286,23 @@ cudaError_t launch_db_decode(cudaStream_t st, const unsigned char *img, const Db
                              XRec *out, unsigned long long cap_out, unsigned long long *n_out, uint64_t *launches) {
     if (!nbuckets) return cudaSuccess;
     db_decode_kernel<<<nbuckets < 65535u ? nbuckets : 65535u, TPB, 0, st>>>(img, buckets, nbuckets, out, cap_out, n_out);
+    ++*launches;
+    return cudaGetLastError();
+}
+
+// band histogram of the image's records -> hist[1 << KQ_DB_ORDER_BITS] (zeroed by the caller)
+cudaError_t launch_db_band_hist(cudaStream_t st, const unsigned char *img, const DbBucket *buckets, unsigned nbuckets,
+                                unsigned long long *hist, uint64_t *launches) {
+    if (!nbuckets) return cudaSuccess;
+    db_band_hist_kernel<<<std::min<unsigned>(nbuckets, (unsigned)sm_count() * 8), TPB, 0, st>>>(img, buckets, nbuckets, hist);
+    ++*launches;
+    return cudaGetLastError();
+}
+// decode into band order; cursor[] = exclusive scan of the band histogram (advanced by the kernel)
+cudaError_t launch_db_decode_ordered(cudaStream_t st, const unsigned char *img, const DbBucket *buckets, unsigned nbuckets,
+                                     XRec *out, unsigned long long cap_out, unsigned long long *cursor, uint64_t *launches) {
+    if (!nbuckets) return cudaSuccess;
+    db_decode_ordered_kernel<<<nbuckets < 65535u ? nbuckets : 65535u, TPB, 0, st>>>(img, buckets, nbuckets, out, cap_out, cursor);
     ++*launches;
     return cudaGetLastError();
 }

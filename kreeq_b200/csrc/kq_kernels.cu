@@ -46,6 +46,8 @@ Tuning &tuning() {
         v.pipeline = (int)num("KQ_PIPELINE", 3); if (v.pipeline < 2 || v.pipeline > 4) v.pipeline = 3;
         v.cursor_stride = (int)num("KQ_CURSOR_STRIDE", 8); if (v.cursor_stride < 1 || v.cursor_stride > 32) v.cursor_stride = 8;
         v.warp_insert = (int)num("KQ_WARP_INSERT", 1);
+        v.db_ordered = (int)num("KQ_DB_ORDERED", 1);
+        v.coarse_bias = (int)num("KQ_COARSE_BIAS", 0); if (v.coarse_bias < 0 || v.coarse_bias > 4) v.coarse_bias = 0;
         v.s3_threads = (int)num("KQ_S3_THREADS", 256); v.s3_ctas = (int)num("KQ_S3_CTAS", 3); if (v.s3_ctas < 1 || v.s3_ctas > 8) v.s3_ctas = 3;
         return v;
     }();

@@ -71,6 +71,8 @@ struct Tuning {
     int smem_insert;           // 0 = count with L2 CAS (insert_tuples_kernel) also on multi-slice tables
     int direct_pct;            // batches below this share of the table's slots skip the sweep (fused kernel)
     int db_host;               // .kreeq codec on the host (cross-check of the device codec)
+    int coarse_bias;           // level-1 bins: 2^v times fewer (and larger) than the square-root split
+    int db_ordered;            // 1 = databases are decoded into table order before they are put / merged
     int warp_insert;           // 1 = slices of at most 2^10 slots are counted by one warp each (no shared-memory atomics)
     int s3_threads, s3_ctas;   // shared-memory insert: threads per CTA (256 / 384 / 512), CTAs per SM in the grid
     int fs_variant;            // level-2 scatter: 0 auto (two CTAs per SM when the bins allow), 1 one CTA, 2 two CTAs
@@ -206,6 +208,11 @@ cudaError_t launch_db_count(cudaStream_t st, const XRec *xs, unsigned long long 
 cudaError_t launch_db_build(cudaStream_t st, const XRec *xs, unsigned long long n, int lo, int hi, unsigned char *img,
                             const DbBucket *buckets, unsigned long long *pos_scratch, uint64_t *launches);
 // *out += records that can create a remainder / maps32 entry (a field above a slot lane, or a placeholder)
+constexpr int KQ_DB_ORDER_BITS = 12;   // a database is decoded into 4096 bands of the slice hash (= table order)
+cudaError_t launch_db_band_hist(cudaStream_t st, const unsigned char *img, const DbBucket *buckets, unsigned nbuckets,
+                                unsigned long long *hist, uint64_t *launches);
+cudaError_t launch_db_decode_ordered(cudaStream_t st, const unsigned char *img, const DbBucket *buckets, unsigned nbuckets,
+                                     XRec *out, unsigned long long cap_out, unsigned long long *cursor, uint64_t *launches);
 cudaError_t launch_db_count_big(cudaStream_t st, const XRec *xs, unsigned long long n, unsigned long long *out, uint64_t *launches);
 // uploaded file images -> raw records
 cudaError_t launch_db_decode(cudaStream_t st, const unsigned char *img, const DbBucket *buckets, unsigned nbuckets,

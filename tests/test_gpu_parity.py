@@ -469,3 +469,32 @@ def test_validate_into_page_locked_output(mods):
         assert short.tobytes() == g.evaluateSegment(asm[:1000]).tobytes() and short[980:].tobytes() == bytes(16 * 20)
     rc, rout, racc = ref.validate_segment(asm[:600_000].tobytes())
     assert rout.tobytes()[:16 * 500_000] == pageable.tobytes()[:16 * 500_000]
+
+
+def test_union_of_moderately_covered_databases(mods, tmp_path):
+    """Two read sets of one 150 kbp genome at ~90x each: every genomic key is below a slot lane (127) in both
+    databases and passes it in the union, so ~1.5e5 keys get a remainder record in ONE merge launch (the side
+    table starts at 4096 entries), and three databases take the sums past 254 (placeholders + 32-bit records).
+    The databases are large enough to be decoded into table order (>= 65536 records)."""
+    kb, ko = mods
+    k = 21
+    rng = np.random.default_rng(1234)
+    genome = random_genome(rng, 150_000)
+    dirs = []
+    for i in range(3):
+        batch = sample_reads(rng, genome, 90_000, 150, err=0.0)
+        d = str(tmp_path / ("c%d.kreeq" % i)); dirs.append(d)
+        with kb.DBG(k=k, expected_distinct=400_000) as g:
+            g.traverseInReads(batch); g.finalize(); g.save(d)
+            st = g.stats()
+            assert st["distinct"] > 140_000 and 60 < st["total"] / st["distinct"] < 127
+    for order in ([0, 1], [0, 1, 2], [2, 0, 1]):
+        u = ko.union([ko.read_db(dirs[i], check=False) for i in order])
+        with kb.DBG(k=k) as g:
+            g.kunion([dirs[i] for i in order], ref_compatible=True)
+            assert_same_records(g.export(), u.export())
+            assert g.stats() == u.stats()
+            seg = genome.tobytes()[:20000]
+            out = g.evaluateSegment(seg)
+            rc, rout, racc = u.validate_segment(seg)
+            assert out.tobytes() == rout.tobytes()
