@@ -83,6 +83,7 @@ struct kq_ctx {
     uint64_t *d_tuples = nullptr; uint64_t tup_cap = 0;          // tuples (not words)
     unsigned long long *d_hist = nullptr, *d_cursor = nullptr; uint64_t hist_cap = 0;
     unsigned long long *d_total = nullptr, *d_nsrc = nullptr, *d_ticket = nullptr;
+    unsigned long long *d_hot = nullptr;                          // slices left to hot_slices_kernel (HotList)
     uint64_t *d_ovf = nullptr; unsigned long long *d_ovf_n = nullptr; bool ovf_pending = false;
     uint64_t *ovf_list = nullptr; uint64_t ovf_list_cap = 0;    // where the last batch put the tuples of full slices
     // level 2 of the pipeline: tuples in slice order, per-slice counts / offsets, tasks
@@ -299,6 +300,7 @@ int pipeline_scratch(kq_ctx *c, uint64_t tuples, bool level2 = false, uint64_t t
         CU(cudaMalloc(&c->d_tasks, tasks * sizeof(FineTask)));
         c->task_cap = tasks;
     }
+    if (!c->d_hot) CU(cudaMalloc(&c->d_hot, (1 + 3 * (size_t)KQ_HOT_CAP) * 8));
     if (!c->d_ntasks) { CU(cudaMalloc(&c->d_ntasks, sizeof(unsigned))); CU(cudaMalloc(&c->d_task_first, (KQ_MAX_COARSE + 2) * sizeof(unsigned))); }
     const uint64_t h2 = c->task_cap << c->cshift;                     // per-task histograms of the level-2 pass
     if (c->hist2_cap < h2) {
@@ -343,6 +345,11 @@ int settle(kq_ctx *c) {
     rc = read_occ(c, occ); if (rc) return rc;
     c->occ_bound = occ[0];
     return KQ_OK;
+}
+
+// a slice that receives more than eight times its share of a batch (and more than 4096 tuples) is a hot one
+HotList hot_list(kq_ctx *c, uint64_t bound) {
+    return HotList{c->d_hot, KQ_HOT_CAP, (unsigned)std::min<uint64_t>(1u << 30, std::max<uint64_t>(4096, 8 * (bound / c->nslices)))};
 }
 
 // one batch of the pipeline: every instance of src goes into the table
@@ -406,7 +413,8 @@ int run_batch(kq_ctx *c, Source src) {
         time_end(c, t4);
         const int t2 = time_begin(c, 2);
         // tuples of full slices go back into the slab (read completely by now, as large as the batch)
-        CU(launch_smem_insert(c->stream, tv, c->d_tuples2, c->d_fstart, c->d_fhist, 0, 1, c->d_slab, c->slab_cap, c->d_ovf_n, c->d_ticket, &c->launches));
+        CU(launch_smem_insert(c->stream, tv, c->d_tuples2, c->d_fstart, c->d_fhist, 0, 1, c->d_slab, c->slab_cap, c->d_ovf_n, c->d_ticket, &c->launches,
+                              hot_list(c, bound)));
         time_end(c, t2);
         c->ovf_list = c->d_slab; c->ovf_list_cap = c->slab_cap;
         c->ovf_pending = true;
@@ -460,7 +468,8 @@ int run_batch(kq_ctx *c, Source src) {
     time_end(c, t4);
     const int t2 = time_begin(c, 2);
     // tuples of full slices go back into the level-1 buffer (free by now, as large as the batch)
-    CU(launch_smem_insert(c->stream, tv, c->d_tuples2, c->d_fstart, c->d_fhist, 0, 1, c->d_tuples, c->tup_cap, c->d_ovf_n, c->d_ticket, &c->launches));
+    CU(launch_smem_insert(c->stream, tv, c->d_tuples2, c->d_fstart, c->d_fhist, 0, 1, c->d_tuples, c->tup_cap, c->d_ovf_n, c->d_ticket, &c->launches,
+                          hot_list(c, bound)));
     time_end(c, t2);
     c->ovf_list = c->d_tuples; c->ovf_list_cap = c->tup_cap;
     c->ovf_pending = true;
@@ -617,7 +626,7 @@ extern "C" void kq_destroy(kq_ctx *c) {
     cudaFree(c->d_pb); cudaFree(c->d_pi); cudaFree(c->d_tuples); cudaFree(c->d_hist); cudaFree(c->d_cursor);
     cudaFree(c->d_tuples2); cudaFree(c->d_cstart); cudaFree(c->d_fhist); cudaFree(c->d_fcursor); cudaFree(c->d_fstart);
     cudaFree(c->d_tasks); cudaFree(c->d_ntasks); cudaFree(c->d_task_first); cudaFree(c->d_hist2); cudaFree(c->d_scur); cudaFree(c->d_ovf2);
-    cudaFree(c->d_total); cudaFree(c->d_nsrc); cudaFree(c->d_ticket); cudaFree(c->d_ovf); cudaFree(c->d_ovf_n);
+    cudaFree(c->d_total); cudaFree(c->d_nsrc); cudaFree(c->d_ticket); cudaFree(c->d_hot); cudaFree(c->d_ovf); cudaFree(c->d_ovf_n);
     for (void *p : c->ipc_opened) cudaIpcCloseMemHandle(p);
     for (void *p : c->peer_opened) cudaIpcCloseMemHandle(p);
     cudaFree(c->d_peers);

@@ -552,19 +552,56 @@ __device__ __noinline__ unsigned long long excl_spill(const TableView &tv, uint6
     return c - take;
 }
 
-// the lanes that hold ONE instance of the same key add up (warp_combine); lanes with a combined increment stay alone
-__device__ __noinline__ unsigned long long warp_combine_singles(uint64_t key, uint32_t e, bool todo, unsigned long long ci) {
+// Lanes that wait for one slot with the same key add their increments up: the lowest lane of the group takes the
+// others in lane order while the sum stays at or below 63 instances (every field of the sum then fits its 7 bits:
+// a lane counts at most as many edges as instances; and a slot that cannot take 63 more has at least 65, so the
+// spill of 63 never underflows).  Returns the lane's new increment, 0 = another lane counts for this one.
+// All 32 lanes call it; lanes without work pass todo = false.
+constexpr unsigned KQ_MERGE_MAX = 63;
+__device__ __noinline__ unsigned long long warp_merge(uint64_t key, bool todo, unsigned long long ci) {
     const unsigned lane = threadIdx.x & 31;
-    const bool single = todo && (ci >> 56) == 1;
-    const unsigned long long inc = warp_combine(single ? key : ~0ULL - lane, e, single);
-    return single ? inc : ci;                                              // 0 = another lane counts for this one
+    const unsigned act = __ballot_sync(0xffffffffu, todo);
+    const unsigned peers = __match_any_sync(0xffffffffu, todo ? key : ~0ULL - lane) & act;   // distinct dummies: no false match
+    unsigned long long acc = 0; unsigned acc_n = 0; bool mine = false;
+    for (unsigned m = act; m; m &= m - 1) {
+        const int src = __ffs(m) - 1;
+        const unsigned long long v = __shfl_sync(0xffffffffu, ci, src);
+        if ((peers >> src) & 1u) {
+            const unsigned n = (unsigned)(v >> 56);
+            if (acc_n == 0 || acc_n + n <= KQ_MERGE_MAX) { acc += v; acc_n += n; mine |= src == (int)lane; }
+        }
+    }
+    if (!todo) return ci;
+    if (lane == (unsigned)__ffs(peers) - 1) return acc;
+    return mine ? 0ULL : ci;
+}
+
+// complete insert of one (merged) increment by ONE lane while the other lanes of the warp wait: plain loads and
+// stores on the warp's slice; 1 = new key
+template <int TW>
+__device__ __noinline__ unsigned excl_insert(uint32_t piece_a, unsigned mask, unsigned limit, const TableView &tv, uint64_t key,
+                                             unsigned long long inc, uint64_t *ovf, unsigned long long ovf_cap, unsigned long long *ovf_n) {
+    const unsigned long long tag = key + 1;
+    unsigned slot = (unsigned)home_hash(key) & mask;
+    for (unsigned probes = 0; probes < limit; ++probes, slot = (slot + 1) & mask) {
+        unsigned long long t, c;
+        asm volatile("ld.shared.v2.u64 {%0, %1}, [%2];" : "=l"(t), "=l"(c) : "r"(piece_a + (slot << 4)) : "memory");
+        if (t != 0 && t != tag) continue;
+        if (t == 0) c = 0;
+        if (cnt_cov(c) + (unsigned)(inc >> 56) > KQ_LANE_MAX) c = excl_spill(tv, key, c);
+        c += inc;
+        asm volatile("st.shared.v2.u64 [%0], {%1, %2};" ::"r"(piece_a + (slot << 4)), "l"(tag), "l"(c) : "memory");
+        return t == 0;
+    }
+    smem_give_back<TW>(ovf, ovf_cap, ovf_n, key, inc);
+    return 0;
 }
 
 template <int TW>
 __global__ void __launch_bounds__(256, 3)
 warp_insert_kernel(TableView tv, const uint64_t *__restrict__ tuples, const unsigned long long *__restrict__ fstart,
                    const void *__restrict__ fcount_, unsigned long long cap, int stride, uint64_t *ovf,
-                   unsigned long long ovf_cap, unsigned long long *ovf_n, unsigned long long *ticket) {
+                   unsigned long long ovf_cap, unsigned long long *ovf_n, unsigned long long *ticket, HotList hot) {
     const unsigned long long *fcount = static_cast<const unsigned long long *>(fcount_);     // level-2 layout: exact counts
     const unsigned *fcur = static_cast<const unsigned *>(fcount_);                             // one-pass layout: 32-bit cursors
     extern __shared__ __align__(128) unsigned char sm_w[];
@@ -600,7 +637,19 @@ warp_insert_kernel(TableView tv, const uint64_t *__restrict__ tuples, const unsi
         while (todo_slices) {
             const int src = __ffs(todo_slices) - 1; todo_slices &= todo_slices - 1;
             const unsigned n = (unsigned)__shfl_sync(0xffffffffu, my_n, src);      // (a batch brings fewer than 2^32 tuples)
-            const uint64_t *tp = tuples + __shfl_sync(0xffffffffu, my_start, src) * TW;
+            const unsigned long long start = __shfl_sync(0xffffffffu, my_start, src);
+            if (hot.buf && n > hot.limit) {
+                // a slice with many times its share of the batch holds a run of one key (poly-A, a satellite): one
+                // warp would work on it long after the others are done -- hot_slices_kernel counts it with all SMs
+                unsigned long long j = 0;
+                if (lane == 0) j = atomicAdd(&hot.buf[0], 1ULL);
+                j = __shfl_sync(0xffffffffu, j, 0);
+                if (j < hot.cap) {
+                    if (lane == 0) { hot.buf[1 + 3 * j] = start; hot.buf[2 + 3 * j] = n; hot.buf[3 + 3 * j] = s0 + src; }
+                    continue;
+                }
+            }
+            const uint64_t *tp = tuples + start * TW;
             Slot *gpiece = tv.T + ((s0 + src) << tv.slice_bits);
             if (lane == 0) { mbar_expect_tx(bar, bytes); bulk_g2s(piece, gpiece, bytes, bar); }
             unsigned head = 64;                                            // first tuple of the slice nobody holds yet
@@ -645,9 +694,15 @@ warp_insert_kernel(TableView tv, const uint64_t *__restrict__ tuples, const unsi
                 __syncwarp();
                 if (__popc(__ballot_sync(0xffffffffu, lost)) >= 12) {
                     // neighbours in the stream with one key (poly-A, satellites): they add up, one lane counts for all
+                    // and that lane counts at once, before new tuples of the run arrive (the lock gives no lane priority:
+                    // a lane that only waits with its sum would starve behind the single tuples that keep coming)
                     const bool todo = live && !done;
-                    const unsigned long long inc = warp_combine_singles(ck, ce, todo, ci);
-                    if (todo) { if (inc) ci = inc; else done = true; }
+                    const unsigned long long inc = warp_merge(ck, todo, ci);
+                    for (unsigned m = __ballot_sync(0xffffffffu, todo && inc != 0); m; m &= m - 1) {
+                        if (lane == (unsigned)__ffs(m) - 1) fresh += excl_insert<TW>(piece_a, mask, limit, tv, ck, inc, ovf, ovf_cap, ovf_n);
+                        __syncwarp();
+                    }
+                    done |= todo;
                 }
                 const unsigned dm = __ballot_sync(0xffffffffu, done);
                 if (done) {
@@ -669,6 +724,39 @@ warp_insert_kernel(TableView tv, const uint64_t *__restrict__ tuples, const unsi
         }
     }
     if (lane == 0) bulk_wait_all();
+    unsigned long long f = fresh;
+    for (int o = 16; o; o >>= 1) f += __shfl_xor_sync(0xffffffffu, f, o);
+    if (lane == 0 && f) atomicAdd(&sh_fresh, f);
+    __syncthreads();
+    if (threadIdx.x == 0 && sh_fresh) atomicAdd(&tv.occ[0], sh_fresh);
+}
+
+// The slices warp_insert_kernel left out: every warp of the grid takes 32 tuples at a time, the lanes with one key add
+// up (warp_combine) and one lane per key counts the sum into the slice in HBM (CAS through L2).
+template <int TW>
+__global__ void __launch_bounds__(256)
+hot_slices_kernel(TableView tv, const uint64_t *__restrict__ tuples, HotList hot, uint64_t *ovf, unsigned long long ovf_cap,
+                  unsigned long long *ovf_n) {
+    __shared__ unsigned long long sh_fresh;
+    if (threadIdx.x == 0) sh_fresh = 0;
+    __syncthreads();
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    const unsigned slots = 1u << tv.slice_bits, mask = slots - 1;
+    const unsigned long long nh = min(hot.buf[0], (unsigned long long)hot.cap);
+    unsigned fresh = 0;
+    for (unsigned long long h = 0; h < nh; ++h) {
+        const unsigned long long start = hot.buf[1 + 3 * h], n = hot.buf[2 + 3 * h], s = hot.buf[3 + 3 * h];
+        Slot *piece = tv.T + (s << tv.slice_bits);
+        const uint64_t *tp = tuples + start * TW;
+        for (unsigned long long i0 = ((unsigned long long)blockIdx.x * nw + warp) * 32; i0 < n; i0 += (unsigned long long)gridDim.x * nw * 32) {
+            const unsigned long long i = i0 + lane;
+            uint64_t key = 0; uint32_t e = 255u;
+            if (i < n) t_unpack<TW>(tp, i, key, e);
+            const bool live = e != 255u;
+            const unsigned long long inc = warp_combine(live ? key : ~0ULL - lane, e, live);
+            if (inc) fresh += smem_insert_slow<TW>(piece, mask, slots, tv, key, inc, ovf, ovf_cap, ovf_n);
+        }
+    }
     unsigned long long f = fresh;
     for (int o = 16; o; o >>= 1) f += __shfl_xor_sync(0xffffffffu, f, o);
     if (lane == 0 && f) atomicAdd(&sh_fresh, f);
@@ -769,7 +857,8 @@ cudaError_t launch_fine_scatter(cudaStream_t st, const TableView &tv, const uint
 
 cudaError_t launch_smem_insert(cudaStream_t st, const TableView &tv, const uint64_t *tuples, const unsigned long long *fstart,
                                const void *fcount, unsigned long long cap, int stride, uint64_t *ovf,
-                               unsigned long long ovf_cap, unsigned long long *ovf_n, unsigned long long *ticket, uint64_t *launches) {
+                               unsigned long long ovf_cap, unsigned long long *ovf_n, unsigned long long *ticket, uint64_t *launches,
+                               HotList hot) {
     cudaError_t e = cudaMemsetAsync(ticket, 0, sizeof(unsigned long long), st);
     if (e != cudaSuccess) return e;
     if (tuning().warp_insert && tv.slice_bits <= 10) {
@@ -783,10 +872,12 @@ cudaError_t launch_smem_insert(cudaStream_t st, const TableView &tv, const uint6
         e = cudaFuncSetAttribute(warp_insert_kernel<TWV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_w);   \
         if (e != cudaSuccess) return e;                                                                                \
         cudaFuncSetAttribute(warp_insert_kernel<TWV>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared); \
-        warp_insert_kernel<TWV><<<grid_w, nw * 32, smem_w, st>>>(tv, tuples, fstart, fcount, cap, stride, ovf, ovf_cap, ovf_n, ticket); } while (0)
+        warp_insert_kernel<TWV><<<grid_w, nw * 32, smem_w, st>>>(tv, tuples, fstart, fcount, cap, stride, ovf, ovf_cap, ovf_n, ticket, hot); \
+        if (hot.buf) hot_slices_kernel<TWV><<<(unsigned)sm_count() * 4, 256, 0, st>>>(tv, tuples, hot, ovf, ovf_cap, ovf_n); } while (0)
+        if (hot.buf) { e = cudaMemsetAsync(hot.buf, 0, sizeof(unsigned long long), st); if (e != cudaSuccess) return e; }
         if (tuple_words(tv.k) == 1) KQ_WI_LAUNCH(1); else KQ_WI_LAUNCH(2);
 #undef KQ_WI_LAUNCH
-        ++*launches;
+        *launches += hot.buf ? 2 : 1;
         return cudaGetLastError();
     }
     const size_t smem = sizeof(Slot) << tv.slice_bits;

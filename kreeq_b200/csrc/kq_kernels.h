@@ -143,9 +143,12 @@ cudaError_t launch_fine_scatter(cudaStream_t st, const TableView &tv, const uint
                                 unsigned long long *cursor, const unsigned *hist2, const unsigned long long *fstart, uint64_t *launches);
 // count the tuples [fstart[s], fstart[s] + fcount[s]) of every slice s in shared memory
 // (fstart == NULL: fcount is the one-pass scatter's array of 32-bit cursors, slice s owns [s * cap, s * cap + min(cursor[s * stride], cap)))
+// slices with more than `limit` tuples of a batch are left to hot_slices_kernel: buf[0] = entries, then {start, n, slice}
+struct HotList { unsigned long long *buf; unsigned cap; unsigned limit; };
+constexpr unsigned KQ_HOT_CAP = 1u << 16;
 cudaError_t launch_smem_insert(cudaStream_t st, const TableView &tv, const uint64_t *tuples, const unsigned long long *fstart,
                                const void *fcount, unsigned long long cap, int stride, uint64_t *ovf,
-                               unsigned long long ovf_cap, unsigned long long *ovf_n, unsigned long long *ticket, uint64_t *launches);
+                               unsigned long long ovf_cap, unsigned long long *ovf_n, unsigned long long *ticket, uint64_t *launches, HotList hot = HotList{nullptr, 0, 0});
 
 // routed pipeline, steps 1-3: hist[nranks << nb_bits] of this rank's tuples; from the all-gathered
 // histograms H[nranks][P] the start of this rank's tuples inside every destination bin (cursor[P]) and what

@@ -32,7 +32,12 @@ __device__ __forceinline__ unsigned long long table_slots(const TableView &tv) {
 __global__ void __launch_bounds__(TPB, CTAS_PER_SM)
 stats_kernel(TableView tv, DevStats *ds, unsigned long long *hist, unsigned long long *big, unsigned long long big_cap) {
     __shared__ unsigned long long sh[4];
+    // coverages below 1024 (nearly every key: error k-mers at 1, genomic ones around the sequencing depth) are
+    // counted in shared memory -- one global atomic per key on hist[1] serialises in L2
+    constexpr unsigned LOW = 1024;
+    __shared__ unsigned low[LOW];
     if (threadIdx.x < 4) sh[threadIdx.x] = 0;
+    for (unsigned i = threadIdx.x; i < LOW; i += TPB) low[i] = 0;
     __syncthreads();
     unsigned long long total = 0, uniq = 0, distinct = 0, edges = 0;
     const uint64_t stride = (uint64_t)gridDim.x * TPB, cap = table_slots(tv);
@@ -44,7 +49,8 @@ stats_kernel(TableView tv, DevStats *ds, unsigned long long *hist, unsigned long
 #pragma unroll
         for (int w = 0; w < 4; ++w) edges += (r.fw[w] > 0 || r.bw[w] > 0);   // precedence quirk :253-254
         ++distinct;
-        if (r.cov < (uint32_t)HIST_BINS) { atomicAdd(&hist[r.cov], 1ULL); total += r.cov; }
+        if (r.cov < LOW) { atomicAdd(&low[r.cov], 1u); total += r.cov; }
+        else if (r.cov < (uint32_t)HIST_BINS) { atomicAdd(&hist[r.cov], 1ULL); total += r.cov; }
         else {
             const unsigned long long j = atomicAdd(&ds->big_n, 1ULL);
             if (j < big_cap) big[j] = r.cov;
@@ -56,6 +62,8 @@ stats_kernel(TableView tv, DevStats *ds, unsigned long long *hist, unsigned long
     block_add(uniq, &ds->unique, &sh[1]);
     block_add(distinct, &ds->distinct, &sh[2]);
     block_add(edges, &ds->edges, &sh[3]);
+    for (unsigned i = threadIdx.x; i < LOW; i += TPB)
+        if (low[i]) atomicAdd(&hist[i], (unsigned long long)low[i]);
 }
 
 __global__ void __launch_bounds__(TPB, CTAS_PER_SM)
