@@ -83,6 +83,7 @@ struct kq_ctx {
     uint64_t *d_tuples = nullptr; uint64_t tup_cap = 0;          // tuples (not words)
     unsigned long long *d_hist = nullptr, *d_cursor = nullptr; uint64_t hist_cap = 0;
     unsigned long long *d_total = nullptr, *d_nsrc = nullptr, *d_ticket = nullptr;
+    unsigned long long *d_cend = nullptr, *d_rstat = nullptr;     // one-pass level-1 scatter: region ends, statistics (Regions)
     unsigned long long *d_hot = nullptr;                          // slices left to hot_slices_kernel (HotList)
     uint64_t *d_ovf = nullptr; unsigned long long *d_ovf_n = nullptr; bool ovf_pending = false;
     uint64_t *ovf_list = nullptr; uint64_t ovf_list_cap = 0;    // where the last batch put the tuples of full slices
@@ -272,8 +273,8 @@ namespace {
 int pipeline_scratch(kq_ctx *c, uint64_t tuples, bool level2 = false, uint64_t tuples2 = 0) {
     const uint64_t nbins = coarse_bins(view(c));
     if (c->hist_cap < nbins) {
-        cudaFree(c->d_hist); cudaFree(c->d_cursor); cudaFree(c->d_cstart); c->d_hist = c->d_cursor = c->d_cstart = nullptr; c->hist_cap = 0;
-        CU(cudaMalloc(&c->d_hist, nbins * 8)); CU(cudaMalloc(&c->d_cursor, nbins * 8)); CU(cudaMalloc(&c->d_cstart, nbins * 8));
+        cudaFree(c->d_hist); cudaFree(c->d_cursor); cudaFree(c->d_cstart); cudaFree(c->d_cend); c->d_hist = c->d_cursor = c->d_cstart = c->d_cend = nullptr; c->hist_cap = 0;
+        CU(cudaMalloc(&c->d_hist, nbins * 8)); CU(cudaMalloc(&c->d_cursor, nbins * 8)); CU(cudaMalloc(&c->d_cstart, nbins * 8)); CU(cudaMalloc(&c->d_cend, nbins * 8));
         c->hist_cap = nbins;
     }
     if (!c->d_ovf) CU(cudaMalloc(&c->d_ovf, OVF_CAP * 16));
@@ -301,6 +302,12 @@ int pipeline_scratch(kq_ctx *c, uint64_t tuples, bool level2 = false, uint64_t t
         c->task_cap = tasks;
     }
     if (!c->d_hot) CU(cudaMalloc(&c->d_hot, (1 + 3 * (size_t)KQ_HOT_CAP) * 8));
+    if (!c->d_rstat) CU(cudaMalloc(&c->d_rstat, 3 * 8));
+    if (c->ovf2_cap < OVF_CAP) {
+        cudaFree(c->d_ovf2); c->d_ovf2 = nullptr; c->ovf2_cap = 0;
+        CU(cudaMalloc(&c->d_ovf2, OVF_CAP * 16));
+        c->ovf2_cap = OVF_CAP;
+    }
     if (!c->d_ntasks) { CU(cudaMalloc(&c->d_ntasks, sizeof(unsigned))); CU(cudaMalloc(&c->d_task_first, (KQ_MAX_COARSE + 2) * sizeof(unsigned))); }
     const uint64_t h2 = c->task_cap << c->cshift;                     // per-task histograms of the level-2 pass
     if (c->hist2_cap < h2) {
@@ -439,15 +446,36 @@ int run_batch(kq_ctx *c, Source src) {
     // level 2 + shared-memory insert when a slice fits one CTA's shared memory and its bins the scatter's
     const unsigned ns_max = 1u << c->cshift;
     const bool level2 = tuning().pipeline == 3 && tuning().smem_insert && c->slice_bits <= 13 && fine_pick_cap(ns_max, tw) != 0;
-    int rc = pipeline_scratch(c, bound, level2); if (rc) return rc;
+    // one-pass form (knob, off: measured no faster -- the scatter kernel takes 51.6 instead of 41.8 ms on C2, as much as
+    // the histogram pass it saves): the hash spreads the keys evenly, so every coarse bin gets a fixed region of its share
+    // + 3 % and no histogram pass is needed; chunks that do not fit (runs of one key) go to a list and are counted with L2 CAS
+    // (knob value 2: also for small batches and with almost no slack, so that tests reach the overflow paths)
+    const bool one_pass = level2 && (tuning().one_pass == 2 || (tuning().one_pass == 1 && bound >= (1ull << 24)));
+    // (an odd number of 64-byte units: region starts that are a large power of two apart would put the write streams of
+    // all bins on the same memory channels at the same time)
+    const uint64_t rcap = one_pass ? (((bound / ncoarse + bound / ncoarse / 32 + (tuning().one_pass == 2 ? 64 : 65536) + 15) & ~15ull) + 8) : 0;
+    int rc = pipeline_scratch(c, one_pass ? rcap * ncoarse : bound, level2, bound + (one_pass ? (uint64_t)ncoarse * 64 : 0)); if (rc) return rc;
     const int t3 = time_begin(c, 3);
-    CU(cudaMemsetAsync(c->d_hist, 0, (size_t)ncoarse * 8, c->stream));
-    CU(launch_slice_hist(c->stream, tv, src, c->d_hist, &c->launches));
-    CU(launch_slice_offsets(c->stream, ncoarse, c->d_hist, c->d_cursor, c->d_cstart, c->d_total,
-                            src.tuples ? nullptr : c->d_inst, &c->launches));
-    const int t5 = time_begin(c, 5);
-    CU(launch_slice_scatter(c->stream, tv, src, c->d_tuples, c->d_cursor, cap, &c->launches));
-    time_end(c, t5);
+    if (one_pass) {
+        CU(launch_region_init(c->stream, ncoarse, rcap, c->d_cursor, c->d_cstart, c->d_cend, c->d_rstat, &c->launches));
+        const int t5 = time_begin(c, 5);
+        // (overflow list: the level-2 output buffer, free until the level-2 scatter and as large as the batch)
+        CU(launch_slice_scatter(c->stream, tv, src, c->d_tuples, c->d_cursor, cap, &c->launches, Regions{rcap, c->d_tuples2, c->tup2_cap, c->d_rstat}));
+        time_end(c, t5);
+        // its tuples are counted with L2 CAS right away; the ones whose slice is full wait in the small list (stat[2])
+        CU(launch_insert_tuples(c->stream, tv, c->d_tuples2, c->d_rstat, std::max<uint64_t>(bound / 64, 4096), c->d_ovf2, c->ovf2_cap, c->d_rstat + 2,
+                                c->d_ticket, &c->launches, c->tup2_cap));
+        CU(launch_region_counts(c->stream, ncoarse, c->d_cursor, c->d_cstart, c->d_cend, c->d_hist, c->d_total, c->d_rstat,
+                                src.tuples ? nullptr : c->d_inst, &c->launches));
+    } else {
+        CU(cudaMemsetAsync(c->d_hist, 0, (size_t)ncoarse * 8, c->stream));
+        CU(launch_slice_hist(c->stream, tv, src, c->d_hist, &c->launches));
+        CU(launch_slice_offsets(c->stream, ncoarse, c->d_hist, c->d_cursor, c->d_cstart, c->d_total,
+                                src.tuples ? nullptr : c->d_inst, &c->launches));
+        const int t5 = time_begin(c, 5);
+        CU(launch_slice_scatter(c->stream, tv, src, c->d_tuples, c->d_cursor, cap, &c->launches));
+        time_end(c, t5);
+    }
     time_end(c, t3);
     if (!level2) {
         const int t2 = time_begin(c, 2);
@@ -458,10 +486,11 @@ int run_batch(kq_ctx *c, Source src) {
         return KQ_OK;
     }
     const int t4 = time_begin(c, 4);
-    const unsigned task_bound = (unsigned)std::min<uint64_t>(c->task_cap, bound / tuning().part + ncoarse + 1);
+    const unsigned task_bound = (unsigned)std::min<uint64_t>(c->task_cap, (bound + (uint64_t)ncoarse * 64) / tuning().part + ncoarse + 1);
     CU(launch_fine_plan(c->stream, tv, ncoarse, c->d_cstart, c->d_hist, tuning().part, c->d_tasks, task_bound, c->d_ntasks, c->d_task_first, &c->launches));
     CU(launch_fine_hist(c->stream, tv, c->d_tuples, c->d_tasks, c->d_ntasks, task_bound, ns_max, nullptr, c->d_hist2, &c->launches));
-    CU(launch_fine_offsets(c->stream, tv, ncoarse, c->d_cstart, c->d_task_first, c->d_hist2, ns_max, c->d_fstart, c->d_fhist, &c->launches));
+    // (one-pass form: the level-2 output is dense, bin b starts at the scan of the extents left in d_cursor)
+    CU(launch_fine_offsets(c->stream, tv, ncoarse, one_pass ? c->d_cursor : c->d_cstart, c->d_task_first, c->d_hist2, ns_max, c->d_fstart, c->d_fhist, &c->launches));
     const int t6 = time_begin(c, 6);
     CU(launch_fine_scatter(c->stream, tv, c->d_tuples, c->d_tasks, c->d_ntasks, task_bound, ns_max, c->d_tuples2, nullptr, c->d_hist2, c->d_fstart, &c->launches));
     time_end(c, t6);
@@ -470,6 +499,8 @@ int run_batch(kq_ctx *c, Source src) {
     // tuples of full slices go back into the level-1 buffer (free by now, as large as the batch)
     CU(launch_smem_insert(c->stream, tv, c->d_tuples2, c->d_fstart, c->d_fhist, 0, 1, c->d_tuples, c->tup_cap, c->d_ovf_n, c->d_ticket, &c->launches,
                           hot_list(c, bound)));
+    // tuples of the one-pass scatter's overflow list whose slice was full: same list, same counter as the insert above
+    if (one_pass) CU(launch_insert_tuples(c->stream, tv, c->d_ovf2, c->d_rstat + 2, 4096, c->d_tuples, c->tup_cap, c->d_ovf_n, c->d_ticket, &c->launches, c->ovf2_cap));
     time_end(c, t2);
     c->ovf_list = c->d_tuples; c->ovf_list_cap = c->tup_cap;
     c->ovf_pending = true;
@@ -626,7 +657,7 @@ extern "C" void kq_destroy(kq_ctx *c) {
     cudaFree(c->d_pb); cudaFree(c->d_pi); cudaFree(c->d_tuples); cudaFree(c->d_hist); cudaFree(c->d_cursor);
     cudaFree(c->d_tuples2); cudaFree(c->d_cstart); cudaFree(c->d_fhist); cudaFree(c->d_fcursor); cudaFree(c->d_fstart);
     cudaFree(c->d_tasks); cudaFree(c->d_ntasks); cudaFree(c->d_task_first); cudaFree(c->d_hist2); cudaFree(c->d_scur); cudaFree(c->d_ovf2);
-    cudaFree(c->d_total); cudaFree(c->d_nsrc); cudaFree(c->d_ticket); cudaFree(c->d_hot); cudaFree(c->d_ovf); cudaFree(c->d_ovf_n);
+    cudaFree(c->d_total); cudaFree(c->d_nsrc); cudaFree(c->d_ticket); cudaFree(c->d_hot); cudaFree(c->d_cend); cudaFree(c->d_rstat); cudaFree(c->d_ovf); cudaFree(c->d_ovf_n);
     for (void *p : c->ipc_opened) cudaIpcCloseMemHandle(p);
     for (void *p : c->peer_opened) cudaIpcCloseMemHandle(p);
     cudaFree(c->d_peers);
@@ -718,6 +749,7 @@ extern "C" int kq_set_tuning(const char *name, long long value) {
     else if (n == "db_host" && (value == 0 || value == 1)) t.db_host = (int)value;
     else if (n == "coarse_bias" && value >= 0 && value <= 4) t.coarse_bias = (int)value;
     else if (n == "db_ordered" && (value == 0 || value == 1)) t.db_ordered = (int)value;
+    else if (n == "one_pass" && value >= 0 && value <= 2) t.one_pass = (int)value;
     else if (n == "warp_insert" && (value == 0 || value == 1)) t.warp_insert = (int)value;
     else if (n == "s3_threads" && (value == 256 || value == 384 || value == 512)) t.s3_threads = (int)value;
     else if (n == "s3_ctas" && value >= 1 && value <= 8) t.s3_ctas = (int)value;
@@ -1529,14 +1561,20 @@ struct FileStage { char *buf = nullptr; cudaStream_t st = nullptr; int device = 
 constexpr size_t FILE_CHUNK = 32u << 20;
 constexpr uint64_t kDumpVersion = 0xFFFFFFFFFFFFFFF5ULL;              // SIZE_MAX - 10, phmap_dump.h:47-48
 FileStage *file_stage(int device) {
-    thread_local FileStage s;
-    if (s.device != device) {
-        if (cudaSetDevice(device) != cudaSuccess) return nullptr;
-        if (s.buf) { cudaFreeHost(s.buf); cudaStreamDestroy(s.st); s.buf = nullptr; }
-        if (cudaHostAlloc(&s.buf, FILE_CHUNK, cudaHostAllocDefault) != cudaSuccess) { s.buf = nullptr; return nullptr; }
-        if (cudaStreamCreateWithFlags(&s.st, cudaStreamNonBlocking) != cudaSuccess) { cudaFreeHost(s.buf); s.buf = nullptr; return nullptr; }
+    // one staging buffer per pool thread (portable: every GPU can copy to / from it) and one stream per GPU the thread
+    // has worked for -- a multi-GPU handle sends the same threads from shard to shard
+    constexpr int MAXDEV = 64;
+    thread_local char *buf = nullptr;
+    thread_local FileStage st[MAXDEV];
+    if (device < 0 || device >= MAXDEV) return nullptr;
+    if (cudaSetDevice(device) != cudaSuccess) return nullptr;
+    if (!buf && cudaHostAlloc(&buf, FILE_CHUNK, cudaHostAllocPortable) != cudaSuccess) { buf = nullptr; return nullptr; }
+    FileStage &s = st[device];
+    if (!s.st) {
+        if (cudaStreamCreateWithFlags(&s.st, cudaStreamNonBlocking) != cudaSuccess) { s.st = nullptr; return nullptr; }
         s.device = device;
     }
+    s.buf = buf;
     return &s;
 }
 

@@ -46,6 +46,7 @@ Tuning &tuning() {
         v.pipeline = (int)num("KQ_PIPELINE", 3); if (v.pipeline < 2 || v.pipeline > 4) v.pipeline = 3;
         v.cursor_stride = (int)num("KQ_CURSOR_STRIDE", 8); if (v.cursor_stride < 1 || v.cursor_stride > 32) v.cursor_stride = 8;
         v.warp_insert = (int)num("KQ_WARP_INSERT", 1);
+        v.one_pass = (int)num("KQ_ONE_PASS", 0); if (v.one_pass < 0 || v.one_pass > 2) v.one_pass = 0;
         v.db_ordered = (int)num("KQ_DB_ORDERED", 1);
         v.coarse_bias = (int)num("KQ_COARSE_BIAS", 0); if (v.coarse_bias < 0 || v.coarse_bias > 4) v.coarse_bias = 0;
         v.s3_threads = (int)num("KQ_S3_THREADS", 256); v.s3_ctas = (int)num("KQ_S3_CTAS", 3); if (v.s3_ctas < 1 || v.s3_ctas > 8) v.s3_ctas = 3;
@@ -343,17 +344,60 @@ route_offsets_kernel(RouteMap rt, int me, int cap, int tw, unsigned long long sl
 
 // ---- count, step 3: scatter into slice order -------------------------------------------------------------
 
-// Shared memory: nslices bins of `cap` tuples + one fill counter per bin.  A tuple is appended to its
-// bin with one shared-memory atomic; a bin that reaches `cap` entries is flushed by one warp as ONE
-// coalesced cap * 8 * TW byte store (256 B for cap = 32) at a position reserved with one global atomic
-// on the slice's cursor.  Random 256-byte stores run at ~5.4 TB/s on B200 (r01_gups_footprint_sweep.log).
-// Routed form (RT): bins are (owner rank, hash range) and a bin's tuples go to the receive slab of its owner
-// -- rt.out[owner], a peer-mapped pointer -- so the flush below IS the all-to-all: 64..256-byte stores
-// straight over NVLink, overlapped with the extraction of the next tuples.
-template <int TW, int R, int NT, bool RT>
+// One-pass form (no histogram pass): coarse bin b owns the fixed region [b * rcap, end[b]) of the output.  A chunk of n
+// tuples reserved at g that does not fit (a bin with more than its share + 3 %: runs of one key) goes to the overflow
+// list instead (position | KQ_REGION_OVF; the list is as large as the batch); what is left of the region in front of
+// it is filled with sentinel tuples (edge byte 0xFF), so [start, min(cursor, end)) is all tuples or sentinels.
+constexpr unsigned long long KQ_REGION_OVF = 1ULL << 63;
+template <int TW>
+__device__ __noinline__ unsigned long long region_miss(unsigned long long *stat, uint64_t *out, unsigned long long end, unsigned long long g, unsigned n) {
+    if (g < end) {
+        for (unsigned long long w = g * TW; w < end * TW; ++w) out[w] = ~0ULL;
+        atomicAdd(&stat[1], end - g);                                  // sentinels inside the region
+    }
+    return atomicAdd(&stat[0], (unsigned long long)n) | KQ_REGION_OVF;
+}
+template <int TW>
+__device__ __forceinline__ unsigned long long region_place(const Regions &rg, uint64_t *out, unsigned b, unsigned long long g, unsigned n) {
+    const unsigned long long end = (unsigned long long)(b + 1) * rg.rcap;   // (no load: the reservation's round trip is the critical path)
+    return g + n <= end ? g : region_miss<TW>(rg.stat, out, end, g, n);
+}
+
+// start / end / cursor of the fixed regions; hist (tuples per bin) and the totals once the scatter is done
+__global__ void region_init_kernel(unsigned nbins, unsigned long long rcap, unsigned long long *cursor, unsigned long long *start,
+                                   unsigned long long *end, unsigned long long *stat) {
+    const unsigned b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b == 0) { stat[0] = 0; stat[1] = 0; stat[2] = 0; }
+    if (b < nbins) { cursor[b] = start[b] = (unsigned long long)b * rcap; end[b] = (unsigned long long)(b + 1) * rcap; }
+}
+__global__ void __launch_bounds__(1024, 1)
+region_counts_kernel(unsigned nbins, unsigned long long *cursor, const unsigned long long *start, const unsigned long long *end,
+                     unsigned long long *hist, unsigned long long *total, const unsigned long long *stat, unsigned long long *instances) {
+    // hist[b] = extent of bin b (tuples + sentinels); cursor[b] becomes the exclusive scan of the extents: where the bin's
+    // tuples start in the level-2 output (the regions themselves are far apart)
+    __shared__ unsigned long long part[1024];
+    const unsigned per = (nbins + 1023) / 1024, b0 = threadIdx.x * per, b1 = min(nbins, b0 + per);
+    unsigned long long mine = 0;
+    for (unsigned b = b0; b < b1; ++b) { const unsigned long long n = min(cursor[b], end[b]) - start[b]; hist[b] = n; mine += n; }
+    part[threadIdx.x] = mine;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long run = 0;
+        for (int i = 0; i < 1024; ++i) { const unsigned long long v = part[i]; part[i] = run; run += v; }
+        *total = run;
+        if (instances) *instances += run - stat[1] + stat[0];
+    }
+    __syncthreads();
+    unsigned long long s = part[threadIdx.x];
+    for (unsigned b = b0; b < b1; ++b) { cursor[b] = s; s += hist[b]; }
+}
+
+// ---- count, step 3 (two-pass form) ---------------------------------------------------------------------------------
+
+template <int TW, int R, int NT, bool RT, bool OP = false>
 __global__ void __launch_bounds__(NT, 1)
 slice_scatter_kernel(TableView tv, Source src, uint64_t *__restrict__ out, unsigned long long *cursor, int cap, RouteMap rt,
-                     unsigned long long *back) {
+                     unsigned long long *back, Regions rg) {
     extern __shared__ uint64_t sm[];
     const unsigned P = bin_count<RT>(tv, rt);
     uint64_t *bins = sm;
@@ -392,6 +436,11 @@ slice_scatter_kernel(TableView tv, Source src, uint64_t *__restrict__ out, unsig
                 unsigned long long g = 0;
                 if (full) { g = atomicAdd(&cursor[b], (unsigned long long)cap); fill[b] = f - cap; }
                 unsigned todo = __ballot_sync(0xffffffffu, full);
+                if (OP) {                                            // (almost never: a chunk that does not fit its bin's region)
+                    const unsigned long long end = (unsigned long long)(b + 1) * rg.rcap;
+                    const bool miss = full && g + (unsigned)cap > end;
+                    if (__any_sync(0xffffffffu, miss) && miss) g = region_miss<TW>(rg.stat, out, end, g, (unsigned)cap);
+                }
                 // a bin is copied by min(32, words) lanes, so a warp moves 32 / that many full bins at a time
                 while (todo) {
                     const unsigned l = lpb == 32 ? (unsigned)__ffs(todo) - 1 : __fns(todo, 0, (int)sub + 1);   // the sub-th bin still to do
@@ -400,7 +449,7 @@ slice_scatter_kernel(TableView tv, Source src, uint64_t *__restrict__ out, unsig
                     const unsigned long long gg = __shfl_sync(0xffffffffu, g, l & 31u);
                     if (l < 32) {
                         const uint64_t *srcw = bins + (size_t)(b0 + l) * cap * TW;
-                        uint64_t *dst = (RT ? rt.out[(b0 + l) >> rt.nb_bits] : out) + gg * TW;
+                        uint64_t *dst = (RT ? rt.out[(b0 + l) >> rt.nb_bits] : (OP && (gg & KQ_REGION_OVF)) ? rg.ovf : out) + (OP ? gg & ~KQ_REGION_OVF : gg) * TW;
                         for (unsigned w = lane & (lpb - 1); w < (unsigned)cap * TW; w += lpb) __stcs(dst + w, srcw[w]);
                     }
                 }
@@ -422,14 +471,17 @@ slice_scatter_kernel(TableView tv, Source src, uint64_t *__restrict__ out, unsig
         const unsigned f = b < P ? fill[b] : 0;
         unsigned long long g = 0;
         // routed: what is left goes to the END of this rank's region of the bin, the aligned front is for full bins
-        if (f) g = RT ? atomicAdd(&back[b], 0ULL - f) - f : atomicAdd(&cursor[b], (unsigned long long)f);
+        if (f) {
+            g = RT ? atomicAdd(&back[b], 0ULL - f) - f : atomicAdd(&cursor[b], (unsigned long long)f);
+            if (OP) g = region_place<TW>(rg, out, b, g, f);
+        }
         unsigned todo = __ballot_sync(0xffffffffu, f != 0);
         while (todo) {
             const int l = __ffs(todo) - 1; todo &= todo - 1;
             const unsigned long long gg = __shfl_sync(0xffffffffu, g, l);
             const unsigned ff = __shfl_sync(0xffffffffu, f, l);
             const uint64_t *srcw = bins + (size_t)(b0 + l) * cap * TW;
-            uint64_t *dst = (RT ? rt.out[(b0 + l) >> rt.nb_bits] : out) + gg * TW;
+            uint64_t *dst = (RT ? rt.out[(b0 + l) >> rt.nb_bits] : (OP && (gg & KQ_REGION_OVF)) ? rg.ovf : out) + (OP ? gg & ~KQ_REGION_OVF : gg) * TW;
             for (unsigned w = lane; w < ff * TW; w += 32) __stcs(dst + w, srcw[w]);
         }
     }
@@ -548,11 +600,11 @@ constexpr int INS_TILE = TPB * 8;   // tuples per ticket
 template <int TW, int CPS>
 __global__ void __launch_bounds__(TPB, CPS)
 insert_tuples_kernel(TableView tv, const uint64_t *__restrict__ tuples, const unsigned long long *n_ptr,
-                     uint64_t *ovf, unsigned long long ovf_cap, unsigned long long *ovf_n, unsigned long long *ticket) {
+                     uint64_t *ovf, unsigned long long ovf_cap, unsigned long long *ovf_n, unsigned long long *ticket, unsigned long long n_cap) {
     __shared__ unsigned long long sh[2];
     if (threadIdx.x == 0) sh[0] = 0;
     unsigned long long fresh = 0;
-    const uint64_t n = *n_ptr;
+    const uint64_t n = min(*n_ptr, n_cap);                            // (a list that overflowed was flagged by its writer)
     for (;;) {
         __syncthreads();
         if (threadIdx.x == 0) sh[1] = atomicAdd(ticket, 1ULL);
@@ -569,7 +621,7 @@ insert_tuples_kernel(TableView tv, const uint64_t *__restrict__ tuples, const un
             const int st = insert_instance(tv, key, e);
             if (st < 0) {                                             // slice full: keep the tuple for after a grow
                 const unsigned long long j = atomicAdd(ovf_n, 1ULL);
-                if (j < ovf_cap) tuple_store<TW>(ovf, j, key, e);
+                if (j < ovf_cap) tuple_store<TW>(ovf, j, key, e); else atomicOr(tv.err, 1);
             } else fresh += st;
         }
     }
@@ -871,7 +923,7 @@ cudaError_t launch_route_scatter(cudaStream_t st, const TableView &tv, const Sou
         e = cudaFuncSetAttribute(slice_scatter_kernel<TWV, RV, NTV, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
         if (e != cudaSuccess) return e;                                                                             \
         const unsigned grid = std::min<uint64_t>((n + NTV * RV - 1) / (NTV * RV), (uint64_t)sm_count());           \
-        slice_scatter_kernel<TWV, RV, NTV, true><<<grid, NTV, smem, st>>>(v, src, nullptr, cursor, cap, rt, back); } while (0)
+        slice_scatter_kernel<TWV, RV, NTV, true><<<grid, NTV, smem, st>>>(v, src, nullptr, cursor, cap, rt, back, Regions{0, nullptr, 0, nullptr}); } while (0)
     const int variant = tuning().rt_variant;
     if (tw == 1) {
         if (variant == 1) KQ_ROUTE_LAUNCH(1, 8, 1024);
@@ -892,19 +944,33 @@ cudaError_t launch_slice_offsets(cudaStream_t st, unsigned long long nslices, co
     return cudaGetLastError();
 }
 
+cudaError_t launch_region_init(cudaStream_t st, unsigned nbins, unsigned long long rcap, unsigned long long *cursor,
+                               unsigned long long *start, unsigned long long *end, unsigned long long *stat, uint64_t *launches) {
+    region_init_kernel<<<(nbins + 255) / 256, 256, 0, st>>>(nbins, rcap, cursor, start, end, stat);
+    ++*launches;
+    return cudaGetLastError();
+}
+cudaError_t launch_region_counts(cudaStream_t st, unsigned nbins, unsigned long long *cursor, const unsigned long long *start,
+                                 const unsigned long long *end, unsigned long long *hist, unsigned long long *total,
+                                 const unsigned long long *stat, unsigned long long *instances, uint64_t *launches) {
+    region_counts_kernel<<<1, 1024, 0, st>>>(nbins, cursor, start, end, hist, total, stat, instances);
+    ++*launches;
+    return cudaGetLastError();
+}
+
 cudaError_t launch_slice_scatter(cudaStream_t st, const TableView &tv, const Source &src, uint64_t *out,
-                                 unsigned long long *cursor, int cap, uint64_t *launches) {
+                                 unsigned long long *cursor, int cap, uint64_t *launches, Regions rg) {
     const uint64_t n = source_bound(src);
     if (!n) return cudaSuccess;
     const int tw = tuple_words(tv.k);
-    if (tuning().scatter_direct) {
+    if (tuning().scatter_direct && !rg.rcap) {
         const unsigned g = std::min<uint64_t>((n + TPB * RUN - 1) / (TPB * RUN), (uint64_t)sm_count() * 4);
         KQ_TW_DISPATCH(tw, (slice_scatter_direct_kernel<TW><<<g, TPB, 0, st>>>(tv, src, out, cursor)));
         ++*launches;
         return cudaGetLastError();
     }
     const int variant = tuning().sc_variant;
-    if (variant == 5) {
+    if (variant == 5 && !rg.rcap) {
         // ring form (measured slower than the two-pass form at one CTA per SM: 51.8 vs 31.6 ms on C2, the global
         // reservation of every flush round is on the critical path): bins of 3/2 cap tuples + two counters; the largest chunk of 64 / 32 / 16 / 8 tuples that fits
         static int max_smem = 0;
@@ -934,8 +1000,11 @@ cudaError_t launch_slice_scatter(cudaStream_t st, const TableView &tv, const Sou
 #define KQ_SCATTER_LAUNCH(TWV, RV, NTV) do {                                                                        \
         e = cudaFuncSetAttribute(slice_scatter_kernel<TWV, RV, NTV, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
         if (e != cudaSuccess) return e;                                                                             \
+        e = cudaFuncSetAttribute(slice_scatter_kernel<TWV, RV, NTV, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+        if (e != cudaSuccess) return e;                                                                             \
         const unsigned grid = std::min<uint64_t>((n + NTV * RV - 1) / (NTV * RV), (uint64_t)sm_count());           \
-        slice_scatter_kernel<TWV, RV, NTV, false><<<grid, NTV, smem, st>>>(tv, src, out, cursor, cap, RouteMap{}, nullptr); } while (0)
+        if (rg.rcap) slice_scatter_kernel<TWV, RV, NTV, false, true><<<grid, NTV, smem, st>>>(tv, src, out, cursor, cap, RouteMap{}, nullptr, rg); \
+        else slice_scatter_kernel<TWV, RV, NTV, false><<<grid, NTV, smem, st>>>(tv, src, out, cursor, cap, RouteMap{}, nullptr, rg); } while (0)
     if (tw == 1) {                                                   // the two-pass form (sc_variant 1..4)
         if (variant == 1) KQ_SCATTER_LAUNCH(1, 8, 512);
         else if (variant == 2) KQ_SCATTER_LAUNCH(1, 8, 1024);
@@ -951,7 +1020,7 @@ cudaError_t launch_slice_scatter(cudaStream_t st, const TableView &tv, const Sou
 cudaError_t launch_insert_tuples(cudaStream_t st, const TableView &tv, const uint64_t *tuples,
                                  const unsigned long long *n, uint64_t n_max, uint64_t *ovf,
                                  unsigned long long ovf_cap, unsigned long long *ovf_n, unsigned long long *ticket,
-                                 uint64_t *launches) {
+                                 uint64_t *launches, uint64_t n_cap) {
     if (!n_max) return cudaSuccess;
     cudaError_t e = cudaMemsetAsync(ticket, 0, sizeof(unsigned long long), st);
     if (e != cudaSuccess) return e;
@@ -959,8 +1028,8 @@ cudaError_t launch_insert_tuples(cudaStream_t st, const TableView &tv, const uin
     // L2 round trips and its rate follows the warps in flight (3/4/5/6/7/8 CTAs: 125/101/86/76/70/67 ms on C2)
     const int ctas = tuning().insert_ctas;
     const unsigned grid = (unsigned)std::min<uint64_t>((n_max + INS_TILE - 1) / INS_TILE, (uint64_t)sm_count() * ctas);
-    if (ctas > CTAS_PER_SM) KQ_TW_DISPATCH(tuple_words(tv.k), (insert_tuples_kernel<TW, 8><<<grid, TPB, 0, st>>>(tv, tuples, n, ovf, ovf_cap, ovf_n, ticket)));
-    else KQ_TW_DISPATCH(tuple_words(tv.k), (insert_tuples_kernel<TW, CTAS_PER_SM><<<grid, TPB, 0, st>>>(tv, tuples, n, ovf, ovf_cap, ovf_n, ticket)));
+    if (ctas > CTAS_PER_SM) KQ_TW_DISPATCH(tuple_words(tv.k), (insert_tuples_kernel<TW, 8><<<grid, TPB, 0, st>>>(tv, tuples, n, ovf, ovf_cap, ovf_n, ticket, n_cap ? n_cap : n_max)));
+    else KQ_TW_DISPATCH(tuple_words(tv.k), (insert_tuples_kernel<TW, CTAS_PER_SM><<<grid, TPB, 0, st>>>(tv, tuples, n, ovf, ovf_cap, ovf_n, ticket, n_cap ? n_cap : n_max)));
     ++*launches;
     return cudaGetLastError();
 }

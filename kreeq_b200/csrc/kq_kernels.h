@@ -73,6 +73,7 @@ struct Tuning {
     int db_host;               // .kreeq codec on the host (cross-check of the device codec)
     int coarse_bias;           // level-1 bins: 2^v times fewer (and larger) than the square-root split
     int db_ordered;            // 1 = databases are decoded into table order before they are put / merged
+    int one_pass;              // 1 = level-1 scatter into fixed regions, no histogram pass (overflow -> list)
     int warp_insert;           // 1 = slices of at most 2^10 slots are counted by one warp each (no shared-memory atomics)
     int s3_threads, s3_ctas;   // shared-memory insert: threads per CTA (256 / 384 / 512), CTAs per SM in the grid
     int fs_variant;            // level-2 scatter: 0 auto (two CTAs per SM when the bins allow), 1 one CTA, 2 two CTAs
@@ -107,14 +108,22 @@ cudaError_t launch_slice_offsets(cudaStream_t st, unsigned long long nbins, cons
                                  unsigned long long *cursor, unsigned long long *start, unsigned long long *total,
                                  unsigned long long *instances, uint64_t *launches);
 // 3. scatter tuples into slice order (out holds *total tuples afterwards)
+// one-pass level-1 scatter: fixed region ends per coarse bin; `ovf` = list for the chunks that do not fit (as large as
+// the batch); stat[0] = tuples in that list, stat[1] = sentinels written into regions, stat[2] = free for the caller
+struct Regions { unsigned long long rcap; uint64_t *ovf; unsigned long long ovf_cap; unsigned long long *stat; };   // rcap = 0: exact layout
+cudaError_t launch_region_init(cudaStream_t st, unsigned nbins, unsigned long long rcap, unsigned long long *cursor,
+                               unsigned long long *start, unsigned long long *end, unsigned long long *stat, uint64_t *launches);
+cudaError_t launch_region_counts(cudaStream_t st, unsigned nbins, unsigned long long *cursor, const unsigned long long *start,
+                                 const unsigned long long *end, unsigned long long *hist, unsigned long long *total,
+                                 const unsigned long long *stat, unsigned long long *instances, uint64_t *launches);
 cudaError_t launch_slice_scatter(cudaStream_t st, const TableView &tv, const Source &src, uint64_t *out,
-                                 unsigned long long *cursor, int cap, uint64_t *launches);
+                                 unsigned long long *cursor, int cap, uint64_t *launches, Regions rg = Regions{0, nullptr, 0, nullptr});
 // 4. insert slice-ordered tuples; tuples whose slice is full are appended to ovf (capacity ovf_cap,
 //    ovf_n counts every failure, also those that did not fit)
 cudaError_t launch_insert_tuples(cudaStream_t st, const TableView &tv, const uint64_t *tuples,
                                  const unsigned long long *n, uint64_t n_max, uint64_t *ovf,
                                  unsigned long long ovf_cap, unsigned long long *ovf_n, unsigned long long *ticket,
-                                 uint64_t *launches);
+                                 uint64_t *launches, uint64_t n_cap = 0);
 // ---- level 2 + shared-memory insert (kq_count3.cu) --------------------------------------------------------
 // bins of the level-1 scatter: 2^cshift consecutive slices each
 inline unsigned coarse_bins(const TableView &tv) { return (unsigned)(((tv.nslices - 1) >> tv.cshift) + 1); }

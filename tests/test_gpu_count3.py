@@ -22,7 +22,7 @@ def tuned():
     """set knobs for one test, restore the defaults afterwards"""
     from kreeq_b200._lib import lib
     L = lib()
-    defaults = {"single_slice_bits": 21, "piece_bits": 9, "fine_part": 1 << 18, "smem_insert": 1, "direct_pct": 25, "warp_insert": 1}
+    defaults = {"single_slice_bits": 21, "piece_bits": 9, "fine_part": 1 << 18, "smem_insert": 1, "direct_pct": 25, "warp_insert": 1, "one_pass": 0}
 
     def set_(**kw):
         for n, v in kw.items():
@@ -79,6 +79,19 @@ def test_small_slices_wrong_hint(mods, tuned):
     genome = random_genome(rng, 400_000)
     batch = sample_reads(rng, genome, 12_000, 150, err=0.01)
     _run(kb, ko, 21, [batch], 60_000)           # ~0.75 M distinct arrive
+
+
+@pytest.mark.parametrize("k,piece", [(21, 8), (31, 9)])
+def test_one_pass_level1_with_overflowing_regions(mods, tuned, k, piece):
+    """one_pass = 2: level-1 scatter into fixed regions with (almost) no slack: many coarse bins overflow, their chunks
+    are counted directly by the scatter kernel, region tails are filled with sentinels; plus runs of one key"""
+    kb, ko = mods
+    tuned(single_slice_bits=8, piece_bits=piece, fine_part=2048, direct_pct=0, one_pass=2)
+    rng = np.random.default_rng(31 + k)
+    genome = random_genome(rng, 150_000)
+    batches = [sample_reads(rng, genome, 7000, 150, err=0.01, n_rate=0.001) + (b"A" * 3000 + b"N") * 4,
+               sample_reads(rng, genome, 3000, 150, err=0.02)]
+    _run(kb, ko, k, batches, 900_000, genome.tobytes())
 
 
 def test_cta_owned_slices_still_available(mods, tuned):
