@@ -421,7 +421,7 @@ template <int TW, int NT>
 __global__ void __launch_bounds__(NT, 3)
 smem_insert_kernel(TableView tv, const uint64_t *__restrict__ tuples, const unsigned long long *__restrict__ fstart,
                    const void *__restrict__ fcount_, unsigned long long cap, int stride, uint64_t *ovf,
-                   unsigned long long ovf_cap, unsigned long long *ovf_n, unsigned long long *ticket) {
+                   unsigned long long ovf_cap, unsigned long long *ovf_n, unsigned long long *ticket, HotList hot) {
     const unsigned long long *fcount = static_cast<const unsigned long long *>(fcount_);     // level-2 layout: exact counts
     const unsigned *fcur = static_cast<const unsigned *>(fcount_);                             // one-pass layout: 32-bit cursors
     extern __shared__ __align__(128) unsigned char sm_piece[];
@@ -442,8 +442,17 @@ smem_insert_kernel(TableView tv, const uint64_t *__restrict__ tuples, const unsi
         if (threadIdx.x == 0) {
             // next slice that has tuples (the counts are read by one thread: most slices of a small batch are empty)
             unsigned long long s, cnt = 0;
-            for (;;) { s = atomicAdd(ticket, 1ULL); if (s >= tv.nslices) break; cnt = fstart ? fcount[s] : fcur[s * stride]; if (cnt) break; }
-            sh_ticket = s; sh_n = fstart ? cnt : min(cnt, cap);
+            for (;;) {
+                s = atomicAdd(ticket, 1ULL); if (s >= tv.nslices) break;
+                cnt = fstart ? fcount[s] : min((unsigned long long)fcur[s * stride], cap);
+                if (!cnt) continue;
+                if (hot.buf && cnt > hot.limit) {                       // a run of one key: left to hot_slices_kernel (all SMs)
+                    const unsigned long long j = atomicAdd(&hot.buf[0], 1ULL);
+                    if (j < hot.cap) { hot.buf[1 + 3 * j] = fstart ? fstart[s] : s * cap; hot.buf[2 + 3 * j] = cnt; hot.buf[3 + 3 * j] = s; continue; }
+                }
+                break;
+            }
+            sh_ticket = s; sh_n = cnt;
             if (s < tv.nslices) {
                 mbar_expect_tx(&bar, bytes); bulk_g2s(piece, tv.T + (s << tv.slice_bits), bytes, &bar);
                 // the slice's tuples start their way into L2 now (one instruction for the whole range)
@@ -886,12 +895,18 @@ cudaError_t launch_smem_insert(cudaStream_t st, const TableView &tv, const uint6
         e = cudaFuncSetAttribute(smem_insert_kernel<TWV, NTV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
         if (e != cudaSuccess) return e;                                                                                \
         cudaFuncSetAttribute(smem_insert_kernel<TWV, NTV>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared); \
-        smem_insert_kernel<TWV, NTV><<<grid, NTV, smem, st>>>(tv, tuples, fstart, fcount, cap, stride, ovf, ovf_cap, ovf_n, ticket); } while (0)
+        smem_insert_kernel<TWV, NTV><<<grid, NTV, smem, st>>>(tv, tuples, fstart, fcount, cap, stride, ovf, ovf_cap, ovf_n, ticket, hot); } while (0)
+    if (hot.buf) { e = cudaMemsetAsync(hot.buf, 0, sizeof(unsigned long long), st); if (e != cudaSuccess) return e; }
     const int nt = tuning().s3_threads;
     if (tuple_words(tv.k) == 1) { if (nt == 256) KQ_SI_LAUNCH(1, 256); else if (nt == 384) KQ_SI_LAUNCH(1, 384); else KQ_SI_LAUNCH(1, 512); }
     else { if (nt == 256) KQ_SI_LAUNCH(2, 256); else if (nt == 384) KQ_SI_LAUNCH(2, 384); else KQ_SI_LAUNCH(2, 512); }
 #undef KQ_SI_LAUNCH
     ++*launches;
+    if (hot.buf) {
+        if (tuple_words(tv.k) == 1) hot_slices_kernel<1><<<(unsigned)sm_count() * 4, 256, 0, st>>>(tv, tuples, hot, ovf, ovf_cap, ovf_n);
+        else hot_slices_kernel<2><<<(unsigned)sm_count() * 4, 256, 0, st>>>(tv, tuples, hot, ovf, ovf_cap, ovf_n);
+        ++*launches;
+    }
     return cudaGetLastError();
 }
 

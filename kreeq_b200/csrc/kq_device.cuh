@@ -24,7 +24,7 @@ constexpr uint32_t KQ_LANE_MAX = 127u;         // a slot lane counts to 127, the
 constexpr uint32_t KQ_REM_FLOOR = 64u;         // counted slots that own a remainder never drop below this coverage
 constexpr uint32_t KQ_LARGEST = 4294967295u;   // LARGEST, include/kreeq.h:68
 constexpr int KQ_MAX_SLICE_BITS = 21;          // a table of up to 2^21 slots (32 MiB, L2 resident) is ONE slice
-constexpr int KQ_PIECE_BITS = 9;               // larger tables: slices of 2^9 slots = 8 KiB, counted into by ONE warp (up to 2^12: one CTA)
+constexpr int KQ_PIECE_BITS = 12;              // larger tables: slices of 2^12 slots = 64 KiB, one CTA's shared memory (measured best; 2^9: one warp each)
 constexpr int KQ_MAX_COARSE = 4096;            // bins of the level-1 scatter at most
 
 constexpr unsigned long long CNT_PLACEHOLDER = 1ull << 63;

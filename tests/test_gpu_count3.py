@@ -22,7 +22,7 @@ def tuned():
     """set knobs for one test, restore the defaults afterwards"""
     from kreeq_b200._lib import lib
     L = lib()
-    defaults = {"single_slice_bits": 21, "piece_bits": 9, "fine_part": 1 << 18, "smem_insert": 1, "direct_pct": 25, "warp_insert": 1, "one_pass": 0}
+    defaults = {"single_slice_bits": 21, "piece_bits": 12, "fine_part": 1 << 18, "smem_insert": 1, "direct_pct": 25, "warp_insert": 1, "one_pass": 0}
 
     def set_(**kw):
         for n, v in kw.items():
