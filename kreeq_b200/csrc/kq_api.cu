@@ -750,6 +750,7 @@ extern "C" int kq_set_tuning(const char *name, long long value) {
     else if (n == "coarse_bias" && value >= 0 && value <= 4) t.coarse_bias = (int)value;
     else if (n == "db_ordered" && (value == 0 || value == 1)) t.db_ordered = (int)value;
     else if (n == "one_pass" && value >= 0 && value <= 2) t.one_pass = (int)value;
+    else if (n == "cta_lock" && (value == 0 || value == 1)) t.cta_lock = (int)value;
     else if (n == "warp_insert" && (value == 0 || value == 1)) t.warp_insert = (int)value;
     else if (n == "s3_threads" && (value == 256 || value == 384 || value == 512)) t.s3_threads = (int)value;
     else if (n == "s3_ctas" && value >= 1 && value <= 8) t.s3_ctas = (int)value;

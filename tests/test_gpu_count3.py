@@ -22,7 +22,7 @@ def tuned():
     """set knobs for one test, restore the defaults afterwards"""
     from kreeq_b200._lib import lib
     L = lib()
-    defaults = {"single_slice_bits": 21, "piece_bits": 12, "fine_part": 1 << 18, "smem_insert": 1, "direct_pct": 25, "warp_insert": 1, "one_pass": 0}
+    defaults = {"single_slice_bits": 21, "piece_bits": 12, "fine_part": 1 << 18, "smem_insert": 1, "direct_pct": 25, "warp_insert": 1, "one_pass": 0, "cta_lock": 0}
 
     def set_(**kw):
         for n, v in kw.items():
@@ -94,10 +94,11 @@ def test_one_pass_level1_with_overflowing_regions(mods, tuned, k, piece):
     _run(kb, ko, k, batches, 900_000, genome.tobytes())
 
 
-def test_cta_owned_slices_still_available(mods, tuned):
-    """warp_insert = 0: small slices counted by the CTA-owned kernel (shared-memory CAS)"""
+@pytest.mark.parametrize("cta_lock", [1, 0])
+def test_cta_owned_slices(mods, tuned, cta_lock):
+    """warp_insert = 0: small slices counted by the CTA-owned kernels (lock bytes + barriers / shared-memory CAS)"""
     kb, ko = mods
-    tuned(single_slice_bits=8, piece_bits=8, fine_part=2048, direct_pct=0, warp_insert=0)
+    tuned(single_slice_bits=8, piece_bits=8, fine_part=2048, direct_pct=0, warp_insert=0, cta_lock=cta_lock)
     rng = np.random.default_rng(78)
     genome = random_genome(rng, 100_000)
     batch = (b"A" * 400 + b"N") * 3 + sample_reads(rng, genome, 5000, 150, err=0.01)
