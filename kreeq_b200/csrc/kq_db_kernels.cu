@@ -237,7 +237,7 @@ db_count_big_kernel(const XRec *__restrict__ xs, unsigned long long n, unsigned 
         for (int w = 0; w < 4; ++w) mx = max(mx, max(x.r.fw[w], x.r.bw[w]));
         mine += mx > KQ_LANE_MAX || (x.flags & F_PLACEHOLDER);
     }
-    mine = __reduce_add_sync(0xffffffffu, (unsigned)mine);
+    for (int o = 16; o; o >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, o);   // 64-bit: a thread may carry more than 2^32
     if ((threadIdx.x & 31) == 0 && mine) atomicAdd(out, mine);
 }
 

@@ -74,7 +74,7 @@ static inline unsigned grid_for(uint64_t n, int per_thread = 1) {
 
 // block-wide sum of per-thread counters (< 2^32 per thread), one global atomic per CTA
 __device__ __forceinline__ void block_add(unsigned long long v, unsigned long long *dst, unsigned long long *sh) {
-    v = __reduce_add_sync(0xffffffffu, (unsigned)v);
+    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);   // 64-bit: a thread may carry more than 2^32
     if ((threadIdx.x & 31) == 0 && v) atomicAdd(sh, v);
     __syncthreads();
     if (threadIdx.x == 0 && *sh) atomicAdd(dst, *sh);
@@ -204,7 +204,7 @@ count_direct_kernel(TableView tv, Source src, unsigned long long *instances,
 template <int TW>
 __global__ void __launch_bounds__(TPB, 4)
 scatter_fine_kernel(TableView tv, Source src, uint64_t *__restrict__ out, unsigned cap, unsigned *cursor,
-                    int stride, unsigned long long *instances, uint64_t *ovf, unsigned long long ovf_cap, unsigned long long *ovf_n, int experiment) {
+                    int stride, unsigned long long *instances, uint64_t *ovf, unsigned long long ovf_cap, unsigned long long *ovf_n) {
     __shared__ unsigned long long sh[2];
     if (threadIdx.x < 2) sh[threadIdx.x] = 0;
     __syncthreads();
@@ -220,7 +220,6 @@ scatter_fine_kernel(TableView tv, Source src, uint64_t *__restrict__ out, unsign
             if ((m >> i & 1u) && e[i] == 255u) m &= ~(1u << i);             // padding of the routed layout
             const unsigned live = m >> i & 1u;
             sl[i] = live ? (unsigned)slice_of_key(key[i], tv.nslices) : 0u;
-            if (experiment == 2) { at[i] = (unsigned)(key[i] * 2654435761u) % (cap ? cap : 1u); continue; }   // timing experiment: no atomics
             asm volatile("{\n .reg .pred q;\n setp.ne.u32 q, %2, 0;\n mov.u32 %0, 0;\n"
                          " @q atom.relaxed.gpu.global.add.u32 %0, [%1], 1;\n}"
                          : "=r"(at[i]) : "l"(cursor + (size_t)sl[i] * stride), "r"(live) : "memory");
@@ -229,7 +228,6 @@ scatter_fine_kernel(TableView tv, Source src, uint64_t *__restrict__ out, unsign
         for (int i = 0; i < RUN; ++i) {
             if (!(m >> i & 1u)) continue;
             ++inst;
-            if (experiment == 1) continue;                                     // timing experiment: no stores
             if (at[i] < cap) { tuple_store<TW>(out, (uint64_t)sl[i] * cap + at[i], key[i], e[i]); continue; }
             const int r = insert_instance(tv, key[i], e[i]);                // over-subscribed slice: count it now
             if (r < 0) {
@@ -871,8 +869,7 @@ cudaError_t launch_scatter_fine(cudaStream_t st, const TableView &tv, const Sour
     const uint64_t n = source_bound(src);
     if (!n) return cudaSuccess;
     const unsigned grid = std::min<uint64_t>((n + TPB * RUN - 1) / (TPB * RUN), (uint64_t)sm_count() * 4);
-    static const int experiment = [] { const char *e = std::getenv("KQ_K1_EXPERIMENT"); return e ? std::atoi(e) : 0; }();   // timing experiments only (results are wrong)
-    KQ_TW_DISPATCH(tuple_words(tv.k), (scatter_fine_kernel<TW><<<grid, TPB, 0, st>>>(tv, src, out, cap, cursor, stride, instances, ovf, ovf_cap, ovf_n, experiment)));
+    KQ_TW_DISPATCH(tuple_words(tv.k), (scatter_fine_kernel<TW><<<grid, TPB, 0, st>>>(tv, src, out, cap, cursor, stride, instances, ovf, ovf_cap, ovf_n)));
     ++*launches;
     return cudaGetLastError();
 }

@@ -18,7 +18,7 @@ static inline unsigned grid_for(uint64_t n) {
 }
 
 __device__ __forceinline__ void block_add(unsigned long long v, unsigned long long *dst, unsigned long long *sh) {
-    v = __reduce_add_sync(0xffffffffu, (unsigned)v);
+    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);   // 64-bit: a thread may carry more than 2^32
     if ((threadIdx.x & 31) == 0 && v) atomicAdd(sh, v);
     __syncthreads();
     if (threadIdx.x == 0 && *sh) atomicAdd(dst, *sh);

@@ -106,8 +106,11 @@ class RoutedCounter:
             recv_counts = exchange_counts(self.counts)
             sc = self.counts.cpu().numpy()
             rc = recv_counts.cpu().numpy()
-            if sc.max() > self.cap or rc.sum() > self.recv.shape[0]:
-                raise RuntimeError("route buffers too small: %s > %d" % (sc, self.cap))
+            # the verdict is collective: a rank that raised alone would leave the others waiting in the exchange
+            bad = torch.tensor([1 if (sc.max() > self.cap or rc.sum() > self.recv.shape[0]) else 0], dtype=torch.int32, device=self.counts.device)
+            dist.all_reduce(bad, op=dist.ReduceOp.MAX, group=getattr(self, "group", None))
+            if int(bad.item()):
+                raise RuntimeError("route buffers too small on some rank (here: %s against %d per peer)" % (sc, self.cap))
             nrecv = exchange_tuples(self.send, sc, rc, self.recv)
             self.a2a_bytes += (int(sc.sum()) - int(sc[self.rank])) * self.tb
             check(L.kq_dev_insert_tuples(g.handle, C.c_void_p(self.recv.data_ptr()), nrecv), g.handle)
