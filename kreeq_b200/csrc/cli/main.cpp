@@ -353,6 +353,8 @@ int run_validate(Options &o) {                    // Input::read case 0, src/inp
         if (kdb < 1) { fprintf(stderr, "Cannot load DBG input. Exiting.\n"); return EXIT_FAILURE; }
         if (o.k_given && o.k != kdb)
             fprintf(stderr, "Warning: -k %d ignored, database was built with k=%d.\n", o.k, kdb);
+        else if (!o.k_given && kdb != 21)   // the reference constructs its DBG before it reads the database's k (src/input.cpp:88 vs :100)
+            fprintf(stderr, "Note: database k=%d is used; the reference would validate with its default k=21 unless -k %d is given.\n", kdb, kdb);
         k_used = kdb;
         if (create(&ctx, kdb, o) != KQ_OK) die(nullptr, 0);
         CHECK(ctx, kq_multi_db_load(ctx, o.dbs[0].c_str()));

@@ -309,7 +309,7 @@ int pipeline_scratch(kq_ctx *c, uint64_t tuples, bool level2 = false, uint64_t t
         c->ovf2_cap = OVF_CAP;
     }
     if (!c->d_ntasks) { CU(cudaMalloc(&c->d_ntasks, sizeof(unsigned))); CU(cudaMalloc(&c->d_task_first, (KQ_MAX_COARSE + 2) * sizeof(unsigned))); }
-    const uint64_t h2 = c->task_cap << c->cshift;                     // per-task histograms of the level-2 pass
+    const uint64_t h2 = c->task_cap * std::max<uint64_t>(1ull << c->cshift, c->route_ns_max);   // per-task histograms of the level-2 pass
     if (c->hist2_cap < h2) {
         cudaFree(c->d_hist2); c->d_hist2 = nullptr; c->hist2_cap = 0;
         CU(cudaMalloc(&c->d_hist2, h2 * sizeof(unsigned)));
@@ -411,11 +411,12 @@ int run_batch(kq_ctx *c, Source src) {
         fine_pick_cap(c->route_ns_max, tw) != 0) {
         int rc = pipeline_scratch(c, 0, true, bound); if (rc) return rc;
         const int t4 = time_begin(c, 4);
-        CU(cudaMemsetAsync(c->d_fhist, 0, c->nslices * 8, c->stream));
-        CU(launch_fine_hist(c->stream, tv, src.tuples, c->d_tasks, c->d_ntasks, c->route_task_bound, c->route_ns_max, c->d_fhist, nullptr, &c->launches));
+        // per-task histograms -> private cursors, as in the local pipeline (a slice may lie across two bins of the slab)
+        CU(launch_fine_hist(c->stream, tv, src.tuples, c->d_tasks, c->d_ntasks, c->route_task_bound, c->route_ns_max, nullptr, c->d_hist2, &c->launches));
+        CU(launch_route_fine_offsets(c->stream, tv, c->route.nb_bits, c->d_tasks, c->d_task_first, c->d_hist2, c->route_ns_max, c->d_fhist, &c->launches));
         CU(launch_slice_offsets(c->stream, c->nslices, c->d_fhist, c->d_fcursor, c->d_fstart, c->d_total, nullptr, &c->launches));
         const int t6 = time_begin(c, 6);
-        CU(launch_fine_scatter(c->stream, tv, src.tuples, c->d_tasks, c->d_ntasks, c->route_task_bound, c->route_ns_max, c->d_tuples2, c->d_fcursor, nullptr, nullptr, &c->launches));
+        CU(launch_fine_scatter(c->stream, tv, src.tuples, c->d_tasks, c->d_ntasks, c->route_task_bound, c->route_ns_max, c->d_tuples2, nullptr, c->d_hist2, c->d_fstart, &c->launches));
         time_end(c, t6);
         time_end(c, t4);
         const int t2 = time_begin(c, 2);
@@ -991,7 +992,7 @@ extern "C" int kq_route_scatter(kq_ctx *c, const uint64_t *d_bases, const uint64
         c->route_ns_max = (unsigned)(c->nslices / nb + 2);
         int rc = pipeline_scratch(c, 0, true, totals[c->rank]); if (rc) return rc;
         const unsigned bound = (unsigned)std::min<uint64_t>(c->task_cap, totals[c->rank] / tuning().part + nb + 1);
-        CU(launch_route_plan(c->stream, view(c), c->route, c->rank, cap, d_all_hist, tuning().part, c->d_tasks, bound, c->d_ntasks, &c->launches));
+        CU(launch_route_plan(c->stream, view(c), c->route, c->rank, cap, d_all_hist, tuning().part, c->d_tasks, bound, c->d_ntasks, c->d_task_first, &c->launches));
         c->route_task_bound = bound; c->route_extent = totals[c->rank];
     }
     c->route_real = totals[c->nranks + c->rank];

@@ -82,7 +82,7 @@ fine_plan_kernel(TableView tv, unsigned ncoarse, const unsigned long long *start
 // local table whatever its geometry: one task = at most `part` consecutive tuples of one bin's extent.
 __global__ void __launch_bounds__(1024, 1)
 route_plan_kernel(TableView tv, int nranks, int nb_bits, int me, int cap, const unsigned long long *H,
-                  unsigned long long part, FineTask *tasks, unsigned task_cap, unsigned *ntasks) {
+                  unsigned long long part, FineTask *tasks, unsigned task_cap, unsigned *ntasks, unsigned *task_first) {
     __shared__ unsigned long long ext[KQ_ROUTE_PLAN_BINS + 1];
     __shared__ unsigned first[KQ_ROUTE_PLAN_BINS + 1];
     const unsigned nb = 1u << nb_bits, P = (unsigned)nranks * nb;
@@ -100,6 +100,7 @@ route_plan_kernel(TableView tv, int nranks, int nb_bits, int me, int cap, const 
         *ntasks = t < task_cap ? t : task_cap;
     }
     __syncthreads();
+    for (unsigned j = threadIdx.x; j <= nb; j += 1024) task_first[j] = first[j] < task_cap ? first[j] : task_cap;
     for (unsigned j = threadIdx.x; j < nb; j += 1024) {
         const unsigned long long lo = ext[j], hi = ext[j + 1];
         const unsigned long long h_lo = (unsigned long long)j << (32 - nb_bits), h_hi = (((unsigned long long)j + 1) << (32 - nb_bits)) - 1;
@@ -169,6 +170,29 @@ fine_offsets_kernel(TableView tv, const unsigned long long *__restrict__ start, 
     }
     __syncthreads();
     for (unsigned f = threadIdx.x; f < ns; f += 1024) fstart[s_lo + f] = tot[f];
+}
+
+// Routed slab: the bins are hash ranges, and a slice can lie across the border of two of them (or span many, on a small
+// table).  One thread per slice s: the tasks of all bins whose hash range meets the slice's, in task order --
+// hist2[t][s - s_lo(t)] becomes the offset of task t inside the slice's region, fcount[s] the slice's total
+// (slice_offsets_kernel then turns the totals into fstart).
+__global__ void __launch_bounds__(256)
+route_fine_offsets_kernel(TableView tv, int nb_bits, const FineTask *__restrict__ tasks, const unsigned *__restrict__ task_first,
+                          unsigned *hist2, unsigned ns_max, unsigned long long *fcount) {
+    const unsigned long long ns = tv.nslices;
+    for (unsigned long long s = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; s < ns; s += (unsigned long long)gridDim.x * blockDim.x) {
+        // hashes h with (h * ns) >> 32 == s: [ceil(s 2^32 / ns), ceil((s + 1) 2^32 / ns) - 1]
+        const unsigned long long h_lo = ((s << 32) + ns - 1) / ns, h_hi = (((s + 1) << 32) + ns - 1) / ns - 1;
+        const unsigned j_lo = (unsigned)(h_lo >> (32 - nb_bits)), j_hi = (unsigned)(h_hi >> (32 - nb_bits));
+        unsigned long long run = 0;
+        for (unsigned t = task_first[j_lo]; t < task_first[j_hi + 1]; ++t) {
+            const unsigned s_lo = tasks[t].s_lo;
+            if (s < s_lo || s >= (unsigned long long)s_lo + tasks[t].ns) continue;
+            unsigned *p = hist2 + (size_t)t * ns_max + (unsigned)(s - s_lo);
+            const unsigned v = *p; *p = (unsigned)run; run += v;
+        }
+        fcount[s] = run;
+    }
 }
 
 // ---- scatter into slice order ----------------------------------------------------------------------------------
@@ -949,8 +973,17 @@ cudaError_t launch_fine_plan(cudaStream_t st, const TableView &tv, unsigned ncoa
 }
 
 cudaError_t launch_route_plan(cudaStream_t st, const TableView &tv, const RouteMap &rt, int me, int cap, const unsigned long long *H,
-                              unsigned long long part, FineTask *tasks, unsigned task_cap, unsigned *ntasks, uint64_t *launches) {
-    route_plan_kernel<<<1, 1024, 0, st>>>(tv, rt.nranks, rt.nb_bits, me, cap, H, part, tasks, task_cap, ntasks);
+                              unsigned long long part, FineTask *tasks, unsigned task_cap, unsigned *ntasks, unsigned *task_first,
+                              uint64_t *launches) {
+    route_plan_kernel<<<1, 1024, 0, st>>>(tv, rt.nranks, rt.nb_bits, me, cap, H, part, tasks, task_cap, ntasks, task_first);
+    ++*launches;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_route_fine_offsets(cudaStream_t st, const TableView &tv, int nb_bits, const FineTask *tasks, const unsigned *task_first,
+                                      unsigned *hist2, unsigned ns_max, unsigned long long *fcount, uint64_t *launches) {
+    const unsigned grid = (unsigned)std::min<unsigned long long>((tv.nslices + 255) / 256, (unsigned long long)sm_count() * 8);
+    route_fine_offsets_kernel<<<grid, 256, 0, st>>>(tv, nb_bits, tasks, task_first, hist2, ns_max, fcount);
     ++*launches;
     return cudaGetLastError();
 }

@@ -142,7 +142,9 @@ cudaError_t launch_fine_offsets(cudaStream_t st, const TableView &tv, unsigned n
                                 unsigned long long *fcount, uint64_t *launches);
 // tasks over the receive slab of rank `me` (routed pipeline; H = all-gathered histograms, cap = flush chunk)
 cudaError_t launch_route_plan(cudaStream_t st, const TableView &tv, const RouteMap &rt, int me, int cap, const unsigned long long *H,
-                              unsigned long long part, FineTask *tasks, unsigned task_cap, unsigned *ntasks, uint64_t *launches);
+                              unsigned long long part, FineTask *tasks, unsigned task_cap, unsigned *ntasks, unsigned *task_first, uint64_t *launches);
+cudaError_t launch_route_fine_offsets(cudaStream_t st, const TableView &tv, int nb_bits, const FineTask *tasks, const unsigned *task_first,
+                                      unsigned *hist2, unsigned ns_max, unsigned long long *fcount, uint64_t *launches);
 // hist2 == NULL: fhist[s] += tuples of slice s; else hist2[t * ns_max + f] = tuples of slice s_lo + f in task t
 cudaError_t launch_fine_hist(cudaStream_t st, const TableView &tv, const uint64_t *in, const FineTask *tasks,
                              const unsigned *ntasks, unsigned task_bound, unsigned ns_max, unsigned long long *fhist,
