@@ -506,7 +506,10 @@ def main_ours(args):
     # do not move
     vmode = os.environ.get("KQ_VALIDATE", "routed") if world > 1 else None     # "peer": probe the owners' tables over NVLink loads
     peers = shard.PeerTables(g, world, dev, keep=True) if vmode == "peer" else None
-    router_v = shard.RoutedValidator(g, rank, world, contig, dev) if vmode == "routed" else None
+    # routed validate: up to 2^26 assembly positions per round (inboxes of nranks x that many 16-byte queries per rank)
+    v_chunk = max(contig, min(sum(s.size for s in segs), 1 << 26))
+    router_v = shard.RoutedValidator(g, rank, world, v_chunk, dev) if vmode == "routed" else None
+    v_rounds = router_v.rounds_of(d_asm) if router_v is not None else []
     v_bufs = []
     if router_v is not None and not args.no_e2e:
         words = L.kq_packed_words(contig)
@@ -545,8 +548,8 @@ def main_ours(args):
             # every rank validates its own genome: queries are routed to the owners, rows come back (two stream
             # barriers per contig); only the three QV counters are reduced
             g.finalize()
-            for b, m, n_ in d_asm:
-                router_v.chunk_packed(b, m, n_)
+            for rnd in v_rounds:                       # several contigs per round: one pair of barriers for all of them
+                router_v.round_packed(rnd)
             router_v.counters()
             return
         # KQ_VALIDATE=peer: each k-mer is probed in its owner's shard over peer memory

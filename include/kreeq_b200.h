@@ -243,7 +243,15 @@ int  kq_peer_disconnect(kq_ctx *ctx);
 int  kq_vroute_setup(kq_ctx *ctx, uint64_t chunk_positions, void **d_inbox, void *ipc_inbox64, void **d_rows, void *ipc_rows64);
 int  kq_vroute_connect(kq_ctx *ctx, void *const *inboxes, void *const *rows);
 int  kq_vroute_send(kq_ctx *ctx, const uint64_t *d_bases, const uint64_t *d_invalid, uint64_t base0, uint64_t c0, uint64_t n, uint64_t kcount);
+/* several segments in ONE round (one pair of barriers for all of them): rows of this call go to [row0, row0 + n) of the
+ * row slab, the counts are published to the owners with the call that passes last = 1 (row0 + n <= chunk of
+ * kq_vroute_setup).  kq_vroute_send == kq_vroute_send_at(.., 0, 1). */
+int  kq_vroute_send_at(kq_ctx *ctx, const uint64_t *d_bases, const uint64_t *d_invalid, uint64_t base0, uint64_t c0,
+                       uint64_t n, uint64_t kcount, uint64_t row0, int last);
 int  kq_vroute_answer(kq_ctx *ctx, uint32_t cov_cutoff);
+/* after the barrier that follows kq_vroute_answer: the owners stored their answers in this rank's answer boxes in
+ * query order (coalesced peer stores); this puts them into their rows.  Then kq_vroute_rows / kq_vroute_copy_rows. */
+int  kq_vroute_place(kq_ctx *ctx);
 int  kq_vroute_rows(kq_ctx *ctx, kq_base **d_rows);
 int  kq_vroute_copy_rows(kq_ctx *ctx, kq_base *host_dst, uint64_t n);      /* slab rows [0, n) -> host, async on the stream */
 int  kq_vroute_counters(kq_ctx *ctx, kq_qv *acc, int reset);

@@ -90,7 +90,9 @@ PROTOTYPES = {
     "kq_vroute_setup": (_i, [_vp, _u64, C.POINTER(_vp), _vp, C.POINTER(_vp), _vp]),
     "kq_vroute_connect": (_i, [_vp, C.POINTER(_vp), C.POINTER(_vp)]),
     "kq_vroute_send": (_i, [_vp, _vp, _vp, _u64, _u64, _u64, _u64]),
+    "kq_vroute_send_at": (_i, [_vp, _vp, _vp, _u64, _u64, _u64, _u64, _u64, _i]),
     "kq_vroute_answer": (_i, [_vp, C.c_uint32]),
+    "kq_vroute_place": (_i, [_vp]),
     "kq_vroute_rows": (_i, [_vp, C.POINTER(_vp)]),
     "kq_vroute_copy_rows": (_i, [_vp, _vp, _u64]),
     "kq_vroute_counters": (_i, [_vp, C.POINTER(KqQV), _i]),

@@ -106,6 +106,7 @@ struct kq_ctx {
     // routed validate: inbox the peers' queries arrive in, row slab their answers arrive in, local cursors / counters
     unsigned char *d_vinbox = nullptr; uint64_t vcap = 0; Base *d_vrows = nullptr;
     unsigned long long *d_vcursor = nullptr, *d_vacc = nullptr; VRoute vroute{}; bool vroute_ready = false;
+    unsigned *d_vpos = nullptr;                                       // rows of the queries sent in the current round (VRoute::poslog)
     bool hold_pending = false;                   // kq_multi routes the pending reads itself: nothing else may flush them
     Stage st[NBUF]; int next_stage = 0;
     uint64_t launches = 0, h2d = 0, d2h = 0;
@@ -663,7 +664,7 @@ extern "C" void kq_destroy(kq_ctx *c) {
     for (void *p : c->peer_opened) cudaIpcCloseMemHandle(p);
     cudaFree(c->d_peers);
     cudaFree(c->d_slab); cudaFree(c->d_rcursor); cudaFree(c->d_rback); cudaFree(c->d_rtotals);
-    cudaFree(c->d_vinbox); cudaFree(c->d_vrows); cudaFree(c->d_vcursor); cudaFree(c->d_vacc);
+    cudaFree(c->d_vinbox); cudaFree(c->d_vrows); cudaFree(c->d_vcursor); cudaFree(c->d_vacc); cudaFree(c->d_vpos);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     delete c;
 }
@@ -1103,10 +1104,13 @@ extern "C" int kq_vroute_setup(kq_ctx *c, uint64_t chunk, void **d_inbox, void *
     const size_t qbytes = (size_t)c->nranks * chunk * 16;
     CU(cudaMalloc(&c->d_vinbox, qbytes + KQ_MAX_RANKS * 8));
     CU(cudaMemsetAsync(c->d_vinbox + qbytes, 0, KQ_MAX_RANKS * 8, c->stream));
-    CU(cudaMalloc(&c->d_vrows, chunk * sizeof(Base)));
+    // row slab + one answer box per owner (the owners store their answers there in query order, kq_vroute_place sorts them in)
+    CU(cudaMalloc(&c->d_vrows, ((size_t)c->nranks + 1) * chunk * sizeof(Base)));
+    cudaFree(c->d_vpos); c->d_vpos = nullptr;
+    CU(cudaMalloc(&c->d_vpos, (size_t)c->nranks * chunk * sizeof(unsigned)));
     if (!c->d_vcursor) {
-        CU(cudaMalloc(&c->d_vcursor, KQ_MAX_RANKS * 8)); CU(cudaMalloc(&c->d_vacc, 3 * 8));
-        CU(cudaMemsetAsync(c->d_vcursor, 0, KQ_MAX_RANKS * 8, c->stream)); CU(cudaMemsetAsync(c->d_vacc, 0, 3 * 8, c->stream));
+        CU(cudaMalloc(&c->d_vcursor, 2 * KQ_MAX_RANKS * 8)); CU(cudaMalloc(&c->d_vacc, 3 * 8));    // cursors, then `sent`
+        CU(cudaMemsetAsync(c->d_vcursor, 0, 2 * KQ_MAX_RANKS * 8, c->stream)); CU(cudaMemsetAsync(c->d_vacc, 0, 3 * 8, c->stream));
     }
     CU(cudaStreamSynchronize(c->stream));
     c->vcap = chunk;
@@ -1123,6 +1127,7 @@ extern "C" int kq_vroute_connect(kq_ctx *c, void *const *inboxes, void *const *r
     VRoute &v = c->vroute;
     v = VRoute{};
     v.nranks = c->nranks; v.me = c->rank; v.shift = view(c).shard_shift; v.cap = c->vcap; v.cursor = c->d_vcursor;
+    v.sent = c->d_vcursor + KQ_MAX_RANKS; v.poslog = c->d_vpos;
     for (int r = 0; r < c->nranks; ++r) {
         if (!inboxes[r] || !rows[r]) return fail(c, KQ_EINVAL, "kq_vroute_connect: NULL pointer");
         v.inbox[r] = inboxes[r];
@@ -1134,16 +1139,20 @@ extern "C" int kq_vroute_connect(kq_ctx *c, void *const *inboxes, void *const *r
     return KQ_OK;
 }
 
-extern "C" int kq_vroute_send(kq_ctx *c, const uint64_t *d_bases, const uint64_t *d_invalid, uint64_t base0, uint64_t c0, uint64_t n, uint64_t kcount) {
+extern "C" int kq_vroute_send_at(kq_ctx *c, const uint64_t *d_bases, const uint64_t *d_invalid, uint64_t base0, uint64_t c0, uint64_t n,
+                                uint64_t kcount, uint64_t row0, int last) {
     if (!c || (n && (!d_bases || !d_invalid))) return KQ_EINVAL;
     if (!c->vroute_ready) return fail(c, KQ_ESTATE, "kq_vroute_send: call kq_vroute_connect first");
-    if (n > c->vcap) return fail(c, KQ_EINVAL, "kq_vroute_send: chunk larger than the one given to kq_vroute_setup");
+    if (row0 + n > c->vcap) return fail(c, KQ_EINVAL, "kq_vroute_send: more positions in a round than given to kq_vroute_setup");
     CU(cudaSetDevice(c->device));
     const int t = time_begin(c, 1), t8 = time_begin(c, 8);
-    CU(launch_vroute_send(c->stream, view(c), d_bases, d_invalid, base0, c0, n, kcount, c->d_vrows, c->d_vacc, c->vroute, &c->launches));
+    CU(launch_vroute_send(c->stream, view(c), d_bases, d_invalid, base0, c0, n, kcount, c->d_vrows, c->d_vacc, c->vroute, &c->launches, row0, last != 0));
     time_end(c, t8);
     time_end(c, t);
     return KQ_OK;
+}
+extern "C" int kq_vroute_send(kq_ctx *c, const uint64_t *d_bases, const uint64_t *d_invalid, uint64_t base0, uint64_t c0, uint64_t n, uint64_t kcount) {
+    return kq_vroute_send_at(c, d_bases, d_invalid, base0, c0, n, kcount, 0, 1);
 }
 
 extern "C" int kq_vroute_answer(kq_ctx *c, uint32_t cutoff) {
@@ -1152,6 +1161,18 @@ extern "C" int kq_vroute_answer(kq_ctx *c, uint32_t cutoff) {
     CU(cudaSetDevice(c->device));
     const int t = time_begin(c, 1), t9 = time_begin(c, 9);
     CU(launch_vroute_answer(c->stream, view(c), c->d_vinbox, c->vroute.counts[c->rank], (uint64_t)c->nranks * c->vcap, cutoff, c->d_vacc, c->vroute, &c->launches));
+    time_end(c, t9);
+    time_end(c, t);
+    return KQ_OK;
+}
+
+// after the barrier that follows kq_vroute_answer: the answers the owners left in this rank's boxes go to their rows
+extern "C" int kq_vroute_place(kq_ctx *c) {
+    if (!c) return KQ_EINVAL;
+    if (!c->vroute_ready) return fail(c, KQ_ESTATE, "kq_vroute_place: call kq_vroute_connect first");
+    CU(cudaSetDevice(c->device));
+    const int t = time_begin(c, 1), t9 = time_begin(c, 9);
+    CU(launch_vroute_place(c->stream, c->vcap, c->vroute, &c->launches));
     time_end(c, t9);
     time_end(c, t);
     return KQ_OK;

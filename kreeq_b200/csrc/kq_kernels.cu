@@ -742,7 +742,7 @@ __device__ __forceinline__ uint4 evaluate_row(const Rec32 &kh, int found, uint32
 
 __global__ void __launch_bounds__(TPB, CTAS_PER_SM)
 vroute_send_kernel(TableView tv, const uint64_t *__restrict__ B, const uint64_t *__restrict__ M, uint64_t base0, uint64_t c0,
-                   uint64_t n, uint64_t kcount, Base *__restrict__ rows, unsigned long long *acc3, VRoute vr) {
+                   uint64_t n, uint64_t kcount, Base *__restrict__ rows, unsigned long long *acc3, VRoute vr, uint64_t row0) {
     __shared__ unsigned long long sh[2];
     if (threadIdx.x < 2) sh[threadIdx.x] = 0;
     __syncthreads();
@@ -759,7 +759,7 @@ vroute_send_kernel(TableView tv, const uint64_t *__restrict__ B, const uint64_t 
                 if (km.valid) dest = (int)((km.key & 127) >> vr.shift);
                 else { ++missing; ++counted; }                        // never found; still counts (kreeq.cpp:216)
             }
-            if (dest < 0) __stcs(reinterpret_cast<uint4 *>(rows) + i, make_uint4(0, 0, 0, 0));
+            if (dest < 0) __stcs(reinterpret_cast<uint4 *>(rows) + row0 + i, make_uint4(0, 0, 0, 0));
         }
         const unsigned peers = __match_any_sync(0xffffffffu, dest);
         if (dest < 0) continue;
@@ -769,8 +769,9 @@ vroute_send_kernel(TableView tv, const uint64_t *__restrict__ B, const uint64_t 
         slot = __shfl_sync(peers, slot, leader) + __popc(peers & ((1u << lane) - 1));
         const uint64_t c = c0 + i;
         const unsigned meta = km.nxt | km.prv << 3 | (km.isFw ? 64u : 0u) | (c < kcount - 1 ? 128u : 0u) | (c > 0 ? 256u : 0u);
-        uint4 q; q.x = (unsigned)km.key; q.y = (unsigned)(km.key >> 32); q.z = (unsigned)i; q.w = meta;
+        uint4 q; q.x = (unsigned)km.key; q.y = (unsigned)(km.key >> 32); q.z = (unsigned)(row0 + i); q.w = meta;
         reinterpret_cast<uint4 *>(vr.inbox[dest])[(uint64_t)vr.me * vr.cap + slot] = q;
+        vr.poslog[(uint64_t)dest * vr.cap + slot] = q.z;               // where the answer in slot `slot` of owner dest's box belongs
     }
     block_add(missing, &acc3[0], &sh[0]);
     block_add(counted, &acc3[1], &sh[1]);
@@ -779,7 +780,7 @@ vroute_send_kernel(TableView tv, const uint64_t *__restrict__ B, const uint64_t 
 // after the send kernel: tell every owner how many queries this rank left in its inbox, reset the cursors
 __global__ void vroute_publish_kernel(VRoute vr) {
     const int o = threadIdx.x;
-    if (o < vr.nranks) { vr.counts[o][vr.me] = vr.cursor[o]; vr.cursor[o] = 0; }
+    if (o < vr.nranks) { vr.counts[o][vr.me] = vr.cursor[o]; vr.sent[o] = vr.cursor[o]; vr.cursor[o] = 0; }
 }
 
 __global__ void __launch_bounds__(TPB, 8)
@@ -805,11 +806,34 @@ vroute_answer_kernel(TableView tv, const uint4 *__restrict__ inbox, const unsign
         const uint4 o = evaluate_row(kh, found, cutoff, (q.w & 64u) != 0, q.w & 7u, (q.w >> 3) & 7u, (q.w & 128u) != 0, (q.w & 256u) != 0,
                                      missing, edge_missing);
         ++counted;
-        reinterpret_cast<uint4 *>(vr.rows[s])[q.z] = o;              // the origin's row slab (peer store)
+        // answers go to this owner's box at the origin in query order: consecutive threads store consecutive 16-byte
+        // rows (whole lines over NVLink); the origin puts them in their places (vroute_place_kernel)
+        reinterpret_cast<uint4 *>(vr.rows[s])[vr.cap + (uint64_t)vr.me * vr.cap + (j - first[s])] = o;
     }
     block_add(missing, &acc3[0], &sh[0]);
     block_add(counted, &acc3[1], &sh[1]);
     block_add(edge_missing, &acc3[2], &sh[2]);
+}
+
+// origin side: answer j of owner o's box belongs to row poslog[o][j] (the boxes are read front to back, the rows of one
+// box ascend: neighbouring threads write neighbouring lines)
+__global__ void __launch_bounds__(TPB, 8)
+vroute_place_kernel(VRoute vr) {
+    __shared__ unsigned long long first[KQ_MAX_RANKS + 1];
+    if (threadIdx.x == 0) {
+        unsigned long long run = 0;
+        for (int o = 0; o < vr.nranks; ++o) { first[o] = run; run += vr.sent[o]; }
+        first[vr.nranks] = run;
+    }
+    __syncthreads();
+    uint4 *rows = reinterpret_cast<uint4 *>(vr.rows[vr.me]);
+    const uint64_t total = first[vr.nranks], stride = (uint64_t)gridDim.x * TPB;
+    for (uint64_t j = (uint64_t)blockIdx.x * TPB + threadIdx.x; j < total; j += stride) {
+        int o = 0;
+        while (j >= first[o + 1]) ++o;
+        const uint64_t at = (uint64_t)o * vr.cap + (j - first[o]);
+        rows[vr.poslog[at]] = __ldcs(rows + vr.cap + at);
+    }
 }
 
 __global__ void __launch_bounds__(TPB, CTAS_PER_SM)
@@ -1055,10 +1079,9 @@ cudaError_t launch_validate(cudaStream_t st, const TableView &tv, const uint64_t
 
 cudaError_t launch_vroute_send(cudaStream_t st, const TableView &tv, const uint64_t *B, const uint64_t *M, uint64_t base0,
                                uint64_t c0, uint64_t n, uint64_t kcount, Base *rows, unsigned long long *acc3, const VRoute &vr,
-                               uint64_t *launches) {
-    if (n) { vroute_send_kernel<<<grid_for(n), TPB, 0, st>>>(tv, B, M, base0, c0, n, kcount, rows, acc3, vr); ++*launches; }
-    vroute_publish_kernel<<<1, 32, 0, st>>>(vr);                      // also for an empty chunk: the owners read the counts
-    ++*launches;
+                               uint64_t *launches, uint64_t row0, bool publish) {
+    if (n) { vroute_send_kernel<<<grid_for(n), TPB, 0, st>>>(tv, B, M, base0, c0, n, kcount, rows, acc3, vr, row0); ++*launches; }
+    if (publish) { vroute_publish_kernel<<<1, 32, 0, st>>>(vr); ++*launches; }   // also for an empty chunk: the owners read the counts
     return cudaGetLastError();
 }
 
@@ -1067,6 +1090,14 @@ cudaError_t launch_vroute_answer(cudaStream_t st, const TableView &tv, const voi
     if (!max_queries) return cudaSuccess;
     const unsigned grid = (unsigned)std::min<uint64_t>((max_queries + TPB - 1) / TPB, (uint64_t)sm_count() * 8);
     vroute_answer_kernel<<<grid, TPB, 0, st>>>(tv, static_cast<const uint4 *>(inbox), counts, cutoff, acc3, vr);
+    ++*launches;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_vroute_place(cudaStream_t st, uint64_t max_queries, const VRoute &vr, uint64_t *launches) {
+    if (!max_queries) return cudaSuccess;
+    const unsigned grid = (unsigned)std::min<uint64_t>((max_queries + TPB - 1) / TPB, (uint64_t)sm_count() * 8);
+    vroute_place_kernel<<<grid, TPB, 0, st>>>(vr);
     ++*launches;
     return cudaGetLastError();
 }

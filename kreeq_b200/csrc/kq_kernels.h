@@ -54,8 +54,10 @@ struct VRoute {
     unsigned long long cap;                        // queries per (owner, sender) region of an inbox
     void *inbox[KQ_MAX_RANKS];                     // inbox[o] + (me * cap + slot) * 16
     unsigned long long *counts[KQ_MAX_RANKS];      // counts[o][me] = queries this rank left at owner o
-    Base *rows[KQ_MAX_RANKS];                      // rows[s][position] = row slab of origin s
+    Base *rows[KQ_MAX_RANKS];                      // row slab of origin s: [cap rows][answer boxes: nranks x cap rows]
     unsigned long long *cursor;                    // local append cursors, one per owner
+    unsigned *poslog;                              // local: poslog[o * cap + slot] = row of the query this rank left in slot `slot` at owner o
+    unsigned long long *sent;                      // local: queries left at every owner in the last round (kept for the place kernel)
 };
 
 int sm_count();   // multiprocessors of the current device (cached)
@@ -187,9 +189,10 @@ cudaError_t launch_validate(cudaStream_t st, const TableView &tv, const uint64_t
 // routed validate: phase 1 on the origin (queries -> owners' inboxes, counts published), phase 2 on the owner
 cudaError_t launch_vroute_send(cudaStream_t st, const TableView &tv, const uint64_t *B, const uint64_t *M, uint64_t base0,
                                uint64_t c0, uint64_t n, uint64_t kcount, Base *rows, unsigned long long *acc3, const VRoute &vr,
-                               uint64_t *launches);
+                               uint64_t *launches, uint64_t row0 = 0, bool publish = true);
 cudaError_t launch_vroute_answer(cudaStream_t st, const TableView &tv, const void *inbox, const unsigned long long *counts,
                                  uint64_t max_queries, uint32_t cutoff, unsigned long long *acc3, const VRoute &vr, uint64_t *launches);
+cudaError_t launch_vroute_place(cudaStream_t st, uint64_t max_queries, const VRoute &vr, uint64_t *launches);
 cudaError_t launch_lookup(cudaStream_t st, const TableView &tv, const uint64_t *keys, uint64_t n, Rec32 *rec,
                           uint8_t *found, uint64_t *launches);
 

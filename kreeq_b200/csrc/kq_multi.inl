@@ -415,7 +415,8 @@ extern "C" int kq_multi_validate_segment(kq_multi *m, const char *seq, uint64_t 
             int e = kq_vroute_send(c, s.d_bases, s.d_inv, a0, c0, n, kcount); if (e) return e;
             e = meet(m, g); if (e) return e;                            // every inbox is complete
             e = kq_vroute_answer(c, cutoff); if (e) return e;
-            e = meet(m, g); if (e) return e;                            // every row slab is complete; the inboxes are free
+            e = meet(m, g); if (e) return e;                            // every answer box is complete; the inboxes are free
+            e = kq_vroute_place(c); if (e) return e;                    // answers -> rows (local)
             if (n) {
                 CU(cudaMemcpyAsync(out + c0, c->d_vrows, n * sizeof(Base), cudaMemcpyDeviceToHost, c->stream));
                 c->d2h += n * sizeof(Base);

@@ -289,7 +289,38 @@ class RoutedValidator:
         check(L.kq_vroute_send(g.handle, pb, pi, 0, 0, length, kcount), g.handle)
         self._barrier()                               # every inbox is complete
         check(L.kq_vroute_answer(g.handle, cutoff), g.handle)
-        self._barrier()                               # every row slab is complete, the inboxes are free again
+        self._barrier()                               # every answer box is complete, the inboxes are free again
+        check(L.kq_vroute_place(g.handle), g.handle)  # answers -> rows (local)
+
+    def round_packed(self, segments, cutoff=0):
+        """One round over several packed device-resident segments [(d_bases, d_invalid, length), ..] whose lengths add up
+        to at most `chunk`: every segment's queries are sent, then ONE pair of stream barriers serves them all.
+        Afterwards the rows of segment i start at row sum(lengths[:i]) of this rank's slab.  Collective (ranks without
+        work pass [])."""
+        g, L = self.g, lib()
+        row0 = 0
+        segs = [s_ for s_ in segments if s_[2]]
+        for i, (d_bases, d_invalid, length) in enumerate(segs):
+            check(L.kq_vroute_send_at(g.handle, C.c_void_p(d_bases.data_ptr()), C.c_void_p(d_invalid.data_ptr()), 0, 0, length,
+                                      max(0, length - g.k + 1), row0, 1 if i == len(segs) - 1 else 0), g.handle)
+            row0 += length
+        if not segs:
+            check(L.kq_vroute_send(g.handle, None, None, 0, 0, 0, 0), g.handle)
+        self._barrier()                               # every inbox is complete
+        check(L.kq_vroute_answer(g.handle, cutoff), g.handle)
+        self._barrier()                               # every answer box is complete, the inboxes are free again
+        check(L.kq_vroute_place(g.handle), g.handle)  # answers -> rows (local)
+
+    def rounds_of(self, segments):
+        """cut a list of (d_bases, d_invalid, length) into rounds of at most `chunk` positions (a longer segment alone)"""
+        out, cur, tot = [], [], 0
+        for s_ in segments:
+            if cur and tot + s_[2] > self.chunk:
+                out.append(cur); cur, tot = [], 0
+            cur.append(s_); tot += s_[2]
+        if cur:
+            out.append(cur)
+        return out
 
     def counters(self, reset=True):
         """the three QV counters summed over all ranks (collective)"""

@@ -142,3 +142,79 @@ def test_cli_gpus_flag_same_output(mods, tmp_path):
     assert outs["g1"][:5] == outs["g4"][:5]
     assert outs["g1"][3] == outs["g1"][4]
     assert_same_records(outs["g1"][5], outs["g4"][5])
+
+
+def test_routed_validate_several_segments_per_round(mods):
+    """kq_vroute_send_at: the queries of several segments go out before ONE pair of barriers; rows of segment i start
+    at the sum of the lengths before it.  Two shards (handles) in this process, their inboxes / row slabs connected
+    by plain pointers."""
+    import ctypes as C
+    import torch
+    kb, ko = mods
+    from kreeq_b200._lib import BASE, KqQV, check, lib
+    L = lib()
+    k, G = 21, 2
+    genome, batches = problem(4242, k, genome_bp=90_000, n_batches=3)
+    ref = ko.Table(k)
+    for b in batches:
+        ref.count_batch(b)
+    segs = [genome.tobytes()[:30_000], genome.tobytes()[30_000:52_000] + b"A" * 300, genome.tobytes()[52_000:], b"ACGT"]
+    mine = {0: [0, 2], 1: [1, 3]}                                   # segments of rank 0 / rank 1 (the last is shorter than k)
+    hs = []
+    try:
+        for r in range(G):
+            g = kb.DBG(k=k, expected_distinct=400_000)
+            check(L.kq_set_shard(g.handle, r, G), g.handle)
+            for b in batches:
+                g.traverseInReads(b)
+            g.finalize()
+            hs.append(g)
+        chunk = 70_000
+        inbox, rows = (C.c_void_p * G)(), (C.c_void_p * G)()
+        for r, g in enumerate(hs):
+            a, b_ = C.c_void_p(), C.c_void_p()
+            check(L.kq_vroute_setup(g.handle, chunk, C.byref(a), None, C.byref(b_), None), g.handle)
+            inbox[r], rows[r] = a.value, b_.value
+        for g in hs:
+            check(L.kq_vroute_connect(g.handle, inbox, rows), g.handle)
+        keep = []
+        for r, g in enumerate(hs):
+            row0 = 0
+            for j, i in enumerate(mine[r]):
+                a = np.frombuffer(segs[i], dtype=np.uint8)
+                bases, inv = kb.pack_host(a)
+                db = torch.from_numpy(bases.view(np.int64)).cuda(); di = torch.from_numpy(inv.view(np.int64)).cuda()
+                keep += [db, di]
+                check(L.kq_vroute_send_at(g.handle, C.c_void_p(db.data_ptr()), C.c_void_p(di.data_ptr()), 0, 0, a.size,
+                                          max(0, a.size - k + 1), row0, 1 if j == len(mine[r]) - 1 else 0), g.handle)
+                row0 += a.size
+        for g in hs:
+            g.sync()
+        for g in hs:
+            check(L.kq_vroute_answer(g.handle, 0), g.handle)
+        for g in hs:
+            g.sync()
+        for g in hs:
+            check(L.kq_vroute_place(g.handle), g.handle)
+        tot = [0, 0, 0]
+        for r, g in enumerate(hs):
+            n = sum(len(segs[i]) for i in mine[r])
+            out = np.zeros(n, dtype=BASE)
+            check(L.kq_vroute_copy_rows(g.handle, C.c_void_p(out.ctypes.data), n), g.handle)
+            g.sync()
+            row0 = 0
+            for i in mine[r]:
+                rc, rout, racc = ref.validate_segment(segs[i])
+                assert out[row0:row0 + len(segs[i])].tobytes() == rout.tobytes(), (r, i)
+                row0 += len(segs[i])
+            q = KqQV()
+            check(L.kq_vroute_counters(g.handle, C.byref(q), 1), g.handle)
+            tot = [tot[0] + q.missing, tot[1] + q.kcount, tot[2] + q.edge_missing]
+        want = [0, 0, 0]
+        for s_ in segs:
+            racc = ref.validate_segment(s_)[2]
+            want = [want[j] + racc[j] for j in range(3)]
+        assert tot == want
+    finally:
+        for g in hs:
+            g.close()
