@@ -748,6 +748,8 @@ def main_ours(args):
     if res["kn_count"]:
         pipeline = int(os.environ.get("KQ_PIPELINE", "3"))
         insert_name = "smem_insert_kernel" if pipeline >= 3 else "insert_tuples_kernel"
+        if world > 1 and os.environ.get("KQ_ROUTE_SMEM", "0") != "1":
+            insert_name = "insert_tuples_kernel"        # the routed slab is counted with L2 CAS
         scat_name = ("slice_scatter_kernel<routed>" if world > 1 else "slice_scatter_kernel") if pipeline != 4 else "scatter_fine_kernel"
         per_step = {"slice_hist_kernel (+offsets)": (res["kt_scat"] - res["kt_s1"]) / args.steps, scat_name: res["kt_s1"] / args.steps,
                     "fine_hist_kernel (+plan, offsets)": (res["kt_l2"] - res["kt_s2"]) / args.steps, "fine_scatter_kernel": res["kt_s2"] / args.steps,

@@ -407,8 +407,11 @@ int run_batch(kq_ctx *c, Source src) {
         time_end(c, t0);
         return KQ_OK;
     }
-    // routed pipeline: the slab is in bin order already, its tasks were planned by kq_route_scatter
-    if (tuning().pipeline == 3 && src.ordered && c->route_task_bound && bound == c->route_extent && c->nslices > 1 && tuning().smem_insert && c->slice_bits <= 13 &&
+    // routed pipeline: the slab is in bin order already, its tasks were planned by kq_route_scatter.  Knob route_smem,
+    // off by default: the L2 CAS insert over the slab (below; a bin's hash range is an L2-sized window of the table)
+    // takes 69 ms per 2.6 G tuples at any GPU count, level-2 scatter + shared-memory insert 70 / 82 / 116 ms at 2 / 4 / 8 GPUs
+    // (the slab's bins get wider as the ranks share 2 048 bins)
+    if (tuning().route_smem && tuning().pipeline == 3 && src.ordered && c->route_task_bound && bound == c->route_extent && c->nslices > 1 && tuning().smem_insert && c->slice_bits <= 13 &&
         fine_pick_cap(c->route_ns_max, tw) != 0) {
         int rc = pipeline_scratch(c, 0, true, bound); if (rc) return rc;
         const int t4 = time_begin(c, 4);
@@ -753,6 +756,7 @@ extern "C" int kq_set_tuning(const char *name, long long value) {
     else if (n == "db_ordered" && (value == 0 || value == 1)) t.db_ordered = (int)value;
     else if (n == "one_pass" && value >= 0 && value <= 2) t.one_pass = (int)value;
     else if (n == "cta_lock" && (value == 0 || value == 1)) t.cta_lock = (int)value;
+    else if (n == "route_smem" && (value == 0 || value == 1)) t.route_smem = (int)value;
     else if (n == "warp_insert" && (value == 0 || value == 1)) t.warp_insert = (int)value;
     else if (n == "s3_threads" && (value == 256 || value == 384 || value == 512)) t.s3_threads = (int)value;
     else if (n == "s3_ctas" && value >= 1 && value <= 8) t.s3_ctas = (int)value;
@@ -988,7 +992,7 @@ extern "C" int kq_route_scatter(kq_ctx *c, const uint64_t *d_bases, const uint64
     // what this rank receives goes through the level-2 scatter and the shared-memory insert: plan its tasks from the
     // same histograms (bin extents inside the slab, slices a bin's hash range maps to on the local table)
     c->route_task_bound = 0;
-    if (tuning().pipeline == 3 && c->nslices > 1 && totals[c->rank] && (1 << c->route.nb_bits) <= KQ_ROUTE_PLAN_BINS) {
+    if (tuning().route_smem && tuning().pipeline == 3 && c->nslices > 1 && totals[c->rank] && (1 << c->route.nb_bits) <= KQ_ROUTE_PLAN_BINS) {
         const unsigned nb = 1u << c->route.nb_bits;
         c->route_ns_max = (unsigned)(c->nslices / nb + 2);
         int rc = pipeline_scratch(c, 0, true, totals[c->rank]); if (rc) return rc;

@@ -46,6 +46,7 @@ Tuning &tuning() {
         v.pipeline = (int)num("KQ_PIPELINE", 3); if (v.pipeline < 2 || v.pipeline > 4) v.pipeline = 3;
         v.cursor_stride = (int)num("KQ_CURSOR_STRIDE", 8); if (v.cursor_stride < 1 || v.cursor_stride > 32) v.cursor_stride = 8;
         v.warp_insert = (int)num("KQ_WARP_INSERT", 1);
+        v.route_smem = (int)num("KQ_ROUTE_SMEM", 0);
         v.cta_lock = (int)num("KQ_CTA_LOCK", 0);
         v.one_pass = (int)num("KQ_ONE_PASS", 0); if (v.one_pass < 0 || v.one_pass > 2) v.one_pass = 0;
         v.db_ordered = (int)num("KQ_DB_ORDERED", 1);

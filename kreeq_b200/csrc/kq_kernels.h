@@ -77,6 +77,7 @@ struct Tuning {
     int db_ordered;            // 1 = databases are decoded into table order before they are put / merged
     int one_pass;              // 1 = level-1 scatter into fixed regions, no histogram pass (overflow -> list)
     int cta_lock;              // 1 = CTA-owned slices are counted with the lock-byte protocol (cta_insert_kernel) instead of shared-memory CAS
+    int route_smem;            // 1 = the routed slab goes through the level-2 scatter + shared-memory insert (0: L2 CAS insert over the slab)
     int warp_insert;           // 1 = slices of at most 2^10 slots are counted by one warp each (no shared-memory atomics)
     int s3_threads, s3_ctas;   // shared-memory insert: threads per CTA (256 / 384 / 512), CTAs per SM in the grid
     int fs_variant;            // level-2 scatter: 0 auto (two CTAs per SM when the bins allow), 1 one CTA, 2 two CTAs

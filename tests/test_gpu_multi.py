@@ -63,6 +63,33 @@ def test_count_validate_any_gpu_count(mods, k, G):
         assert found[:300].all() and rec[:300].tobytes() == rr[:300].tobytes()
 
 
+@pytest.mark.parametrize("k,G", [(21, 2), (31, 4)])
+def test_routed_slab_through_level2_and_shared_memory_insert(mods, k, G):
+    """route_smem = 1 (off by default): the owner's slab goes through route_plan / per-task histograms /
+    route_fine_offsets / level-2 scatter with private cursors / shared-memory insert; small slices so that slab bins span
+    several slices and slices lie across bins"""
+    kb, ko = mods
+    from kreeq_b200._lib import lib
+    L = lib()
+    knobs = {"route_smem": (1, 0), "single_slice_bits": (8, 21), "piece_bits": (8, 12), "fine_part": (2048, 1 << 18), "direct_pct": (0, 25)}
+    try:
+        for n, (v, _) in knobs.items():
+            assert L.kq_set_tuning(n.encode(), v) == 0
+        genome, batches = problem(9100 + k + G, k)
+        ref = ko.Table(k)
+        n_ref = sum(ref.count_batch(b) for b in batches)
+        with kb.MultiDBG(k=k, devices=devices_for(G), expected_distinct=600_000, round_positions=300_000) as g:
+            for b in batches:
+                g.traverseInReads(b)
+            g.finalize()
+            assert g.instances() == n_ref
+            assert_same_records(g.export(), ref.export())
+            assert g.stats() == ref.stats()
+    finally:
+        for n, (_, d) in knobs.items():
+            L.kq_set_tuning(n.encode(), d)
+
+
 def test_save_load_union_sharded(mods, tmp_path):
     """databases written by 4 shards (16 maps + one .hc.part each, merged) are the files one GPU writes: the strict
     phmap decoder reads them, one GPU loads them, 2 shards merge them in three orders like the oracle's union"""
