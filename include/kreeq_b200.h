@@ -297,10 +297,15 @@ int  kq_reserve(kq_ctx *ctx, uint64_t extra_distinct);
  * kq_count_finish / kq_sync, and before anything that reads the table. */
 int  kq_set_flush_positions(kq_ctx *ctx, uint64_t positions);
 
-/* process-wide tuning knobs (defaults: measured best on B200; the KQ_* environment variables are read
- * once, at first use): "single_slice_bits" (a table of up to 2^v slots is one slice), "piece_bits" (log2 slots per
- * slice of larger tables), "fine_part", "smem_insert" (0: count with L2 CAS), "direct_pct", "scatter_cap",
- * "insert_ctas", "validate_ctas", "db_host".  Geometry knobs apply to tables created or grown afterwards. */
+/* process-wide tuning knobs (defaults: measured best on B200; the KQ_* environment variables of
+ * the same names are read once, at first use).  Geometry: "single_slice_bits" (a table of up to 2^v slots is one
+ * slice), "piece_bits" (log2 slots per slice of larger tables: 12 = one CTA's shared memory, <= 10: one warp's),
+ * "coarse_bias".  Count pipeline: "pipeline" (2 L2 CAS insert, 3 two scatter levels + shared-memory insert, 4 one-pass
+ * scatter), "smem_insert", "warp_insert", "cta_lock", "one_pass" (2: also small batches, almost no slack: tests),
+ * "fine_part", "direct_pct", "scatter_cap", "insert_ctas", "s3_threads", "s3_ctas", "cursor_stride"; multi-GPU:
+ * "route_smem" (1: the routed slab goes through level 2 + shared-memory insert instead of L2 CAS); validate:
+ * "validate_ctas"; databases: "db_host", "db_ordered".  Geometry knobs apply to tables created or grown afterwards.
+ * Unknown name or value out of range -> KQ_EINVAL. */
 int  kq_set_tuning(const char *name, long long value);
 
 /* counters for bench.py: kernels launched by this handle, bytes copied */
