@@ -804,6 +804,35 @@ def main_ours(args):
                        "validate_value": asm_k * world / (e["validate_ms"] * 1e-3),
                        "host_input_bytes_per_step": int(reads_np.size + sum(s.size for s in segs)), "steps": min(args.steps, 2),
                        "validate_out": "pageable host memory (staged)" if args.pageable_out else "page-locked host memory (direct)"}
+    if world == 1 and not args.no_e2e:
+        # the same validate pass with compact rows back (kq_validate_segment_compact: 4 bytes per base over PCIe instead
+        # of 16; rows rebuilt from them are checked against the 16-byte rows of the last segment)
+        try:
+            from kreeq_b200._lib import BASE4, WIDE, KqQV
+            h4_t = torch.empty(contig * 4, dtype=torch.uint8, pin_memory=True)
+            h4 = h4_t.numpy().view(BASE4)
+            wide = np.zeros(1 << 20, dtype=WIDE)
+
+            def compact_pass():
+                acc4 = KqQV()
+                nw_last = 0
+                for seg in segs:
+                    nw = C.c_size_t(wide.size)
+                    check(L.kq_validate_segment_compact(g.handle, C.c_void_p(seg.ctypes.data), seg.size, 0, C.c_void_p(h4.ctypes.data),
+                                                        C.c_void_p(wide.ctypes.data), C.byref(nw), C.byref(acc4)), g.handle)
+                    nw_last = nw.value
+                return acc4, nw_last
+            compact_pass()
+            t0c = time.perf_counter(); acc4, nw_last = compact_pass(); dtc = time.perf_counter() - t0c
+            full = np.zeros(segs[-1].size, dtype=kreeq_b200.BASE); accf = KqQV()
+            check(L.kq_validate_segment(g.handle, C.c_void_p(segs[-1].ctypes.data), segs[-1].size, 0, C.c_void_p(full.ctypes.data), C.byref(accf)), g.handle)
+            back = np.zeros(segs[-1].size, dtype=kreeq_b200.BASE)
+            check(L.kq_expand_rows(C.c_void_p(h4.ctypes.data), segs[-1].size, C.c_void_p(wide.ctypes.data), nw_last, C.c_void_p(back.ctypes.data)))
+            line["e2e"]["validate_compact"] = {"value": asm_k / dtc, "unit": "k-mers/s", "ms": dtc * 1e3, "d2h_bytes": int(4 * sum(s.size for s in segs)),
+                                               "rows_match_16_byte_rows": bool(back.tobytes() == full.tobytes()), "wide_rows_last_segment": int(nw_last),
+                                               "what": "kq_validate_segment_compact from host ASCII, {cov, fw, bw, flags} bytes into page-locked memory (host wall clock)"}
+        except Exception as ex:                          # a side measurement must not cost the line
+            line["e2e"]["validate_compact"] = {"error": str(ex)}
     if world == 1 and not args.no_union:
         # database rows (A4 / A8): 2 x 5.8e7-record databases of a 10 Mbp genome saved, merged, saved, loaded
         from kreeq_b200.dbbench import union_rows

@@ -136,6 +136,17 @@ int  kq_hist(kq_ctx *ctx, uint64_t *cov, uint64_t *n, size_t *len);
  * fast since 16 bytes per base make the host copy the bottleneck). */
 int  kq_validate_segment(kq_ctx *ctx, const char *seq, uint64_t len,
                          uint32_t cov_cutoff, kq_base *out, kq_qv *acc);
+/* Same pass with a quarter of the bytes back over PCIe (16 bytes per base make the device-to-host copy the whole cost of
+ * an end-to-end validate): out[i] = {cov, fw, bw} as bytes + flags (bit 0 isFw, bit 1 "wide"); a row with a value above
+ * 254 has the wide bit set, 255 in the fields that do not fit, and its full DBGbase row with its position in `wide`
+ * (*nwide in: capacity of `wide`, out: rows listed; more rows than the capacity or than 2^20 -> KQ_ENOMEM, use
+ * kq_validate_segment).  kq_expand_rows rebuilds the DBGbase array on the host.  Ours; the reference has no such form
+ * (its writers take DBGbase, src/kreeq-output.cpp:138-399). */
+typedef struct { uint8_t cov, fw, bw, flags; } kq_base4;
+typedef struct { uint64_t pos; kq_base row; } kq_wide_row;
+int  kq_validate_segment_compact(kq_ctx *ctx, const char *seq, uint64_t len, uint32_t cov_cutoff, kq_base4 *out,
+                                 kq_wide_row *wide, size_t *nwide, kq_qv *acc);
+int  kq_expand_rows(const kq_base4 *in, uint64_t len, const kq_wide_row *wide, size_t nwide, kq_base *out);
 /* errorRate src/kreeq.cpp:36-40 and QV = -10 log10(err) :87,96 */
 double kq_error_rate(uint64_t missing, uint64_t total, int k);
 double kq_qv_value(uint64_t missing, uint64_t total, int k);

@@ -17,7 +17,9 @@ ERR_NAMES = {-1: "KQ_EINVAL", -2: "KQ_ENODEV", -3: "KQ_ECUDA", -4: "KQ_ENOMEM", 
 
 REC32 = np.dtype([("fw", "<u4", 4), ("bw", "<u4", 4), ("cov", "<u4")])                       # kq_rec32 / DBGkmer32
 BASE = np.dtype([("fw", "<u4"), ("bw", "<u4"), ("cov", "<u4"), ("isFw", "u1"), ("pad", "u1", 3)])  # kq_base / DBGbase
-assert REC32.itemsize == 36 and BASE.itemsize == 16
+BASE4 = np.dtype([("cov", "u1"), ("fw", "u1"), ("bw", "u1"), ("flags", "u1")])                           # kq_base4
+WIDE = np.dtype([("pos", "<u8"), ("row", BASE)])                                                        # kq_wide_row
+assert REC32.itemsize == 36 and BASE.itemsize == 16 and BASE4.itemsize == 4 and WIDE.itemsize == 24
 
 
 class KqStats(C.Structure):
@@ -62,6 +64,8 @@ PROTOTYPES = {
     "kq_validate_segment": (_i, [_vp, _vp, _u64, C.c_uint32, _vp, C.POINTER(KqQV)]),
     "kq_error_rate": (C.c_double, [_u64, _u64, _i]),
     "kq_qv_value": (C.c_double, [_u64, _u64, _i]),
+    "kq_validate_segment_compact": (_i, [_vp, _vp, _u64, C.c_uint32, _vp, _vp, C.POINTER(_sz), C.POINTER(KqQV)]),
+    "kq_expand_rows": (_i, [_vp, _u64, _vp, _sz, _vp]),
     "kq_lookup_batch": (_i, [_vp, _vp, _sz, _vp, _vp]),
     "kq_lookup_batch_static": (_i, [_vp, _vp, _sz, _vp, _vp]),
     "kq_lookup_static_max": (_sz, []),

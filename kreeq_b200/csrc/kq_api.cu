@@ -106,6 +106,7 @@ struct kq_ctx {
     // routed validate: inbox the peers' queries arrive in, row slab their answers arrive in, local cursors / counters
     unsigned char *d_vinbox = nullptr; uint64_t vcap = 0; Base *d_vrows = nullptr;
     unsigned long long *d_vcursor = nullptr, *d_vacc = nullptr; VRoute vroute{}; bool vroute_ready = false;
+    uint32_t *d_out4[8] = {}; kq_wide_row *d_wide = nullptr; unsigned long long *d_wide_n = nullptr;   // compact validate rows
     unsigned *d_vpos = nullptr;                                       // rows of the queries sent in the current round (VRoute::poslog)
     bool hold_pending = false;                   // kq_multi routes the pending reads itself: nothing else may flush them
     Stage st[NBUF]; int next_stage = 0;
@@ -667,7 +668,7 @@ extern "C" void kq_destroy(kq_ctx *c) {
     for (void *p : c->peer_opened) cudaIpcCloseMemHandle(p);
     cudaFree(c->d_peers);
     cudaFree(c->d_slab); cudaFree(c->d_rcursor); cudaFree(c->d_rback); cudaFree(c->d_rtotals);
-    cudaFree(c->d_vinbox); cudaFree(c->d_vrows); cudaFree(c->d_vcursor); cudaFree(c->d_vacc); cudaFree(c->d_vpos);
+    cudaFree(c->d_vinbox); cudaFree(c->d_vrows); cudaFree(c->d_vcursor); cudaFree(c->d_vacc); cudaFree(c->d_vpos); for (auto *p : c->d_out4) cudaFree(p); cudaFree(c->d_wide); cudaFree(c->d_wide_n);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     delete c;
 }
@@ -1231,7 +1232,16 @@ extern "C" int kq_dev_validate_packed(kq_ctx *c, const uint64_t *d_bases, const 
     return KQ_OK;
 }
 
-extern "C" int kq_validate_segment(kq_ctx *c, const char *seq, uint64_t len, uint32_t cutoff, kq_base *out, kq_qv *acc) {
+namespace {
+
+constexpr unsigned long long WIDE_CAP = 1ull << 20;                  // rows of one call that do not fit a byte per field
+static_assert(sizeof(kq_wide_row) == sizeof(WideRow) && sizeof(kq_wide_row) == 24 && sizeof(kq_base4) == 4, "compact row layouts");
+
+// kq_validate_segment (16-byte DBGbase rows) and kq_validate_segment_compact (4-byte rows + a list of the rare rows that
+// do not fit a byte per field) share the staging loop: `out` receives `rb` bytes per position
+int validate_impl(kq_ctx *c, const char *seq, uint64_t len, uint32_t cutoff, void *out_v, size_t rb, kq_wide_row *wide, size_t *nwide, kq_qv *acc) {
+    unsigned char *out = static_cast<unsigned char *>(out_v);
+    const bool compact = rb == 4;
     if (!c || (!seq && len) || (!out && len) || !acc) return KQ_EINVAL;
     if (len == 0) return KQ_OK;
     CU(cudaSetDevice(c->device));
@@ -1239,7 +1249,12 @@ extern "C" int kq_validate_segment(kq_ctx *c, const char *seq, uint64_t len, uin
     const uint64_t k = (uint64_t)c->k;
     const uint64_t kcount = len >= k ? len - k + 1 : 0;                // src/kreeq.cpp:123-126
     CU(cudaMemsetAsync(c->d_acc, 0, 3 * sizeof(unsigned long long), c->stream));
-    const uint64_t VCH = 4ull << 20;                                   // output entries per staged chunk
+    const uint64_t VCH = 4ull << 20;
+    if (compact) {
+        if (!c->d_out4[0]) for (int i = 0; i < NBUF; ++i) CU(cudaMalloc(&c->d_out4[i], VCH * 4));
+        if (!c->d_wide) { CU(cudaMalloc(&c->d_wide, WIDE_CAP * sizeof(kq_wide_row))); CU(cudaMalloc(&c->d_wide_n, 8)); }
+        CU(cudaMemsetAsync(c->d_wide_n, 0, 8, c->stream));
+    }                                   // output entries per staged chunk
     // A caller that hands in page-locked memory (cudaHostAlloc / cudaHostRegister) gets the rows copied straight
     // into it; pageable memory goes through the pinned staging slot and one host copy (which, at 16 bytes per
     // base, costs more than the PCIe transfer).
@@ -1255,10 +1270,10 @@ extern "C" int kq_validate_segment(kq_ctx *c, const char *seq, uint64_t len, uin
         int rc = stage_acquire(c, *p.s); if (rc) return rc;
         if (direct) return KQ_OK;
         const size_t grain = 1 << 18, tasks = (p.n + grain - 1) / grain;
-        Base *src = p.s->h_out; kq_base *dst = out + p.c0; const uint64_t n = p.n;
+        const unsigned char *src = reinterpret_cast<const unsigned char *>(p.s->h_out); unsigned char *dst = out + p.c0 * rb; const uint64_t n = p.n;
         global_pool().parallel_for(tasks, [&](size_t t) {
             const size_t b = t * grain, e = std::min<size_t>(n, b + grain);
-            std::memcpy(dst + b, src + b, (e - b) * sizeof(Base));
+            std::memcpy(dst + b * rb, src + b * rb, (e - b) * rb);
         });
         return KQ_OK;
     };
@@ -1283,8 +1298,16 @@ extern "C" int kq_validate_segment(kq_ctx *c, const char *seq, uint64_t len, uin
         // results leave on the copy stream, so the next chunk's kernel runs under this chunk's transfer
         CU(cudaEventRecord(s.kernel_done, c->stream));
         CU(cudaStreamWaitEvent(c->copy_stream, s.kernel_done, 0));
-        CU(cudaMemcpyAsync(direct ? (void *)(out + c0) : (void *)s.h_out, s.d_out, n * sizeof(Base), cudaMemcpyDeviceToHost, c->copy_stream));
-        c->d2h += n * sizeof(Base);
+        const void *d_rows = s.d_out;
+        if (compact) {                              // 16-byte rows -> 4-byte rows (+ the wide list) on the device: a quarter of the bytes cross PCIe
+            uint32_t *d4 = c->d_out4[&s - c->st];
+            CU(launch_compact_rows(c->stream, s.d_out, n, c0, d4, c->d_wide, WIDE_CAP, c->d_wide_n, &c->launches));
+            CU(cudaEventRecord(s.kernel_done, c->stream));
+            CU(cudaStreamWaitEvent(c->copy_stream, s.kernel_done, 0));
+            d_rows = d4;
+        }
+        CU(cudaMemcpyAsync(direct ? (void *)(out + c0 * rb) : (void *)s.h_out, d_rows, n * rb, cudaMemcpyDeviceToHost, c->copy_stream));
+        c->d2h += n * rb;
         CU(cudaEventRecord(s.done, c->copy_stream)); s.busy = true;
         pend[npend++] = Pending{&s, c0, n};
     }
@@ -1295,7 +1318,43 @@ extern "C" int kq_validate_segment(kq_ctx *c, const char *seq, uint64_t len, uin
     c->d2h += sizeof h;
     int rc = check_device_error(c); if (rc) return rc;
     acc->missing += h[0]; acc->kcount += h[1]; acc->edge_missing += h[2];
+    if (compact) {
+        unsigned long long nw = 0;
+        CU(cudaMemcpy(&nw, c->d_wide_n, 8, cudaMemcpyDeviceToHost));
+        const size_t cap = nwide ? *nwide : 0;
+        if (nwide) *nwide = (size_t)nw;
+        if (nw > WIDE_CAP || nw > cap)
+            return fail(c, KQ_ENOMEM, "kq_validate_segment_compact: " + std::to_string(nw) + " rows have a value above 254 (list capacity " +
+                                      std::to_string(std::min<size_t>(cap, WIDE_CAP)) + "): use kq_validate_segment or a larger list");
+        if (nw) { CU(cudaMemcpy(wide, c->d_wide, nw * sizeof(kq_wide_row), cudaMemcpyDeviceToHost)); c->d2h += nw * sizeof(kq_wide_row); }
+    }
     return KQ_OK;
+}
+
+}  // namespace
+
+extern "C" int kq_validate_segment(kq_ctx *c, const char *seq, uint64_t len, uint32_t cutoff, kq_base *out, kq_qv *acc) {
+    return validate_impl(c, seq, len, cutoff, out, sizeof(kq_base), nullptr, nullptr, acc);
+}
+
+extern "C" int kq_expand_rows(const kq_base4 *in, uint64_t len, const kq_wide_row *wide, size_t nwide, kq_base *out) {
+    if ((len && (!in || !out)) || (nwide && !wide)) return KQ_EINVAL;
+    const size_t grain = 1 << 18, tasks = (size_t)((len + grain - 1) / grain);
+    global_pool().parallel_for(tasks, [&](size_t t) {
+        const uint64_t b = (uint64_t)t * grain, e = std::min<uint64_t>(len, b + grain);
+        for (uint64_t i = b; i < e; ++i) {
+            kq_base r; r.fw = in[i].fw; r.bw = in[i].bw; r.cov = in[i].cov; r.isFw = in[i].flags & 1; r.pad[0] = r.pad[1] = r.pad[2] = 0;
+            out[i] = r;
+        }
+    });
+    for (size_t j = 0; j < nwide; ++j) { if (wide[j].pos >= len) return KQ_EINVAL; out[wide[j].pos] = wide[j].row; }
+    return KQ_OK;
+}
+
+extern "C" int kq_validate_segment_compact(kq_ctx *c, const char *seq, uint64_t len, uint32_t cutoff, kq_base4 *out,
+                                           kq_wide_row *wide, size_t *nwide, kq_qv *acc) {
+    if (len && (!nwide || (*nwide && !wide))) return KQ_EINVAL;
+    return validate_impl(c, seq, len, cutoff, out, sizeof(kq_base4), wide, nwide, acc);
 }
 
 extern "C" int kq_lookup_batch(kq_ctx *c, const uint64_t *keys, size_t n, kq_rec32 *rec, uint8_t *found) {

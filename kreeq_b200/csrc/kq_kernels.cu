@@ -715,6 +715,22 @@ validate_kernel(TableView tv, const uint64_t *__restrict__ B, const uint64_t *__
     block_add(edge_missing, &acc3[2], &sh[2]);
 }
 
+// 16-byte DBGbase rows -> {cov, fw, bw, flags} bytes; rows with a value above 254 also go to the wide list with their position
+__global__ void __launch_bounds__(TPB, 8)
+compact_rows_kernel(const Base *__restrict__ rows, uint64_t n, uint64_t pos0, uint32_t *__restrict__ out4, WideRow *wide,
+                    unsigned long long wide_cap, unsigned long long *wide_n) {
+    const uint64_t stride = (uint64_t)gridDim.x * TPB;
+    for (uint64_t i = (uint64_t)blockIdx.x * TPB + threadIdx.x; i < n; i += stride) {
+        const uint4 r = __ldcs(reinterpret_cast<const uint4 *>(rows) + i);          // fw, bw, cov, isFw
+        const bool big = r.x > 254u || r.y > 254u || r.z > 254u;
+        out4[i] = min(r.z, 255u) | min(r.x, 255u) << 8 | min(r.y, 255u) << 16 | ((r.w & 1u) | (big ? 2u : 0u)) << 24;
+        if (big) {
+            const unsigned long long j = atomicAdd(wide_n, 1ULL);
+            if (j < wide_cap) { wide[j].pos = pos0 + i; wide[j].fw = r.x; wide[j].bw = r.y; wide[j].cov = r.z; wide[j].isfw = r.w; }
+        }
+    }
+}
+
 // ---- validate across GPUs: queries to the owners, rows back (SURVEY 8e "Collective") -------------------------------
 //
 // Phase 1 (origin GPU): every valid window of the chunk becomes a 16-byte query {key, position, neighbours} appended
@@ -1074,6 +1090,14 @@ cudaError_t launch_validate(cudaStream_t st, const TableView &tv, const uint64_t
     const unsigned grid = (unsigned)std::min<uint64_t>((n + TPB - 1) / TPB, (uint64_t)sm_count() * ctas);
     if (ctas > CTAS_PER_SM) validate_kernel<8><<<grid, TPB, 0, st>>>(tv, B, M, base0, c0, n, kcount, cutoff, out, acc3, peers, npeers);
     else validate_kernel<CTAS_PER_SM><<<grid, TPB, 0, st>>>(tv, B, M, base0, c0, n, kcount, cutoff, out, acc3, peers, npeers);
+    ++*launches;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_compact_rows(cudaStream_t st, const Base *rows, uint64_t n, uint64_t pos0, uint32_t *out4, void *wide,
+                                unsigned long long wide_cap, unsigned long long *wide_n, uint64_t *launches) {
+    if (!n) return cudaSuccess;
+    compact_rows_kernel<<<grid_for(n), TPB, 0, st>>>(rows, n, pos0, out4, static_cast<WideRow *>(wide), wide_cap, wide_n);
     ++*launches;
     return cudaGetLastError();
 }

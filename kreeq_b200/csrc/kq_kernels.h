@@ -188,6 +188,9 @@ cudaError_t launch_validate(cudaStream_t st, const TableView &tv, const uint64_t
                             uint64_t base0, uint64_t c0, uint64_t n, uint64_t kcount, uint32_t cutoff,
                             Base *out, unsigned long long *acc3, const TableView *peers, int npeers, uint64_t *launches);
 // routed validate: phase 1 on the origin (queries -> owners' inboxes, counts published), phase 2 on the owner
+struct WideRow { unsigned long long pos; uint32_t fw, bw, cov, isfw; };   // == kq_wide_row (24 bytes; isfw = isFw byte + padding)
+cudaError_t launch_compact_rows(cudaStream_t st, const Base *rows, uint64_t n, uint64_t pos0, uint32_t *out4, void *wide,
+                                unsigned long long wide_cap, unsigned long long *wide_n, uint64_t *launches);
 cudaError_t launch_vroute_send(cudaStream_t st, const TableView &tv, const uint64_t *B, const uint64_t *M, uint64_t base0,
                                uint64_t c0, uint64_t n, uint64_t kcount, Base *rows, unsigned long long *acc3, const VRoute &vr,
                                uint64_t *launches, uint64_t row0 = 0, bool publish = true);

@@ -498,3 +498,37 @@ def test_union_of_moderately_covered_databases(mods, tmp_path):
             out = g.evaluateSegment(seg)
             rc, rout, racc = u.validate_segment(seg)
             assert out.tobytes() == rout.tobytes()
+
+
+def test_compact_validate_rows(mods):
+    """kq_validate_segment_compact + kq_expand_rows == kq_validate_segment, bit for bit, including rows whose coverage
+    or edge counts pass 254 (wide list), several staged chunks, and the list-too-small error"""
+    import ctypes as C
+    kb, ko = mods
+    from kreeq_b200._lib import BASE, BASE4, WIDE, KQ_ENOMEM, KqQV, check, lib
+    L = lib()
+    k = 21
+    rng = np.random.default_rng(77)
+    genome = random_genome(rng, 60_000)
+    hot = random_genome(rng, 300).tobytes()
+    batch = sample_reads(rng, genome, 9000, 150, err=0.01) + (hot + b"N") * 400 + (b"A" * 300 + b"N") * 3
+    seg = genome.tobytes() + hot + b"A" * 200 + genome.tobytes()[:9_000_000 // 1000]
+    seg = seg * 80                                                     # ~5.5 M positions: two staged chunks
+    with kb.DBG(k=k, expected_distinct=600_000) as g:
+        g.traverseInReads(batch); g.finalize()
+        a = np.frombuffer(seg, dtype=np.uint8)
+        full = np.zeros(a.size, dtype=BASE); acc = KqQV()
+        check(L.kq_validate_segment(g.handle, C.c_void_p(a.ctypes.data), a.size, 0, C.c_void_p(full.ctypes.data), C.byref(acc)), g.handle)
+        assert int(full["cov"].max()) > 254
+        out4 = np.zeros(a.size, dtype=BASE4); wide = np.zeros(1 << 20, dtype=WIDE); nw = C.c_size_t(wide.size); acc4 = KqQV()
+        check(L.kq_validate_segment_compact(g.handle, C.c_void_p(a.ctypes.data), a.size, 0, C.c_void_p(out4.ctypes.data),
+                                            C.c_void_p(wide.ctypes.data), C.byref(nw), C.byref(acc4)), g.handle)
+        assert (acc4.missing, acc4.kcount, acc4.edge_missing) == (acc.missing, acc.kcount, acc.edge_missing)
+        assert 0 < nw.value == int(((out4["flags"] & 2) != 0).sum())
+        back = np.zeros(a.size, dtype=BASE)
+        check(L.kq_expand_rows(C.c_void_p(out4.ctypes.data), a.size, C.c_void_p(wide.ctypes.data), nw.value, C.c_void_p(back.ctypes.data)))
+        assert back.tobytes() == full.tobytes()
+        small = C.c_size_t(3)
+        rc = L.kq_validate_segment_compact(g.handle, C.c_void_p(a.ctypes.data), a.size, 0, C.c_void_p(out4.ctypes.data),
+                                           C.c_void_p(wide.ctypes.data), C.byref(small), C.byref(acc4))
+        assert rc == KQ_ENOMEM and small.value == nw.value
