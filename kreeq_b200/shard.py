@@ -242,6 +242,21 @@ class PeerTables:
         return False
 
 
+def cut_rounds(segments, chunk):
+    """[(.., .., length), ..] -> consecutive groups whose lengths add up to at most `chunk` (a segment longer than
+    `chunk` is refused: its rows would not fit the slab)"""
+    out, cur, tot = [], [], 0
+    for s_ in segments:
+        if s_[2] > chunk:
+            raise ValueError("segment of %d positions exceeds the round capacity %d" % (s_[2], chunk))
+        if cur and tot + s_[2] > chunk:
+            out.append(cur); cur, tot = [], 0
+        cur.append(s_); tot += s_[2]
+    if cur:
+        out.append(cur)
+    return out
+
+
 class RoutedValidator:
     """Validate against a key-sharded table with routed queries (kq_vroute_*, SURVEY 8e "Collective"): per chunk of
     assembly positions every rank sends 16-byte (key, position, neighbours) queries into the OWNERS' inboxes (peer
@@ -312,15 +327,8 @@ class RoutedValidator:
         check(L.kq_vroute_place(g.handle), g.handle)  # answers -> rows (local)
 
     def rounds_of(self, segments):
-        """cut a list of (d_bases, d_invalid, length) into rounds of at most `chunk` positions (a longer segment alone)"""
-        out, cur, tot = [], [], 0
-        for s_ in segments:
-            if cur and tot + s_[2] > self.chunk:
-                out.append(cur); cur, tot = [], 0
-            cur.append(s_); tot += s_[2]
-        if cur:
-            out.append(cur)
-        return out
+        """cut a list of (d_bases, d_invalid, length) into rounds of at most `chunk` positions"""
+        return cut_rounds(segments, self.chunk)
 
     def counters(self, reset=True):
         """the three QV counters summed over all ranks (collective)"""

@@ -83,3 +83,16 @@ def test_two_rank_routing_equals_single_table(tmp_path):
     assert np.array_equal(keys[o], rk) and recs[o].tobytes() == rr.tobytes()
     rc, out, acc = ref.validate_segment(genome.tobytes())
     assert tuple(parts[0]["acc"]) == (acc[0], acc[1]) == tuple(parts[1]["acc"])
+
+
+def test_cut_rounds_groups_segments_up_to_the_round_capacity():
+    """host logic of the routed validate rounds (RoutedValidator.rounds_of): order kept, capacity respected"""
+    import pytest
+    from kreeq_b200.shard import cut_rounds
+    segs = [(None, None, n) for n in (10, 20, 30, 5, 40, 40, 1)]
+    rounds = cut_rounds(segs, 60)
+    assert [[s[2] for s in r] for r in rounds] == [[10, 20, 30], [5, 40], [40, 1]]
+    assert cut_rounds([], 60) == []
+    assert [[s[2] for s in r] for r in cut_rounds(segs, 1000)] == [[10, 20, 30, 5, 40, 40, 1]]
+    with pytest.raises(ValueError):
+        cut_rounds([(None, None, 61)], 60)
